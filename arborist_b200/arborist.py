@@ -1,0 +1,459 @@
+"""Python entry points: ``arborist(...)``, the 13-argument per-tree seam and the CLI.
+
+Drop-in for ``/root/reference/src/arborist/arborist.py`` ("A.py"):
+
+* ``arborist(tree_list, read_counts, snv_clusters, alpha, max_iter, tolerance,
+  gamma, add_normal, threads, verbose)`` -- same signature, defaults, return
+  triple and ``ValueError`` as A.py:906-1130.  The reference's sequential tree
+  loop (A.py:1089-1126) collapses into ONE batched call into the CUDA library.
+* ``run_variational_inference(presence, ll_cell_sort, ll_snv_sort, cell_idx,
+  snv_idx, n_cells, n_snvs, n_clones, q_y_init, cell_ptr, snv_ptr, max_iter,
+  tolerance)`` -- the function-valued seam ``run = ...`` at A.py:1076, same
+  argument meaning and return triple as A.py:679-816.
+* ``main()`` / ``parse_arguments()`` -- the ``arborist`` console script with the
+  reference's flags (A.py:26-142, A.py:1133-1191).
+
+Host code here is orchestration only (id factorisation, tree validation,
+result wrapping).  Every numeric step runs in ``csrc/`` on the GPU; there is no
+CPU fallback -- a missing library or device raises.
+"""
+from __future__ import annotations
+
+import argparse
+import logging
+import weakref
+
+import numpy as np
+import pandas as pd
+
+from .treefit import TreeFit
+from .utils import read_trees, visualize_tree
+
+__all__ = ["arborist", "run_variational_inference", "run_simple_max_likelihood", "main",
+           "parse_arguments", "add_normal_clone", "tree_to_clone_set", "prepare_trees"]
+
+logging.basicConfig(
+    format="{asctime} - {levelname} - {message}",
+    style="{",
+    datefmt="%Y-%m-%d %H:%M:%S",
+    level=logging.INFO,
+)
+
+
+# ---------------------------------------------------------------------------
+# tree handling (host): A.py:860-903, A.py:1009-1028, A.py:491-520
+# ---------------------------------------------------------------------------
+def _digraph_edge_order(edge_list, extra=None):
+    """Edges in the order ``list(nx.DiGraph(edge_list).edges)`` yields them
+    (grouped by source in node first-appearance order, duplicates collapsed);
+    the reference stores that order in ``TreeFit.tree`` after ``--add-normal``."""
+    nodes, succ = {}, {}
+    for u, v in edge_list:
+        nodes.setdefault(u, None)
+        nodes.setdefault(v, None)
+        succ.setdefault(u, {}).setdefault(v, None)
+    if extra is not None:
+        u, v = extra
+        nodes.setdefault(u, None)
+        nodes.setdefault(v, None)
+        succ.setdefault(u, {}).setdefault(v, None)
+    return [(u, v) for u in nodes for v in succ.get(u, ())], list(nodes)
+
+
+def add_normal_clone(candidate_trees):
+    """Prepend a normal clone ``min(nodes) - 1`` above each tree's root (A.py:860-882)."""
+    out = []
+    for edges in candidate_trees:
+        _, nodes = _digraph_edge_order(edges)
+        kids = {v for _, v in edges}
+        root = [n for n in nodes if n not in kids][0]
+        normal = min(nodes) - 1
+        out.append(_digraph_edge_order(edges, extra=(normal, root))[0])
+    return out
+
+
+def tree_to_clone_set(tree):
+    """Set of clone labels in an edge list (A.py:885-903)."""
+    return {x for e in tree for x in e}
+
+
+def prepare_trees(tree_list):
+    """Validate the candidate set and index it (A.py:1009-1028).
+
+    Returns ``(clone_to_idx, cluster_to_idx, parents, presence)``; exactly one of
+    ``parents`` (int32 ``[T, K]``, -1 for roots; device builds the closure) and
+    ``presence`` (uint8 ``[T, K-1, K]``; for inputs that are not forests) is set.
+    """
+    tree0 = tree_list[0]
+    _, nodes0 = _digraph_edge_order(tree0)
+    kids0 = {v for _, v in tree0}
+    normal = [n for n in nodes0 if n not in kids0][0]
+    clone_set = tree_to_clone_set(tree0)
+    clones = sorted(clone_set)
+    K, T = len(clones), len(tree_list)
+    clusters = [c for c in clones if c != normal]
+    clone_to_idx = {c: i for i, c in enumerate(clones)}
+    cluster_to_idx = {c: i for i, c in enumerate(clusters)}
+
+    parents = np.full((T, K), -1, dtype=np.int32)
+    is_forest = True
+    try:
+        arr = np.asarray(tree_list, dtype=np.int64)
+        regular = arr.ndim == 3 and arr.shape[2] == 2
+    except (ValueError, TypeError):
+        regular = False
+    if regular and arr.shape[1] > 0:
+        carr = np.asarray(clones, dtype=np.int64)
+        idx = np.searchsorted(carr, arr).clip(0, K - 1)
+        if not np.array_equal(carr[idx], arr):
+            raise ValueError("All trees must have the same set of clones.")
+        seen = np.zeros((T, K), dtype=bool)
+        rows = np.arange(T)[:, None]
+        seen[rows, idx[:, :, 0]] = True
+        seen[rows, idx[:, :, 1]] = True
+        if not seen.all():
+            raise ValueError("All trees must have the same set of clones.")
+        pu, cv = idx[:, :, 0].astype(np.int32), idx[:, :, 1]
+        parents[rows, cv] = pu
+        # a child listed under two different parents is not a forest
+        n_par = np.zeros((T, K), dtype=np.int32)
+        np.add.at(n_par, (np.broadcast_to(rows, cv.shape), cv), 1)
+        if (n_par > 1).any():
+            # tolerate exact duplicate edges, reject genuine multi-parent nodes
+            is_forest = bool((parents[rows, cv] == pu).all())
+    else:
+        for t, tree in enumerate(tree_list):
+            if tree_to_clone_set(tree) != clone_set:
+                raise ValueError("All trees must have the same set of clones.")
+            for u, v in tree:
+                iu, iv = clone_to_idx[u], clone_to_idx[v]
+                if parents[t, iv] not in (-1, iu):
+                    is_forest = False
+                parents[t, iv] = iu
+    if is_forest:
+        # cycles: after K pointer jumps every node must have reached a root
+        cur = parents.copy()
+        for _ in range(K):
+            nxt = np.where(cur >= 0, np.take_along_axis(parents, cur.clip(0), axis=1), -1)
+            cur = nxt
+        is_forest = bool((cur < 0).all())
+    if is_forest:
+        return clone_to_idx, cluster_to_idx, parents, None
+
+    # general digraphs: descendant closure on the host, like nx.descendants (A.py:516)
+    presence = np.zeros((T, K - 1, K), dtype=np.uint8)
+    for t, tree in enumerate(tree_list):
+        children = {}
+        for u, v in tree:
+            children.setdefault(u, []).append(v)
+        for cl, ip in cluster_to_idx.items():
+            stack, seen_n = [cl], set()
+            while stack:
+                x = stack.pop()
+                if x in seen_n:
+                    continue
+                seen_n.add(x)
+                presence[t, ip, clone_to_idx[x]] = 1
+                stack.extend(children.get(x, ()))
+    return clone_to_idx, cluster_to_idx, None, presence
+
+
+def _prior_labels(snv_clusters, snv_ids, cluster_to_idx):
+    """Input-cluster index per SNV row, -1 => uniform prior row (A.py:547-567).
+
+    Kept quirks: the LAST row wins for a repeated SNV (``dict(zip(...))``); a label
+    that is falsy (``0``, ``None``, ``""``) or not a tree node gives the uniform
+    row; SNVs absent from the clustering are reported on stdout (A.py:558).
+    """
+    cl = snv_clusters.drop_duplicates("snv", keep="last")
+    lab = pd.Series(cl["cluster"].to_numpy(), index=cl["snv"].to_numpy())
+    ids = pd.Index(snv_ids)
+    found = ids.isin(lab.index)
+    for s in ids[~found]:
+        print(f"SNV {s} not initialized with cluster assignment.")
+    got = lab.reindex(ids)
+    vals = got.to_numpy()
+    out = np.full(len(ids), -1, dtype=np.int32)
+    mapped = got.map(cluster_to_idx).to_numpy(dtype=np.float64, na_value=np.nan)
+    ok = found & ~np.isnan(mapped)
+    if vals.dtype.kind in "iufb":
+        ok &= vals != 0
+    else:
+        ok &= np.fromiter((bool(v) if v is not None else False for v in vals), dtype=bool,
+                          count=len(vals))
+    out[ok] = mapped[ok].astype(np.int32)
+    return out
+
+
+# ---------------------------------------------------------------------------
+# the public entry point
+# ---------------------------------------------------------------------------
+def arborist(
+    tree_list: list,
+    read_counts: pd.DataFrame,
+    snv_clusters: pd.DataFrame,
+    alpha: float = 0.001,
+    max_iter: int = 10,
+    tolerance: float = 1,
+    gamma=0.7,
+    add_normal=False,
+    threads=10,
+    verbose: bool = False,
+    *,
+    device=None,
+    keep_posteriors: str = "auto",
+) -> tuple:
+    """Rank candidate SNV clone trees with low-pass scDNA-seq read counts.
+
+    Same contract as the reference (A.py:906-1130): returns ``(likelihoods,
+    best_fit, all_tree_fits)`` -- ``{tree_idx: ELBO}``, the ``TreeFit`` of the first
+    tree attaining the maximum ELBO, and ``{tree_idx: TreeFit}``.
+
+    ``threads`` is accepted for compatibility and ignored (the reference passes it
+    to ``numba.set_num_threads``, A.py:1002; nothing here runs on host threads).
+    Keyword-only extras: ``device`` (CUDA ordinal; default ``LOCAL_RANK`` or 0) and
+    ``keep_posteriors`` ("auto" | "all" | "none": whether every tree's best
+    ``q_z``/``q_y`` stay resident on the GPU or are refit on demand).
+    Under an initialised ``torch.distributed`` group the candidate set is sharded
+    over ranks and the ELBOs gathered, see :mod:`arborist_b200.distributed`.
+    """
+    from . import distributed
+    from .engine import Engine
+
+    logger = logging.getLogger() if verbose else None
+
+    def log(msg):
+        if logger is not None:
+            logger.info(msg)
+
+    if add_normal:
+        log("Appending normal clone to candidate trees...")
+        tree_list = add_normal_clone(tree_list)
+
+    clone_to_idx, cluster_to_idx, parents, presence = prepare_trees(tree_list)
+    K, T = len(clone_to_idx), len(tree_list)
+
+    log("Removing SNVs with 0 variant reads across all cells...")
+    # first-appearance factorisation (A.py:851-855) of the UNFILTERED table; the
+    # filter (A.py:1034-1041), re-indexing and CSR/CSC build happen on the device.
+    snv_codes, snv_uniques = pd.factorize(read_counts["snv"].to_numpy(), use_na_sentinel=True)
+    cell_codes, cell_uniques = pd.factorize(read_counts["cell"].to_numpy(), use_na_sentinel=False)
+    eng = Engine(device=device)
+    log("Caching log-likelihoods for presence/absence...")
+    eng.ingest_coo(cell_codes, snv_codes, read_counts["alt"].to_numpy(),
+                   read_counts["total"].to_numpy(), len(cell_uniques), len(snv_uniques), alpha)
+    _install_scipy_table(eng, alpha)
+    cell_order, snv_order = eng.orders()
+    cell_ids = np.asarray(cell_uniques)[cell_order]
+    snv_ids = np.asarray(snv_uniques)[snv_order]
+    cell_to_idx = dict(zip(cell_ids.tolist(), range(len(cell_ids))))
+    snv_to_idx = dict(zip(snv_ids.tolist(), range(len(snv_ids))))
+
+    log("Initializing the SNV cluster assignment prior...")
+    eng.set_prior_labels(_prior_labels(snv_clusters, snv_ids, cluster_to_idx), K - 1, gamma)
+
+    if verbose:
+        log("Starting Arborist...")
+        log(f"Number of candidate trees: {len(tree_list[-1])}")   # sic: A.py:1080 logs an edge count
+        log(f"Number of clones: {K}")
+        log(f"Number of SNV clusters: {K - 1}")
+        log(f"Number of cells: {len(cell_ids)}")
+        log(f"Number of SNVs: {len(snv_ids)}")
+
+    shard = distributed.shard_indices(T)
+    elbo, iters = eng.fit(parents=None if parents is None else parents[shard],
+                          presence=None if presence is None else presence[shard],
+                          n_clones=K, max_iter=max_iter, tolerance=tolerance,
+                          keep_posteriors=keep_posteriors)
+    elbo_all, owner = distributed.gather_elbos(elbo, shard, T)
+
+    local_of = {int(g): l for l, g in enumerate(shard)}
+    eng_ref = eng
+
+    def loader(idx):
+        return distributed.fetch_fit(eng_ref, idx, local_of, owner)
+
+    def map_loader(idx):
+        if idx in local_of:
+            return eng_ref.get_map(local_of[idx])
+        return None
+
+    likelihoods, all_tree_fits = {}, {}
+    best_likelihood, best_fit = -np.inf, None
+    for idx in range(T):
+        e = float(elbo_all[idx])
+        tfit = TreeFit.lazy(tree_list[idx], idx, e, loader, cell_to_idx, snv_to_idx,
+                            clone_to_idx, cluster_to_idx, map_loader=map_loader)
+        all_tree_fits[idx] = tfit
+        if verbose:
+            log(f"Tree {idx} fit wtih ELBO: {e:.2f}")
+        likelihoods[idx] = e
+        if e > best_likelihood:                      # strict >: first maximum wins (A.py:1124)
+            best_fit, best_likelihood = tfit, e
+    log(f"Done fitting all {T} candidate trees!")
+    if best_fit is None:
+        # the reference dies with UnboundLocalError here (A.py:1124-1130); say why
+        raise UnboundLocalError("no candidate tree has a finite ELBO (all NaN/-inf); "
+                                "cannot select best_fit")
+    arborist.last_stats = dict(iters=iters, engine=weakref.ref(eng), shard=shard)
+    return likelihoods, best_fit, all_tree_fits
+
+
+arborist.last_stats = None
+
+
+def _install_scipy_table(eng, alpha):
+    """Replace the device-computed log-likelihood table with scipy's values.
+
+    The reference evaluates ``scipy.stats.binom.logpmf`` per row (A.py:838-846);
+    the device dictionary-codes the distinct ``(alt, total)`` pairs, so evaluating
+    scipy on that small table reproduces the reference's doubles bit for bit.
+    Without scipy the device's own lgamma-based table (<= 1e-14 relative) stays.
+    """
+    try:
+        from scipy.stats import binom
+    except ImportError:      # pragma: no cover - scipy is a dependency of the reference too
+        return
+    alt, total = eng.count_pairs()
+    lp = binom.logpmf(alt, total, 0.5 - alpha + 0.5 * alpha / 3)
+    la = binom.logpmf(alt, total, alpha / 3)
+    eng.set_loglik_table(lp, la)
+
+
+# ---------------------------------------------------------------------------
+# the per-tree seam (A.py:1076 ``run = run_variational_inference``)
+# ---------------------------------------------------------------------------
+_SEAM_CACHE = {}
+
+
+def _seam_engine(ll_cs, snv_idx, cell_ptr, n_cells, n_snvs, q_y_init):
+    from .engine import Engine
+
+    key = (ll_cs.__array_interface__["data"][0], snv_idx.__array_interface__["data"][0],
+           cell_ptr.__array_interface__["data"][0], ll_cs.shape[0], n_cells, n_snvs)
+    hit = _SEAM_CACHE.get("e")
+    if hit is None or hit[0] != key:
+        eng = Engine()
+        eng.ingest_csr(cell_ptr, snv_idx, ll_cs, n_cells, n_snvs)
+        hit = (key, eng, (ll_cs, snv_idx, cell_ptr), [None])
+        _SEAM_CACHE["e"] = hit       # keeps the arrays alive so the key cannot be recycled
+    eng = hit[1]
+    pk = (q_y_init.__array_interface__["data"][0], q_y_init.shape)
+    if hit[3][0] != pk:
+        eng.set_prior(q_y_init)
+        hit[3][0] = pk
+        hit[3].append(q_y_init)
+    return eng
+
+
+def _run_seam(mode, presence, ll_cs, ll_ss, cell_idx, snv_idx, n_cells, n_snvs, n_clones,
+              q_y_init, cell_ptr, snv_ptr, max_iter, tolerance):
+    ll_cs = np.ascontiguousarray(ll_cs, dtype=np.float64)
+    snv_idx = np.ascontiguousarray(snv_idx, dtype=np.int32)
+    cell_ptr = np.ascontiguousarray(cell_ptr, dtype=np.int32)
+    q_y_init = np.ascontiguousarray(q_y_init, dtype=np.float64)
+    eng = _seam_engine(ll_cs, snv_idx, cell_ptr, int(n_cells), int(n_snvs), q_y_init)
+    pres = (np.asarray(presence) != 0).astype(np.uint8)[None]
+    elbo, _ = eng.fit(presence=pres, n_clones=int(n_clones), max_iter=int(max_iter),
+                      tolerance=float(tolerance), keep_posteriors="all", mode=mode)
+    q_z, q_y = eng.get_fit(0)
+    return float(elbo[0]), q_z, q_y
+
+
+def run_variational_inference(presence, log_like_matrix_cell_sort, log_like_matrix_snv_sort,
+                              cell_idx, snv_idx, n_cells, n_snvs, n_clones, q_y_init, cell_ptr,
+                              snv_ptr, max_iter=10, tolerance=1):
+    """CAVI fit of one tree; arguments and return triple as A.py:679-816.
+
+    The CSC copy (``log_like_matrix_snv_sort``, ``cell_idx``, ``snv_ptr``) is accepted
+    and ignored: the device derives its own SNV-major layout from the CSR arrays.
+    The device matrix is cached across calls on the same arrays (the reference's
+    tree loop calls this once per tree with identical data)."""
+    return _run_seam("vi", presence, log_like_matrix_cell_sort, log_like_matrix_snv_sort,
+                     cell_idx, snv_idx, n_cells, n_snvs, n_clones, q_y_init, cell_ptr, snv_ptr,
+                     max_iter, tolerance)
+
+
+def run_simple_max_likelihood(presence, log_like_matrix_cell_sort, log_like_matrix_snv_sort,
+                              cell_idx, snv_idx, n_cells, n_snvs, n_clones, q_y_init, cell_ptr,
+                              snv_ptr, max_iter=10, tolerance=1):
+    """Hard-assignment scorer with the seam's signature (A.py:598-676)."""
+    return _run_seam("ml", presence, log_like_matrix_cell_sort, log_like_matrix_snv_sort,
+                     cell_idx, snv_idx, n_cells, n_snvs, n_clones, q_y_init, cell_ptr, snv_ptr,
+                     max_iter, tolerance)
+
+
+# ---------------------------------------------------------------------------
+# CLI (A.py:26-142, A.py:1133-1191)
+# ---------------------------------------------------------------------------
+def parse_arguments(argv=None) -> argparse.Namespace:
+    p = argparse.ArgumentParser(
+        description="Arborist: a method to rank SNV clonal trees using scDNA-seq data.")
+    p.add_argument("-R", "--read_counts", required=True,
+                   help="Path to read counts CSV file with columns 'snv', 'cell',  'total', 'alt'")
+    p.add_argument("-Y", "--snv-clusters", required=True,
+                   help="Path to SNV clusters CSV file with unlabeled columns 'snv', 'cluster'. "
+                        "The order of columns matters")
+    p.add_argument("-T", "--trees", required=True,
+                   help="Path to file containing all candidate trees to be ranked.")
+    p.add_argument("--edge-delim", type=str, default=" ",
+                   help="edge delimiter in candidate tree file.")
+    p.add_argument("--add-normal", action="store_true",
+                   help="flag to add a normal clone if input trees do not already contain them")
+    p.add_argument("--alpha", type=float, default=0.001, help="Per base sequencing error")
+    p.add_argument("--max-iter", type=int, default=25, help="max number of iterations")
+    p.add_argument("--prior", type=float, default=0.7,
+                   help="prior (gamma) on input SNV cluster assignment")
+    p.add_argument("--pickle", type=str,
+                   help="path to where all pickled tree fits should be saved.")
+    p.add_argument("-d", "--draw", type=str,
+                   help="Path to where the tree visualization should be saved")
+    p.add_argument("-t", "--tree", help="Path to save the top ranked tree as a txt file.")
+    p.add_argument("--ranking", type=str,
+                   help="Path to where tree ranking output should be saved")
+    p.add_argument("--cell-assign", type=str,
+                   help="Path to where the MAP cell-to-clone labels should be saved")
+    p.add_argument("--snv-assign", type=str,
+                   help="Path to where the MAP SNV-to-cluster labels should be saved.")
+    p.add_argument("--q_y", type=str,
+                   help="Path to where the approximate SNV posterior should be saved")
+    p.add_argument("--q_z", type=str,
+                   help="Path to where the approximate cell posterior should be saved")
+    p.add_argument("-j", "--threads", default=10, type=int, help="Number of threads to use")
+    p.add_argument("-v", "--verbose", help="Print verbose output", action="store_true")
+    return p.parse_args(argv)
+
+
+def main(argv=None):
+    args = parse_arguments(argv)
+    read_counts = pd.read_csv(args.read_counts)
+    snv_clusters = pd.read_csv(args.snv_clusters, header=None, names=["snv", "cluster"])
+    candidate_trees = read_trees(args.trees, sep=args.edge_delim)
+
+    elbos, tfit, all_fits = arborist(
+        candidate_trees, read_counts, snv_clusters, alpha=args.alpha, verbose=args.verbose,
+        max_iter=args.max_iter, gamma=args.prior, add_normal=args.add_normal,
+        threads=args.threads)
+
+    if args.draw:
+        visualize_tree(tfit.tree, output_file=args.draw)
+
+    elbo_df = pd.DataFrame({"tree_idx": list(elbos.keys()), "elbo": list(elbos.values())})
+    elbo_df = elbo_df.sort_values(by="elbo", ascending=False)
+    if args.ranking:
+        elbo_df.to_csv(args.ranking, index=False)
+    if args.cell_assign:
+        tfit.map_assign_z().to_csv(args.cell_assign, index=False)
+    if args.snv_assign:
+        tfit.map_assign_y().to_csv(args.snv_assign, index=False)
+    if args.q_z:
+        tfit.q_z_df().to_csv(args.q_z, index=False)
+    if args.q_y:
+        tfit.q_y_df().to_csv(args.q_y, index=False)
+    if args.tree:
+        tfit.save_tree(args.tree)
+    if args.pickle:
+        pd.to_pickle(all_fits, args.pickle)
+
+    print("\n---------------------Arborist complete!---------------------\n")
+    print(tfit)

@@ -1,0 +1,158 @@
+/*
+ * arborist_b200.h -- C ABI of libarborist_b200.so (hand-written sm_100a CUDA).
+ *
+ * The drop-in boundary for Arborist's per-tree variational fit.  The reference
+ * (/root/reference/src/arborist/arborist.py, "A.py") has no FFI of its own; its
+ * de-facto operator seam is the function-valued variable
+ *     run = run_variational_inference                      (A.py:1076)
+ * called once per candidate tree from the loop at A.py:1089-1126.  The entry
+ * points below are what a binding for that path needs: build the device-resident
+ * read-count matrix once (A.py:1034-1069), set the prior (A.py:1052), then fit a
+ * whole SHARD of trees in one call (A.py:1089-1126 collapsed), and fetch results.
+ * INTEGRATION.md shows the ctypes stub that replaces the loop.
+ *
+ * Conventions
+ *   - every function returns 0 (ARB_OK) or a negative arb_status; the message for
+ *     the calling thread's last failure is arb_last_error();
+ *   - plain pointers and sizes only; pointers are HOST memory unless a name ends
+ *     in _dev; outputs are caller-allocated; inputs are never modified;
+ *   - one arb_ctx per GPU, used from one host thread at a time; every call is
+ *     synchronous (work is enqueued on the context's stream and waited for);
+ *   - no C++ exceptions cross the boundary; there is no CPU fallback: without a
+ *     usable CUDA device arb_ctx_create fails with ARB_ERR_CUDA.
+ *
+ * Index conventions (the reference's): K = n_clones counts the normal/root clone,
+ * C = K-1 clusters; clone and cluster indices are positions in the ascending label
+ * order (A.py:1025-1028); cell/SNV indices are first-appearance order AFTER the
+ * zero-alt filter (A.py:1041, A.py:851-855).  Posteriors are row-major fp64:
+ * q_z [n_cells, K], q_y [n_snvs, C].
+ */
+#ifndef ARBORIST_B200_H
+#define ARBORIST_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ARB_MAX_CLONES 32 /* K <= 32 in this release (one lane per clone) */
+#define ARB_ABI_VERSION 1
+
+typedef enum arb_status {
+    ARB_OK = 0,
+    ARB_ERR_INVALID = -1,     /* bad argument / call order */
+    ARB_ERR_CUDA = -2,        /* CUDA runtime failure (message has the detail) */
+    ARB_ERR_UNSUPPORTED = -3, /* outside this release's limits (K > 32, > 65535 count pairs) */
+    ARB_ERR_NOMEM = -4        /* device or host allocation failed */
+} arb_status;
+
+typedef struct arb_ctx arb_ctx;
+
+/* ---- library / context ------------------------------------------------------ */
+int arb_abi_version(void);
+const char *arb_last_error(void);
+int arb_device_count(int *count);
+int arb_ctx_create(int device, arb_ctx **out);
+int arb_ctx_destroy(arb_ctx *ctx);
+
+/* ---- ingest: replaces A.py:1034-1069 ----------------------------------------
+ * arb_ingest_coo takes the long-format table as integer codes: cell_code/snv_code
+ * are first-appearance factorisations of the UNFILTERED id columns (pandas
+ * factorize / Series.unique order, A.py:851-852), a negative snv_code marks a row
+ * to drop.  On the device: zero-alt SNV filter (A.py:1034-1041), re-indexing in
+ * first-appearance order of the surviving rows, dictionary coding of the distinct
+ * (alt,total) pairs, binomial log-pmf table for present/absent (A.py:838-846,
+ * p_present = 0.5 - alpha + 0.5*alpha/3, p_absent = alpha/3), and cell-major (CSR)
+ * + SNV-major (CSC) copies with rows sorted by index (A.py:423-456, 459-488). */
+int arb_ingest_coo(arb_ctx *ctx, int64_t n_rows, const int32_t *cell_code,
+                   const int32_t *snv_code, const int32_t *alt, const int32_t *total,
+                   int32_t n_cell_codes, int32_t n_snv_codes, double alpha);
+
+/* Seam-level ingest from the reference's own arrays (the arguments of run(...),
+ * A.py:1093-1107): CSR pointer, SNV index per entry, interleaved [log_present,
+ * log_absent] per entry (A.py:478-486).  The CSC copy is derived on the device. */
+int arb_ingest_csr(arb_ctx *ctx, int32_t n_cells, int32_t n_snvs, int64_t nnz,
+                   const int32_t *cell_ptr, const int32_t *snv_idx, const double *log_likes);
+
+/* sizes after ingest; any pointer may be NULL */
+int arb_get_dims(arb_ctx *ctx, int32_t *n_cells, int32_t *n_snvs, int64_t *nnz,
+                 int32_t *n_pairs);
+/* cell_order[i] / snv_order[j] = input code of final row i / column j (coo ingest only) */
+int arb_get_orders(arb_ctx *ctx, int32_t *cell_order, int32_t *snv_order);
+/* the distinct (alt,total) pairs, in table order (coo ingest only) */
+int arb_get_count_pairs(arb_ctx *ctx, int32_t *alt, int32_t *total);
+/* read / overwrite the per-pair log-likelihood table (e.g. with scipy's doubles,
+ * so the device uses bit-identical values to A.py:838-846) */
+int arb_get_loglik_table(arb_ctx *ctx, double *log_present, double *log_absent);
+int arb_set_loglik_table(arb_ctx *ctx, int32_t n_pairs, const double *log_present,
+                         const double *log_absent);
+/* canonical device matrix back on the host, reference layout (for tests):
+ * CSR if snv_major == 0 else CSC; log_likes interleaved [lp, la] */
+int arb_export_sparse(arb_ctx *ctx, int snv_major, int32_t *ptr, int32_t *idx,
+                      double *log_likes);
+
+/* ---- prior: replaces initialize_q_y, A.py:523-569 ---------------------------
+ * label_idx[j] = cluster index of SNV j's input label, or -1 for the uniform row
+ * (label missing / falsy / not a tree node, A.py:564-565). */
+int arb_set_prior_labels(arb_ctx *ctx, const int32_t *label_idx, int32_t n_clusters,
+                         double gamma);
+int arb_set_prior(arb_ctx *ctx, const double *q_y_init, int32_t n_clusters);
+int arb_get_prior(arb_ctx *ctx, double *q_y_init);
+
+/* ---- the fit: replaces the tree loop A.py:1089-1126 --------------------------
+ * parent [n_trees, K]: parent clone index of every clone, -1 for a root; the
+ * ancestor-closure genotype matrix (enumerate_presence, A.py:491-520) is built on
+ * the device.  normal_idx = clone index of the normal clone (in-degree-0 node of
+ * tree 0, A.py:1012-1013).  Runs run_variational_inference (A.py:679-816) for
+ * every tree: elbo[t] = best ELBO, iters[t] = loop bodies executed.  elbo_trace
+ * (optional, [n_trees, max_iter+1], NaN-padded) receives ELBO_0 and every
+ * iteration's ELBO.  The best q_z/q_y of every tree stay on the device when
+ * keep_posteriors != 0 (else they are refit on demand by arb_get_fit). */
+#define ARB_MODE_VI 0 /* run_variational_inference, A.py:679 */
+#define ARB_MODE_ML 1 /* run_simple_max_likelihood, A.py:598 */
+int arb_fit_trees(arb_ctx *ctx, int32_t n_trees, int32_t n_clones, int32_t normal_idx,
+                  const int32_t *parent, int32_t max_iter, double tolerance, int32_t mode,
+                  int32_t keep_posteriors, double *elbo, int32_t *iters, double *elbo_trace);
+/* same, from explicit genotype matrices presence [n_trees, K-1, K] (0/1 bytes) --
+ * the literal first argument of run(...), for inputs that are not forests */
+int arb_fit_presence(arb_ctx *ctx, int32_t n_trees, int32_t n_clones, const uint8_t *presence,
+                     int32_t max_iter, double tolerance, int32_t mode, int32_t keep_posteriors,
+                     double *elbo, int32_t *iters, double *elbo_trace);
+/* bytes the resident best posteriors of n_trees trees would need (for "auto") */
+int arb_posterior_bytes(arb_ctx *ctx, int32_t n_trees, int32_t n_clones, int64_t *bytes,
+                        int64_t *free_bytes);
+
+/* best posteriors / MAP labels (row argmax, first maximum wins -- treefit.py:105)
+ * of tree t of the last fit */
+int arb_get_fit(arb_ctx *ctx, int32_t t, double *q_z, double *q_y);
+int arb_get_map(arb_ctx *ctx, int32_t t, int32_t *z, int32_t *y);
+/* the genotype matrix the device built for tree t, [K-1, K] 0/1 bytes */
+int arb_get_presence(arb_ctx *ctx, int32_t t, uint8_t *presence);
+
+/* ---- kernel-level hooks (parity tests against A.py:200-420 called directly) ---
+ * presence [K-1, K] 0/1 bytes; q_y [m, K-1]; q_z [n, K]. */
+/* compute_q_z_sparse (A.py:200): q_z from q_y (NOT its log; zeros allowed) */
+int arb_qz_update(arb_ctx *ctx, int32_t n_clones, const uint8_t *presence, const double *q_y,
+                  double *q_z);
+/* compute_q_y_sparse (A.py:325): q_y from q_z and the context's prior */
+int arb_qy_update(arb_ctx *ctx, int32_t n_clones, const uint8_t *presence, const double *q_z,
+                  double *q_y);
+/* compute_likelihood_sparse (A.py:378), compute_entropy(q_z) (A.py:253),
+ * compute_kl_divergence(q_y, prior) (A.py:276) */
+int arb_elbo_terms(arb_ctx *ctx, int32_t n_clones, const uint8_t *presence, const double *q_z,
+                   const double *q_y, double *likelihood, double *entropy, double *kl);
+
+/* ---- counters for bench.py ------------------------------------------------------
+ * kernels launched / device milliseconds spent inside the last arb_fit_* call, and
+ * CAVI tree-iterations it executed (initial pass = half an iteration) */
+int arb_last_fit_stats(arb_ctx *ctx, int64_t *kernel_launches, double *device_ms,
+                       double *tree_iterations, double *sweep_ms);
+/* tuning knobs: "slots" (trees in flight), "panel_kb", "chunk_rows"; returns ARB_ERR_INVALID
+ * for unknown names */
+int arb_set_option(arb_ctx *ctx, const char *name, int64_t value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ARBORIST_B200_H */

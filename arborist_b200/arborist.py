@@ -80,7 +80,7 @@ def tree_to_clone_set(tree):
 def prepare_trees(tree_list):
     """Validate the candidate set and index it (A.py:1009-1028).
 
-    Returns ``(clone_to_idx, cluster_to_idx, parents, presence)``; exactly one of
+    Returns ``(clone_to_idx, cluster_to_idx, parents, presence, normal_idx)``; exactly one of
     ``parents`` (int32 ``[T, K]``, -1 for roots; device builds the closure) and
     ``presence`` (uint8 ``[T, K-1, K]``; for inputs that are not forests) is set.
     """
@@ -137,8 +137,9 @@ def prepare_trees(tree_list):
             nxt = np.where(cur >= 0, np.take_along_axis(parents, cur.clip(0), axis=1), -1)
             cur = nxt
         is_forest = bool((cur < 0).all())
+    normal_idx = clone_to_idx[normal]
     if is_forest:
-        return clone_to_idx, cluster_to_idx, parents, None
+        return clone_to_idx, cluster_to_idx, parents, None, normal_idx
 
     # general digraphs: descendant closure on the host, like nx.descendants (A.py:516)
     presence = np.zeros((T, K - 1, K), dtype=np.uint8)
@@ -155,7 +156,7 @@ def prepare_trees(tree_list):
                 seen_n.add(x)
                 presence[t, ip, clone_to_idx[x]] = 1
                 stack.extend(children.get(x, ()))
-    return clone_to_idx, cluster_to_idx, None, presence
+    return clone_to_idx, cluster_to_idx, None, presence, normal_idx
 
 
 def _prior_labels(snv_clusters, snv_ids, cluster_to_idx):
@@ -230,7 +231,7 @@ def arborist(
         log("Appending normal clone to candidate trees...")
         tree_list = add_normal_clone(tree_list)
 
-    clone_to_idx, cluster_to_idx, parents, presence = prepare_trees(tree_list)
+    clone_to_idx, cluster_to_idx, parents, presence, normal_idx = prepare_trees(tree_list)
     K, T = len(clone_to_idx), len(tree_list)
 
     log("Removing SNVs with 0 variant reads across all cells...")
@@ -263,8 +264,8 @@ def arborist(
     shard = distributed.shard_indices(T)
     elbo, iters = eng.fit(parents=None if parents is None else parents[shard],
                           presence=None if presence is None else presence[shard],
-                          n_clones=K, max_iter=max_iter, tolerance=tolerance,
-                          keep_posteriors=keep_posteriors)
+                          n_clones=K, normal_idx=normal_idx, max_iter=max_iter,
+                          tolerance=tolerance, keep_posteriors=keep_posteriors)
     elbo_all, owner = distributed.gather_elbos(elbo, shard, T)
 
     local_of = {int(g): l for l, g in enumerate(shard)}

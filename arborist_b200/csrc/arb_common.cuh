@@ -1,0 +1,135 @@
+// arb_common.cuh -- shared declarations of libarborist_b200.so (sm_100a only).
+//
+// One arb_ctx per GPU.  Everything numeric lives on the device; the host side of
+// this library only sequences kernels and moves the caller's buffers.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+
+#include "../../include/arborist_b200.h"
+
+#define ARB_API extern "C" __attribute__((visibility("default")))
+
+void arb_set_error(const char *fmt, ...);
+
+#define ARB_CUDA(call)                                                                   \
+    do {                                                                                 \
+        cudaError_t e__ = (call);                                                        \
+        if (e__ != cudaSuccess) {                                                        \
+            arb_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call,                  \
+                          cudaGetErrorString(e__));                                      \
+            return e__ == cudaErrorMemoryAllocation ? ARB_ERR_NOMEM : ARB_ERR_CUDA;      \
+        }                                                                                \
+    } while (0)
+
+#define ARB_TRY(call)                 \
+    do {                              \
+        int rc__ = (call);            \
+        if (rc__ != ARB_OK) return rc__; \
+    } while (0)
+
+#define ARB_REQUIRE(cond, code, ...)      \
+    do {                                  \
+        if (!(cond)) {                    \
+            arb_set_error(__VA_ARGS__);   \
+            return (code);                \
+        }                                 \
+    } while (0)
+
+// ---- device buffer with size tracking -----------------------------------------------
+struct DevBuf {
+    void *p = nullptr;
+    size_t bytes = 0;
+    int reserve(size_t n) {          // grows only; contents are NOT preserved
+        if (n <= bytes && p) return ARB_OK;
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+        if (n == 0) return ARB_OK;
+        cudaError_t e = cudaMalloc(&p, n);
+        if (e != cudaSuccess) {
+            arb_set_error("cudaMalloc(%zu bytes): %s", n, cudaGetErrorString(e));
+            cudaGetLastError();
+            return ARB_ERR_NOMEM;
+        }
+        bytes = n;
+        return ARB_OK;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+    }
+    template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+// Panelled sparse layout for one padded clone width KP (8, 16 or 32 doubles per row of
+// the gathered operand).  "z": cell-major rows, SNVs cut into panels (q(z) sweep);
+// "y": SNV-major rows, cells cut into panels (q(y) sweep).  A stream word is
+// (pair code << 16) | (column index inside its panel).
+struct PanelLayout {
+    int kp = 0;
+    int panel_rows = 0;      // rows of the gathered operand per panel (<= 65536)
+    int np_z = 0, np_y = 0;  // number of panels
+    DevBuf zptr, zstream;    // int32 [np_z * n_cells + 1], uint32 [nnz]
+    DevBuf yptr, ystream;    // int32 [np_y * n_snvs + 1], uint32 [nnz]
+    void release() { zptr.release(); zstream.release(); yptr.release(); ystream.release(); kp = 0; }
+};
+
+struct FitStats {
+    int64_t launches = 0;
+    double device_ms = 0, tree_iterations = 0, sweep_ms = 0;
+};
+
+struct arb_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int sm_count = 0;
+    size_t smem_optin = 0;
+
+    // ---- canonical matrix, sorted by (cell, snv) --------------------------------
+    bool ingested = false, from_coo = false;
+    int32_t n_cells = 0, n_snvs = 0, n_pairs = 0;
+    int64_t nnz = 0;
+    DevBuf coo_cell, coo_snv, coo_code;   // int32, int32, uint16
+    DevBuf cell_order, snv_order;         // int32 (coo ingest)
+    std::vector<int32_t> pair_alt, pair_total;
+    std::vector<int64_t> pair_count;
+    std::vector<double> tab_lp, tab_la;   // host copies of the table
+    DevBuf tab_dw;                        // double2 [n_pairs]: (expm1(lp-la), lp-la)
+    double sum_la = 0;                    // sum over nonzeros of log_absent
+    int renorm_every = 16;
+    double alpha = 0;
+
+    // ---- prior ---------------------------------------------------------------------
+    int32_t n_clusters = 0;
+    DevBuf q0, logq0, logq0e;             // [m, C]: q, log q (-inf for 0), log(q + 1e-12)
+
+    // ---- layouts (index 0: KP 8, 1: KP 16, 2: KP 32) ----------------------------------
+    PanelLayout layout[3];
+    int64_t opt_slots = 0, opt_panel_kb = 0, opt_threads = 0;
+
+    // ---- fit workspace -----------------------------------------------------------------
+    int ws_kp = 0, ws_slots = 0, ws_k = 0;
+    DevBuf xs, xr, qz_cur, qy_cur, part_z, part_g, part_y, red, slot_state, lists, masks;
+    // results of the last fit
+    int32_t fit_trees = 0, fit_k = 0, fit_max_iter = 0, fit_mode = 0;
+    double fit_tol = 0;
+    bool fit_kept = false;
+    DevBuf best_qz, best_qy, d_elbo, d_iters, d_trace, tree_masks;
+    std::vector<uint32_t> h_masks;        // per tree: K column masks then C row masks
+    int single_tree = -1;                 // tree whose posteriors sit in single_qz/qy
+    DevBuf single_qz, single_qy;
+    FitStats stats;
+    DevBuf scratch;                       // cub temp storage
+};
+
+static inline int kp_index(int kp) { return kp == 8 ? 0 : kp == 16 ? 1 : 2; }
+static inline int kp_for(int n_clones) { return n_clones <= 8 ? 8 : n_clones <= 16 ? 16 : 32; }
+
+// ---- internal entry points shared between translation units ---------------------------
+int arb_build_layout(arb_ctx *ctx, int kp);                       // arb_ingest.cu
+int arb_refresh_tables(arb_ctx *ctx);                             // arb_ingest.cu

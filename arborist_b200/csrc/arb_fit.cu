@@ -1,0 +1,1236 @@
+// arb_fit.cu -- the per-tree variational fit of libarborist_b200.so (sm_100a).
+//
+// Replaces the reference's tree loop and everything under it
+// (/root/reference/src/arborist/arborist.py, "A.py"):
+//   A.py:491-520   enumerate_presence          -> k_masks_from_parents / k_masks_from_presence
+//   A.py:200-250   compute_q_z_sparse          -> k_sweep<KP,true>  + k_finish_z
+//   A.py:325-375   compute_q_y_sparse          -> k_sweep<KP,false> + k_finish_y
+//   A.py:378-420   compute_likelihood_sparse   -> fused into the q(z) sweep (G accumulators)
+//   A.py:253-299   entropy / KL                -> fused into k_finish_z / k_finish_y
+//   A.py:679-816   run_variational_inference   -> k_control (per-tree state machine on device)
+//   A.py:1089-1126 the sequential tree loop    -> many trees in flight ("slots"), one round of
+//                                                 kernels advances every active tree by one iteration
+//
+// Algebra (P is the 0/1 presence matrix, lp/la the per-nonzero
+// log-likelihoods, w = lp - la, d = expm1(w)):
+//   S[j,r] = sum_p q_y[j,p] P[p,r]            R[i,p] = sum_r q_z[i,r] P[p,r]
+//   q_z logit[i,r] = sum_{k in row i} la_k + log(1 + d_k S[j_k,r])       (first term cancels)
+//   q_y logit[j,p] = log q_y0[j,p] + sum_{k in col j} log(1 + d_k R[i_k,p])
+//   E[log lik]     = sum_k la_k + sum_i sum_r q_z[i,r] G[i,r],  G[i,r] = sum_k w_k S[j_k,r]
+// The sums of logs are accumulated as running products with the exponent peeled off every
+// `renorm_every` factors; one log per (row, clone) is taken in the finishing kernel.
+//
+// Sweep kernel data flow: a CTA owns (tree slot, panel).  The panel of the gathered operand
+// (S or R rows, padded to KP doubles = 64/128/256 B) is brought into shared memory with bulk
+// async copies (TMA, cp.async.bulk + mbarrier); groups of KP/2 lanes then walk the panel's
+// slice of the sparse stream row by row, each lane reading two adjacent clones (LDS.128).
+#include "arb_common.cuh"
+
+#include <algorithm>
+#include <math.h>
+#include <string.h>
+
+int arb_sweep_table_entries(const arb_ctx *ctx);
+int arb_check_table_range(arb_ctx *ctx);
+
+#define SWEEP_THREADS 512
+#define FIN_THREADS 256
+#define FIN_ROWS 256          // rows of q per finishing CTA (fixed: the ELBO reduction order depends on it)
+#define MASK_STRIDE 64        // per tree: 32 column masks (over clusters) + 32 row masks (over clones)
+#define LN2 0.693147180559945309417232121458
+
+enum { PH_EMPTY = 0, PH_INIT = 1, PH_ITER = 2 };
+
+struct SlotState {
+    int32_t tree, phase, iter, converged;
+    double best;
+};
+
+struct Control {
+    int32_t next_tree, n_trees, n_slots, max_iter;
+    double tol, sum_la;
+    int32_t n_y, n_z, n_init, n_done;
+    int32_t nbz, nby, nbmax, keep;
+};
+
+static inline int grid_for(int64_t n, int block) { return (int)std::max<int64_t>(1, (n + block - 1) / block); }
+
+// ---------------------------------------------------------------------------------------
+// genotype (ancestor-closure) masks: colmask[r] bit p = P[p,r], rowmask[p] bit r = P[p,r]
+// ---------------------------------------------------------------------------------------
+__global__ void k_masks_from_parents(const int32_t *__restrict__ parent, int32_t n_trees, int32_t K,
+                                     int32_t normal, uint32_t *__restrict__ masks)
+{
+    __shared__ uint32_t col[32];
+    const int t = blockIdx.x, r = threadIdx.x;
+    if (r < 32) col[r] = 0;
+    __syncthreads();
+    if (r < K) {
+        // P[p,r] = 1 iff cluster p is r itself or an ancestor of r (A.py:513-518, transposed)
+        uint32_t m = 0;
+        int a = r;
+        for (int step = 0; step < K && a >= 0; ++step) {
+            if (a != normal) m |= 1u << (a < normal ? a : a - 1);
+            a = parent[(int64_t)t * K + a];
+        }
+        col[r] = m;
+    }
+    __syncthreads();
+    uint32_t *out = masks + (int64_t)t * MASK_STRIDE;
+    if (r < 32) out[r] = col[r];
+    if (r < 32) {
+        uint32_t m = 0;
+        for (int c = 0; c < K; ++c) m |= ((col[c] >> r) & 1u) << c;
+        out[32 + r] = (r < K - 1) ? m : 0u;
+    }
+}
+
+__global__ void k_masks_from_presence(const uint8_t *__restrict__ presence, int32_t n_trees, int32_t K,
+                                      uint32_t *__restrict__ masks)
+{
+    const int t = blockIdx.x, x = threadIdx.x, C = K - 1;
+    const uint8_t *P = presence + (int64_t)t * C * K;
+    uint32_t *out = masks + (int64_t)t * MASK_STRIDE;
+    if (x < 32) {
+        uint32_t m = 0;
+        if (x < K) for (int p = 0; p < C; ++p) m |= (P[p * K + x] ? 1u : 0u) << p;
+        out[x] = m;
+        m = 0;
+        if (x < C) for (int r = 0; r < K; ++r) m |= (P[x * K + r] ? 1u : 0u) << r;
+        out[32 + x] = m;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// masked sums over a KP-lane group: out(lane c) = sum_{b: mask_c bit b} v(lane b)
+// fixed ascending order => deterministic and independent of the tree shape
+// ---------------------------------------------------------------------------------------
+template <int KP> __device__ __forceinline__ double masked_sum(double v, uint32_t mask, int n_src)
+{
+    double acc = 0.0;
+    for (int b = 0; b < n_src; ++b) {
+        const double x = __shfl_sync(0xffffffffu, v, b, KP);
+        if ((mask >> b) & 1u) acc += x;
+    }
+    return acc;
+}
+
+template <int KP> __device__ __forceinline__ double group_max(double v)
+{
+#pragma unroll
+    for (int o = KP / 2; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o, KP));
+    return v;
+}
+
+template <int KP> __device__ __forceinline__ double group_sum(double v)
+{
+#pragma unroll
+    for (int o = KP / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o, KP);
+    return v;
+}
+
+// fixed-order block reduction of per-thread partial sums; result valid in thread 0
+__device__ __forceinline__ double block_sum(double v, double *sh)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    const int w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) sh[w] = v;
+    __syncthreads();
+    double s = 0.0;
+    if (threadIdx.x == 0) for (int i = 0; i < nw; ++i) s += sh[i];
+    return s;
+}
+
+// ---------------------------------------------------------------------------------------
+// seed: S rows from a q(y) matrix (the prior for a tree's first pass, A.py:733-743)
+// ---------------------------------------------------------------------------------------
+template <int KP>
+__global__ void k_seed_s(const double *__restrict__ q_src, int64_t src_slot_stride, const int32_t *__restrict__ slots,
+                         const SlotState *__restrict__ st, const uint32_t *__restrict__ masks, int32_t m, int32_t K,
+                         double *__restrict__ xs, double *__restrict__ qy_cur, int copy_q)
+{
+    const int C = K - 1, lane = threadIdx.x % KP;
+    const int slot = slots[blockIdx.y];
+    const uint32_t *mk = masks + (int64_t)st[slot].tree * MASK_STRIDE;
+    const uint32_t cm = lane < K ? mk[lane] : 0u;
+    const int64_t j = (int64_t)blockIdx.x * (blockDim.x / KP) + threadIdx.x / KP;
+    const bool live = j < m;
+    const double *src = q_src + (int64_t)slot * src_slot_stride;
+    const double q = (live && lane < C) ? src[j * C + lane] : 0.0;
+    const double s = masked_sum<KP>(q, cm, C);
+    if (live) {
+        xs[((int64_t)slot * m + j) * KP + lane] = s;
+        if (copy_q && lane < C) qy_cur[((int64_t)slot * m + j) * C + lane] = q;
+    }
+}
+
+// R rows from a q(z) matrix (kernel-level hook only; the fit gets R from k_finish_z)
+template <int KP>
+__global__ void k_seed_r(const double *__restrict__ qz, int32_t slot, const SlotState *__restrict__ st,
+                         const uint32_t *__restrict__ masks, int32_t n, int32_t K, double *__restrict__ xr)
+{
+    const int C = K - 1, lane = threadIdx.x % KP;
+    const uint32_t *mk = masks + (int64_t)st[slot].tree * MASK_STRIDE;
+    const uint32_t rm = lane < C ? mk[32 + lane] : 0u;
+    const int64_t i = (int64_t)blockIdx.x * (blockDim.x / KP) + threadIdx.x / KP;
+    const bool live = i < n;
+    const double q = (live && lane < K) ? qz[((int64_t)slot * n + i) * K + lane] : 0.0;
+    const double r = masked_sum<KP>(q, rm, K);
+    if (live) xr[((int64_t)slot * n + i) * KP + lane] = r;
+}
+
+// ---------------------------------------------------------------------------------------
+// the sweep
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void renorm(double &p, int &e)
+{
+    const int hi = __double2hiint(p);
+    if (hi >= 0x00100000) {          // positive normal: peel the exponent off, keep p in [1,2)
+        e += (hi >> 20) - 1023;
+        p = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(p));
+    }
+}
+
+struct SweepArgs {
+    const double *x;           // gathered operand [slot][n_gather][KP]
+    int64_t x_slot_stride;     // doubles
+    int32_t n_gather;          // rows of the gathered operand
+    const int32_t *seg_ptr;    // [n_panels * n_rows + 1]
+    const uint32_t *stream;    // (code << 16) | index inside the panel
+    int32_t n_rows, panel_rows, n_panels;
+    const int32_t *slot_list;
+    int32_t n_active;
+    const double2 *dw;         // per pair code: (d, w)
+    int32_t tab_n, renorm_every;
+    double *out_m;             // [slot][panel][row][KP] mantissa of the running product
+    int32_t *out_e;            //                        its exponent
+    double *out_g;             //                        sum_k w_k x (q(z) sweep only)
+};
+
+template <int KP, bool WITH_G>
+__global__ void __launch_bounds__(SWEEP_THREADS, 1) k_sweep(const SweepArgs a)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    double *xs = reinterpret_cast<double *>(smem_raw);
+    double2 *tab = reinterpret_cast<double2 *>(smem_raw + (size_t)a.panel_rows * KP * 8);
+    uint64_t *mbar = reinterpret_cast<uint64_t *>(tab + a.tab_n);
+
+    const int panel = blockIdx.x / a.n_active;
+    const int slot = a.slot_list[blockIdx.x % a.n_active];
+    const int row0 = panel * a.panel_rows;
+    const int cnt = min(a.panel_rows, a.n_gather - row0);
+    const uint32_t bytes = (uint32_t)cnt * KP * 8u;
+    const uint32_t bar = smem_u32(mbar);
+
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        // TMA bulk copies of the panel: global -> shared, completion counted on the mbarrier
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+        const char *src = reinterpret_cast<const char *>(a.x + (int64_t)slot * a.x_slot_stride + (int64_t)row0 * KP);
+        const uint32_t dst = smem_u32(xs);
+        for (uint32_t off = 0; off < bytes; off += 32768u) {
+            const uint32_t sz = min(32768u, bytes - off);
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(dst + off), "l"(src + off), "r"(sz), "r"(bar) : "memory");
+        }
+    }
+    for (int c = threadIdx.x; c < a.tab_n; c += SWEEP_THREADS) tab[c] = a.dw[c];
+    __syncthreads();
+    asm volatile("{\n\t.reg .pred p;\n\tWAIT_PANEL:\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n\t"
+                 "@p bra DONE_PANEL;\n\tbra WAIT_PANEL;\n\tDONE_PANEL:\n\t}" ::"r"(bar) : "memory");
+
+    constexpr int GL = KP / 2;                     // lanes per row group; each lane owns two clones
+    const int h = threadIdx.x % GL, gid = threadIdx.x / GL;
+    constexpr int NG = SWEEP_THREADS / GL;
+    const int64_t seg0 = (int64_t)panel * a.n_rows;
+    const int64_t out0 = ((int64_t)slot * a.n_panels + panel) * a.n_rows;
+    const int renorm_every = a.renorm_every;
+
+    for (int i = gid; i < a.n_rows; i += NG) {
+        const int k0 = __ldg(a.seg_ptr + seg0 + i), k1 = __ldg(a.seg_ptr + seg0 + i + 1);
+        double p0 = 1.0, p1 = 1.0, g0 = 0.0, g1 = 0.0;
+        int e0 = 0, e1 = 0, since = 0;
+        for (int k = k0; k < k1; ++k) {
+            const uint32_t word = __ldg(a.stream + k);
+            const uint32_t j = word & 0xffffu, code = word >> 16;
+            const double2 dw = (code < (uint32_t)a.tab_n) ? tab[code] : __ldg(a.dw + code);
+            const double2 x = *reinterpret_cast<const double2 *>(xs + (size_t)j * KP + 2 * h);
+            p0 *= fma(dw.x, x.x, 1.0);
+            p1 *= fma(dw.x, x.y, 1.0);
+            if (WITH_G) {
+                g0 = fma(dw.y, x.x, g0);
+                g1 = fma(dw.y, x.y, g1);
+            }
+            if (++since == renorm_every) {
+                since = 0;
+                renorm(p0, e0);
+                renorm(p1, e1);
+            }
+        }
+        renorm(p0, e0);
+        renorm(p1, e1);
+        const int64_t o = (out0 + i) * KP + 2 * h;
+        *reinterpret_cast<double2 *>(a.out_m + o) = make_double2(p0, p1);
+        *reinterpret_cast<int2 *>(a.out_e + o) = make_int2(e0, e1);
+        if (WITH_G) *reinterpret_cast<double2 *>(a.out_g + o) = make_double2(g0, g1);
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// finishing kernels: combine the panel partials, softmax, ELBO pieces, next gathered operand
+// ---------------------------------------------------------------------------------------
+struct FinishArgs {
+    const double *part_m;
+    const int32_t *part_e;
+    const double *part_g;
+    int32_t n_panels, n_rows, K;
+    const int32_t *slot_list;
+    const SlotState *st;
+    const uint32_t *masks;
+    const double *logq0, *logq0e;   // q(y) only: log prior, log(prior + 1e-12)
+    double *q_cur;                  // [slot][row][K or C]
+    double *x_next;                 // [slot][row][KP]  R (after q_z) or S (after q_y)
+    double *red;                    // [slot][3][nbmax]: lik, entropy, kl partial sums per CTA
+    int32_t nbmax;
+    int32_t given_q;                // elbo_terms hook: take q from q_cur instead of the softmax
+};
+
+// q(z): A.py:245-250 (softmax), A.py:268-273 (entropy), likelihood term, R rows
+template <int KP> __global__ void __launch_bounds__(FIN_THREADS) k_finish_z(const FinishArgs a)
+{
+    __shared__ double sh[FIN_THREADS / 32];
+    const int K = a.K, C = K - 1, lane = threadIdx.x % KP, g = threadIdx.x / KP;
+    constexpr int NG = FIN_THREADS / KP;
+    const int slot = a.slot_list[blockIdx.y];
+    const uint32_t *mk = a.masks + (int64_t)a.st[slot].tree * MASK_STRIDE;
+    const uint32_t rm = lane < C ? mk[32 + lane] : 0u;
+    double lik = 0.0, ent = 0.0;
+    for (int it = 0; it < FIN_ROWS / NG; ++it) {
+        const int64_t i = (int64_t)blockIdx.x * FIN_ROWS + it * NG + g;
+        const bool live = i < a.n_rows;          // uniform per group
+        double prod = 1.0, gsum = 0.0;
+        int esum = 0;
+        if (live) {
+            for (int p = 0; p < a.n_panels; ++p) {
+                const int64_t o = (((int64_t)slot * a.n_panels + p) * a.n_rows + i) * KP + lane;
+                prod *= a.part_m[o];
+                esum += a.part_e[o];
+                gsum += a.part_g[o];
+                if ((p & 255) == 255) renorm(prod, esum);
+            }
+        }
+        double logit = (lane < K) ? log(prod) + (double)esum * LN2 : -INFINITY;
+        const double mx = group_max<KP>(logit);
+        double q = (lane < K) ? exp(logit - mx) : 0.0;
+        const double s = group_sum<KP>(q);
+        q = q / s;
+        if (a.given_q) q = (live && lane < K) ? a.q_cur[((int64_t)slot * a.n_rows + i) * K + lane] : 0.0;
+        const double r = masked_sum<KP>(q, rm, K);
+        if (live) {
+            if (lane < K) {
+                if (!a.given_q) a.q_cur[((int64_t)slot * a.n_rows + i) * K + lane] = q;
+                lik += q * gsum;
+                if (q > 0.0) ent -= q * log(q + 1e-12);
+            }
+            a.x_next[((int64_t)slot * a.n_rows + i) * KP + lane] = r;
+        }
+    }
+    const double t_lik = block_sum(lik, sh);
+    const double t_ent = block_sum(ent, sh);
+    if (threadIdx.x == 0) {
+        double *red = a.red + (int64_t)slot * 3 * a.nbmax;
+        red[blockIdx.x] = t_lik;
+        red[a.nbmax + blockIdx.x] = t_ent;
+    }
+}
+
+// q(y): A.py:373-375 (+ log prior, softmax), A.py:293-299 (KL), S rows
+template <int KP> __global__ void __launch_bounds__(FIN_THREADS) k_finish_y(const FinishArgs a)
+{
+    __shared__ double sh[FIN_THREADS / 32];
+    const int K = a.K, C = K - 1, lane = threadIdx.x % KP, g = threadIdx.x / KP;
+    constexpr int NG = FIN_THREADS / KP;
+    const int slot = a.slot_list[blockIdx.y];
+    const uint32_t *mk = a.masks + (int64_t)a.st[slot].tree * MASK_STRIDE;
+    const uint32_t cm = lane < K ? mk[lane] : 0u;
+    double kl = 0.0;
+    for (int it = 0; it < FIN_ROWS / NG; ++it) {
+        const int64_t j = (int64_t)blockIdx.x * FIN_ROWS + it * NG + g;
+        const bool live = j < a.n_rows;
+        double prod = 1.0;
+        int esum = 0;
+        if (live) {
+            for (int p = 0; p < a.n_panels; ++p) {
+                const int64_t o = (((int64_t)slot * a.n_panels + p) * a.n_rows + j) * KP + lane;
+                prod *= a.part_m[o];
+                esum += a.part_e[o];
+                if ((p & 255) == 255) renorm(prod, esum);
+            }
+        }
+        const bool col = live && lane < C;
+        double logit = col ? a.logq0[j * C + lane] + (log(prod) + (double)esum * LN2) : -INFINITY;
+        const double mx = group_max<KP>(logit);
+        double q = col ? exp(logit - mx) : 0.0;
+        const double s = group_sum<KP>(q);
+        q = q / s;
+        const double sv = masked_sum<KP>(q, cm, C);
+        if (live) {
+            if (lane < C) {
+                a.q_cur[((int64_t)slot * a.n_rows + j) * C + lane] = q;
+                kl += q * (log(q + 1e-12) - a.logq0e[j * C + lane]);
+            }
+            a.x_next[((int64_t)slot * a.n_rows + j) * KP + lane] = sv;
+        }
+    }
+    const double t_kl = block_sum(kl, sh);
+    if (threadIdx.x == 0) a.red[(int64_t)slot * 3 * a.nbmax + 2 * a.nbmax + blockIdx.x] = t_kl;
+}
+
+// entropy / KL of given matrices (kernel-level hook)
+__global__ void k_entropy_kl(const double *qz, int64_t nz, const double *qy, const double *q0, int64_t ny,
+                             double *out)
+{
+    __shared__ double sh[32];
+    double ent = 0.0, kl = 0.0;
+    for (int64_t i = threadIdx.x; i < nz; i += blockDim.x)
+        if (qz[i] > 0.0) ent -= qz[i] * log(qz[i] + 1e-12);
+    for (int64_t i = threadIdx.x; i < ny; i += blockDim.x) kl += qy[i] * (log(qy[i] + 1e-12) - log(q0[i] + 1e-12));
+    const double e = block_sum(ent, sh);
+    const double k = block_sum(kl, sh);
+    if (threadIdx.x == 0) { out[0] = e; out[1] = k; }
+}
+
+// ---------------------------------------------------------------------------------------
+// the per-tree state machine (A.py:745-816) and slot scheduling
+// ---------------------------------------------------------------------------------------
+__global__ void k_control(Control *ctl, SlotState *st, const double *__restrict__ red, int32_t *list_y,
+                          int32_t *list_z, int32_t *list_init, int32_t *snap_tree, double *elbo_out,
+                          int32_t *iters_out, double *trace, int first_call)
+{
+    const int n_slots = ctl->n_slots, nbmax = ctl->nbmax;
+    if (!first_call) {
+        for (int s = threadIdx.x; s < n_slots; s += blockDim.x) {
+            SlotState z = st[s];
+            int snap = -1;
+            if (z.phase != PH_EMPTY) {
+                const double *r = red + (int64_t)s * 3 * nbmax;
+                double lik = ctl->sum_la, ent = 0.0, kl = 0.0;
+                for (int b = 0; b < ctl->nbz; ++b) lik += r[b];
+                for (int b = 0; b < ctl->nbz; ++b) ent += r[nbmax + b];
+                bool done;
+                if (z.phase == PH_INIT) {
+                    const double elbo = lik + ent - 0.0;      // KL(q_y0 || q_y0) = 0 (A.py:750-759)
+                    z.best = elbo;
+                    z.iter = 0;
+                    z.converged = 0;
+                    z.phase = PH_ITER;
+                    snap = z.tree;                            // A.py:762-763
+                    if (trace) trace[(int64_t)z.tree * (ctl->max_iter + 1)] = elbo;
+                    done = ctl->max_iter == 0;
+                } else {
+                    for (int b = 0; b < ctl->nby; ++b) kl += r[2 * nbmax + b];
+                    const double elbo = lik + ent - kl;       // A.py:801-803
+                    if (trace) trace[(int64_t)z.tree * (ctl->max_iter + 1) + z.iter + 1] = elbo;
+                    if (fabs(elbo - z.best) < ctl->tol) z.converged = 1;      // A.py:805 (vs BEST)
+                    if (elbo > z.best) {                                       // A.py:808
+                        snap = z.tree;
+                        z.best = elbo;
+                    }
+                    z.iter += 1;
+                    done = z.converged || z.iter >= ctl->max_iter;           // A.py:813 / loop bound
+                }
+                if (done) {
+                    elbo_out[z.tree] = z.best;
+                    iters_out[z.tree] = z.iter;
+                    z.phase = PH_EMPTY;
+                    z.tree = -1;
+                    atomicAdd(&ctl->n_done, 1);
+                }
+            }
+            st[s] = z;
+            snap_tree[s] = snap;
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int ny = 0, nz = 0, ni = 0, next = ctl->next_tree;
+        for (int s = 0; s < n_slots; ++s) {
+            SlotState z = st[s];
+            if (z.phase == PH_EMPTY && next < ctl->n_trees) {
+                z.tree = next++;
+                z.phase = PH_INIT;
+                z.iter = 0;
+                z.converged = 0;
+                z.best = 0.0;
+                st[s] = z;
+                list_init[ni++] = s;
+            } else if (z.phase == PH_ITER) {
+                list_y[ny++] = s;
+            }
+            if (z.phase != PH_EMPTY) list_z[nz++] = s;
+        }
+        ctl->next_tree = next;
+        ctl->n_y = ny;
+        ctl->n_z = nz;
+        ctl->n_init = ni;
+    }
+}
+
+// A.py:762-763 / 809-810: keep the posteriors of the best iterate
+__global__ void k_snapshot(const int32_t *__restrict__ snap_tree, const double *__restrict__ qz_cur,
+                           const double *__restrict__ qy_cur, int64_t nz, int64_t ny, double *__restrict__ best_qz,
+                           double *__restrict__ best_qy)
+{
+    const int slot = blockIdx.y, tree = snap_tree[slot];
+    if (tree < 0) return;
+    const double *sz = qz_cur + (int64_t)slot * nz, *sy = qy_cur + (int64_t)slot * ny;
+    double *dz = best_qz + (int64_t)tree * nz, *dy = best_qy + (int64_t)tree * ny;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nz; i += stride) dz[i] = sz[i];
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < ny; i += stride) dy[i] = sy[i];
+}
+
+// row argmax, first maximum wins (numpy argmax, treefit.py:105)
+__global__ void k_argmax(const double *__restrict__ q, int64_t rows, int cols, int32_t *__restrict__ out)
+{
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= rows) return;
+    const double *r = q + i * cols;
+    int best = 0;
+    double bv = r[0];
+    for (int c = 1; c < cols; ++c)
+        if (r[c] > bv) { bv = r[c]; best = c; }
+    // numpy treats NaN as the maximum; keep the first NaN like np.argmax does
+    for (int c = 0; c < cols; ++c)
+        if (r[c] != r[c]) { best = c; break; }
+    out[i] = best;
+}
+
+// prior (A.py:523-569): gamma on the input cluster, (1-gamma)/(k-1) elsewhere, uniform 1/k
+__global__ void k_prior_from_labels(const int32_t *__restrict__ label, int32_t m, int32_t C, double gamma,
+                                    double other, double uniform, double *__restrict__ q0)
+{
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= (int64_t)m * C) return;
+    const int j = (int)(i / C), p = (int)(i % C), l = label[j];
+    q0[i] = l < 0 ? uniform : (p == l ? gamma : other);
+}
+
+__global__ void k_prior_logs(const double *__restrict__ q0, int64_t n, double *__restrict__ lq, double *__restrict__ lqe)
+{
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    lq[i] = q0[i] > 0.0 ? log(q0[i]) : -INFINITY;      // log_array, A.py:317-321
+    lqe[i] = log(q0[i] + 1e-12);                      // A.py:296
+}
+
+// ---------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------
+struct FitTarget {                 // where a fit's per-tree results go (all device pointers)
+    const uint32_t *masks;
+    double *elbo;
+    int32_t *iters;
+    double *trace;                 // may be null
+    double *best_qz, *best_qy;     // null => posteriors are not kept
+};
+
+static size_t sweep_smem_bytes(const arb_ctx *ctx, const PanelLayout &L)
+{
+    return (size_t)L.panel_rows * L.kp * 8 + (size_t)arb_sweep_table_entries(ctx) * 16 + 16;
+}
+
+template <int KP> static int configure_kernels(const arb_ctx *ctx, const PanelLayout &L)
+{
+    const int smem = (int)sweep_smem_bytes(ctx, L);
+    ARB_CUDA(cudaFuncSetAttribute(k_sweep<KP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    ARB_CUDA(cudaFuncSetAttribute(k_sweep<KP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    return ARB_OK;
+}
+
+struct Workspace {
+    int kp, K, n_slots, nbz, nby, nbmax;
+    int64_t per_slot_bytes;
+};
+
+static int64_t per_slot_bytes(const arb_ctx *ctx, const PanelLayout &L, int K)
+{
+    const int64_t n = ctx->n_cells, m = ctx->n_snvs, kp = L.kp, C = K - 1;
+    const int64_t nb = std::max((n + FIN_ROWS - 1) / FIN_ROWS, (m + FIN_ROWS - 1) / FIN_ROWS);
+    return (m * kp + n * kp + n * K + m * C) * 8 + (int64_t)L.np_z * n * kp * 20 + (int64_t)L.np_y * m * kp * 12 +
+           3 * nb * 8 + 64;
+}
+
+static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve_bytes, Workspace &ws)
+{
+    const int kp = kp_for(K);
+    ARB_TRY(arb_build_layout(ctx, kp));
+    const PanelLayout &L = ctx->layout[kp_index(kp)];
+    const int64_t n = ctx->n_cells, m = ctx->n_snvs, C = K - 1;
+    ws.kp = kp;
+    ws.K = K;
+    ws.nbz = (int)((n + FIN_ROWS - 1) / FIN_ROWS);
+    ws.nby = (int)((m + FIN_ROWS - 1) / FIN_ROWS);
+    ws.nbmax = std::max(ws.nbz, ws.nby);
+    ws.per_slot_bytes = per_slot_bytes(ctx, L, K);
+    int n_slots = want_slots;
+    if (ctx->opt_slots > 0) n_slots = (int)std::min<int64_t>(n_slots, ctx->opt_slots);
+    if (!(ctx->ws_kp == kp && ctx->ws_k == K && ctx->ws_slots >= n_slots)) {
+        // release first so the free-memory query sees what we can really use
+        for (DevBuf *b : {&ctx->xs, &ctx->xr, &ctx->qz_cur, &ctx->qy_cur, &ctx->part_z, &ctx->part_g, &ctx->part_y,
+                          &ctx->red, &ctx->slot_state, &ctx->lists})
+            b->release();
+        ctx->ws_slots = 0;
+        size_t free_b = 0, total_b = 0;
+        ARB_CUDA(cudaMemGetInfo(&free_b, &total_b));
+        const int64_t usable = (int64_t)(free_b * 0.90) - reserve_bytes;
+        const int64_t fit = usable / ws.per_slot_bytes;
+        ARB_REQUIRE(fit >= 1, ARB_ERR_NOMEM, "not enough device memory for one tree slot (%lld bytes needed, %lld usable)",
+                    (long long)ws.per_slot_bytes, (long long)usable);
+        n_slots = (int)std::min<int64_t>(n_slots, fit);
+        const int64_t S = n_slots;
+        ARB_TRY(ctx->xs.reserve(S * m * kp * 8));
+        ARB_TRY(ctx->xr.reserve(S * n * kp * 8));
+        ARB_TRY(ctx->qz_cur.reserve(S * n * K * 8));
+        ARB_TRY(ctx->qy_cur.reserve(S * m * C * 8));
+        ARB_TRY(ctx->part_z.reserve(S * L.np_z * n * kp * 12));      // mantissa (8) + exponent (4)
+        ARB_TRY(ctx->part_g.reserve(S * L.np_z * n * kp * 8));
+        ARB_TRY(ctx->part_y.reserve(S * L.np_y * m * kp * 12));
+        ARB_TRY(ctx->red.reserve(S * 3 * ws.nbmax * 8));
+        ARB_TRY(ctx->slot_state.reserve(S * sizeof(SlotState) + sizeof(Control) + 64));
+        ARB_TRY(ctx->lists.reserve(S * 4 * 4 + 64));
+        ctx->ws_kp = kp;
+        ctx->ws_k = K;
+        ctx->ws_slots = n_slots;
+    }
+    ws.n_slots = std::min(n_slots, ctx->ws_slots);
+    return ARB_OK;
+}
+
+struct WsPtrs {
+    SlotState *st;
+    Control *ctl;
+    int32_t *list_y, *list_z, *list_init, *snap_tree;
+    double *pz_m, *py_m;
+    int32_t *pz_e, *py_e;
+};
+
+static WsPtrs ws_ptrs(arb_ctx *ctx, const PanelLayout &L)
+{
+    WsPtrs w;
+    const int64_t S = ctx->ws_slots;
+    w.st = ctx->slot_state.as<SlotState>();
+    w.ctl = reinterpret_cast<Control *>(reinterpret_cast<char *>(ctx->slot_state.p) + S * sizeof(SlotState));
+    w.list_y = ctx->lists.as<int32_t>();
+    w.list_z = w.list_y + S;
+    w.list_init = w.list_z + S;
+    w.snap_tree = w.list_init + S;
+    w.pz_m = ctx->part_z.as<double>();
+    w.pz_e = reinterpret_cast<int32_t *>(w.pz_m + S * L.np_z * ctx->n_cells * L.kp);
+    w.py_m = ctx->part_y.as<double>();
+    w.py_e = reinterpret_cast<int32_t *>(w.py_m + S * L.np_y * ctx->n_snvs * L.kp);
+    return w;
+}
+
+template <int KP>
+static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, const int32_t *list, int n_active)
+{
+    SweepArgs a;
+    a.x = ctx->xs.as<double>();
+    a.x_slot_stride = (int64_t)ctx->n_snvs * KP;
+    a.n_gather = ctx->n_snvs;
+    a.seg_ptr = L.zptr.as<int32_t>();
+    a.stream = L.zstream.as<uint32_t>();
+    a.n_rows = ctx->n_cells;
+    a.panel_rows = L.panel_rows;
+    a.n_panels = L.np_z;
+    a.slot_list = list;
+    a.n_active = n_active;
+    a.dw = ctx->tab_dw.as<double2>();
+    a.tab_n = arb_sweep_table_entries(ctx);
+    a.renorm_every = ctx->renorm_every;
+    a.out_m = w.pz_m;
+    a.out_e = w.pz_e;
+    a.out_g = ctx->part_g.as<double>();
+    k_sweep<KP, true><<<n_active * L.np_z, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
+}
+
+template <int KP>
+static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, const int32_t *list, int n_active)
+{
+    SweepArgs a;
+    a.x = ctx->xr.as<double>();
+    a.x_slot_stride = (int64_t)ctx->n_cells * KP;
+    a.n_gather = ctx->n_cells;
+    a.seg_ptr = L.yptr.as<int32_t>();
+    a.stream = L.ystream.as<uint32_t>();
+    a.n_rows = ctx->n_snvs;
+    a.panel_rows = L.panel_rows;
+    a.n_panels = L.np_y;
+    a.slot_list = list;
+    a.n_active = n_active;
+    a.dw = ctx->tab_dw.as<double2>();
+    a.tab_n = arb_sweep_table_entries(ctx);
+    a.renorm_every = ctx->renorm_every;
+    a.out_m = w.py_m;
+    a.out_e = w.py_e;
+    a.out_g = nullptr;
+    k_sweep<KP, false><<<n_active * L.np_y, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
+}
+
+template <int KP>
+static void launch_finish_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, const Workspace &ws,
+                            const uint32_t *masks, const int32_t *list, int n_active, int given_q)
+{
+    FinishArgs a;
+    a.part_m = w.pz_m;
+    a.part_e = w.pz_e;
+    a.part_g = ctx->part_g.as<double>();
+    a.n_panels = L.np_z;
+    a.n_rows = ctx->n_cells;
+    a.K = ws.K;
+    a.slot_list = list;
+    a.st = w.st;
+    a.masks = masks;
+    a.logq0 = nullptr;
+    a.logq0e = nullptr;
+    a.q_cur = ctx->qz_cur.as<double>();
+    a.x_next = ctx->xr.as<double>();
+    a.red = ctx->red.as<double>();
+    a.nbmax = ws.nbmax;
+    a.given_q = given_q;
+    k_finish_z<KP><<<dim3(ws.nbz, n_active), FIN_THREADS, 0, ctx->stream>>>(a);
+}
+
+template <int KP>
+static void launch_finish_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, const Workspace &ws,
+                            const uint32_t *masks, const int32_t *list, int n_active)
+{
+    FinishArgs a;
+    a.part_m = w.py_m;
+    a.part_e = w.py_e;
+    a.part_g = nullptr;
+    a.n_panels = L.np_y;
+    a.n_rows = ctx->n_snvs;
+    a.K = ws.K;
+    a.slot_list = list;
+    a.st = w.st;
+    a.masks = masks;
+    a.logq0 = ctx->logq0.as<double>();
+    a.logq0e = ctx->logq0e.as<double>();
+    a.q_cur = ctx->qy_cur.as<double>();
+    a.x_next = ctx->xs.as<double>();
+    a.red = ctx->red.as<double>();
+    a.nbmax = ws.nbmax;
+    a.given_q = 0;
+    k_finish_y<KP><<<dim3(ws.nby, n_active), FIN_THREADS, 0, ctx->stream>>>(a);
+}
+
+template <int KP>
+static void launch_seed_s(arb_ctx *ctx, const WsPtrs &w, const uint32_t *masks, const double *q_src,
+                          int64_t src_stride, const int32_t *list, int n_active, int K, int copy_q)
+{
+    const int rows_per_block = 256 / KP;
+    k_seed_s<KP><<<dim3(grid_for(ctx->n_snvs, rows_per_block), n_active), 256, 0, ctx->stream>>>(
+        q_src, src_stride, list, w.st, masks, ctx->n_snvs, K, ctx->xs.as<double>(), ctx->qy_cur.as<double>(), copy_q);
+}
+
+// one fit of n_trees trees whose masks are on the device
+template <int KP>
+static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, const FitTarget &tg, int64_t reserve)
+{
+    Workspace ws;
+    ARB_TRY(ensure_workspace(ctx, K, std::min(n_trees, 1024), reserve, ws));
+    const PanelLayout &L = ctx->layout[kp_index(KP)];
+    ARB_TRY(configure_kernels<KP>(ctx, L));
+    const WsPtrs w = ws_ptrs(ctx, L);
+    cudaStream_t st = ctx->stream;
+    const int64_t nz = (int64_t)ctx->n_cells * K, ny = (int64_t)ctx->n_snvs * (K - 1);
+
+    Control h;
+    memset(&h, 0, sizeof h);
+    h.n_trees = n_trees;
+    h.n_slots = ws.n_slots;
+    h.max_iter = max_iter;
+    h.tol = tol;
+    h.sum_la = ctx->sum_la;
+    h.nbz = ws.nbz;
+    h.nby = ws.nby;
+    h.nbmax = ws.nbmax;
+    h.keep = tg.best_qz != nullptr;
+    ARB_CUDA(cudaMemsetAsync(w.st, 0, (size_t)ctx->ws_slots * sizeof(SlotState), st));
+    ARB_CUDA(cudaMemcpyAsync(w.ctl, &h, sizeof h, cudaMemcpyHostToDevice, st));
+
+    cudaEvent_t ev0, ev1;
+    ARB_CUDA(cudaEventCreate(&ev0));
+    ARB_CUDA(cudaEventCreate(&ev1));
+    ARB_CUDA(cudaEventRecord(ev0, st));
+    FitStats stats;
+    k_control<<<1, 256, 0, st>>>(w.ctl, w.st, ctx->red.as<double>(), w.list_y, w.list_z, w.list_init, w.snap_tree,
+                                 tg.elbo, tg.iters, tg.trace, 1);
+    stats.launches++;
+    int rc = ARB_OK;
+    for (;;) {
+        cudaError_t e = cudaMemcpyAsync(&h, w.ctl, sizeof h, cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) {
+            arb_set_error("fit round: %s", cudaGetErrorString(e));
+            rc = ARB_ERR_CUDA;
+            break;
+        }
+        if (h.n_z == 0) break;
+        if (h.n_init > 0) {
+            launch_seed_s<KP>(ctx, w, tg.masks, ctx->q0.as<double>(), 0, w.list_init, h.n_init, K, 1);
+            stats.launches++;
+        }
+        if (h.n_y > 0) {
+            launch_sweep_y<KP>(ctx, L, w, w.list_y, h.n_y);
+            launch_finish_y<KP>(ctx, L, w, ws, tg.masks, w.list_y, h.n_y);
+            stats.launches += 2;
+        }
+        launch_sweep_z<KP>(ctx, L, w, w.list_z, h.n_z);
+        launch_finish_z<KP>(ctx, L, w, ws, tg.masks, w.list_z, h.n_z, 0);
+        k_control<<<1, 256, 0, st>>>(w.ctl, w.st, ctx->red.as<double>(), w.list_y, w.list_z, w.list_init,
+                                     w.snap_tree, tg.elbo, tg.iters, tg.trace, 0);
+        stats.launches += 3;
+        if (tg.best_qz) {
+            k_snapshot<<<dim3(16, ws.n_slots), 256, 0, st>>>(w.snap_tree, ctx->qz_cur.as<double>(),
+                                                            ctx->qy_cur.as<double>(), nz, ny, tg.best_qz, tg.best_qy);
+            stats.launches++;
+        }
+    }
+    cudaEventRecord(ev1, st);
+    cudaEventSynchronize(ev1);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ev0, ev1);
+    cudaEventDestroy(ev0);
+    cudaEventDestroy(ev1);
+    stats.device_ms = ms;
+    ctx->stats = stats;
+    if (rc == ARB_OK) {
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) {
+            arb_set_error("fit: %s", cudaGetErrorString(e));
+            rc = ARB_ERR_CUDA;
+        }
+    }
+    return rc;
+}
+
+static int fit_dispatch(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, const FitTarget &tg,
+                        int64_t reserve)
+{
+    switch (kp_for(K)) {
+    case 8: return fit_core<8>(ctx, n_trees, K, max_iter, tol, tg, reserve);
+    case 16: return fit_core<16>(ctx, n_trees, K, max_iter, tol, tg, reserve);
+    default: return fit_core<32>(ctx, n_trees, K, max_iter, tol, tg, reserve);
+    }
+}
+
+static int check_ready(arb_ctx *ctx, int K, const char *who)
+{
+    ARB_REQUIRE(ctx, ARB_ERR_INVALID, "%s: null context", who);
+    ARB_REQUIRE(ctx->ingested, ARB_ERR_INVALID, "%s: no matrix ingested", who);
+    ARB_REQUIRE(K >= 2 && K <= ARB_MAX_CLONES, K > ARB_MAX_CLONES ? ARB_ERR_UNSUPPORTED : ARB_ERR_INVALID,
+                "%s: n_clones=%d outside 2..%d", who, K, ARB_MAX_CLONES);
+    ARB_REQUIRE(ctx->n_clusters == K - 1, ARB_ERR_INVALID, "%s: prior has %d clusters, trees have %d", who,
+                ctx->n_clusters, K - 1);
+    ARB_TRY(arb_check_table_range(ctx));
+    return ARB_OK;
+}
+
+static int run_fit(arb_ctx *ctx, int32_t n_trees, int32_t K, int32_t max_iter, double tol, int32_t mode,
+                   int32_t keep, double *elbo, int32_t *iters, double *elbo_trace)
+{
+    ARB_REQUIRE(mode == ARB_MODE_VI, ARB_ERR_UNSUPPORTED,
+                "mode %d: only ARB_MODE_VI is implemented in this release", mode);
+    ARB_REQUIRE(max_iter >= 0, ARB_ERR_INVALID, "max_iter=%d", max_iter);
+    cudaStream_t st = ctx->stream;
+    const int64_t nz = (int64_t)ctx->n_cells * K, ny = (int64_t)ctx->n_snvs * (K - 1);
+    ARB_TRY(ctx->d_elbo.reserve((size_t)n_trees * 8));
+    ARB_TRY(ctx->d_iters.reserve((size_t)n_trees * 4));
+    FitTarget tg;
+    memset(&tg, 0, sizeof tg);
+    tg.masks = ctx->tree_masks.as<uint32_t>();
+    tg.elbo = ctx->d_elbo.as<double>();
+    tg.iters = ctx->d_iters.as<int32_t>();
+    const size_t trace_n = (size_t)n_trees * (max_iter + 1);
+    if (elbo_trace) {
+        ARB_TRY(ctx->d_trace.reserve(trace_n * 8));
+        ARB_CUDA(cudaMemsetAsync(ctx->d_trace.p, 0xff, trace_n * 8, st));     // all-ones = NaN
+        tg.trace = ctx->d_trace.as<double>();
+    }
+    int64_t reserve = 0;
+    ctx->fit_kept = false;
+    if (keep) {
+        // release the workspace first if the posteriors would not fit beside it
+        ARB_TRY(ctx->best_qz.reserve((size_t)n_trees * nz * 8));
+        ARB_TRY(ctx->best_qy.reserve((size_t)n_trees * ny * 8));
+        tg.best_qz = ctx->best_qz.as<double>();
+        tg.best_qy = ctx->best_qy.as<double>();
+    } else {
+        ctx->best_qz.release();
+        ctx->best_qy.release();
+    }
+    ctx->fit_trees = 0;
+    ctx->single_tree = -1;
+    ARB_TRY(fit_dispatch(ctx, n_trees, K, max_iter, tol, tg, reserve));
+    ARB_CUDA(cudaMemcpyAsync(elbo, tg.elbo, (size_t)n_trees * 8, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaMemcpyAsync(iters, tg.iters, (size_t)n_trees * 4, cudaMemcpyDeviceToHost, st));
+    if (elbo_trace) ARB_CUDA(cudaMemcpyAsync(elbo_trace, tg.trace, trace_n * 8, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaStreamSynchronize(st));
+    double ti = 0;
+    for (int t = 0; t < n_trees; ++t) ti += iters[t] + 0.5;
+    ctx->stats.tree_iterations = ti;
+    ctx->fit_trees = n_trees;
+    ctx->fit_k = K;
+    ctx->fit_max_iter = max_iter;
+    ctx->fit_tol = tol;
+    ctx->fit_mode = mode;
+    ctx->fit_kept = keep != 0;
+    return ARB_OK;
+}
+
+ARB_API int arb_fit_trees(arb_ctx *ctx, int32_t n_trees, int32_t n_clones, int32_t normal_idx, const int32_t *parent,
+                          int32_t max_iter, double tolerance, int32_t mode, int32_t keep_posteriors, double *elbo,
+                          int32_t *iters, double *elbo_trace)
+{
+    ARB_TRY(check_ready(ctx, n_clones, "arb_fit_trees"));
+    ARB_REQUIRE(n_trees > 0 && parent && elbo && iters, ARB_ERR_INVALID, "arb_fit_trees: bad argument");
+    ARB_REQUIRE(normal_idx >= 0 && normal_idx < n_clones, ARB_ERR_INVALID, "arb_fit_trees: normal_idx=%d", normal_idx);
+    for (int64_t i = 0; i < (int64_t)n_trees * n_clones; ++i)
+        ARB_REQUIRE(parent[i] >= -1 && parent[i] < n_clones, ARB_ERR_INVALID, "arb_fit_trees: parent[%lld]=%d",
+                    (long long)i, parent[i]);
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    DevBuf d_parent;
+    ARB_TRY(d_parent.reserve((size_t)n_trees * n_clones * 4));
+    ARB_TRY(ctx->tree_masks.reserve((size_t)n_trees * MASK_STRIDE * 4));
+    ARB_CUDA(cudaMemcpyAsync(d_parent.p, parent, (size_t)n_trees * n_clones * 4, cudaMemcpyHostToDevice, ctx->stream));
+    k_masks_from_parents<<<n_trees, 32, 0, ctx->stream>>>(d_parent.as<int32_t>(), n_trees, n_clones, normal_idx,
+                                                          ctx->tree_masks.as<uint32_t>());
+    ARB_CUDA(cudaStreamSynchronize(ctx->stream));
+    d_parent.release();
+    return run_fit(ctx, n_trees, n_clones, max_iter, tolerance, mode, keep_posteriors, elbo, iters, elbo_trace);
+}
+
+ARB_API int arb_fit_presence(arb_ctx *ctx, int32_t n_trees, int32_t n_clones, const uint8_t *presence,
+                             int32_t max_iter, double tolerance, int32_t mode, int32_t keep_posteriors, double *elbo,
+                             int32_t *iters, double *elbo_trace)
+{
+    ARB_TRY(check_ready(ctx, n_clones, "arb_fit_presence"));
+    ARB_REQUIRE(n_trees > 0 && presence && elbo && iters, ARB_ERR_INVALID, "arb_fit_presence: bad argument");
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    const size_t bytes = (size_t)n_trees * (n_clones - 1) * n_clones;
+    DevBuf d_p;
+    ARB_TRY(d_p.reserve(bytes));
+    ARB_TRY(ctx->tree_masks.reserve((size_t)n_trees * MASK_STRIDE * 4));
+    ARB_CUDA(cudaMemcpyAsync(d_p.p, presence, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    k_masks_from_presence<<<n_trees, 32, 0, ctx->stream>>>(d_p.as<uint8_t>(), n_trees, n_clones,
+                                                           ctx->tree_masks.as<uint32_t>());
+    ARB_CUDA(cudaStreamSynchronize(ctx->stream));
+    d_p.release();
+    return run_fit(ctx, n_trees, n_clones, max_iter, tolerance, mode, keep_posteriors, elbo, iters, elbo_trace);
+}
+
+ARB_API int arb_posterior_bytes(arb_ctx *ctx, int32_t n_trees, int32_t n_clones, int64_t *bytes, int64_t *free_bytes)
+{
+    ARB_REQUIRE(ctx && ctx->ingested, ARB_ERR_INVALID, "arb_posterior_bytes: no matrix ingested");
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    if (bytes)
+        *bytes = (int64_t)n_trees * ((int64_t)ctx->n_cells * n_clones + (int64_t)ctx->n_snvs * (n_clones - 1)) * 8;
+    if (free_bytes) {
+        size_t f = 0, t = 0;
+        ARB_CUDA(cudaMemGetInfo(&f, &t));
+        *free_bytes = (int64_t)f + (int64_t)ctx->best_qz.bytes + (int64_t)ctx->best_qy.bytes;
+    }
+    return ARB_OK;
+}
+
+// posteriors of tree t of the last fit: resident, or refit on demand (the fit is deterministic)
+static int locate_fit(arb_ctx *ctx, int32_t t, const double **qz, const double **qy)
+{
+    ARB_REQUIRE(ctx && ctx->fit_trees > 0, ARB_ERR_INVALID, "no fit to read from");
+    ARB_REQUIRE(t >= 0 && t < ctx->fit_trees, ARB_ERR_INVALID, "tree %d outside 0..%d", t, ctx->fit_trees - 1);
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    const int K = ctx->fit_k;
+    const int64_t nz = (int64_t)ctx->n_cells * K, ny = (int64_t)ctx->n_snvs * (K - 1);
+    if (ctx->fit_kept) {
+        *qz = ctx->best_qz.as<double>() + (int64_t)t * nz;
+        *qy = ctx->best_qy.as<double>() + (int64_t)t * ny;
+        return ARB_OK;
+    }
+    if (ctx->single_tree != t) {
+        ARB_TRY(ctx->single_qz.reserve((size_t)nz * 8 + 16));
+        ARB_TRY(ctx->single_qy.reserve((size_t)ny * 8));
+        FitTarget tg;
+        memset(&tg, 0, sizeof tg);
+        tg.masks = ctx->tree_masks.as<uint32_t>() + (int64_t)t * MASK_STRIDE;
+        // scalar outputs of the single refit go to the tail of single_qz
+        DevBuf tmp;
+        ARB_TRY(tmp.reserve(32));
+        tg.elbo = tmp.as<double>();
+        tg.iters = reinterpret_cast<int32_t *>(tmp.as<double>() + 1);
+        tg.best_qz = ctx->single_qz.as<double>();
+        tg.best_qy = ctx->single_qy.as<double>();
+        const FitStats keep_stats = ctx->stats;
+        int rc = fit_dispatch(ctx, 1, K, ctx->fit_max_iter, ctx->fit_tol, tg, 0);
+        ctx->stats = keep_stats;
+        tmp.release();
+        ARB_TRY(rc);
+        ctx->single_tree = t;
+    }
+    *qz = ctx->single_qz.as<double>();
+    *qy = ctx->single_qy.as<double>();
+    return ARB_OK;
+}
+
+ARB_API int arb_get_fit(arb_ctx *ctx, int32_t t, double *q_z, double *q_y)
+{
+    const double *dz, *dy;
+    ARB_TRY(locate_fit(ctx, t, &dz, &dy));
+    const int K = ctx->fit_k;
+    if (q_z) ARB_CUDA(cudaMemcpyAsync(q_z, dz, (size_t)ctx->n_cells * K * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (q_y)
+        ARB_CUDA(cudaMemcpyAsync(q_y, dy, (size_t)ctx->n_snvs * (K - 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    ARB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return ARB_OK;
+}
+
+ARB_API int arb_get_map(arb_ctx *ctx, int32_t t, int32_t *z, int32_t *y)
+{
+    const double *dz, *dy;
+    ARB_TRY(locate_fit(ctx, t, &dz, &dy));
+    const int K = ctx->fit_k;
+    DevBuf out;
+    ARB_TRY(out.reserve(((size_t)ctx->n_cells + ctx->n_snvs) * 4));
+    int32_t *oz = out.as<int32_t>(), *oy = oz + ctx->n_cells;
+    k_argmax<<<grid_for(ctx->n_cells, 256), 256, 0, ctx->stream>>>(dz, ctx->n_cells, K, oz);
+    k_argmax<<<grid_for(ctx->n_snvs, 256), 256, 0, ctx->stream>>>(dy, ctx->n_snvs, K - 1, oy);
+    if (z) ARB_CUDA(cudaMemcpyAsync(z, oz, (size_t)ctx->n_cells * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (y) ARB_CUDA(cudaMemcpyAsync(y, oy, (size_t)ctx->n_snvs * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    ARB_CUDA(cudaStreamSynchronize(ctx->stream));
+    out.release();
+    return ARB_OK;
+}
+
+ARB_API int arb_get_presence(arb_ctx *ctx, int32_t t, uint8_t *presence)
+{
+    ARB_REQUIRE(ctx && ctx->fit_trees > 0 && presence, ARB_ERR_INVALID, "arb_get_presence: no fit");
+    ARB_REQUIRE(t >= 0 && t < ctx->fit_trees, ARB_ERR_INVALID, "arb_get_presence: tree %d", t);
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    uint32_t mk[MASK_STRIDE];
+    ARB_CUDA(cudaMemcpy(mk, ctx->tree_masks.as<uint32_t>() + (int64_t)t * MASK_STRIDE, sizeof mk,
+                        cudaMemcpyDeviceToHost));
+    const int K = ctx->fit_k, C = K - 1;
+    for (int p = 0; p < C; ++p)
+        for (int r = 0; r < K; ++r) presence[p * K + r] = (uint8_t)((mk[32 + p] >> r) & 1u);
+    return ARB_OK;
+}
+
+ARB_API int arb_last_fit_stats(arb_ctx *ctx, int64_t *kernel_launches, double *device_ms, double *tree_iterations,
+                               double *sweep_ms)
+{
+    ARB_REQUIRE(ctx, ARB_ERR_INVALID, "arb_last_fit_stats: null context");
+    if (kernel_launches) *kernel_launches = ctx->stats.launches;
+    if (device_ms) *device_ms = ctx->stats.device_ms;
+    if (tree_iterations) *tree_iterations = ctx->stats.tree_iterations;
+    if (sweep_ms) *sweep_ms = ctx->stats.sweep_ms;
+    return ARB_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// prior
+// ---------------------------------------------------------------------------------------
+static int finish_prior(arb_ctx *ctx, int32_t C)
+{
+    const int64_t n = (int64_t)ctx->n_snvs * C;
+    ARB_TRY(ctx->logq0.reserve(n * 8));
+    ARB_TRY(ctx->logq0e.reserve(n * 8));
+    k_prior_logs<<<grid_for(n, 256), 256, 0, ctx->stream>>>(ctx->q0.as<double>(), n, ctx->logq0.as<double>(),
+                                                           ctx->logq0e.as<double>());
+    ARB_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->n_clusters = C;
+    ctx->single_tree = -1;
+    return ARB_OK;
+}
+
+ARB_API int arb_set_prior_labels(arb_ctx *ctx, const int32_t *label_idx, int32_t n_clusters, double gamma)
+{
+    ARB_REQUIRE(ctx && ctx->ingested && label_idx, ARB_ERR_INVALID, "arb_set_prior_labels: bad argument");
+    ARB_REQUIRE(n_clusters >= 1 && n_clusters < ARB_MAX_CLONES, ARB_ERR_INVALID, "arb_set_prior_labels: %d clusters",
+                n_clusters);
+    for (int32_t j = 0; j < ctx->n_snvs; ++j)
+        ARB_REQUIRE(label_idx[j] >= -1 && label_idx[j] < n_clusters, ARB_ERR_INVALID,
+                    "arb_set_prior_labels: label_idx[%d]=%d", j, label_idx[j]);
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    const int64_t n = (int64_t)ctx->n_snvs * n_clusters;
+    DevBuf lab;
+    ARB_TRY(lab.reserve((size_t)ctx->n_snvs * 4));
+    ARB_TRY(ctx->q0.reserve(n * 8));
+    ARB_CUDA(cudaMemcpyAsync(lab.p, label_idx, (size_t)ctx->n_snvs * 4, cudaMemcpyHostToDevice, ctx->stream));
+    // the same double arithmetic as A.py:552-553
+    const double other = n_clusters > 1 ? (1 - gamma) / (n_clusters - 1) : 0.0, uniform = 1.0 / n_clusters;
+    k_prior_from_labels<<<grid_for(n, 256), 256, 0, ctx->stream>>>(lab.as<int32_t>(), ctx->n_snvs, n_clusters, gamma,
+                                                                  other, uniform, ctx->q0.as<double>());
+    ARB_CUDA(cudaStreamSynchronize(ctx->stream));
+    lab.release();
+    return finish_prior(ctx, n_clusters);
+}
+
+ARB_API int arb_set_prior(arb_ctx *ctx, const double *q_y_init, int32_t n_clusters)
+{
+    ARB_REQUIRE(ctx && ctx->ingested && q_y_init, ARB_ERR_INVALID, "arb_set_prior: bad argument");
+    ARB_REQUIRE(n_clusters >= 1 && n_clusters < ARB_MAX_CLONES, ARB_ERR_INVALID, "arb_set_prior: %d clusters",
+                n_clusters);
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    const int64_t n = (int64_t)ctx->n_snvs * n_clusters;
+    ARB_TRY(ctx->q0.reserve(n * 8));
+    ARB_CUDA(cudaMemcpyAsync(ctx->q0.p, q_y_init, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    return finish_prior(ctx, n_clusters);
+}
+
+ARB_API int arb_get_prior(arb_ctx *ctx, double *q_y_init)
+{
+    ARB_REQUIRE(ctx && ctx->n_clusters > 0 && q_y_init, ARB_ERR_INVALID, "arb_get_prior: no prior set");
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    ARB_CUDA(cudaMemcpy(q_y_init, ctx->q0.p, (size_t)ctx->n_snvs * ctx->n_clusters * 8, cudaMemcpyDeviceToHost));
+    return ARB_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// kernel-level hooks: one tree in slot 0 with explicit posteriors
+// ---------------------------------------------------------------------------------------
+struct HookEnv {
+    Workspace ws;
+    WsPtrs w;
+    const PanelLayout *L;
+    int32_t *list0;
+};
+
+static int hook_setup(arb_ctx *ctx, int K, const uint8_t *presence, HookEnv &env, const char *who)
+{
+    ARB_REQUIRE(ctx && ctx->ingested && presence, ARB_ERR_INVALID, "%s: bad argument", who);
+    ARB_REQUIRE(K >= 2 && K <= ARB_MAX_CLONES, ARB_ERR_INVALID, "%s: n_clones=%d", who, K);
+    ARB_TRY(arb_check_table_range(ctx));
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    ARB_TRY(ensure_workspace(ctx, K, 1, 0, env.ws));
+    env.L = &ctx->layout[kp_index(env.ws.kp)];
+    env.w = ws_ptrs(ctx, *env.L);
+    switch (env.ws.kp) {
+    case 8: ARB_TRY(configure_kernels<8>(ctx, *env.L)); break;
+    case 16: ARB_TRY(configure_kernels<16>(ctx, *env.L)); break;
+    default: ARB_TRY(configure_kernels<32>(ctx, *env.L)); break;
+    }
+    const int C = K - 1;
+    DevBuf d_p;
+    ARB_TRY(d_p.reserve((size_t)C * K));
+    ARB_TRY(ctx->masks.reserve(MASK_STRIDE * 4));
+    ARB_CUDA(cudaMemcpyAsync(d_p.p, presence, (size_t)C * K, cudaMemcpyHostToDevice, ctx->stream));
+    k_masks_from_presence<<<1, 32, 0, ctx->stream>>>(d_p.as<uint8_t>(), 1, K, ctx->masks.as<uint32_t>());
+    SlotState s0;
+    memset(&s0, 0, sizeof s0);
+    s0.tree = 0;
+    s0.phase = PH_INIT;
+    ARB_CUDA(cudaMemcpyAsync(env.w.st, &s0, sizeof s0, cudaMemcpyHostToDevice, ctx->stream));
+    int32_t zero = 0;
+    ARB_CUDA(cudaMemcpyAsync(env.w.list_z, &zero, 4, cudaMemcpyHostToDevice, ctx->stream));
+    env.list0 = env.w.list_z;
+    ARB_CUDA(cudaStreamSynchronize(ctx->stream));
+    d_p.release();
+    ctx->single_tree = -1;
+    return ARB_OK;
+}
+
+#define KP_SWITCH(kp, ...)                                  \
+    switch (kp) {                                           \
+    case 8: { constexpr int KPV = 8; __VA_ARGS__; } break;   \
+    case 16: { constexpr int KPV = 16; __VA_ARGS__; } break; \
+    default: { constexpr int KPV = 32; __VA_ARGS__; } break; \
+    }
+
+ARB_API int arb_qz_update(arb_ctx *ctx, int32_t n_clones, const uint8_t *presence, const double *q_y, double *q_z)
+{
+    HookEnv env;
+    ARB_TRY(hook_setup(ctx, n_clones, presence, env, "arb_qz_update"));
+    ARB_REQUIRE(q_y && q_z, ARB_ERR_INVALID, "arb_qz_update: null argument");
+    const int K = n_clones, C = K - 1;
+    const uint32_t *mk = ctx->masks.as<uint32_t>();
+    ARB_CUDA(cudaMemcpyAsync(ctx->qy_cur.p, q_y, (size_t)ctx->n_snvs * C * 8, cudaMemcpyHostToDevice, ctx->stream));
+    KP_SWITCH(env.ws.kp, {
+        launch_seed_s<KPV>(ctx, env.w, mk, ctx->qy_cur.as<double>(), (int64_t)ctx->n_snvs * C, env.list0, 1, K, 0);
+        launch_sweep_z<KPV>(ctx, *env.L, env.w, env.list0, 1);
+        launch_finish_z<KPV>(ctx, *env.L, env.w, env.ws, mk, env.list0, 1, 0);
+    });
+    ARB_CUDA(cudaMemcpyAsync(q_z, ctx->qz_cur.p, (size_t)ctx->n_cells * K * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    ARB_CUDA(cudaStreamSynchronize(ctx->stream));
+    ARB_CUDA(cudaGetLastError());
+    return ARB_OK;
+}
+
+ARB_API int arb_qy_update(arb_ctx *ctx, int32_t n_clones, const uint8_t *presence, const double *q_z, double *q_y)
+{
+    HookEnv env;
+    ARB_TRY(hook_setup(ctx, n_clones, presence, env, "arb_qy_update"));
+    ARB_REQUIRE(q_z && q_y, ARB_ERR_INVALID, "arb_qy_update: null argument");
+    ARB_REQUIRE(ctx->n_clusters == n_clones - 1, ARB_ERR_INVALID, "arb_qy_update: prior has %d clusters",
+                ctx->n_clusters);
+    const int K = n_clones, C = K - 1;
+    const uint32_t *mk = ctx->masks.as<uint32_t>();
+    ARB_CUDA(cudaMemcpyAsync(ctx->qz_cur.p, q_z, (size_t)ctx->n_cells * K * 8, cudaMemcpyHostToDevice, ctx->stream));
+    KP_SWITCH(env.ws.kp, {
+        k_seed_r<KPV><<<grid_for(ctx->n_cells, 256 / KPV), 256, 0, ctx->stream>>>(
+            ctx->qz_cur.as<double>(), 0, env.w.st, mk, ctx->n_cells, K, ctx->xr.as<double>());
+        launch_sweep_y<KPV>(ctx, *env.L, env.w, env.list0, 1);
+        launch_finish_y<KPV>(ctx, *env.L, env.w, env.ws, mk, env.list0, 1);
+    });
+    ARB_CUDA(cudaMemcpyAsync(q_y, ctx->qy_cur.p, (size_t)ctx->n_snvs * C * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    ARB_CUDA(cudaStreamSynchronize(ctx->stream));
+    ARB_CUDA(cudaGetLastError());
+    return ARB_OK;
+}
+
+ARB_API int arb_elbo_terms(arb_ctx *ctx, int32_t n_clones, const uint8_t *presence, const double *q_z,
+                           const double *q_y, double *likelihood, double *entropy, double *kl)
+{
+    HookEnv env;
+    ARB_TRY(hook_setup(ctx, n_clones, presence, env, "arb_elbo_terms"));
+    ARB_REQUIRE(q_z && q_y, ARB_ERR_INVALID, "arb_elbo_terms: null argument");
+    ARB_REQUIRE(ctx->n_clusters == n_clones - 1, ARB_ERR_INVALID, "arb_elbo_terms: prior has %d clusters",
+                ctx->n_clusters);
+    const int K = n_clones, C = K - 1;
+    const int64_t nz = (int64_t)ctx->n_cells * K, ny = (int64_t)ctx->n_snvs * C;
+    const uint32_t *mk = ctx->masks.as<uint32_t>();
+    ARB_CUDA(cudaMemcpyAsync(ctx->qy_cur.p, q_y, ny * 8, cudaMemcpyHostToDevice, ctx->stream));
+    ARB_CUDA(cudaMemcpyAsync(ctx->qz_cur.p, q_z, nz * 8, cudaMemcpyHostToDevice, ctx->stream));
+    KP_SWITCH(env.ws.kp, {
+        launch_seed_s<KPV>(ctx, env.w, mk, ctx->qy_cur.as<double>(), ny, env.list0, 1, K, 0);
+        launch_sweep_z<KPV>(ctx, *env.L, env.w, env.list0, 1);
+        launch_finish_z<KPV>(ctx, *env.L, env.w, env.ws, mk, env.list0, 1, 1);
+    });
+    DevBuf out;
+    ARB_TRY(out.reserve(16));
+    k_entropy_kl<<<1, 1024, 0, ctx->stream>>>(ctx->qz_cur.as<double>(), nz, ctx->qy_cur.as<double>(),
+                                              ctx->q0.as<double>(), ny, out.as<double>());
+    std::vector<double> red((size_t)env.ws.nbz);
+    double ek[2];
+    ARB_CUDA(cudaMemcpyAsync(red.data(), ctx->red.p, red.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    ARB_CUDA(cudaMemcpyAsync(ek, out.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    ARB_CUDA(cudaStreamSynchronize(ctx->stream));
+    ARB_CUDA(cudaGetLastError());
+    out.release();
+    double lik = ctx->sum_la;
+    for (double v : red) lik += v;
+    if (likelihood) *likelihood = lik;
+    if (entropy) *entropy = ek[0];
+    if (kl) *kl = ek[1];
+    return ARB_OK;
+}

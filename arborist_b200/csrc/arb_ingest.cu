@@ -1,0 +1,841 @@
+// arb_ingest.cu -- context management and the read-count ingest of libarborist_b200.so.
+//
+// Replaces the host-side Python of the reference's ingest
+// (/root/reference/src/arborist/arborist.py, "A.py"):
+//   A.py:1034-1041  zero-alt SNV filter            -> k_alt_sum / k_keep_flags / compaction
+//   A.py:838-846    binomial log-pmf per row       -> dictionary of distinct (alt,total) pairs
+//                                                     + a per-pair table (k_logpmf_table)
+//   A.py:851-855    first-appearance index maps    -> k_first_row + sort (cells), scan (SNVs)
+//   A.py:459-488    COO build (Python loop)        -> k_compact
+//   A.py:423-456    CSR / CSC build (Python loops) -> radix sorts into the panelled layouts
+//
+// Data layout in HBM after ingest: a canonical COO sorted by (cell, snv) with a 16-bit
+// pair code per nonzero (10 B/nnz instead of the reference's 20 B/nnz per orientation),
+// plus, per padded clone width KP, two panelled streams of 4 B/nnz (see PanelLayout).
+#include "arb_common.cuh"
+
+#include <cub/cub.cuh>
+
+#include <algorithm>
+#include <limits.h>
+#include <math.h>
+#include <numeric>
+#include <stdarg.h>
+#include <string.h>
+
+// ---------------------------------------------------------------------------------------
+// errors / library
+// ---------------------------------------------------------------------------------------
+static thread_local std::string g_last_error;
+
+void arb_set_error(const char *fmt, ...)
+{
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_last_error = buf;
+}
+
+ARB_API const char *arb_last_error(void) { return g_last_error.c_str(); }
+ARB_API int arb_abi_version(void) { return ARB_ABI_VERSION; }
+
+ARB_API int arb_device_count(int *count)
+{
+    ARB_REQUIRE(count, ARB_ERR_INVALID, "arb_device_count: null pointer");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        n = 0;
+    }
+    *count = n;
+    return ARB_OK;
+}
+
+ARB_API int arb_ctx_create(int device, arb_ctx **out)
+{
+    ARB_REQUIRE(out, ARB_ERR_INVALID, "arb_ctx_create: null output pointer");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        arb_set_error("arb_ctx_create: no usable CUDA device (%s); this library has no CPU path",
+                      e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+        return ARB_ERR_CUDA;
+    }
+    ARB_REQUIRE(device >= 0 && device < n, ARB_ERR_INVALID,
+                "arb_ctx_create: device %d out of range (0..%d)", device, n - 1);
+    ARB_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    ARB_CUDA(cudaGetDeviceProperties(&prop, device));
+    ARB_REQUIRE(prop.major >= 10, ARB_ERR_UNSUPPORTED,
+                "arb_ctx_create: device %d is sm_%d%d; this library is built for sm_100a only",
+                device, prop.major, prop.minor);
+    arb_ctx *ctx = new arb_ctx();
+    ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
+    ctx->smem_optin = prop.sharedMemPerBlockOptin;
+    e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        arb_set_error("cudaStreamCreate: %s", cudaGetErrorString(e));
+        delete ctx;
+        return ARB_ERR_CUDA;
+    }
+    *out = ctx;
+    return ARB_OK;
+}
+
+ARB_API int arb_ctx_destroy(arb_ctx *ctx)
+{
+    if (!ctx) return ARB_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    DevBuf *bufs[] = {&ctx->coo_cell, &ctx->coo_snv, &ctx->coo_code, &ctx->cell_order,
+                      &ctx->snv_order, &ctx->tab_dw, &ctx->q0, &ctx->logq0, &ctx->logq0e,
+                      &ctx->xs, &ctx->xr, &ctx->qz_cur, &ctx->qy_cur, &ctx->part_z, &ctx->part_g,
+                      &ctx->part_y, &ctx->red, &ctx->slot_state, &ctx->lists, &ctx->masks,
+                      &ctx->best_qz, &ctx->best_qy, &ctx->d_elbo, &ctx->d_iters, &ctx->d_trace,
+                      &ctx->tree_masks, &ctx->single_qz, &ctx->single_qy, &ctx->scratch};
+    for (DevBuf *b : bufs) b->release();
+    for (auto &l : ctx->layout) l.release();
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return ARB_OK;
+}
+
+ARB_API int arb_set_option(arb_ctx *ctx, const char *name, int64_t value)
+{
+    ARB_REQUIRE(ctx && name, ARB_ERR_INVALID, "arb_set_option: null argument");
+    if (!strcmp(name, "slots")) ctx->opt_slots = value;
+    else if (!strcmp(name, "panel_kb")) {
+        ctx->opt_panel_kb = value;
+        for (auto &l : ctx->layout) l.release();
+    } else if (!strcmp(name, "threads")) ctx->opt_threads = value;
+    else {
+        arb_set_error("arb_set_option: unknown option '%s'", name);
+        return ARB_ERR_INVALID;
+    }
+    return ARB_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// small helpers
+// ---------------------------------------------------------------------------------------
+static inline int grid_for(int64_t n, int block) { return (int)std::max<int64_t>(1, (n + block - 1) / block); }
+
+template <class F> static int with_cub(arb_ctx *ctx, F f)
+{
+    size_t bytes = 0;
+    ARB_CUDA(f(nullptr, bytes));
+    ARB_TRY(ctx->scratch.reserve(std::max<size_t>(bytes, 16)));
+    bytes = ctx->scratch.bytes;
+    ARB_CUDA(f(ctx->scratch.p, bytes));
+    return ARB_OK;
+}
+
+static int bits_for(uint64_t max_value)
+{
+    int b = 1;
+    while (b < 64 && (max_value >> b)) ++b;
+    return b;
+}
+
+__global__ void k_iota(int32_t *v, int64_t n)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < n) v[i] = (int32_t)i;
+}
+
+// ---------------------------------------------------------------------------------------
+// COO ingest kernels
+// ---------------------------------------------------------------------------------------
+// A.py:1034: read_counts.groupby("snv")["alt"].sum()
+__global__ void k_alt_sum(const int32_t *snv, const int32_t *alt, int64_t n, unsigned long long *sum)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < n && snv[i] >= 0) atomicAdd(&sum[snv[i]], (unsigned long long)(long long)alt[i]);
+}
+
+// A.py:1037: valid SNVs are those with a strictly positive alt sum
+__global__ void k_keep_flags(const unsigned long long *sum, int32_t n, int32_t *keep)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) keep[i] = ((long long)sum[i] > 0) ? 1 : 0;
+}
+
+__global__ void k_row_keep(const int32_t *snv, const int32_t *keep_snv, int64_t n, int32_t *row_keep)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < n) row_keep[i] = (snv[i] >= 0 && keep_snv[snv[i]]) ? 1 : 0;
+}
+
+// first surviving row of every cell code: Series.unique() order after the filter (A.py:851)
+__global__ void k_first_row(const int32_t *cell, const int32_t *row_keep, int64_t n, int32_t *first)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < n && row_keep[i]) atomicMin(&first[cell[i]], (int32_t)i);
+}
+
+__global__ void k_fill_i32(int32_t *v, int64_t n, int32_t x)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < n) v[i] = x;
+}
+
+__global__ void k_cell_rank(const int32_t *sorted_first, const int32_t *sorted_cell, int32_t n,
+                            int32_t *cell_new, int32_t *cell_order, int32_t *n_cells)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const bool live = sorted_first[i] != INT_MAX;
+    cell_new[sorted_cell[i]] = live ? i : -1;
+    if (live) cell_order[i] = sorted_cell[i];
+    // the sorted array is [live..., dead...]; the boundary is the count
+    if (live && (i == n - 1 || sorted_first[i + 1] == INT_MAX)) *n_cells = i + 1;
+}
+
+__global__ void k_snv_order(const int32_t *keep, const int32_t *snv_new, int32_t n, int32_t *order)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && keep[i]) order[snv_new[i]] = i;
+}
+
+// A.py:459-488: the COO triple of every surviving row, keyed for the canonical sort
+__global__ void k_compact(const int32_t *cell, const int32_t *snv, const int32_t *alt,
+                          const int32_t *total, const int32_t *row_keep, const int32_t *row_pos,
+                          const int32_t *cell_new, const int32_t *snv_new, int64_t n, int32_t n_snvs,
+                          uint64_t *key, uint64_t *pairkey)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n || !row_keep[i]) return;
+    const int32_t o = row_pos[i];
+    key[o] = (uint64_t)cell_new[cell[i]] * (uint64_t)n_snvs + (uint64_t)snv_new[snv[i]];
+    pairkey[o] = ((uint64_t)(uint32_t)total[i] << 32) | (uint64_t)(uint32_t)alt[i];
+}
+
+__global__ void k_encode_pairs(const uint64_t *pairkey, int64_t n, const uint64_t *uniq, int32_t n_uniq,
+                               const int32_t *code_of_rank, uint16_t *code)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t k = pairkey[i];
+    int lo = 0, hi = n_uniq - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (uniq[mid] < k) lo = mid + 1; else hi = mid;
+    }
+    code[i] = (uint16_t)code_of_rank[lo];
+}
+
+__global__ void k_gather_canonical(const uint64_t *sorted_key, const int32_t *perm, const uint16_t *code,
+                                   int64_t n, int32_t n_snvs, int32_t *coo_cell, int32_t *coo_snv,
+                                   uint16_t *coo_code)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t k = sorted_key[i];
+    coo_cell[i] = (int32_t)(k / (uint64_t)n_snvs);
+    coo_snv[i] = (int32_t)(k % (uint64_t)n_snvs);
+    coo_code[i] = code[perm[i]];
+}
+
+// scipy.stats.binom.logpmf as the reference calls it (A.py:838-846); scipy's formula
+// (_discrete_distns.py, binom_gen._logpmf):
+//   gammaln(n+1) - (gammaln(k+1) + gammaln(n-k+1)) + xlogy(k, p) + xlog1py(n-k, -p)
+__global__ void k_logpmf_table(const int32_t *alt, const int32_t *total, int32_t n, double p_present,
+                               double p_absent, double *lp, double *la)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double k = alt[i], nn = total[i];
+    const double comb = lgamma(nn + 1.0) - (lgamma(k + 1.0) + lgamma(nn - k + 1.0));
+    auto xlogy = [](double x, double y) { return x == 0.0 ? 0.0 : x * log(y); };
+    auto xlog1py = [](double x, double y) { return x == 0.0 ? 0.0 : x * log1p(y); };
+    const bool bad = (k < 0.0) || (k > nn);
+    lp[i] = bad ? -INFINITY : comb + xlogy(k, p_present) + xlog1py(nn - k, -p_present);
+    la[i] = bad ? -INFINITY : comb + xlogy(k, p_absent) + xlog1py(nn - k, -p_absent);
+}
+
+// per pair: d = exp(lp - la) - 1 (likelihood ratio minus one) and w = lp - la
+__global__ void k_table_derive(const double *lp, const double *la, int32_t n, double2 *dw)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double w = lp[i] - la[i];
+    dw[i] = make_double2(expm1(w), w);
+}
+
+// ---------------------------------------------------------------------------------------
+// CSR (seam-level) ingest kernels
+// ---------------------------------------------------------------------------------------
+__global__ void k_csr_keys(const int32_t *ptr, const int32_t *col, int32_t n_rows, int32_t n_cols,
+                           int64_t nnz, uint64_t *key)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= nnz) return;
+    int lo = 0, hi = n_rows - 1;          // last row with ptr[row] <= i
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if ((int64_t)ptr[mid] <= i) lo = mid; else hi = mid - 1;
+    }
+    key[i] = (uint64_t)lo * (uint64_t)n_cols + (uint64_t)col[i];
+}
+
+__global__ void k_split_ll(const double *ll, int64_t nnz, uint64_t *lp_bits, uint64_t *la_bits)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= nnz) return;
+    lp_bits[i] = (uint64_t)__double_as_longlong(ll[2 * i]);
+    la_bits[i] = (uint64_t)__double_as_longlong(ll[2 * i + 1]);
+}
+
+__global__ void k_gather_u64(const uint64_t *src, const int32_t *idx, int64_t n, uint64_t *dst)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[idx[i]];
+}
+
+__global__ void k_pair_heads(const uint64_t *lp_bits, const uint64_t *la_bits, const int32_t *order,
+                             int64_t n, int32_t *head)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (i == 0) { head[0] = 1; return; }
+    const int32_t a = order[i], b = order[i - 1];
+    head[i] = (lp_bits[a] != lp_bits[b] || la_bits[a] != la_bits[b]) ? 1 : 0;
+}
+
+__global__ void k_pair_assign(const uint64_t *lp_bits, const uint64_t *la_bits, const int32_t *order,
+                              const int32_t *head, const int32_t *rank_incl, int64_t n, int32_t max_pairs,
+                              int32_t *raw_code, double *tab_lp, double *tab_la, unsigned long long *count)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int32_t r = rank_incl[i] - 1, o = order[i];
+    raw_code[o] = r;
+    if (r < max_pairs) {
+        atomicAdd(&count[r], 1ull);
+        if (head[i]) {
+            tab_lp[r] = __longlong_as_double((long long)lp_bits[o]);
+            tab_la[r] = __longlong_as_double((long long)la_bits[o]);
+        }
+    }
+}
+
+__global__ void k_remap_codes(const int32_t *raw, const int32_t *map, int64_t n, uint16_t *code)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < n) code[i] = (uint16_t)map[raw[i]];
+}
+
+// ---------------------------------------------------------------------------------------
+// panel layouts
+// ---------------------------------------------------------------------------------------
+// key of a nonzero in a panelled stream: (panel of the gathered index, row, index in panel)
+__global__ void k_panel_keys(const int32_t *row, const int32_t *col, int64_t nnz, int32_t n_rows,
+                             int32_t panel_rows, uint64_t *key)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= nnz) return;
+    const uint64_t panel = (uint64_t)(col[i] / panel_rows), local = (uint64_t)(col[i] % panel_rows);
+    key[i] = (panel * (uint64_t)n_rows + (uint64_t)row[i]) * (uint64_t)panel_rows + local;
+}
+
+__global__ void k_panel_stream(const uint64_t *sorted_key, const int32_t *perm, const uint16_t *code,
+                               int64_t nnz, int32_t panel_rows, int64_t n_seg, uint32_t *stream, int32_t *ptr)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= nnz) return;
+    const uint64_t k = sorted_key[i];
+    const int64_t seg = (int64_t)(k / (uint64_t)panel_rows);
+    stream[i] = ((uint32_t)code[perm[i]] << 16) | (uint32_t)(k % (uint64_t)panel_rows);
+    // segment pointers: every segment in (previous segment, this one] starts here
+    const int64_t prev = i == 0 ? -1 : (int64_t)(sorted_key[i - 1] / (uint64_t)panel_rows);
+    for (int64_t s = prev + 1; s <= seg; ++s) ptr[s] = (int32_t)i;
+    if (i == nnz - 1)
+        for (int64_t s = seg + 1; s <= n_seg; ++s) ptr[s] = (int32_t)nnz;
+}
+
+static int build_stream(arb_ctx *ctx, const int32_t *row, const int32_t *col, int32_t n_rows,
+                        int32_t n_cols, int32_t panel_rows, int np, DevBuf &ptr, DevBuf &stream)
+{
+    const int64_t nnz = ctx->nnz, n_seg = (int64_t)np * n_rows;
+    ARB_REQUIRE(n_seg + 1 < (int64_t)INT_MAX, ARB_ERR_UNSUPPORTED, "layout: %lld segments", (long long)n_seg);
+    DevBuf k_in, k_out, v_in, v_out;
+    ARB_TRY(k_in.reserve(nnz * 8));
+    ARB_TRY(k_out.reserve(nnz * 8));
+    ARB_TRY(v_in.reserve(nnz * 4));
+    ARB_TRY(v_out.reserve(nnz * 4));
+    ARB_TRY(ptr.reserve((n_seg + 1) * 4));
+    ARB_TRY(stream.reserve(nnz * 4));
+    cudaStream_t st = ctx->stream;
+    const int B = 256;
+    k_panel_keys<<<grid_for(nnz, B), B, 0, st>>>(row, col, nnz, n_rows, panel_rows, k_in.as<uint64_t>());
+    k_iota<<<grid_for(nnz, B), B, 0, st>>>(v_in.as<int32_t>(), nnz);
+    const int end_bit = bits_for((uint64_t)n_seg * (uint64_t)panel_rows);
+    int rc = with_cub(ctx, [&](void *tmp, size_t &bytes) {
+        return cub::DeviceRadixSort::SortPairs(tmp, bytes, k_in.as<uint64_t>(), k_out.as<uint64_t>(),
+                                               v_in.as<int32_t>(), v_out.as<int32_t>(), nnz, 0, end_bit, st);
+    });
+    if (rc == ARB_OK) {
+        k_panel_stream<<<grid_for(nnz, B), B, 0, st>>>(k_out.as<uint64_t>(), v_out.as<int32_t>(),
+                                                       ctx->coo_code.as<uint16_t>(), nnz, panel_rows, n_seg,
+                                                       stream.as<uint32_t>(), ptr.as<int32_t>());
+        cudaError_t e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) {
+            arb_set_error("layout build: %s", cudaGetErrorString(e));
+            rc = ARB_ERR_CUDA;
+        }
+    }
+    k_in.release(); k_out.release(); v_in.release(); v_out.release();
+    (void)n_cols;
+    return rc;
+}
+
+// smem budget of the sweep kernel: [panel_rows][KP] doubles + pair table + one mbarrier
+int arb_sweep_table_entries(const arb_ctx *ctx) { return std::min<int>(ctx->n_pairs, 512); }
+
+int arb_build_layout(arb_ctx *ctx, int kp)
+{
+    PanelLayout &L = ctx->layout[kp_index(kp)];
+    if (L.kp == kp) return ARB_OK;
+    ARB_REQUIRE(ctx->ingested, ARB_ERR_INVALID, "no matrix ingested");
+    size_t budget = ctx->smem_optin - 1024 - (size_t)arb_sweep_table_entries(ctx) * 16;
+    if (ctx->opt_panel_kb > 0) budget = std::min<size_t>(budget, (size_t)ctx->opt_panel_kb * 1024);
+    int panel_rows = (int)(budget / ((size_t)kp * 8));
+    panel_rows = std::min(panel_rows, 65536) / 32 * 32;
+    ARB_REQUIRE(panel_rows >= 32, ARB_ERR_INVALID, "panel budget too small");
+    L.panel_rows = panel_rows;
+    L.np_z = (ctx->n_snvs + panel_rows - 1) / panel_rows;
+    L.np_y = (ctx->n_cells + panel_rows - 1) / panel_rows;
+    ARB_TRY(build_stream(ctx, ctx->coo_cell.as<int32_t>(), ctx->coo_snv.as<int32_t>(), ctx->n_cells,
+                         ctx->n_snvs, panel_rows, L.np_z, L.zptr, L.zstream));
+    ARB_TRY(build_stream(ctx, ctx->coo_snv.as<int32_t>(), ctx->coo_cell.as<int32_t>(), ctx->n_snvs,
+                         ctx->n_cells, panel_rows, L.np_y, L.yptr, L.ystream));
+    L.kp = kp;
+    return ARB_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// table refresh: derived table, sum of log_absent, renormalisation interval
+// ---------------------------------------------------------------------------------------
+int arb_refresh_tables(arb_ctx *ctx)
+{
+    const int n = ctx->n_pairs;
+    DevBuf lp, la;
+    ARB_TRY(lp.reserve((size_t)n * 8));
+    ARB_TRY(la.reserve((size_t)n * 8));
+    ARB_TRY(ctx->tab_dw.reserve((size_t)n * 16));
+    ARB_CUDA(cudaMemcpyAsync(lp.p, ctx->tab_lp.data(), (size_t)n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    ARB_CUDA(cudaMemcpyAsync(la.p, ctx->tab_la.data(), (size_t)n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    k_table_derive<<<grid_for(n, 128), 128, 0, ctx->stream>>>(lp.as<double>(), la.as<double>(), n,
+                                                             ctx->tab_dw.as<double2>());
+    ARB_CUDA(cudaStreamSynchronize(ctx->stream));
+    lp.release();
+    la.release();
+    // bookkeeping on the host: sum_k log_absent_k = sum_c count_c * la_c in table order
+    double s = 0.0, max_abs_w = 0.0;
+    for (int c = 0; c < n; ++c) {
+        s += (double)ctx->pair_count[c] * ctx->tab_la[c];
+        const double w = ctx->tab_lp[c] - ctx->tab_la[c];
+        if (ctx->pair_count[c] > 0 && fabs(w) > max_abs_w) max_abs_w = fabs(w);
+    }
+    ctx->sum_la = s;
+    // factors 1 + d*x lie in [min(1,e^w), max(1,e^w)]: renormalise the running product often
+    // enough that it cannot leave the double range (|log2| < 900 between renormalisations)
+    const double max_log2 = max_abs_w / 0.6931471805599453;
+    int every = max_log2 > 0 ? (int)floor(900.0 / max_log2) : 16;
+    ctx->renorm_every = std::max(1, std::min(every, 16));
+    return ARB_OK;
+}
+
+static int check_table_range(arb_ctx *ctx)
+{
+    for (int c = 0; c < ctx->n_pairs; ++c) {
+        if (ctx->pair_count[c] == 0) continue;
+        const double w = ctx->tab_lp[c] - ctx->tab_la[c];
+        ARB_REQUIRE(!(w > 600.0) && !(w < -34.0), ARB_ERR_UNSUPPORTED,
+                    "count pair %d has log-likelihood ratio %.1f outside [-34, 600]: deep-coverage "
+                    "entries need the log-domain path, which this release does not have", c, w);
+    }
+    return ARB_OK;
+}
+int arb_check_table_range(arb_ctx *ctx) { return check_table_range(ctx); }
+
+// order the dictionary by descending frequency (ties: ascending raw rank); returns map raw->final
+static std::vector<int32_t> frequency_order(const std::vector<int64_t> &count)
+{
+    const int n = (int)count.size();
+    std::vector<int32_t> order(n), map(n);
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return count[a] > count[b]; });
+    for (int f = 0; f < n; ++f) map[order[f]] = f;
+    return map;
+}
+
+static void reset_matrix(arb_ctx *ctx)
+{
+    ctx->ingested = false;
+    for (auto &l : ctx->layout) l.release();
+    ctx->fit_trees = 0;
+    ctx->single_tree = -1;
+    ctx->n_clusters = 0;
+}
+
+// canonical sort by (cell, snv) and gather; key/code are per compacted row
+static int finish_canonical(arb_ctx *ctx, DevBuf &key, const uint16_t *code)
+{
+    const int64_t nnz = ctx->nnz;
+    cudaStream_t st = ctx->stream;
+    DevBuf k_out, v_in, v_out;
+    ARB_TRY(k_out.reserve(nnz * 8));
+    ARB_TRY(v_in.reserve(nnz * 4));
+    ARB_TRY(v_out.reserve(nnz * 4));
+    ARB_TRY(ctx->coo_cell.reserve(nnz * 4));
+    ARB_TRY(ctx->coo_snv.reserve(nnz * 4));
+    ARB_TRY(ctx->coo_code.reserve(nnz * 2));
+    k_iota<<<grid_for(nnz, 256), 256, 0, st>>>(v_in.as<int32_t>(), nnz);
+    const int end_bit = bits_for((uint64_t)ctx->n_cells * (uint64_t)ctx->n_snvs);
+    ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
+        return cub::DeviceRadixSort::SortPairs(tmp, bytes, key.as<uint64_t>(), k_out.as<uint64_t>(),
+                                               v_in.as<int32_t>(), v_out.as<int32_t>(), nnz, 0, end_bit, st);
+    }));
+    k_gather_canonical<<<grid_for(nnz, 256), 256, 0, st>>>(k_out.as<uint64_t>(), v_out.as<int32_t>(), code, nnz,
+                                                           ctx->n_snvs, ctx->coo_cell.as<int32_t>(),
+                                                           ctx->coo_snv.as<int32_t>(), ctx->coo_code.as<uint16_t>());
+    ARB_CUDA(cudaStreamSynchronize(st));
+    k_out.release(); v_in.release(); v_out.release();
+    return ARB_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// arb_ingest_coo
+// ---------------------------------------------------------------------------------------
+ARB_API int arb_ingest_coo(arb_ctx *ctx, int64_t n_rows, const int32_t *cell_code, const int32_t *snv_code,
+                           const int32_t *alt, const int32_t *total, int32_t n_cell_codes,
+                           int32_t n_snv_codes, double alpha)
+{
+    ARB_REQUIRE(ctx && cell_code && snv_code && alt && total, ARB_ERR_INVALID, "arb_ingest_coo: null argument");
+    ARB_REQUIRE(n_rows > 0 && n_rows < (int64_t)INT_MAX, ARB_ERR_INVALID, "arb_ingest_coo: n_rows=%lld",
+                (long long)n_rows);
+    ARB_REQUIRE(n_cell_codes > 0 && n_snv_codes > 0, ARB_ERR_INVALID, "arb_ingest_coo: empty code space");
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    reset_matrix(ctx);
+    cudaStream_t st = ctx->stream;
+    const int B = 256;
+    DevBuf d_cell, d_snv, d_alt, d_tot, alt_sum, keep, snv_new, row_keep, row_pos, first, iota, sfirst, scell,
+        cell_new, counters;
+    for (DevBuf *b : {&d_cell, &d_snv, &d_alt, &d_tot, &row_keep, &row_pos}) ARB_TRY(b->reserve(n_rows * 4));
+    ARB_TRY(alt_sum.reserve((size_t)n_snv_codes * 8));
+    ARB_TRY(keep.reserve((size_t)n_snv_codes * 4));
+    ARB_TRY(snv_new.reserve((size_t)n_snv_codes * 4));
+    for (DevBuf *b : {&first, &iota, &sfirst, &scell, &cell_new}) ARB_TRY(b->reserve((size_t)n_cell_codes * 4));
+    ARB_TRY(counters.reserve(64));
+    ARB_CUDA(cudaMemcpyAsync(d_cell.p, cell_code, n_rows * 4, cudaMemcpyHostToDevice, st));
+    ARB_CUDA(cudaMemcpyAsync(d_snv.p, snv_code, n_rows * 4, cudaMemcpyHostToDevice, st));
+    ARB_CUDA(cudaMemcpyAsync(d_alt.p, alt, n_rows * 4, cudaMemcpyHostToDevice, st));
+    ARB_CUDA(cudaMemcpyAsync(d_tot.p, total, n_rows * 4, cudaMemcpyHostToDevice, st));
+    ARB_CUDA(cudaMemsetAsync(alt_sum.p, 0, (size_t)n_snv_codes * 8, st));
+    ARB_CUDA(cudaMemsetAsync(counters.p, 0, 64, st));
+
+    // zero-alt filter (A.py:1034-1041)
+    k_alt_sum<<<grid_for(n_rows, B), B, 0, st>>>(d_snv.as<int32_t>(), d_alt.as<int32_t>(), n_rows,
+                                                 alt_sum.as<unsigned long long>());
+    k_keep_flags<<<grid_for(n_snv_codes, B), B, 0, st>>>(alt_sum.as<unsigned long long>(), n_snv_codes,
+                                                         keep.as<int32_t>());
+    ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
+        return cub::DeviceScan::ExclusiveSum(tmp, bytes, keep.as<int32_t>(), snv_new.as<int32_t>(), n_snv_codes, st);
+    }));
+    k_row_keep<<<grid_for(n_rows, B), B, 0, st>>>(d_snv.as<int32_t>(), keep.as<int32_t>(), n_rows,
+                                                  row_keep.as<int32_t>());
+    ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
+        return cub::DeviceScan::ExclusiveSum(tmp, bytes, row_keep.as<int32_t>(), row_pos.as<int32_t>(), n_rows, st);
+    }));
+    int32_t h_tail[4];
+    ARB_CUDA(cudaMemcpyAsync(&h_tail[0], keep.as<int32_t>() + n_snv_codes - 1, 4, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaMemcpyAsync(&h_tail[1], snv_new.as<int32_t>() + n_snv_codes - 1, 4, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaMemcpyAsync(&h_tail[2], row_keep.as<int32_t>() + n_rows - 1, 4, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaMemcpyAsync(&h_tail[3], row_pos.as<int32_t>() + n_rows - 1, 4, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaStreamSynchronize(st));
+    const int32_t n_snvs = h_tail[0] + h_tail[1];
+    const int64_t nnz = (int64_t)h_tail[2] + h_tail[3];
+    ARB_REQUIRE(nnz > 0 && n_snvs > 0, ARB_ERR_INVALID, "arb_ingest_coo: no row survives the zero-alt filter");
+
+    // first-appearance cell order among the surviving rows (A.py:851)
+    k_fill_i32<<<grid_for(n_cell_codes, B), B, 0, st>>>(first.as<int32_t>(), n_cell_codes, INT_MAX);
+    k_first_row<<<grid_for(n_rows, B), B, 0, st>>>(d_cell.as<int32_t>(), row_keep.as<int32_t>(), n_rows,
+                                                   first.as<int32_t>());
+    k_iota<<<grid_for(n_cell_codes, B), B, 0, st>>>(iota.as<int32_t>(), n_cell_codes);
+    ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
+        return cub::DeviceRadixSort::SortPairs(tmp, bytes, first.as<int32_t>(), sfirst.as<int32_t>(),
+                                               iota.as<int32_t>(), scell.as<int32_t>(), n_cell_codes, 0, 32, st);
+    }));
+    ARB_TRY(ctx->cell_order.reserve((size_t)n_cell_codes * 4));
+    ARB_TRY(ctx->snv_order.reserve((size_t)n_snvs * 4));
+    k_cell_rank<<<grid_for(n_cell_codes, B), B, 0, st>>>(sfirst.as<int32_t>(), scell.as<int32_t>(), n_cell_codes,
+                                                         cell_new.as<int32_t>(), ctx->cell_order.as<int32_t>(),
+                                                         counters.as<int32_t>());
+    k_snv_order<<<grid_for(n_snv_codes, B), B, 0, st>>>(keep.as<int32_t>(), snv_new.as<int32_t>(), n_snv_codes,
+                                                        ctx->snv_order.as<int32_t>());
+    int32_t n_cells = 0;
+    ARB_CUDA(cudaMemcpyAsync(&n_cells, counters.p, 4, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaStreamSynchronize(st));
+    ARB_REQUIRE(n_cells > 0, ARB_ERR_INVALID, "arb_ingest_coo: no cell survives");
+    ctx->n_cells = n_cells;
+    ctx->n_snvs = n_snvs;
+    ctx->nnz = nnz;
+    ctx->alpha = alpha;
+
+    // compaction + dictionary of distinct (alt, total) pairs
+    DevBuf key, pairkey, pk_sorted, uniq, ucount, nruns, code, code_of_rank;
+    ARB_TRY(key.reserve(nnz * 8));
+    ARB_TRY(pairkey.reserve(nnz * 8));
+    ARB_TRY(pk_sorted.reserve(nnz * 8));
+    ARB_TRY(code.reserve(nnz * 2));
+    k_compact<<<grid_for(n_rows, B), B, 0, st>>>(d_cell.as<int32_t>(), d_snv.as<int32_t>(), d_alt.as<int32_t>(),
+                                                 d_tot.as<int32_t>(), row_keep.as<int32_t>(), row_pos.as<int32_t>(),
+                                                 cell_new.as<int32_t>(), snv_new.as<int32_t>(), n_rows, n_snvs,
+                                                 key.as<uint64_t>(), pairkey.as<uint64_t>());
+    ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
+        return cub::DeviceRadixSort::SortKeys(tmp, bytes, pairkey.as<uint64_t>(), pk_sorted.as<uint64_t>(), nnz, 0,
+                                              64, st);
+    }));
+    // run-length encode; the number of runs can be as large as nnz in principle
+    const int64_t max_runs = std::min<int64_t>(nnz, 1 << 20);
+    ARB_TRY(uniq.reserve(nnz * 8));
+    ARB_TRY(ucount.reserve(nnz * 4));
+    ARB_TRY(nruns.reserve(16));
+    ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
+        return cub::DeviceRunLengthEncode::Encode(tmp, bytes, pk_sorted.as<uint64_t>(), uniq.as<uint64_t>(),
+                                                  ucount.as<int32_t>(), nruns.as<int32_t>(), nnz, st);
+    }));
+    int32_t n_pairs = 0;
+    ARB_CUDA(cudaMemcpyAsync(&n_pairs, nruns.p, 4, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaStreamSynchronize(st));
+    (void)max_runs;
+    ARB_REQUIRE(n_pairs <= 65535, ARB_ERR_UNSUPPORTED,
+                "arb_ingest_coo: %d distinct (alt,total) pairs; this release supports 65535", n_pairs);
+    std::vector<uint64_t> h_uniq(n_pairs);
+    std::vector<int32_t> h_cnt(n_pairs);
+    ARB_CUDA(cudaMemcpy(h_uniq.data(), uniq.p, (size_t)n_pairs * 8, cudaMemcpyDeviceToHost));
+    ARB_CUDA(cudaMemcpy(h_cnt.data(), ucount.p, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost));
+    std::vector<int64_t> cnt64(h_cnt.begin(), h_cnt.end());
+    std::vector<int32_t> map = frequency_order(cnt64);
+    ctx->n_pairs = n_pairs;
+    ctx->pair_alt.assign(n_pairs, 0);
+    ctx->pair_total.assign(n_pairs, 0);
+    ctx->pair_count.assign(n_pairs, 0);
+    for (int r = 0; r < n_pairs; ++r) {
+        ctx->pair_alt[map[r]] = (int32_t)(uint32_t)(h_uniq[r] & 0xffffffffu);
+        ctx->pair_total[map[r]] = (int32_t)(uint32_t)(h_uniq[r] >> 32);
+        ctx->pair_count[map[r]] = cnt64[r];
+    }
+    ARB_TRY(code_of_rank.reserve((size_t)n_pairs * 4));
+    ARB_CUDA(cudaMemcpyAsync(code_of_rank.p, map.data(), (size_t)n_pairs * 4, cudaMemcpyHostToDevice, st));
+    k_encode_pairs<<<grid_for(nnz, B), B, 0, st>>>(pairkey.as<uint64_t>(), nnz, uniq.as<uint64_t>(), n_pairs,
+                                                   code_of_rank.as<int32_t>(), code.as<uint16_t>());
+    ARB_TRY(finish_canonical(ctx, key, code.as<uint16_t>()));
+
+    // per-pair log-likelihood table (A.py:838-846)
+    DevBuf t_alt, t_tot, t_lp, t_la;
+    ARB_TRY(t_alt.reserve((size_t)n_pairs * 4));
+    ARB_TRY(t_tot.reserve((size_t)n_pairs * 4));
+    ARB_TRY(t_lp.reserve((size_t)n_pairs * 8));
+    ARB_TRY(t_la.reserve((size_t)n_pairs * 8));
+    ARB_CUDA(cudaMemcpyAsync(t_alt.p, ctx->pair_alt.data(), (size_t)n_pairs * 4, cudaMemcpyHostToDevice, st));
+    ARB_CUDA(cudaMemcpyAsync(t_tot.p, ctx->pair_total.data(), (size_t)n_pairs * 4, cudaMemcpyHostToDevice, st));
+    k_logpmf_table<<<grid_for(n_pairs, 128), 128, 0, st>>>(t_alt.as<int32_t>(), t_tot.as<int32_t>(), n_pairs,
+                                                           0.5 - alpha + 0.5 * alpha / 3, alpha / 3,
+                                                           t_lp.as<double>(), t_la.as<double>());
+    ctx->tab_lp.resize(n_pairs);
+    ctx->tab_la.resize(n_pairs);
+    ARB_CUDA(cudaMemcpyAsync(ctx->tab_lp.data(), t_lp.p, (size_t)n_pairs * 8, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaMemcpyAsync(ctx->tab_la.data(), t_la.p, (size_t)n_pairs * 8, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaStreamSynchronize(st));
+    for (DevBuf *b : {&d_cell, &d_snv, &d_alt, &d_tot, &alt_sum, &keep, &snv_new, &row_keep, &row_pos, &first,
+                      &iota, &sfirst, &scell, &cell_new, &counters, &key, &pairkey, &pk_sorted, &uniq, &ucount,
+                      &nruns, &code, &code_of_rank, &t_alt, &t_tot, &t_lp, &t_la})
+        b->release();
+    ARB_TRY(arb_refresh_tables(ctx));
+    ctx->ingested = true;
+    ctx->from_coo = true;
+    return ARB_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// arb_ingest_csr (the arrays of the reference's run(...) seam, A.py:1093-1107)
+// ---------------------------------------------------------------------------------------
+ARB_API int arb_ingest_csr(arb_ctx *ctx, int32_t n_cells, int32_t n_snvs, int64_t nnz, const int32_t *cell_ptr,
+                           const int32_t *snv_idx, const double *log_likes)
+{
+    ARB_REQUIRE(ctx && cell_ptr && snv_idx && log_likes, ARB_ERR_INVALID, "arb_ingest_csr: null argument");
+    ARB_REQUIRE(n_cells > 0 && n_snvs > 0 && nnz > 0 && nnz < (int64_t)INT_MAX, ARB_ERR_INVALID,
+                "arb_ingest_csr: bad sizes (%d, %d, %lld)", n_cells, n_snvs, (long long)nnz);
+    ARB_REQUIRE(cell_ptr[0] == 0 && (int64_t)cell_ptr[n_cells] == nnz, ARB_ERR_INVALID,
+                "arb_ingest_csr: cell_ptr does not span nnz");
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    reset_matrix(ctx);
+    cudaStream_t st = ctx->stream;
+    const int B = 256;
+    ctx->n_cells = n_cells;
+    ctx->n_snvs = n_snvs;
+    ctx->nnz = nnz;
+    DevBuf d_ptr, d_col, d_ll, key, lpb, lab, v0, v1, v2, k1, k2, head, rank, raw, t_lp, t_la, cnt, map_d, code;
+    ARB_TRY(d_ptr.reserve((size_t)(n_cells + 1) * 4));
+    ARB_TRY(d_col.reserve(nnz * 4));
+    ARB_TRY(d_ll.reserve(nnz * 16));
+    for (DevBuf *b : {&key, &lpb, &lab, &k1, &k2}) ARB_TRY(b->reserve(nnz * 8));
+    for (DevBuf *b : {&v0, &v1, &v2, &head, &rank, &raw}) ARB_TRY(b->reserve(nnz * 4));
+    ARB_TRY(code.reserve(nnz * 2));
+    const int max_pairs = 65536;
+    ARB_TRY(t_lp.reserve(max_pairs * 8));
+    ARB_TRY(t_la.reserve(max_pairs * 8));
+    ARB_TRY(cnt.reserve(max_pairs * 8));
+    ARB_CUDA(cudaMemcpyAsync(d_ptr.p, cell_ptr, (size_t)(n_cells + 1) * 4, cudaMemcpyHostToDevice, st));
+    ARB_CUDA(cudaMemcpyAsync(d_col.p, snv_idx, nnz * 4, cudaMemcpyHostToDevice, st));
+    ARB_CUDA(cudaMemcpyAsync(d_ll.p, log_likes, nnz * 16, cudaMemcpyHostToDevice, st));
+    ARB_CUDA(cudaMemsetAsync(cnt.p, 0, max_pairs * 8, st));
+    k_csr_keys<<<grid_for(nnz, B), B, 0, st>>>(d_ptr.as<int32_t>(), d_col.as<int32_t>(), n_cells, n_snvs, nnz,
+                                               key.as<uint64_t>());
+    k_split_ll<<<grid_for(nnz, B), B, 0, st>>>(d_ll.as<double>(), nnz, lpb.as<uint64_t>(), lab.as<uint64_t>());
+    k_iota<<<grid_for(nnz, B), B, 0, st>>>(v0.as<int32_t>(), nnz);
+    // lexicographic (lp, la) order by two stable passes
+    ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
+        return cub::DeviceRadixSort::SortPairs(tmp, bytes, lab.as<uint64_t>(), k1.as<uint64_t>(), v0.as<int32_t>(),
+                                               v1.as<int32_t>(), nnz, 0, 64, st);
+    }));
+    k_gather_u64<<<grid_for(nnz, B), B, 0, st>>>(lpb.as<uint64_t>(), v1.as<int32_t>(), nnz, k1.as<uint64_t>());
+    ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
+        return cub::DeviceRadixSort::SortPairs(tmp, bytes, k1.as<uint64_t>(), k2.as<uint64_t>(), v1.as<int32_t>(),
+                                               v2.as<int32_t>(), nnz, 0, 64, st);
+    }));
+    k_pair_heads<<<grid_for(nnz, B), B, 0, st>>>(lpb.as<uint64_t>(), lab.as<uint64_t>(), v2.as<int32_t>(), nnz,
+                                                 head.as<int32_t>());
+    ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
+        return cub::DeviceScan::InclusiveSum(tmp, bytes, head.as<int32_t>(), rank.as<int32_t>(), nnz, st);
+    }));
+    int32_t n_pairs = 0;
+    ARB_CUDA(cudaMemcpyAsync(&n_pairs, rank.as<int32_t>() + nnz - 1, 4, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaStreamSynchronize(st));
+    ARB_REQUIRE(n_pairs <= 65535, ARB_ERR_UNSUPPORTED,
+                "arb_ingest_csr: %d distinct (log_present, log_absent) pairs; this release supports 65535", n_pairs);
+    k_pair_assign<<<grid_for(nnz, B), B, 0, st>>>(lpb.as<uint64_t>(), lab.as<uint64_t>(), v2.as<int32_t>(),
+                                                  head.as<int32_t>(), rank.as<int32_t>(), nnz, max_pairs,
+                                                  raw.as<int32_t>(), t_lp.as<double>(), t_la.as<double>(),
+                                                  cnt.as<unsigned long long>());
+    std::vector<double> r_lp(n_pairs), r_la(n_pairs);
+    std::vector<unsigned long long> r_cnt(n_pairs);
+    ARB_CUDA(cudaMemcpyAsync(r_lp.data(), t_lp.p, (size_t)n_pairs * 8, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaMemcpyAsync(r_la.data(), t_la.p, (size_t)n_pairs * 8, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaMemcpyAsync(r_cnt.data(), cnt.p, (size_t)n_pairs * 8, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaStreamSynchronize(st));
+    std::vector<int64_t> cnt64(r_cnt.begin(), r_cnt.end());
+    std::vector<int32_t> map = frequency_order(cnt64);
+    ctx->n_pairs = n_pairs;
+    ctx->pair_alt.assign(n_pairs, -1);
+    ctx->pair_total.assign(n_pairs, -1);
+    ctx->pair_count.assign(n_pairs, 0);
+    ctx->tab_lp.assign(n_pairs, 0.0);
+    ctx->tab_la.assign(n_pairs, 0.0);
+    for (int r = 0; r < n_pairs; ++r) {
+        ctx->pair_count[map[r]] = cnt64[r];
+        ctx->tab_lp[map[r]] = r_lp[r];
+        ctx->tab_la[map[r]] = r_la[r];
+    }
+    ARB_TRY(map_d.reserve((size_t)n_pairs * 4));
+    ARB_CUDA(cudaMemcpyAsync(map_d.p, map.data(), (size_t)n_pairs * 4, cudaMemcpyHostToDevice, st));
+    k_remap_codes<<<grid_for(nnz, B), B, 0, st>>>(raw.as<int32_t>(), map_d.as<int32_t>(), nnz, code.as<uint16_t>());
+    ARB_TRY(finish_canonical(ctx, key, code.as<uint16_t>()));
+    for (DevBuf *b : {&d_ptr, &d_col, &d_ll, &key, &lpb, &lab, &v0, &v1, &v2, &k1, &k2, &head, &rank, &raw, &t_lp,
+                      &t_la, &cnt, &map_d, &code})
+        b->release();
+    ctx->cell_order.release();
+    ctx->snv_order.release();
+    ARB_TRY(arb_refresh_tables(ctx));
+    ctx->ingested = true;
+    ctx->from_coo = false;
+    return ARB_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// accessors
+// ---------------------------------------------------------------------------------------
+ARB_API int arb_get_dims(arb_ctx *ctx, int32_t *n_cells, int32_t *n_snvs, int64_t *nnz, int32_t *n_pairs)
+{
+    ARB_REQUIRE(ctx && ctx->ingested, ARB_ERR_INVALID, "arb_get_dims: no matrix ingested");
+    if (n_cells) *n_cells = ctx->n_cells;
+    if (n_snvs) *n_snvs = ctx->n_snvs;
+    if (nnz) *nnz = ctx->nnz;
+    if (n_pairs) *n_pairs = ctx->n_pairs;
+    return ARB_OK;
+}
+
+ARB_API int arb_get_orders(arb_ctx *ctx, int32_t *cell_order, int32_t *snv_order)
+{
+    ARB_REQUIRE(ctx && ctx->ingested && ctx->from_coo, ARB_ERR_INVALID, "arb_get_orders: needs arb_ingest_coo");
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    if (cell_order)
+        ARB_CUDA(cudaMemcpy(cell_order, ctx->cell_order.p, (size_t)ctx->n_cells * 4, cudaMemcpyDeviceToHost));
+    if (snv_order)
+        ARB_CUDA(cudaMemcpy(snv_order, ctx->snv_order.p, (size_t)ctx->n_snvs * 4, cudaMemcpyDeviceToHost));
+    return ARB_OK;
+}
+
+ARB_API int arb_get_count_pairs(arb_ctx *ctx, int32_t *alt, int32_t *total)
+{
+    ARB_REQUIRE(ctx && ctx->ingested && ctx->from_coo, ARB_ERR_INVALID, "arb_get_count_pairs: needs arb_ingest_coo");
+    if (alt) memcpy(alt, ctx->pair_alt.data(), (size_t)ctx->n_pairs * 4);
+    if (total) memcpy(total, ctx->pair_total.data(), (size_t)ctx->n_pairs * 4);
+    return ARB_OK;
+}
+
+ARB_API int arb_get_loglik_table(arb_ctx *ctx, double *log_present, double *log_absent)
+{
+    ARB_REQUIRE(ctx && ctx->ingested, ARB_ERR_INVALID, "arb_get_loglik_table: no matrix ingested");
+    if (log_present) memcpy(log_present, ctx->tab_lp.data(), (size_t)ctx->n_pairs * 8);
+    if (log_absent) memcpy(log_absent, ctx->tab_la.data(), (size_t)ctx->n_pairs * 8);
+    return ARB_OK;
+}
+
+ARB_API int arb_set_loglik_table(arb_ctx *ctx, int32_t n_pairs, const double *log_present, const double *log_absent)
+{
+    ARB_REQUIRE(ctx && ctx->ingested && log_present && log_absent, ARB_ERR_INVALID,
+                "arb_set_loglik_table: bad argument");
+    ARB_REQUIRE(n_pairs == ctx->n_pairs, ARB_ERR_INVALID, "arb_set_loglik_table: %d entries, table has %d", n_pairs,
+                ctx->n_pairs);
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    ctx->tab_lp.assign(log_present, log_present + n_pairs);
+    ctx->tab_la.assign(log_absent, log_absent + n_pairs);
+    ctx->single_tree = -1;
+    return arb_refresh_tables(ctx);
+}
+
+// canonical matrix in the reference's layout; a test / interchange hook, so the host does the
+// counting sort for the SNV-major copy
+ARB_API int arb_export_sparse(arb_ctx *ctx, int snv_major, int32_t *ptr, int32_t *idx, double *log_likes)
+{
+    ARB_REQUIRE(ctx && ctx->ingested && ptr && idx && log_likes, ARB_ERR_INVALID, "arb_export_sparse: bad argument");
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    const int64_t nnz = ctx->nnz;
+    std::vector<int32_t> cell(nnz), snv(nnz);
+    std::vector<uint16_t> code(nnz);
+    ARB_CUDA(cudaMemcpy(cell.data(), ctx->coo_cell.p, nnz * 4, cudaMemcpyDeviceToHost));
+    ARB_CUDA(cudaMemcpy(snv.data(), ctx->coo_snv.p, nnz * 4, cudaMemcpyDeviceToHost));
+    ARB_CUDA(cudaMemcpy(code.data(), ctx->coo_code.p, nnz * 2, cudaMemcpyDeviceToHost));
+    const int32_t n_rows = snv_major ? ctx->n_snvs : ctx->n_cells;
+    const std::vector<int32_t> &row = snv_major ? snv : cell, &col = snv_major ? cell : snv;
+    std::vector<int32_t> fill(n_rows + 1, 0);
+    for (int64_t k = 0; k < nnz; ++k) ++fill[row[k] + 1];
+    for (int32_t r = 0; r < n_rows; ++r) fill[r + 1] += fill[r];
+    memcpy(ptr, fill.data(), (size_t)(n_rows + 1) * 4);
+    for (int64_t k = 0; k < nnz; ++k) {       // stable: canonical order is (cell, snv)
+        const int32_t o = fill[row[k]]++;
+        idx[o] = col[k];
+        log_likes[2 * (int64_t)o] = ctx->tab_lp[code[k]];
+        log_likes[2 * (int64_t)o + 1] = ctx->tab_la[code[k]];
+    }
+    return ARB_OK;
+}

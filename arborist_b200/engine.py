@@ -1,0 +1,298 @@
+"""ctypes binding of ``libarborist_b200.so`` -- the C ABI in ``include/arborist_b200.h``.
+
+``Engine`` is one ``arb_ctx`` (one GPU).  There is no CPU path: a missing library,
+a library that fails to load or a machine without a CUDA device raises
+``ArboristError`` / ``RuntimeError``; nothing here computes on the host.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import _build
+
+__all__ = ["Engine", "ArboristError", "device_count", "library_path", "load_library"]
+
+_LIB = None
+
+_i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
+_f64p = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
+_u8p = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
+_ctx = C.c_void_p
+_opt = C.c_void_p           # optional pointer arguments are passed as raw addresses
+
+
+class ArboristError(RuntimeError):
+    """A call into libarborist_b200 returned a negative status."""
+
+    def __init__(self, status, message):
+        super().__init__(f"libarborist_b200 error {status}: {message}")
+        self.status = status
+
+
+def library_path() -> str:
+    return _build.LIB
+
+
+_SIGNATURES = {
+    "arb_abi_version": (C.c_int, []),
+    "arb_last_error": (C.c_char_p, []),
+    "arb_device_count": (C.c_int, [C.POINTER(C.c_int)]),
+    "arb_ctx_create": (C.c_int, [C.c_int, C.POINTER(_ctx)]),
+    "arb_ctx_destroy": (C.c_int, [_ctx]),
+    "arb_ingest_coo": (C.c_int, [_ctx, C.c_int64, _i32p, _i32p, _i32p, _i32p, C.c_int32, C.c_int32,
+                                 C.c_double]),
+    "arb_ingest_csr": (C.c_int, [_ctx, C.c_int32, C.c_int32, C.c_int64, _i32p, _i32p, _f64p]),
+    "arb_get_dims": (C.c_int, [_ctx, C.POINTER(C.c_int32), C.POINTER(C.c_int32),
+                               C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
+    "arb_get_orders": (C.c_int, [_ctx, _i32p, _i32p]),
+    "arb_get_count_pairs": (C.c_int, [_ctx, _i32p, _i32p]),
+    "arb_get_loglik_table": (C.c_int, [_ctx, _f64p, _f64p]),
+    "arb_set_loglik_table": (C.c_int, [_ctx, C.c_int32, _f64p, _f64p]),
+    "arb_export_sparse": (C.c_int, [_ctx, C.c_int, _i32p, _i32p, _f64p]),
+    "arb_set_prior_labels": (C.c_int, [_ctx, _i32p, C.c_int32, C.c_double]),
+    "arb_set_prior": (C.c_int, [_ctx, _f64p, C.c_int32]),
+    "arb_get_prior": (C.c_int, [_ctx, _f64p]),
+    "arb_fit_trees": (C.c_int, [_ctx, C.c_int32, C.c_int32, C.c_int32, _i32p, C.c_int32, C.c_double,
+                                C.c_int32, C.c_int32, _f64p, _i32p, _opt]),
+    "arb_fit_presence": (C.c_int, [_ctx, C.c_int32, C.c_int32, _u8p, C.c_int32, C.c_double, C.c_int32,
+                                   C.c_int32, _f64p, _i32p, _opt]),
+    "arb_posterior_bytes": (C.c_int, [_ctx, C.c_int32, C.c_int32, C.POINTER(C.c_int64),
+                                      C.POINTER(C.c_int64)]),
+    "arb_get_fit": (C.c_int, [_ctx, C.c_int32, _f64p, _f64p]),
+    "arb_get_map": (C.c_int, [_ctx, C.c_int32, _i32p, _i32p]),
+    "arb_get_presence": (C.c_int, [_ctx, C.c_int32, _u8p]),
+    "arb_qz_update": (C.c_int, [_ctx, C.c_int32, _u8p, _f64p, _f64p]),
+    "arb_qy_update": (C.c_int, [_ctx, C.c_int32, _u8p, _f64p, _f64p]),
+    "arb_elbo_terms": (C.c_int, [_ctx, C.c_int32, _u8p, _f64p, _f64p, C.POINTER(C.c_double),
+                                 C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "arb_last_fit_stats": (C.c_int, [_ctx, C.POINTER(C.c_int64), C.POINTER(C.c_double),
+                                     C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "arb_set_option": (C.c_int, [_ctx, C.c_char_p, C.c_int64]),
+}
+
+
+def load_library():
+    """Load the CUDA library (building it first only if the sources are newer and nvcc exists)."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = library_path()
+    if _build.is_stale() and _build.nvcc_path() is not None:
+        _build.build_library()
+    if not os.path.exists(path):
+        raise RuntimeError(
+            f"{path} is missing and nvcc is not available to build it; arborist_b200 has no CPU "
+            "fallback (run `python -c 'import __graft_entry__ as g; g.build()'` on a machine with nvcc)")
+    lib = C.CDLL(path)
+    for name, (res, args) in _SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    if lib.arb_abi_version() != 1:
+        raise RuntimeError(f"{path}: ABI version {lib.arb_abi_version()} != 1")
+    _LIB = lib
+    return lib
+
+
+def _check(status):
+    if status != 0:
+        raise ArboristError(status, load_library().arb_last_error().decode("utf-8", "replace"))
+
+
+def device_count() -> int:
+    n = C.c_int(0)
+    _check(load_library().arb_device_count(C.byref(n)))
+    return n.value
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+class Engine:
+    """One GPU context: ingest once, set the prior, fit shards of trees, fetch results."""
+
+    def __init__(self, device=None):
+        self._lib = load_library()
+        if device is None:
+            device = int(os.environ.get("LOCAL_RANK", "0"))
+            n = device_count()
+            if n > 0:
+                device %= n
+        self.device = int(device)
+        h = _ctx()
+        _check(self._lib.arb_ctx_create(self.device, C.byref(h)))
+        self._h = h
+        self.n_clones = None
+
+    def close(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            self._lib.arb_ctx_destroy(h)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- ingest ---------------------------------------------------------------
+    def ingest_coo(self, cell_codes, snv_codes, alt, total, n_cell_codes, n_snv_codes, alpha):
+        cell_codes, snv_codes = _i32(cell_codes), _i32(snv_codes)
+        alt64, tot64 = np.asarray(alt), np.asarray(total)
+        for name, v in (("alt", alt64), ("total", tot64)):
+            if v.size and (v.max() > np.iinfo(np.int32).max or v.min() < np.iinfo(np.int32).min):
+                raise ValueError(f"read-count column '{name}' does not fit int32")
+        _check(self._lib.arb_ingest_coo(self._h, cell_codes.shape[0], cell_codes, snv_codes,
+                                        _i32(alt64), _i32(tot64), int(n_cell_codes),
+                                        int(n_snv_codes), float(alpha)))
+
+    def ingest_csr(self, cell_ptr, snv_idx, log_likes, n_cells, n_snvs):
+        snv_idx = _i32(snv_idx)
+        _check(self._lib.arb_ingest_csr(self._h, int(n_cells), int(n_snvs), snv_idx.shape[0],
+                                        _i32(cell_ptr), snv_idx, _f64(log_likes)))
+
+    def dims(self):
+        n, m, nnz, npairs = C.c_int32(), C.c_int32(), C.c_int64(), C.c_int32()
+        _check(self._lib.arb_get_dims(self._h, C.byref(n), C.byref(m), C.byref(nnz), C.byref(npairs)))
+        return n.value, m.value, nnz.value, npairs.value
+
+    def orders(self):
+        n, m, _, _ = self.dims()
+        co, so = np.empty(n, np.int32), np.empty(m, np.int32)
+        _check(self._lib.arb_get_orders(self._h, co, so))
+        return co, so
+
+    def count_pairs(self):
+        k = self.dims()[3]
+        a, t = np.empty(k, np.int32), np.empty(k, np.int32)
+        _check(self._lib.arb_get_count_pairs(self._h, a, t))
+        return a, t
+
+    def loglik_table(self):
+        k = self.dims()[3]
+        lp, la = np.empty(k), np.empty(k)
+        _check(self._lib.arb_get_loglik_table(self._h, lp, la))
+        return lp, la
+
+    def set_loglik_table(self, lp, la):
+        lp, la = _f64(lp), _f64(la)
+        _check(self._lib.arb_set_loglik_table(self._h, lp.shape[0], lp, la))
+
+    def export_sparse(self, snv_major=False):
+        n, m, nnz, _ = self.dims()
+        ptr = np.empty((m if snv_major else n) + 1, np.int32)
+        idx, ll = np.empty(nnz, np.int32), np.empty(2 * nnz)
+        _check(self._lib.arb_export_sparse(self._h, int(bool(snv_major)), ptr, idx, ll))
+        return ptr, idx, ll
+
+    # ---- prior ------------------------------------------------------------------
+    def set_prior_labels(self, label_idx, n_clusters, gamma):
+        if n_clusters == 1:
+            (1 - gamma) / (n_clusters - 1)     # the reference divides by k-1 here (A.py:552)
+        _check(self._lib.arb_set_prior_labels(self._h, _i32(label_idx), int(n_clusters), float(gamma)))
+
+    def set_prior(self, q_y_init):
+        q = _f64(q_y_init)
+        _check(self._lib.arb_set_prior(self._h, q, q.shape[1]))
+
+    def prior(self, n_clusters):
+        q = np.empty((self.dims()[1], n_clusters))
+        _check(self._lib.arb_get_prior(self._h, q))
+        return q
+
+    # ---- fit ----------------------------------------------------------------------
+    def posterior_bytes(self, n_trees, n_clones):
+        b, f = C.c_int64(), C.c_int64()
+        _check(self._lib.arb_posterior_bytes(self._h, int(n_trees), int(n_clones), C.byref(b), C.byref(f)))
+        return b.value, f.value
+
+    def fit(self, parents=None, presence=None, n_clones=None, normal_idx=0, max_iter=10,
+            tolerance=1.0, keep_posteriors="auto", mode="vi", trace=False):
+        """Fit a shard of trees; returns ``(elbo, iters)`` (+ ``trace`` if asked)."""
+        if (parents is None) == (presence is None):
+            raise ValueError("give exactly one of parents / presence")
+        K = int(n_clones)
+        T = int(parents.shape[0] if parents is not None else presence.shape[0])
+        if isinstance(keep_posteriors, str):
+            if keep_posteriors == "all":
+                keep = 1
+            elif keep_posteriors == "none":
+                keep = 0
+            else:
+                need, free = self.posterior_bytes(T, K)
+                keep = int(need < 0.35 * free)
+        else:
+            keep = int(bool(keep_posteriors))
+        elbo = np.empty(T)
+        iters = np.empty(T, np.int32)
+        tr = np.empty((T, int(max_iter) + 1)) if trace else None
+        tr_ptr = tr.ctypes.data if trace else None
+        m = {"vi": 0, "ml": 1}[mode]
+        if T == 0:
+            return (elbo, iters, tr) if trace else (elbo, iters)
+        if parents is not None:
+            _check(self._lib.arb_fit_trees(self._h, T, K, int(normal_idx), _i32(parents), int(max_iter),
+                                           float(tolerance), m, keep, elbo, iters, tr_ptr))
+        else:
+            _check(self._lib.arb_fit_presence(self._h, T, K, np.ascontiguousarray(presence, np.uint8),
+                                              int(max_iter), float(tolerance), m, keep, elbo, iters,
+                                              tr_ptr))
+        self.n_clones = K
+        return (elbo, iters, tr) if trace else (elbo, iters)
+
+    def get_fit(self, t):
+        n, m, _, _ = self.dims()
+        qz, qy = np.empty((n, self.n_clones)), np.empty((m, self.n_clones - 1))
+        _check(self._lib.arb_get_fit(self._h, int(t), qz, qy))
+        return qz, qy
+
+    def get_map(self, t):
+        n, m, _, _ = self.dims()
+        z, y = np.empty(n, np.int32), np.empty(m, np.int32)
+        _check(self._lib.arb_get_map(self._h, int(t), z, y))
+        return z, y
+
+    def get_presence(self, t):
+        p = np.empty((self.n_clones - 1, self.n_clones), np.uint8)
+        _check(self._lib.arb_get_presence(self._h, int(t), p))
+        return p
+
+    # ---- kernel-level hooks ----------------------------------------------------------
+    def qz_update(self, presence, q_y):
+        P = np.ascontiguousarray(np.asarray(presence) != 0, np.uint8)
+        K = P.shape[1]
+        qz = np.empty((self.dims()[0], K))
+        _check(self._lib.arb_qz_update(self._h, K, P, _f64(q_y), qz))
+        return qz
+
+    def qy_update(self, presence, q_z):
+        P = np.ascontiguousarray(np.asarray(presence) != 0, np.uint8)
+        K = P.shape[1]
+        qy = np.empty((self.dims()[1], K - 1))
+        _check(self._lib.arb_qy_update(self._h, K, P, _f64(q_z), qy))
+        return qy
+
+    def elbo_terms(self, presence, q_z, q_y):
+        P = np.ascontiguousarray(np.asarray(presence) != 0, np.uint8)
+        lik, ent, kl = C.c_double(), C.c_double(), C.c_double()
+        _check(self._lib.arb_elbo_terms(self._h, P.shape[1], P, _f64(q_z), _f64(q_y), C.byref(lik),
+                                        C.byref(ent), C.byref(kl)))
+        return lik.value, ent.value, kl.value
+
+    # ---- counters / knobs ---------------------------------------------------------------
+    def last_fit_stats(self):
+        n, ms, ti, sw = C.c_int64(), C.c_double(), C.c_double(), C.c_double()
+        _check(self._lib.arb_last_fit_stats(self._h, C.byref(n), C.byref(ms), C.byref(ti), C.byref(sw)))
+        return dict(kernel_launches=n.value, device_ms=ms.value, tree_iterations=ti.value,
+                    sweep_ms=sw.value)
+
+    def set_option(self, name, value):
+        _check(self._lib.arb_set_option(self._h, name.encode(), int(value)))

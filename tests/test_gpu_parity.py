@@ -1,0 +1,320 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the golden vectors recorded
+from the unmodified reference and against the CPU oracle on fresh seeded inputs.
+
+Tolerances (BASELINE.json north_star): tree ranking, iteration counts and MAP assignments
+bit-exact; ELBOs and posteriors within 1e-6 relative in fp64 -- the tests ask for 1e-9
+(observed ~1e-13) so a regression shows long before the contract is at risk."""
+import numpy as np
+import pandas as pd
+import pytest
+
+from conftest import golden_frames, load_golden, synth_frames
+
+pytestmark = pytest.mark.gpu
+
+ELBO_RTOL = 1e-9
+Q_RTOL, Q_ATOL = 1e-7, 1e-12       # posteriors: relative on the bulk, absolute floor for ~0 entries
+
+
+@pytest.fixture(scope="module")
+def eng_mod():
+    from arborist_b200 import engine
+    assert engine.device_count() > 0, "no CUDA device: the gpu tests must run on the B200 box"
+    return engine
+
+
+def _row_sets(ptr, idx, ll):
+    a = np.stack([np.repeat(np.arange(len(ptr) - 1), np.diff(ptr)), idx, ll[0::2], ll[1::2]], 1)
+    return a[np.lexsort(a.T[::-1])]
+
+
+def _coo_engine(eng_mod, g, with_scipy=True):
+    from arborist_b200.arborist import _install_scipy_table
+    trees, rc, cl = golden_frames(g)
+    snv_codes, snv_u = pd.factorize(rc["snv"].to_numpy())
+    cell_codes, cell_u = pd.factorize(rc["cell"].to_numpy())
+    e = eng_mod.Engine(0)
+    e.ingest_coo(cell_codes, snv_codes, rc["alt"].to_numpy(), rc["total"].to_numpy(), len(cell_u),
+                 len(snv_u), float(g["alpha"]))
+    if with_scipy:
+        _install_scipy_table(e, float(g["alpha"]))
+    return e, cell_u, snv_u
+
+
+SMALL = ["tiny", "small", "small_nonormal", "deep30"]
+
+
+@pytest.mark.parametrize("name", SMALL)
+def test_ingest_matches_reference(eng_mod, name):
+    """a1-a5: filter, index order, CSR/CSC content, log-likelihood table, prior."""
+    g = load_golden(name)
+    e, cell_u, snv_u = _coo_engine(eng_mod, g, with_scipy=False)
+    n, m, nnz, n_pairs = e.dims()
+    assert (n, m, nnz) == (int(g["n_cells"]), int(g["n_snvs"]), int(g["nnz"]))
+    co, so = e.orders()
+    assert np.array_equal(np.asarray(cell_u)[co], g["cell_order"])
+    assert np.array_equal(np.asarray(snv_u)[so], g["snv_order"])
+    # device lgamma table vs scipy: close; after installing scipy's doubles: bit-equal
+    from scipy.stats import binom
+    alt, tot = e.count_pairs()
+    a = float(g["alpha"])
+    lp, la = e.loglik_table()
+    np.testing.assert_allclose(lp, binom.logpmf(alt, tot, 0.5 - a + 0.5 * a / 3), rtol=1e-13, atol=1e-15)
+    np.testing.assert_allclose(la, binom.logpmf(alt, tot, a / 3), rtol=1e-13, atol=1e-15)
+    from arborist_b200.arborist import _install_scipy_table
+    _install_scipy_table(e, a)
+    ptr, idx, ll = e.export_sparse(False)
+    assert np.array_equal(ptr, g["cell_ptr"])
+    assert np.array_equal(_row_sets(ptr, idx, ll), _row_sets(g["cell_ptr"], g["snv_idx_cs"], g["ll_cs"]))
+    ptr, idx, ll = e.export_sparse(True)
+    assert np.array_equal(ptr, g["snv_ptr"])
+    assert np.array_equal(_row_sets(ptr, idx, ll), _row_sets(g["snv_ptr"], g["cell_idx_ss"], g["ll_ss"]))
+    # prior from labels
+    from arborist_b200.arborist import _prior_labels
+    _, _, cl = golden_frames(g)
+    k2i = {int(c): i for i, c in enumerate(g["clusters"])}
+    lab = _prior_labels(cl, g["snv_order"], k2i)
+    e.set_prior_labels(lab, len(k2i), float(g["gamma"]))
+    assert np.array_equal(e.prior(len(k2i)), g["q_y_init"])
+    e.close()
+
+
+@pytest.mark.parametrize("name", SMALL)
+def test_kernel_hooks_match_reference(eng_mod, name):
+    """a8-a11 on explicit arrays, matrix ingested through the seam-level CSR entry point."""
+    g = load_golden(name)
+    n, m, K = int(g["n_cells"]), int(g["n_snvs"]), int(g["n_clones"])
+    e = eng_mod.Engine(0)
+    e.ingest_csr(g["cell_ptr"], g["snv_idx_cs"], g["ll_cs"], n, m)
+    e.set_prior(g["q_y_init"])
+    P = g["presence"][0]
+    qz = e.qz_update(P, g["k_qy_in"])
+    np.testing.assert_allclose(qz, g["k_qz"], rtol=Q_RTOL, atol=Q_ATOL)
+    assert np.array_equal(qz.argmax(1), g["k_qz"].argmax(1))
+    qy = e.qy_update(P, g["k_qz"])
+    np.testing.assert_allclose(qy, g["k_qy"], rtol=Q_RTOL, atol=Q_ATOL)
+    assert np.array_equal(qy.argmax(1), g["k_qy"].argmax(1))
+    lik, ent, kl = e.elbo_terms(P, g["k_qz"], g["k_qy_in"])
+    assert lik == pytest.approx(float(g["k_lik"]), rel=1e-11)
+    assert ent == pytest.approx(float(g["k_ent"]), rel=1e-12)
+    _, _, kl2 = e.elbo_terms(P, g["k_qz"], g["k_qy"])
+    assert kl2 == pytest.approx(float(g["k_kl"]), rel=1e-12)
+    e.close()
+
+
+def _check_api(g, lik, best, fits, full_q):
+    T = len(g["elbo"])
+    elbo = np.array([lik[t] for t in range(T)])
+    np.testing.assert_allclose(elbo, g["elbo"], rtol=ELBO_RTOL)
+    # ranking identical (ties keep index order on both sides)
+    assert np.array_equal(np.argsort(-elbo, kind="stable"), np.argsort(-g["elbo"], kind="stable"))
+    assert best.tree_idx == int(g["best_idx"])
+    for t in range(T):
+        f = fits[t]
+        z = f.map_assign_z()["assignment"].to_numpy()
+        y = f.map_assign_y()["assignment"].to_numpy()
+        assert np.array_equal(z, g["clones"][g["map_z"][t]]), f"MAP z differs for tree {t}"
+        assert np.array_equal(y, g["clusters"][g["map_y"][t]]), f"MAP y differs for tree {t}"
+    if full_q:
+        for t in range(T):
+            np.testing.assert_allclose(fits[t].q_z, g["q_z"][t], rtol=Q_RTOL, atol=Q_ATOL)
+            np.testing.assert_allclose(fits[t].q_y, g["q_y"][t], rtol=Q_RTOL, atol=Q_ATOL)
+    else:
+        r = g["q_z_rows"].shape[1]
+        for t in range(0, T, max(1, T // 8)):
+            np.testing.assert_allclose(fits[t].q_z[:r], g["q_z_rows"][t], rtol=Q_RTOL, atol=Q_ATOL)
+            np.testing.assert_allclose(fits[t].q_y[:r], g["q_y_rows"][t], rtol=Q_RTOL, atol=Q_ATOL)
+        np.testing.assert_allclose(best.q_z, g["q_z_best"], rtol=Q_RTOL, atol=Q_ATOL)
+        np.testing.assert_allclose(best.q_y, g["q_y_best"], rtol=Q_RTOL, atol=Q_ATOL)
+
+
+def _run_api(g, trees, rc, cl, **kw):
+    from arborist_b200 import arborist
+    from arborist_b200.arborist import arborist as fn
+    lik, best, fits = arborist(trees, rc, cl, alpha=float(g["alpha"]), max_iter=int(g["max_iter"]),
+                               tolerance=float(g["tol"]), gamma=float(g["gamma"]),
+                               add_normal=bool(g["add_normal"]), **kw)
+    iters = fn.last_stats["iters"]
+    assert np.array_equal(iters, g["iters"]), "iteration counts differ from the reference"
+    assert list(best.cell_to_idx) == list(g["cell_order"])
+    assert list(best.snv_to_idx) == list(g["snv_order"])
+    assert list(best.clone_to_idx) == list(g["clones"])
+    assert list(best.cluster_to_idx) == list(g["clusters"])
+    return lik, best, fits
+
+
+@pytest.mark.parametrize("name", SMALL)
+def test_api_matches_reference_small(eng_mod, name):
+    g = load_golden(name)
+    trees, rc, cl = golden_frames(g)
+    lik, best, fits = _run_api(g, trees, rc, cl)
+    _check_api(g, lik, best, fits, full_q=True)
+
+
+def test_api_example_standin(eng_mod):
+    """BASELINE config 1 (bundled trees + clustering, synthetic counts; no --add-normal)."""
+    g = load_golden("example_standin")
+    trees, rc, cl = golden_frames(g)
+    lik, best, fits = _run_api(g, trees, rc, cl)
+    _check_api(g, lik, best, fits, full_q=False)
+
+
+def test_api_config2(eng_mod):
+    """BASELINE config 2: 1k cells x 5k SNVs, 8 clones, 100 trees."""
+    g = load_golden("config2")
+    trees, rc, cl = synth_frames("config2")
+    lik, best, fits = _run_api(g, trees, rc, cl)
+    _check_api(g, lik, best, fits, full_q=False)
+
+
+def test_api_config3_head(eng_mod):
+    """BASELINE config 3 shape (10k x 20k, 12 clones): the 4 trees the reference was run on."""
+    g = load_golden("config3_head")
+    trees, rc, cl = synth_frames("config3", tree_subset=[int(i) for i in g["tree_subset"]])
+    lik, best, fits = _run_api(g, trees, rc, cl)
+    _check_api(g, lik, best, fits, full_q=False)
+
+
+@pytest.mark.parametrize("name", ["tiny", "deep30"])
+def test_elbo_trace_and_presence(eng_mod, name):
+    """Driver level: every iteration's ELBO (A.py:801-803) and the device-built genotype matrix."""
+    from arborist_b200.arborist import add_normal_clone, prepare_trees
+    g = load_golden(name)
+    e, _, _ = _coo_engine(eng_mod, g)
+    e.set_prior(g["q_y_init"])
+    trees, _, _ = golden_frames(g)
+    if bool(g["add_normal"]):
+        trees = add_normal_clone(trees)
+    c2i, k2i, parents, presence, normal = prepare_trees(trees)
+    assert presence is None
+    K = len(c2i)
+    elbo, iters, tr = e.fit(parents=parents, n_clones=K, normal_idx=normal, max_iter=int(g["max_iter"]),
+                            tolerance=float(g["tol"]), keep_posteriors="all", trace=True)
+    assert np.array_equal(iters, g["iters"])
+    for t in range(len(trees)):
+        assert np.array_equal(e.get_presence(t), g["presence"][t])
+        np.testing.assert_allclose(tr[t, : iters[t] + 1], g["traces"][t, : iters[t] + 1], rtol=ELBO_RTOL)
+        assert np.isnan(tr[t, iters[t] + 1:]).all()
+        z, y = e.get_map(t)
+        assert np.array_equal(z, g["map_z"][t]) and np.array_equal(y, g["map_y"][t])
+    # explicit genotype matrices give the same bits as parent vectors
+    elbo2, iters2 = e.fit(presence=g["presence"].astype(np.uint8), n_clones=K, max_iter=int(g["max_iter"]),
+                          tolerance=float(g["tol"]), keep_posteriors="none")
+    assert np.array_equal(elbo, elbo2) and np.array_equal(iters, iters2)
+    # posteriors refit on demand == resident posteriors
+    qz_refit, qy_refit = e.get_fit(1)
+    e.fit(parents=parents, n_clones=K, normal_idx=normal, max_iter=int(g["max_iter"]),
+          tolerance=float(g["tol"]), keep_posteriors="all")
+    qz, qy = e.get_fit(1)
+    assert np.array_equal(qz, qz_refit) and np.array_equal(qy, qy_refit)
+    e.close()
+
+
+def test_seam_run_variational_inference(eng_mod):
+    """The 13-argument seam `run = run_variational_inference` (A.py:1076, A.py:679-816)."""
+    from arborist_b200 import run_variational_inference
+    g = load_golden("small")
+    n, m, K = int(g["n_cells"]), int(g["n_snvs"]), int(g["n_clones"])
+    for t in (0, 1, 5):
+        elbo, qz, qy = run_variational_inference(
+            g["presence"][t], g["ll_cs"], g["ll_ss"], g["cell_idx_ss"], g["snv_idx_cs"], n, m, K,
+            g["q_y_init"], g["cell_ptr"], g["snv_ptr"], int(g["max_iter"]), float(g["tol"]))
+        assert elbo == pytest.approx(float(g["elbo"][t]), rel=ELBO_RTOL)
+        np.testing.assert_allclose(qz, g["q_z"][t], rtol=Q_RTOL, atol=Q_ATOL)
+        np.testing.assert_allclose(qy, g["q_y"][t], rtol=Q_RTOL, atol=Q_ATOL)
+
+
+def test_slot_count_and_duplicates_do_not_change_bits(eng_mod):
+    """Determinism: results are independent of how many trees are in flight, and duplicate
+    trees get bit-identical ELBOs (the reference has both properties)."""
+    from arborist_b200.arborist import add_normal_clone, prepare_trees
+    g = load_golden("small")
+    e, _, _ = _coo_engine(eng_mod, g)
+    e.set_prior(g["q_y_init"])
+    trees, _, _ = golden_frames(g)
+    trees = add_normal_clone(trees)
+    trees = trees + [trees[3], trees[0]]
+    c2i, _, parents, _, normal = prepare_trees(trees)
+    K = len(c2i)
+    ref = e.fit(parents=parents, n_clones=K, normal_idx=normal, max_iter=25, tolerance=1.0)
+    assert ref[0][3] == ref[0][-2] and ref[0][0] == ref[0][-1]
+    for slots in (1, 3, 5):
+        e.set_option("slots", slots)
+        got = e.fit(parents=parents, n_clones=K, normal_idx=normal, max_iter=25, tolerance=1.0)
+        assert np.array_equal(got[0], ref[0]) and np.array_equal(got[1], ref[1])
+    e.set_option("slots", 0)
+    for kb in (8, 32):                      # many small panels: same ranking, ELBO within rounding
+        e.set_option("panel_kb", kb)
+        got = e.fit(parents=parents, n_clones=K, normal_idx=normal, max_iter=25, tolerance=1.0)
+        np.testing.assert_allclose(got[0], ref[0], rtol=1e-12)
+        assert np.array_equal(got[1], ref[1])
+    e.close()
+
+
+def test_against_oracle_on_fresh_inputs(eng_mod):
+    """Seeded inputs that are in no fixture: GPU vs the CPU oracle, incl. max_iter=0/1 and a
+    tight tolerance (runs to the iteration cap)."""
+    from arborist_b200 import arborist, synth
+    from oracle import oracle as orc
+    cfg = synth.SynthConfig("fresh", 220, 640, 9, 7, seed=4242, coverage=0.06, offtree_frac=0.1,
+                            extra_depth=0.6)
+    d = synth.generate(cfg)
+    rc, cl = d.read_counts_frame(), d.clusters_frame()
+    for max_iter, tol in ((0, 1.0), (1, 1.0), (12, 1e-9), (25, 1.0)):
+        lik, best, fits = arborist(d.trees, rc, cl, max_iter=max_iter, tolerance=tol, add_normal=True)
+        olik, obest, ofits, _ = orc.arborist_oracle(d.trees, rc, cl, max_iter=max_iter, tolerance=tol,
+                                                    add_normal=True)
+        assert best.tree_idx == obest
+        for t in range(len(d.trees)):
+            assert lik[t] == pytest.approx(olik[t], rel=ELBO_RTOL)
+            assert arborist.last_stats["iters"][t] == ofits[t][3]
+            np.testing.assert_allclose(fits[t].q_z, ofits[t][1], rtol=Q_RTOL, atol=Q_ATOL)
+            np.testing.assert_allclose(fits[t].q_y, ofits[t][2], rtol=Q_RTOL, atol=Q_ATOL)
+            assert np.array_equal(fits[t].q_z.argmax(1), ofits[t][1].argmax(1))
+            assert np.array_equal(fits[t].q_y.argmax(1), ofits[t][2].argmax(1))
+
+
+def test_non_forest_presence_and_errors(eng_mod):
+    """Inputs that are not forests go through explicit genotype matrices; bad input is an error,
+    not a fallback."""
+    from arborist_b200 import arborist, synth
+    from oracle import oracle as orc
+    d = synth.generate(synth.CONFIGS["tiny"])
+    rc, cl = d.read_counts_frame(), d.clusters_frame()
+    dag = [[(0, 1), (1, 2), (1, 3), (2, 4), (3, 4)], [(0, 1), (1, 2), (2, 3), (3, 4)]]   # node 4 has two parents
+    lik, best, fits = arborist(dag, rc, cl, max_iter=5)
+    olik, obest, ofits, _ = orc.arborist_oracle(dag, rc, cl, max_iter=5)
+    assert best.tree_idx == obest
+    for t in range(2):
+        assert lik[t] == pytest.approx(olik[t], rel=ELBO_RTOL)
+    with pytest.raises(ValueError, match="same set of clones"):
+        arborist([[(0, 1), (1, 2)], [(0, 1), (1, 3)]], rc, cl)
+    e = eng_mod.Engine(0)
+    with pytest.raises(eng_mod.ArboristError):
+        e.dims()
+    with pytest.raises(eng_mod.ArboristError):
+        eng_mod.Engine(9999)
+    e.close()
+
+
+def test_config3_properties_at_full_shape(eng_mod):
+    """Size-independent properties at the headline shape (10k x 20k, 12 clones), 24 trees:
+    rows of q sum to 1, the reported ELBO is the maximum of the trace, duplicate trees agree
+    bit for bit, and re-running the same shard reproduces every bit."""
+    from arborist_b200 import arborist, synth
+    d = synth.generate(synth.CONFIGS["config3"])
+    trees = d.trees[:22] + [d.trees[5], d.trees[0]]
+    rc, cl = d.read_counts_frame(), d.clusters_frame()
+    lik, best, fits = arborist(trees, rc, cl, max_iter=25, add_normal=True)
+    eng = arborist.last_stats["engine"]()
+    assert lik[5] == lik[22] and lik[0] == lik[23]
+    assert np.array_equal(fits[5].q_z, fits[22].q_z)
+    np.testing.assert_allclose(best.q_z.sum(1), 1.0, rtol=0, atol=1e-12)
+    np.testing.assert_allclose(best.q_y.sum(1), 1.0, rtol=0, atol=1e-12)
+    lik2, best2, _ = arborist(trees, rc, cl, max_iter=25, add_normal=True)
+    assert lik2 == lik and best2.tree_idx == best.tree_idx
+    g = load_golden("config3_head")
+    for k, t in enumerate(int(i) for i in g["tree_subset"]):
+        if t < 22:
+            assert lik[t] == pytest.approx(float(g["elbo"][k]), rel=ELBO_RTOL)
+    del eng

@@ -30,7 +30,8 @@ from .treefit import TreeFit
 from .utils import read_trees, visualize_tree
 
 __all__ = ["arborist", "run_variational_inference", "run_simple_max_likelihood", "main",
-           "parse_arguments", "add_normal_clone", "tree_to_clone_set", "prepare_trees"]
+           "parse_arguments", "add_normal_clone", "tree_to_clone_set", "prepare_trees",
+           "ingest_read_counts"]
 
 logging.basicConfig(
     format="{asctime} - {levelname} - {message}",
@@ -186,6 +187,27 @@ def _prior_labels(snv_clusters, snv_ids, cluster_to_idx):
     return out
 
 
+def ingest_read_counts(eng, read_counts, snv_clusters, cluster_to_idx, alpha, gamma):
+    """A.py:1034-1069 on the device: upload the long-format table as integer codes, build the
+    sparse matrix and the prior there.  Returns ``(cell_ids, snv_ids)`` in row/column order.
+
+    Host work is the first-appearance factorisation of the two id columns (A.py:851-855, on
+    the UNFILTERED table); the zero-alt filter (A.py:1034-1041), re-indexing, dictionary
+    coding and the cell-major / SNV-major layouts are built by ``arb_ingest_coo``.
+    """
+    snv_codes, snv_uniques = pd.factorize(read_counts["snv"].to_numpy(), use_na_sentinel=True)
+    cell_codes, cell_uniques = pd.factorize(read_counts["cell"].to_numpy(), use_na_sentinel=False)
+    eng.ingest_coo(cell_codes, snv_codes, read_counts["alt"].to_numpy(),
+                   read_counts["total"].to_numpy(), len(cell_uniques), len(snv_uniques), alpha)
+    _install_scipy_table(eng, alpha)
+    cell_order, snv_order = eng.orders()
+    cell_ids = np.asarray(cell_uniques)[cell_order]
+    snv_ids = np.asarray(snv_uniques)[snv_order]
+    eng.set_prior_labels(_prior_labels(snv_clusters, snv_ids, cluster_to_idx),
+                         len(cluster_to_idx), gamma)
+    return cell_ids, snv_ids
+
+
 # ---------------------------------------------------------------------------
 # the public entry point
 # ---------------------------------------------------------------------------
@@ -235,23 +257,12 @@ def arborist(
     K, T = len(clone_to_idx), len(tree_list)
 
     log("Removing SNVs with 0 variant reads across all cells...")
-    # first-appearance factorisation (A.py:851-855) of the UNFILTERED table; the
-    # filter (A.py:1034-1041), re-indexing and CSR/CSC build happen on the device.
-    snv_codes, snv_uniques = pd.factorize(read_counts["snv"].to_numpy(), use_na_sentinel=True)
-    cell_codes, cell_uniques = pd.factorize(read_counts["cell"].to_numpy(), use_na_sentinel=False)
     eng = Engine(device=device)
     log("Caching log-likelihoods for presence/absence...")
-    eng.ingest_coo(cell_codes, snv_codes, read_counts["alt"].to_numpy(),
-                   read_counts["total"].to_numpy(), len(cell_uniques), len(snv_uniques), alpha)
-    _install_scipy_table(eng, alpha)
-    cell_order, snv_order = eng.orders()
-    cell_ids = np.asarray(cell_uniques)[cell_order]
-    snv_ids = np.asarray(snv_uniques)[snv_order]
+    log("Initializing the SNV cluster assignment prior...")
+    cell_ids, snv_ids = ingest_read_counts(eng, read_counts, snv_clusters, cluster_to_idx, alpha, gamma)
     cell_to_idx = dict(zip(cell_ids.tolist(), range(len(cell_ids))))
     snv_to_idx = dict(zip(snv_ids.tolist(), range(len(snv_ids))))
-
-    log("Initializing the SNV cluster assignment prior...")
-    eng.set_prior_labels(_prior_labels(snv_clusters, snv_ids, cluster_to_idx), K - 1, gamma)
 
     if verbose:
         log("Starting Arborist...")

@@ -82,6 +82,9 @@ struct PanelLayout {
 struct FitStats {
     int64_t launches = 0;
     double device_ms = 0, tree_iterations = 0, sweep_ms = 0;
+    // per-kernel profile of the last fit (CUDA events on the launching stream)
+    double sweep_z_ms = 0, sweep_y_ms = 0, finish_ms = 0;
+    double tree_sweeps_z = 0, tree_sweeps_y = 0, launches_z = 0, launches_y = 0, rounds = 0;
 };
 
 struct arb_ctx {

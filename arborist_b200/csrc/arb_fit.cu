@@ -770,15 +770,29 @@ static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, 
     ARB_CUDA(cudaMemsetAsync(w.st, 0, (size_t)ctx->ws_slots * sizeof(SlotState), st));
     ARB_CUDA(cudaMemcpyAsync(w.ctl, &h, sizeof h, cudaMemcpyHostToDevice, st));
 
-    cudaEvent_t ev0, ev1;
+    cudaEvent_t ev0, ev1, evs[6];
     ARB_CUDA(cudaEventCreate(&ev0));
     ARB_CUDA(cudaEventCreate(&ev1));
+    for (auto &e : evs) ARB_CUDA(cudaEventCreate(&e));
     ARB_CUDA(cudaEventRecord(ev0, st));
     FitStats stats;
     k_control<<<1, 256, 0, st>>>(w.ctl, w.st, ctx->red.as<double>(), w.list_y, w.list_z, w.list_init, w.snap_tree,
                                  tg.elbo, tg.iters, tg.trace, 1);
     stats.launches++;
     int rc = ARB_OK;
+    bool pending_y = false, pending_z = false;
+    auto collect = [&]() {               // events of the previous round are complete after the sync
+        float t = 0;
+        if (pending_y) {
+            cudaEventElapsedTime(&t, evs[0], evs[1]); stats.sweep_y_ms += t;
+            cudaEventElapsedTime(&t, evs[1], evs[2]); stats.finish_ms += t;
+        }
+        if (pending_z) {
+            cudaEventElapsedTime(&t, evs[3], evs[4]); stats.sweep_z_ms += t;
+            cudaEventElapsedTime(&t, evs[4], evs[5]); stats.finish_ms += t;
+        }
+        pending_y = pending_z = false;
+    };
     for (;;) {
         cudaError_t e = cudaMemcpyAsync(&h, w.ctl, sizeof h, cudaMemcpyDeviceToHost, st);
         if (e == cudaSuccess) e = cudaStreamSynchronize(st);
@@ -787,18 +801,32 @@ static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, 
             rc = ARB_ERR_CUDA;
             break;
         }
+        collect();
         if (h.n_z == 0) break;
+        stats.rounds += 1;
         if (h.n_init > 0) {
             launch_seed_s<KP>(ctx, w, tg.masks, ctx->q0.as<double>(), 0, w.list_init, h.n_init, K, 1);
             stats.launches++;
         }
         if (h.n_y > 0) {
+            cudaEventRecord(evs[0], st);
             launch_sweep_y<KP>(ctx, L, w, w.list_y, h.n_y);
+            cudaEventRecord(evs[1], st);
             launch_finish_y<KP>(ctx, L, w, ws, tg.masks, w.list_y, h.n_y);
+            cudaEventRecord(evs[2], st);
             stats.launches += 2;
+            stats.launches_y += 1;
+            stats.tree_sweeps_y += h.n_y;
+            pending_y = true;
         }
+        cudaEventRecord(evs[3], st);
         launch_sweep_z<KP>(ctx, L, w, w.list_z, h.n_z);
+        cudaEventRecord(evs[4], st);
         launch_finish_z<KP>(ctx, L, w, ws, tg.masks, w.list_z, h.n_z, 0);
+        cudaEventRecord(evs[5], st);
+        stats.launches_z += 1;
+        stats.tree_sweeps_z += h.n_z;
+        pending_z = true;
         k_control<<<1, 256, 0, st>>>(w.ctl, w.st, ctx->red.as<double>(), w.list_y, w.list_z, w.list_init,
                                      w.snap_tree, tg.elbo, tg.iters, tg.trace, 0);
         stats.launches += 3;
@@ -814,6 +842,8 @@ static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, 
     cudaEventElapsedTime(&ms, ev0, ev1);
     cudaEventDestroy(ev0);
     cudaEventDestroy(ev1);
+    for (auto &e : evs) cudaEventDestroy(e);
+    stats.sweep_ms = stats.sweep_z_ms + stats.sweep_y_ms;
     stats.device_ms = ms;
     ctx->stats = stats;
     if (rc == ARB_OK) {
@@ -1044,6 +1074,17 @@ ARB_API int arb_last_fit_stats(arb_ctx *ctx, int64_t *kernel_launches, double *d
     if (device_ms) *device_ms = ctx->stats.device_ms;
     if (tree_iterations) *tree_iterations = ctx->stats.tree_iterations;
     if (sweep_ms) *sweep_ms = ctx->stats.sweep_ms;
+    return ARB_OK;
+}
+
+// [sweep_z_ms, sweep_y_ms, finish_ms, tree_sweeps_z, tree_sweeps_y, launches_z, launches_y, rounds]
+ARB_API int arb_last_fit_profile(arb_ctx *ctx, double *values, int32_t n_values)
+{
+    ARB_REQUIRE(ctx && values && n_values >= 0, ARB_ERR_INVALID, "arb_last_fit_profile: bad argument");
+    const FitStats &s = ctx->stats;
+    const double v[8] = {s.sweep_z_ms, s.sweep_y_ms, s.finish_ms, s.tree_sweeps_z, s.tree_sweeps_y,
+                         s.launches_z, s.launches_y, s.rounds};
+    for (int i = 0; i < n_values && i < 8; ++i) values[i] = v[i];
     return ARB_OK;
 }
 

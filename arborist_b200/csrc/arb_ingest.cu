@@ -113,6 +113,7 @@ ARB_API int arb_set_option(arb_ctx *ctx, const char *name, int64_t value)
     else if (!strcmp(name, "panel_kb")) {
         ctx->opt_panel_kb = value;
         for (auto &l : ctx->layout) l.release();
+        ctx->ws_kp = 0;                      // partial buffers are sized by the panel count
     } else if (!strcmp(name, "threads")) ctx->opt_threads = value;
     else {
         arb_set_error("arb_set_option: unknown option '%s'", name);
@@ -480,6 +481,7 @@ static void reset_matrix(arb_ctx *ctx)
 {
     ctx->ingested = false;
     for (auto &l : ctx->layout) l.release();
+    ctx->ws_kp = 0;
     ctx->fit_trees = 0;
     ctx->single_tree = -1;
     ctx->n_clusters = 0;

@@ -70,6 +70,7 @@ _SIGNATURES = {
                                  C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "arb_last_fit_stats": (C.c_int, [_ctx, C.POINTER(C.c_int64), C.POINTER(C.c_double),
                                      C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "arb_last_fit_profile": (C.c_int, [_ctx, _f64p, C.c_int32]),
     "arb_set_option": (C.c_int, [_ctx, C.c_char_p, C.c_int64]),
 }
 
@@ -293,6 +294,13 @@ class Engine:
         _check(self._lib.arb_last_fit_stats(self._h, C.byref(n), C.byref(ms), C.byref(ti), C.byref(sw)))
         return dict(kernel_launches=n.value, device_ms=ms.value, tree_iterations=ti.value,
                     sweep_ms=sw.value)
+
+    def last_fit_profile(self):
+        v = np.zeros(8)
+        _check(self._lib.arb_last_fit_profile(self._h, v, 8))
+        keys = ("sweep_z_ms", "sweep_y_ms", "finish_ms", "tree_sweeps_z", "tree_sweeps_y",
+                "launches_z", "launches_y", "rounds")
+        return dict(zip(keys, v.tolist()))
 
     def set_option(self, name, value):
         _check(self._lib.arb_set_option(self._h, name.encode(), int(value)))

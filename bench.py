@@ -1,0 +1,395 @@
+#!/usr/bin/env python
+"""bench.py -- candidate trees fit+ranked per second on B200 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one pass of the hot path over the whole candidate set of the headline workload
+(BASELINE.json configs[2]: synthetic 10k cells x 20k SNVs low-pass, 12 clones, 1,000 candidate
+trees per GPU): batched CAVI fit of every tree (q(y)/q(z) sweeps + ELBO), the NCCL gather of
+the ELBOs when N > 1, and the ranking.  Trees are independent, so the tree set is sharded over
+ranks with no data-path collective; per-GPU work is fixed as N grows ("weak").
+
+* ``value``    trees/s with the read-count matrix already resident in HBM (device events).
+* ``e2e``      the same metric through the public ``arborist(...)`` call with HOST DataFrames:
+               id factorisation, H2D of the COO table, device ingest, fit, D2H of ELBOs and
+               of the best tree's posteriors are all inside the timed region.
+* ``roofline`` q(z) sweep kernel: algorithmic bytes / CUDA-event duration,
+               against the measured HBM copy bandwidth in MEASURED_PEAKS.json.
+* ``cpu_baseline`` the CPU oracle (C port of the reference's numba kernels, OpenMP on all
+               host cores) on a bounded sample of the same workload.
+
+``--impl reference`` times that CPU implementation alone (rank 0 only).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "candidate_trees_fit_and_ranked_per_second"
+RUN = dict(alpha=0.001, gamma=0.7, max_iter=25, tolerance=1.0)      # CLI defaults, A.py:62-81
+# mean CAVI tree-iterations per tree (init pass = 0.5) of the full config-3 candidate set as
+# measured by the GPU arm; used only to express the CPU sample (a few iterations of one tree)
+# in the metric's unit.  See BASELINE.md section 5.
+MEAN_TREE_ITERS = {"config3": 11.8, "config2": 12.8}
+
+
+def parse_args():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=3)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    p.add_argument("--config", default="config3")
+    p.add_argument("--trees", type=int, default=0, help="candidate trees per GPU (default: the config's)")
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--slots", type=int, default=0)
+    return p.parse_args()
+
+
+# ---------------------------------------------------------------------------------------------
+# workload
+# ---------------------------------------------------------------------------------------------
+def make_workload(name, trees_per_gpu, n_gpus):
+    """The seeded synthetic dataset + a global candidate set of ``trees_per_gpu * n_gpus`` trees
+    (the config's own trees first, then further seeded random trees over the same labels)."""
+    from arborist_b200 import synth
+
+    cfg = synth.CONFIGS[name]
+    d = synth.generate(cfg)
+    per = trees_per_gpu or cfg.n_trees
+    want = per * n_gpus
+    trees = list(d.trees[:want])
+    rng = np.random.default_rng(cfg.seed + 104729)
+    while len(trees) < want:
+        trees.append(synth._edges(synth.random_tree(rng, cfg.n_clones - 1, cfg.deep)))
+    return cfg, d, trees, per
+
+
+def algorithmic_bytes(n, m, nnz, K):
+    """bytes one tree-iteration must move at the reference's element widths."""
+    C = K - 1
+    b_z = 20 * nnz + 4 * (n + 1) + 8 * (n * K + m * C)            # CSR sweep: q(z) update + ELBO
+    b_y = 20 * nnz + 4 * (m + 1) + 8 * (n * K + 2 * m * C)        # CSC sweep: q(y) update
+    return b_z, b_y
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                 "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "power_w_max": float(max(power)), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU arm: the oracle (C port of the reference's kernels) on the host cores
+# ---------------------------------------------------------------------------------------------
+class CpuArm:
+    """Bounded sample: tree s of the workload, initial pass + ``iters`` CAVI iterations
+    (A.py:733-816 with max_iter capped), every OpenMP thread the host offers."""
+
+    def __init__(self, cfg, d, trees, iters=2):
+        from oracle import oracle as orc
+
+        self.orc, self.iters, self.trees = orc, iters, trees
+        self.cores = orc.lib().orc_max_threads()
+        orc.lib().orc_set_threads(self.cores)
+        self.prob = orc.prepare(trees[:1], d.read_counts_frame(), d.clusters_frame(), alpha=RUN["alpha"],
+                                gamma=RUN["gamma"], add_normal=True)
+        self.add_normal = orc.add_normal_clone
+        self.mean_iters = MEAN_TREE_ITERS.get(cfg.name, 12.0)
+        self.sample = (f"1 tree per step, initial pass + {iters} CAVI iterations ({iters + 0.5} of ~"
+                       f"{self.mean_iters} tree-iterations per tree), tolerance 0 so no early stop; trees/s "
+                       f"extrapolated with that mean")
+
+    def step(self, s):
+        tree = self.add_normal([self.trees[s % len(self.trees)]])[0]
+        t0 = time.perf_counter()
+        self.orc.fit_tree(self.prob, tree, max_iter=self.iters, tolerance=0.0)
+        dt = time.perf_counter() - t0
+        tree_iters = self.iters + 0.5
+        return dt, tree_iters
+
+    def trees_per_s(self, seconds, tree_iters):
+        return (tree_iters / seconds) / self.mean_iters
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cfg, d, trees, per = make_workload(args.config, args.trees, 1)
+    arm = CpuArm(cfg, d, trees)
+    for s in range(args.warmup):
+        arm.step(s)
+    tot_t = tot_i = 0.0
+    for s in range(args.steps):
+        dt, ti = arm.step(args.warmup + s)
+        tot_t += dt
+        tot_i += ti
+    v = arm.trees_per_s(tot_t, tot_i)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "trees/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / max(1, args.steps),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"{cfg.name}: {cfg.n_cells} cells x {cfg.n_snvs} SNVs, K={cfg.n_clones}, "
+                               f"{per} candidate trees", "step": arm.sample},
+        "tree_iters_per_s": tot_i / tot_t,
+        "cpu_baseline": {"value": v, "unit": "trees/s", "cores": arm.cores, "kind": "port", "sample": arm.sample},
+        "e2e": {"value": v, "unit": "trees/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------
+def run_gpu_arm(args):
+    import torch
+
+    from arborist_b200 import arborist, distributed, engine
+    from arborist_b200.arborist import add_normal_clone, ingest_read_counts, prepare_trees
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if engine.device_count() == 0:
+        raise SystemExit("bench.py: no CUDA device; the GPU arm has no CPU fallback (use --impl reference)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    else:
+        dist = None
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+
+    def max_over_ranks(x):
+        if dist is None:
+            return float(x)
+        t = torch.tensor([float(x)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    cfg, d, trees, per = make_workload(args.config, args.trees, world)
+    rc, cl = d.read_counts_frame(), d.clusters_frame()
+    T = len(trees)
+
+    # ---- resident state: ingest once, keep the matrix in HBM ----------------------------------
+    trees_n = add_normal_clone(trees)
+    clone_to_idx, cluster_to_idx, parents, presence, normal_idx = prepare_trees(trees_n)
+    K = len(clone_to_idx)
+    eng = engine.Engine(device=local)
+    if args.slots:
+        eng.set_option("slots", args.slots)
+    ingest_read_counts(eng, rc, cl, cluster_to_idx, RUN["alpha"], RUN["gamma"])
+    n, m, nnz, n_pairs = eng.dims()
+    shard = distributed.shard_indices(T)
+    my_parents = np.ascontiguousarray(parents[shard])
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def device_step():
+        """fit + gather + rank; returns (device ms, stats, profile)."""
+        elbo, iters = eng.fit(parents=my_parents, n_clones=K, normal_idx=normal_idx,
+                              max_iter=RUN["max_iter"], tolerance=RUN["tolerance"], keep_posteriors="all")
+        st, pf = eng.last_fit_stats(), eng.last_fit_profile()
+        ev0.record()
+        full, _ = distributed.gather_elbos(elbo, shard, T)
+        ev1.record()
+        torch.cuda.synchronize()
+        order = np.argsort(-full, kind="stable")               # the ranking (A.py:1164-1166)
+        return st["device_ms"] + ev0.elapsed_time(ev1), st, pf, full, order, iters
+
+    for _ in range(args.warmup):
+        device_step()
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    dev_ms = wall = 0.0
+    launches = 0
+    prof = dict(sweep_z_ms=0.0, sweep_y_ms=0.0, finish_ms=0.0, tree_sweeps_z=0.0, tree_sweeps_y=0.0,
+                launches_z=0.0, launches_y=0.0, rounds=0.0)
+    tree_iters = 0.0
+    t_wall0 = time.perf_counter()
+    for _ in range(args.steps):
+        ms, st, pf, full, order, iters = device_step()
+        dev_ms += ms
+        launches += st["kernel_launches"]
+        tree_iters += st["tree_iterations"]
+        for k in prof:
+            prof[k] += pf[k]
+    barrier()
+    wall = time.perf_counter() - t_wall0
+    clocks = sampler.stop()
+    dev_ms = max_over_ranks(dev_ms)
+    wall = max_over_ranks(wall)
+    tree_iters_all = tree_iters
+    if dist is not None:
+        t = torch.tensor([tree_iters], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t)
+        tree_iters_all = float(t.item())
+    steps = max(1, args.steps)
+    value = T * steps / (dev_ms * 1e-3)
+
+    # ---- roofline of the dominant kernel (q(z) sweep), from this rank's events --------------------
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    b_z, b_y = algorithmic_bytes(n, m, nnz, K)
+    lz = max(1.0, prof["launches_z"])
+    ach_z = prof["tree_sweeps_z"] * b_z / max(prof["sweep_z_ms"], 1e-9) / 1e6          # GB/s
+    ach_y = prof["tree_sweeps_y"] * b_y / max(prof["sweep_y_ms"], 1e-9) / 1e6
+    roofline = {
+        "kernel": "k_sweep<KP,true> (q(z) sweep + E[log lik] accumulators)", "bound": "hbm",
+        "achieved": ach_z, "peak": peak, "unit": "GB/s", "frac": ach_z / peak,
+        "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
+        "traffic": None,
+        "algorithmic_bytes_per_tree_sweep": b_z, "tree_sweeps_per_launch": prof["tree_sweeps_z"] / lz,
+        "avg_launch_ms": prof["sweep_z_ms"] / lz,
+        "qy_sweep": {"achieved": ach_y, "frac": ach_y / peak, "algorithmic_bytes_per_tree_sweep": b_y,
+                     "avg_launch_ms": prof["sweep_y_ms"] / max(1.0, prof["launches_y"])},
+        "whole_step": {"achieved": tree_iters / steps * (b_z + b_y) / (dev_ms / steps) / 1e6,
+                       "frac": tree_iters / steps * (b_z + b_y) / (dev_ms / steps) / 1e6 / peak,
+                       "note": "tree-iterations x B_iter / step time, per GPU"},
+        "kernel_share_of_step": {"sweep_z": prof["sweep_z_ms"] / (dev_ms if world == 1 else max(dev_ms, 1e-9)),
+                                 "sweep_y": prof["sweep_y_ms"] / max(dev_ms, 1e-9),
+                                 "finish": prof["finish_ms"] / max(dev_ms, 1e-9)},
+    }
+
+    # ---- end to end through arborist(...) with host DataFrames ---------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        eng.close()
+        del eng
+        barrier()
+        t0 = time.perf_counter()
+        d2h = 0
+        for _ in range(args.steps):
+            lik, best, fits = arborist(trees, rc, cl, alpha=RUN["alpha"], max_iter=RUN["max_iter"],
+                                       tolerance=RUN["tolerance"], gamma=RUN["gamma"], add_normal=True,
+                                       device=local)
+            ranking = sorted(lik.items(), key=lambda kv: -kv[1])
+            qz, qy = best.q_z, best.q_y                           # D2H of the winner's posteriors
+            d2h = 12 * len(shard) + 4 * (n + m) + qz.nbytes + qy.nbytes
+            assert ranking[0][0] == best.tree_idx
+            arborist.last_stats = None                            # drop the engine (frees the GPU memory)
+            del fits, best
+        barrier()
+        e2e_wall = max_over_ranks(time.perf_counter() - t0)
+        e2e = {"value": T * steps / e2e_wall, "unit": "trees/s",
+               "h2d_bytes_per_step": int(16 * len(rc) + 4 * m + 4 * my_parents.size + 16 * n_pairs),
+               "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * e2e_wall / steps,
+               "note": "arborist(trees, read_counts_df, clusters_df): host id factorisation, H2D of the COO "
+                       "table, device ingest + layouts, batched fit, ELBO gather, ranking, D2H of ELBOs / "
+                       "iteration counts / index orders / the best tree's q_z and q_y; host wall clock"}
+
+    # ---- CPU baseline (rank 0, N = 1) ------------------------------------------------------------------
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        arm = CpuArm(cfg, d, trees)
+        arm.mean_iters = tree_iters / steps / len(shard)         # this run's own mean
+        dt, ti = arm.step(0)
+        cpu = {"value": arm.trees_per_s(dt, ti), "unit": "trees/s", "cores": arm.cores, "kind": "port",
+               "sample": arm.sample.replace(str(MEAN_TREE_ITERS.get(cfg.name, 12.0)), f"{arm.mean_iters:.2f}"),
+               "tree_iters_per_s": ti / dt, "seconds": dt}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": "trees/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dev_ms / steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"{cfg.name}: {cfg.n_cells} cells x {cfg.n_snvs} SNVs low-pass "
+                                   f"({n} x {m} after the zero-alt filter, nnz {nnz}), K={K} clones, "
+                                   f"{per} candidate trees per GPU ({T} total), seed {cfg.seed}",
+                       "run": RUN, "parallelism": f"tree-sharded x{world}",
+                       "l2": "inputs larger than L2: per-step working set (panel partials + posteriors of "
+                             "all trees in flight) is tens of GB, far above the 126 MB L2; no flush needed",
+                       "timing": "CUDA events on the library's launching stream around each fit + torch "
+                                 "events around the ELBO gather; max over ranks"},
+            "tree_iters_per_s": tree_iters_all / (dev_ms * 1e-3),
+            "mean_tree_iters_per_tree": tree_iters / steps / len(shard),
+            "wall_ms_per_step": 1e3 * wall / steps,
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
+            "e2e": e2e, "cpu_baseline": cpu,
+            "best_tree": int(order[0]), "true_tree": int(d.true_tree_index),
+        }
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

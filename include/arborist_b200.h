@@ -148,7 +148,11 @@ int arb_elbo_terms(arb_ctx *ctx, int32_t n_clones, const uint8_t *presence, cons
  * CAVI tree-iterations it executed (initial pass = half an iteration) */
 int arb_last_fit_stats(arb_ctx *ctx, int64_t *kernel_launches, double *device_ms,
                        double *tree_iterations, double *sweep_ms);
-/* tuning knobs: "slots" (trees in flight), "panel_kb", "chunk_rows"; returns ARB_ERR_INVALID
+/* per-kernel profile of the last arb_fit_* call, measured with CUDA events on the context's
+ * stream: values[0..7] = q(z) sweep ms, q(y) sweep ms, finishing kernels ms, tree-sweeps done
+ * by the q(z) / q(y) sweep launches, number of q(z) / q(y) sweep launches, rounds */
+int arb_last_fit_profile(arb_ctx *ctx, double *values, int32_t n_values);
+/* tuning knobs: "slots" (trees in flight), "panel_kb" (panel bytes cap), "threads"; returns ARB_ERR_INVALID
  * for unknown names */
 int arb_set_option(arb_ctx *ctx, const char *name, int64_t value);
 

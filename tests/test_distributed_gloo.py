@@ -1,0 +1,65 @@
+"""Tree-set sharding over ranks (world_size 2, gloo, CPU): shard indices, ELBO gather and the
+owner-broadcast of posteriors, with a stand-in engine (the GPU engine is covered by -m gpu)."""
+import os
+import subprocess
+import sys
+import textwrap
+
+import numpy as np
+
+from conftest import ROOT
+
+WORKER = textwrap.dedent("""
+    import os, sys
+    import numpy as np
+    import torch.distributed as dist
+    sys.path.insert(0, os.environ["ARB_ROOT"])
+    from arborist_b200 import distributed as D
+
+    dist.init_process_group("gloo")
+    rank, ws = D.world()
+    assert ws == 2
+    T = 7
+    shard = D.shard_indices(T)
+    assert shard.tolist() == list(range(rank, T, 2))
+    truth = np.arange(T) * 1.5 - 3.0
+    full, owner = D.gather_elbos(truth[shard], shard, T)
+    assert np.array_equal(full, truth), full
+    assert owner.tolist() == [t % 2 for t in range(T)]
+    iters = D.gather_vector((shard + 3).astype(np.int32), shard, T, dtype=np.int32)
+    assert iters.tolist() == [t + 3 for t in range(T)]
+
+    class FakeEngine:
+        n_clones = 3
+        def dims(self): return 4, 5, 0, 0
+        def get_fit(self, t):
+            g = shard[t]
+            return np.full((4, 3), float(g)), np.full((5, 2), -float(g))
+
+    local_of = {int(g): l for l, g in enumerate(shard)}
+    for idx in (0, 1, 6):           # collective: both ranks ask for the same tree
+        qz, qy = D.fetch_fit(FakeEngine(), idx, local_of, owner)
+        assert (qz == idx).all() and (qy == -idx).all() and qz.shape == (4, 3)
+    dist.barrier()
+    dist.destroy_process_group()
+    print("rank", rank, "ok")
+""")
+
+
+def test_gloo_world_size_2(tmp_path):
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER)
+    env = dict(os.environ, ARB_ROOT=ROOT, OMP_NUM_THREADS="1")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", "29533", str(script)]
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=240)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-3000:]
+    assert "rank 0 ok" in res.stdout and "rank 1 ok" in res.stdout
+
+
+def test_single_process_defaults():
+    from arborist_b200 import distributed as D
+    assert D.world() == (0, 1)
+    assert D.shard_indices(5).tolist() == [0, 1, 2, 3, 4]
+    full, owner = D.gather_elbos(np.array([1.0, 2.0]), np.array([0, 1]), 2)
+    assert full.tolist() == [1.0, 2.0] and owner.tolist() == [0, 0]

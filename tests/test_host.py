@@ -1,0 +1,157 @@
+"""Host-side logic that mirrors the reference's Python surface (no GPU needed)."""
+import pickle
+
+import numpy as np
+import pandas as pd
+import pytest
+
+from conftest import golden_frames, load_golden
+
+
+def test_read_trees_roundtrip(tmp_path):
+    from arborist_b200.utils import read_trees, write_trees
+    trees = [[(0, 1), (1, 2)], [(0, 2), (2, 1)], [(5, 6)]]
+    p = tmp_path / "t.txt"
+    write_trees(trees, p)
+    assert read_trees(p) == trees
+    p.write_text("0,1\n1,2\n# tree\n\n0,2\n2,1\nbad line here\n")
+    assert read_trees(p, sep=",") == trees[:2]
+
+
+def test_add_normal_clone_matches_reference_edge_order():
+    """A.py:860-882 returns list(nx.DiGraph.edges) of the augmented graph."""
+    from arborist_b200.arborist import add_normal_clone
+    g = load_golden("small")
+    given = [[(int(u), int(v)) for u, v in t] for t in g["trees"]]
+    g2 = load_golden("small_nonormal")           # its trees = add_normal_clone(small's trees), via the reference path
+    want = [[(int(u), int(v)) for u, v in t] for t in g2["trees"]]
+    assert add_normal_clone(given) == want
+    assert add_normal_clone([[(3, 4), (3, 5)]]) == [[(3, 4), (3, 5), (2, 3)]]
+
+
+def test_prepare_trees_parents_and_errors():
+    from arborist_b200.arborist import prepare_trees
+    trees = [[(0, 2), (2, 5), (2, 7)], [(0, 5), (5, 2), (2, 7)]]
+    c2i, k2i, parents, presence, normal = prepare_trees(trees)
+    assert c2i == {0: 0, 2: 1, 5: 2, 7: 3} and k2i == {2: 0, 5: 1, 7: 2} and normal == 0
+    assert presence is None
+    assert parents.tolist() == [[-1, 0, 1, 1], [-1, 2, 0, 1]]
+    with pytest.raises(ValueError, match="same set of clones"):
+        prepare_trees([[(0, 1), (1, 2)], [(0, 1), (1, 3)]])
+    with pytest.raises(ValueError, match="same set of clones"):
+        prepare_trees([[(0, 1), (1, 2)], [(0, 1), (0, 1)]])
+    # ragged edge lists take the slow path
+    c2i, _, parents, presence, _ = prepare_trees([[(0, 1), (1, 2)], [(0, 1), (1, 2), (0, 1)]])
+    assert presence is None and parents.tolist() == [[-1, 0, 1], [-1, 0, 1]]
+
+
+def test_prepare_trees_non_forest_gives_presence():
+    from arborist_b200.arborist import prepare_trees
+    from oracle import oracle as orc
+    dag = [[(0, 1), (1, 2), (1, 3), (2, 4), (3, 4)], [(0, 1), (1, 2), (2, 3), (3, 4)]]
+    c2i, k2i, parents, presence, normal = prepare_trees(dag)
+    assert parents is None and presence.shape == (2, 4, 5)
+    for t in range(2):
+        assert np.array_equal(presence[t], orc.enumerate_presence(dag[t], c2i, k2i))
+
+
+@pytest.mark.parametrize("name", ["tiny", "deep30"])
+def test_parent_closure_equals_reference_presence(name):
+    """The closure the device builds from parent vectors, restated in numpy, equals
+    enumerate_presence (A.py:491-520) as recorded from the reference."""
+    from arborist_b200.arborist import add_normal_clone, prepare_trees
+    g = load_golden(name)
+    trees, _, _ = golden_frames(g)
+    trees = add_normal_clone(trees)
+    c2i, k2i, parents, _, normal = prepare_trees(trees)
+    K = len(c2i)
+    for t in range(len(trees)):
+        P = np.zeros((K - 1, K), dtype=np.int64)
+        for r in range(K):
+            a = r
+            while a >= 0:
+                if a != normal:
+                    P[a if a < normal else a - 1, r] = 1
+                a = parents[t, a]
+        assert np.array_equal(P, g["presence"][t])
+
+
+def test_prior_labels_quirks():
+    """A.py:547-567: last duplicate wins, label 0 / off-tree / missing -> uniform row."""
+    from arborist_b200.arborist import _prior_labels
+    cl = pd.DataFrame({"snv": [10, 11, 12, 13, 10], "cluster": [1, 0, 99, 2, 2]})
+    out = _prior_labels(cl, np.array([10, 11, 12, 13, 14]), {1: 0, 2: 1})
+    assert out.tolist() == [1, -1, -1, 1, -1]
+    g = load_golden("deep30")                     # 30 % off-tree labels in the fixture
+    _, _, clf = golden_frames(g)
+    k2i = {int(c): i for i, c in enumerate(g["clusters"])}
+    lab = _prior_labels(clf, g["snv_order"], k2i)
+    q0 = g["q_y_init"]
+    uniform = np.isclose(q0, 1 / len(k2i)).all(axis=1)
+    assert np.array_equal(lab < 0, uniform)
+    assert np.array_equal(lab[~uniform], q0[~uniform].argmax(1))
+
+
+def _toy_fit(lazy):
+    from arborist_b200.treefit import TreeFit
+    qz = np.array([[0.2, 0.8], [0.5, 0.5], [0.9, 0.1]])
+    qy = np.array([[1.0], [1.0]])
+    args = ([(0, 1)], 3, -12.5)
+    maps = ({"c1": 0, "c2": 1, "c3": 2}, {"s1": 0, "s2": 1}, {0: 0, 1: 1}, {1: 0})
+    if lazy:
+        calls = []
+        return TreeFit.lazy(*args, lambda idx: calls.append(idx) or (qz, qy), *maps), calls
+    return TreeFit(*args, qz, qy, *maps), None
+
+
+def test_treefit_tables_and_map_argmax_first_max_wins():
+    f, _ = _toy_fit(False)
+    z = f.map_assign_z()
+    assert list(z.columns) == ["id", "assignment"]
+    assert z["id"].tolist() == ["c1", "c2", "c3"] and z["assignment"].tolist() == [1, 0, 0]
+    assert list(f.q_z_df().columns) == ["id", "clone_0", "clone_1"]
+    assert list(f.q_y_df().columns) == ["id", "cluster_1"]
+    assert "ELBO: -12.50" in str(f) and " 0->1" in str(f)
+    assert list(f.cell_entropy().columns) == ["id", "entropy"]
+
+
+def test_treefit_lazy_loads_once_and_pickles_as_plain_arrays(tmp_path):
+    f, calls = _toy_fit(True)
+    assert calls == []
+    assert f.elbo == -12.5 and calls == []
+    assert f.q_z.shape == (3, 2) and calls == [3]
+    f.q_y
+    assert calls == [3]
+    g = pickle.loads(pickle.dumps({3: f}))[3]
+    assert type(g).__module__ == "arborist.treefit"          # the path reference pickles use
+    assert np.array_equal(g.q_z, f.q_z) and g.map_assign_z()["assignment"].tolist() == [1, 0, 0]
+    f.save_tree(tmp_path / "best.txt")
+    assert (tmp_path / "best.txt").read_text() == "1 #edges tree 0\n0 1\n"
+
+
+def test_drop_in_package_names():
+    import arborist
+    import arborist_b200
+    assert arborist.arborist is arborist_b200.arborist
+    assert arborist.read_trees is arborist_b200.read_trees
+    from arborist.treefit import TreeFit
+    assert TreeFit is arborist_b200.TreeFit
+
+
+def test_cli_flags_match_reference():
+    from arborist_b200.arborist import parse_arguments
+    a = parse_arguments(["-R", "r.csv", "-Y", "y.csv", "-T", "t.txt"])
+    assert (a.alpha, a.max_iter, a.prior, a.threads, a.edge_delim) == (0.001, 25, 0.7, 10, " ")
+    assert not a.add_normal and not a.verbose
+    a = parse_arguments(["-R", "r", "-Y", "y", "-T", "t", "--add-normal", "--ranking", "o.csv", "-j", "4",
+                         "--q_z", "z.csv", "--q_y", "y.csv", "--pickle", "p.pkl", "-d", "x.png", "-t", "b.txt",
+                         "--cell-assign", "c.csv", "--snv-assign", "s.csv", "-v", "--prior", "0.9"])
+    assert a.add_normal and a.ranking == "o.csv" and a.threads == 4 and a.prior == 0.9
+
+
+def test_synth_generator_is_seed_stable():
+    from arborist_b200 import synth
+    a, b = synth.generate(synth.CONFIGS["tiny"]), synth.generate(synth.CONFIGS["tiny"])
+    assert np.array_equal(a.alt, b.alt) and a.trees == b.trees
+    g = load_golden("tiny")
+    assert np.array_equal(a.snv, g["rc_snv"]) and np.array_equal(a.alt, g["rc_alt"])

@@ -16,6 +16,18 @@ ELBO_RTOL = 1e-9
 Q_RTOL, Q_ATOL = 1e-7, 1e-12       # posteriors: relative on the bulk, absolute floor for ~0 entries
 
 
+def assert_map_equal(q, q_ref):
+    """MAP labels must be identical wherever the reference's own maximum is decided by more
+    than rounding: rows whose top two reference posteriors differ by < 1e-9 relative are exact
+    mathematical ties (e.g. sibling leaves with identical evidence) that the reference breaks
+    by the last bit of its log-sum-exp; there the chosen label must still be one of the tied."""
+    a, b = q.argmax(1), q_ref.argmax(1)
+    diff = np.nonzero(a != b)[0]
+    for i in diff:
+        top = q_ref[i, b[i]]
+        assert abs(q_ref[i, a[i]] - top) <= 1e-9 * top, f"MAP differs on row {i} beyond a tie"
+
+
 @pytest.fixture(scope="module")
 def eng_mod():
     from arborist_b200 import engine
@@ -270,8 +282,8 @@ def test_against_oracle_on_fresh_inputs(eng_mod):
             assert arborist.last_stats["iters"][t] == ofits[t][3]
             np.testing.assert_allclose(fits[t].q_z, ofits[t][1], rtol=Q_RTOL, atol=Q_ATOL)
             np.testing.assert_allclose(fits[t].q_y, ofits[t][2], rtol=Q_RTOL, atol=Q_ATOL)
-            assert np.array_equal(fits[t].q_z.argmax(1), ofits[t][1].argmax(1))
-            assert np.array_equal(fits[t].q_y.argmax(1), ofits[t][2].argmax(1))
+            assert_map_equal(fits[t].q_z, ofits[t][1])
+            assert_map_equal(fits[t].q_y, ofits[t][2])
 
 
 def test_non_forest_presence_and_errors(eng_mod):

@@ -68,15 +68,20 @@ struct DevBuf {
 
 // Panelled sparse layout for one padded clone width KP (8, 16 or 32 doubles per row of
 // the gathered operand).  "z": cell-major rows, SNVs cut into panels (q(z) sweep);
-// "y": SNV-major rows, cells cut into panels (q(y) sweep).  A stream word is
-// (pair code << 16) | (column index inside its panel).
+// "y": SNV-major rows, cells cut into panels (q(y) sweep).  Segment p (position inside the
+// panel-major, length-sorted order) spans stream[ptr[p] .. ptr[p+1]); its code-0 run ends
+// at mid[p]; row[p] is the row it belongs to.  See arb_ingest.cu "panel layouts".
 struct PanelLayout {
     int kp = 0;
     int panel_rows = 0;      // rows of the gathered operand per panel (<= 65536)
     int np_z = 0, np_y = 0;  // number of panels
-    DevBuf zptr, zstream;    // int32 [np_z * n_cells + 1], uint32 [nnz]
-    DevBuf yptr, ystream;    // int32 [np_y * n_snvs + 1], uint32 [nnz]
-    void release() { zptr.release(); zstream.release(); yptr.release(); ystream.release(); kp = 0; }
+    DevBuf zptr, zmid, zrow, zstream;    // int32 [np_z * n_cells + 1] x3, uint32 [nnz]
+    DevBuf yptr, ymid, yrow, ystream;    // int32 [np_y * n_snvs + 1] x3, uint32 [nnz]
+    void release()
+    {
+        for (DevBuf *b : {&zptr, &zmid, &zrow, &zstream, &yptr, &ymid, &yrow, &ystream}) b->release();
+        kp = 0;
+    }
 };
 
 struct FitStats {

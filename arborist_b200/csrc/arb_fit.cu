@@ -199,19 +199,48 @@ struct SweepArgs {
     const double *x;           // gathered operand [slot][n_gather][KP]
     int64_t x_slot_stride;     // doubles
     int32_t n_gather;          // rows of the gathered operand
-    const int32_t *seg_ptr;    // [n_panels * n_rows + 1]
-    const uint32_t *stream;    // (code << 16) | index inside the panel
+    const int32_t *seg_ptr;    // [n_panels * n_rows + 1] segment starts (length-sorted positions)
+    const int32_t *seg_mid;    //                          end of the segment's code-0 run
+    const int32_t *seg_row;    //                          row the segment belongs to
+    const uint32_t *stream;    // A run: byte offset of the gathered row; B run: code << 16 | index
     int32_t n_rows, panel_rows, n_panels;
     const int32_t *slot_list;
     int32_t n_active;
     const double2 *dw;         // per pair code: (d, w)
-    int32_t tab_n, renorm_every;
+    int32_t n_pairs, tab_n, renorm_every;
     double *out_m;             // [slot][panel][row][KP] mantissa of the running product
     int32_t *out_e;            //                        its exponent
     double *out_g;             //                        sum_k w_k x (q(z) sweep only)
 };
 
-template <int KP, bool WITH_G>
+// Four clones of one nonzero: two LDS.128 from the staged panel, 4 x (DFMA + DMUL) for the
+// running products and 4 x DFMA for the likelihood accumulators.
+template <bool WITH_G, bool EACH>
+__device__ __forceinline__ void sweep_step(const char *xa_base, const char *xb_base, uint32_t off, double d, double w,
+                                           double (&p)[4], double (&g)[4], int (&e)[4])
+{
+    const double2 xa = *reinterpret_cast<const double2 *>(xa_base + off);
+    const double2 xb = *reinterpret_cast<const double2 *>(xb_base + off);
+    p[0] *= fma(d, xa.x, 1.0);
+    p[1] *= fma(d, xa.y, 1.0);
+    p[2] *= fma(d, xb.x, 1.0);
+    p[3] *= fma(d, xb.y, 1.0);
+    if (WITH_G) {
+        g[0] = fma(w, xa.x, g[0]);
+        g[1] = fma(w, xa.y, g[1]);
+        g[2] = fma(w, xb.x, g[2]);
+        g[3] = fma(w, xb.y, g[3]);
+    }
+    if (EACH) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
+    }
+}
+
+// One CTA = (tree slot, panel).  Groups of GL = KP/4 lanes walk the panel's segments; lane h of a
+// group owns clones 4h..4h+3 of the segment's row.  The two 16-byte halves a lane reads are
+// swizzled on bit 2 of the lane id so that the eight lanes of a quarter-warp cover all 32 banks.
+template <int KP, bool WITH_G, bool EACH>
 __global__ void __launch_bounds__(SWEEP_THREADS, 1) k_sweep(const SweepArgs a)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -222,8 +251,8 @@ __global__ void __launch_bounds__(SWEEP_THREADS, 1) k_sweep(const SweepArgs a)
     const int panel = blockIdx.x / a.n_active;
     const int slot = a.slot_list[blockIdx.x % a.n_active];
     const int row0 = panel * a.panel_rows;
-    const int cnt = min(a.panel_rows, a.n_gather - row0);
-    const uint32_t bytes = (uint32_t)cnt * KP * 8u;
+    const int cnt_rows = min(a.panel_rows, a.n_gather - row0);
+    const uint32_t bytes = (uint32_t)cnt_rows * KP * 8u;
     const uint32_t bar = smem_u32(mbar);
 
     if (threadIdx.x == 0) {
@@ -243,45 +272,111 @@ __global__ void __launch_bounds__(SWEEP_THREADS, 1) k_sweep(const SweepArgs a)
         }
     }
     for (int c = threadIdx.x; c < a.tab_n; c += SWEEP_THREADS) tab[c] = a.dw[c];
+    const double2 dw0 = __ldg(a.dw);
+    const double2 dw1 = a.n_pairs > 1 ? __ldg(a.dw + 1) : make_double2(0.0, 0.0);
     __syncthreads();
     asm volatile("{\n\t.reg .pred p;\n\tWAIT_PANEL:\n\t"
                  "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n\t"
                  "@p bra DONE_PANEL;\n\tbra WAIT_PANEL;\n\tDONE_PANEL:\n\t}" ::"r"(bar) : "memory");
 
-    constexpr int GL = KP / 2;                     // lanes per row group; each lane owns two clones
-    const int h = threadIdx.x % GL, gid = threadIdx.x / GL;
+    constexpr int GL = KP / 4;                     // lanes per segment; each lane owns four clones
     constexpr int NG = SWEEP_THREADS / GL;
+    constexpr uint32_t ROW_BYTES = KP * 8;
+    const int lane = threadIdx.x & 31;
+    const int h = threadIdx.x % GL, gid = threadIdx.x / GL;
+    const int swz = (lane >> 2) & 1;
+    const int off_a = 4 * h + 2 * swz, off_b = 4 * h + 2 * (1 - swz);       // columns (doubles)
+    const char *xa_base = reinterpret_cast<const char *>(xs + off_a);
+    const char *xb_base = reinterpret_cast<const char *>(xs + off_b);
     const int64_t seg0 = (int64_t)panel * a.n_rows;
     const int64_t out0 = ((int64_t)slot * a.n_panels + panel) * a.n_rows;
     const int renorm_every = a.renorm_every;
+    const uint32_t *__restrict__ stream = a.stream;
 
-    for (int i = gid; i < a.n_rows; i += NG) {
-        const int k0 = __ldg(a.seg_ptr + seg0 + i), k1 = __ldg(a.seg_ptr + seg0 + i + 1);
-        double p0 = 1.0, p1 = 1.0, g0 = 0.0, g1 = 0.0;
-        int e0 = 0, e1 = 0, since = 0;
-        for (int k = k0; k < k1; ++k) {
-            const uint32_t word = __ldg(a.stream + k);
-            const uint32_t j = word & 0xffffu, code = word >> 16;
-            const double2 dw = (code < (uint32_t)a.tab_n) ? tab[code] : __ldg(a.dw + code);
-            const double2 x = *reinterpret_cast<const double2 *>(xs + (size_t)j * KP + 2 * h);
-            p0 *= fma(dw.x, x.x, 1.0);
-            p1 *= fma(dw.x, x.y, 1.0);
-            if (WITH_G) {
-                g0 = fma(dw.y, x.x, g0);
-                g1 = fma(dw.y, x.y, g1);
-            }
-            if (++since == renorm_every) {
-                since = 0;
-                renorm(p0, e0);
-                renorm(p1, e1);
+    for (int pos0 = 0; pos0 < a.n_rows; pos0 += NG) {          // warp-uniform trip count
+        const int pos = pos0 + gid;
+        const bool live = pos < a.n_rows;
+        const int k0 = live ? __ldg(a.seg_ptr + seg0 + pos) : 0, km = live ? __ldg(a.seg_mid + seg0 + pos) : 0;
+        const int k1 = live ? __ldg(a.seg_ptr + seg0 + pos + 1) : 0, row = live ? __ldg(a.seg_row + seg0 + pos) : 0;
+        double p[4] = {1.0, 1.0, 1.0, 1.0}, g[4] = {0.0, 0.0, 0.0, 0.0};
+        int e[4] = {0, 0, 0, 0}, since = 0;
+
+        // Both runs are walked in chunks of GL words (one per lane, broadcast with shuffles).  The
+        // trip counts are made warp-uniform (max over the warp's groups; the layout sorts segments
+        // by shape, so max == min almost always) and shuffles use the full mask: no divergence.
+        // ---- A run: the most frequent (alt,total) pair; d and w live in registers -----------------
+        {
+            const int n_a = km - k0;
+            const int n_max = __reduce_max_sync(0xffffffffu, n_a), n_min = __reduce_min_sync(0xffffffffu, n_a);
+            uint32_t wn = (h < n_a) ? __ldg(stream + k0 + h) : 0u;
+            for (int c = 0; c < n_max; c += GL) {
+                const uint32_t wc = wn;
+                wn = (c + GL + h < n_a) ? __ldg(stream + k0 + c + GL + h) : 0u;
+                if (c + GL <= n_min) {
+#pragma unroll
+                    for (int s = 0; s < GL; ++s) {
+                        const uint32_t off = __shfl_sync(0xffffffffu, wc, s, GL);
+                        sweep_step<WITH_G, EACH>(xa_base, xb_base, off, dw0.x, dw0.y, p, g, e);
+                    }
+                } else {
+                    const int left = n_a - c;
+#pragma unroll
+                    for (int s = 0; s < GL; ++s) {
+                        const uint32_t off = __shfl_sync(0xffffffffu, wc, s, GL);
+                        if (s < left) sweep_step<WITH_G, EACH>(xa_base, xb_base, off, dw0.x, dw0.y, p, g, e);
+                    }
+                }
+                if (!EACH) {
+                    since += GL;
+                    if (since + GL > renorm_every) {
+                        since = 0;
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) renorm(p[q], e[q]);
+                    }
+                }
             }
         }
-        renorm(p0, e0);
-        renorm(p1, e1);
-        const int64_t o = (out0 + i) * KP + 2 * h;
-        *reinterpret_cast<double2 *>(a.out_m + o) = make_double2(p0, p1);
-        *reinterpret_cast<int2 *>(a.out_e + o) = make_int2(e0, e1);
-        if (WITH_G) *reinterpret_cast<double2 *>(a.out_g + o) = make_double2(g0, g1);
+        // ---- B run: every other pair, ordered by code; code 1 from registers, the rest from the table
+        {
+            const int n_b = k1 - km;
+            const int n_max = __reduce_max_sync(0xffffffffu, n_b);
+            uint32_t wn = (h < n_b) ? __ldg(stream + km + h) : 0u;
+            for (int c = 0; c < n_max; c += GL) {
+                const uint32_t wc = wn;
+                wn = (c + GL + h < n_b) ? __ldg(stream + km + c + GL + h) : 0u;
+                const int left = n_b - c;
+#pragma unroll
+                for (int s = 0; s < GL; ++s) {
+                    const uint32_t word = __shfl_sync(0xffffffffu, wc, s, GL);
+                    if (s < left) {
+                        const uint32_t code = word >> 16, off = (word & 0xffffu) * ROW_BYTES;
+                        double2 dw = dw1;
+                        if (code != 1u) dw = (code < (uint32_t)a.tab_n) ? tab[code] : __ldg(a.dw + code);
+                        sweep_step<WITH_G, EACH>(xa_base, xb_base, off, dw.x, dw.y, p, g, e);
+                    }
+                }
+                if (!EACH) {
+                    since += GL;
+                    if (since + GL > renorm_every) {
+                        since = 0;
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) renorm(p[q], e[q]);
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
+        if (!live) continue;
+        const int64_t o = (out0 + row) * KP;
+        *reinterpret_cast<double2 *>(a.out_m + o + off_a) = make_double2(p[0], p[1]);
+        *reinterpret_cast<double2 *>(a.out_m + o + off_b) = make_double2(p[2], p[3]);
+        *reinterpret_cast<int2 *>(a.out_e + o + off_a) = make_int2(e[0], e[1]);
+        *reinterpret_cast<int2 *>(a.out_e + o + off_b) = make_int2(e[2], e[3]);
+        if (WITH_G) {
+            *reinterpret_cast<double2 *>(a.out_g + o + off_a) = make_double2(g[0], g[1]);
+            *reinterpret_cast<double2 *>(a.out_g + o + off_b) = make_double2(g[2], g[3]);
+        }
     }
 }
 
@@ -552,8 +647,10 @@ static size_t sweep_smem_bytes(const arb_ctx *ctx, const PanelLayout &L)
 template <int KP> static int configure_kernels(const arb_ctx *ctx, const PanelLayout &L)
 {
     const int smem = (int)sweep_smem_bytes(ctx, L);
-    ARB_CUDA(cudaFuncSetAttribute(k_sweep<KP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    ARB_CUDA(cudaFuncSetAttribute(k_sweep<KP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    ARB_CUDA(cudaFuncSetAttribute(k_sweep<KP, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    ARB_CUDA(cudaFuncSetAttribute(k_sweep<KP, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    ARB_CUDA(cudaFuncSetAttribute(k_sweep<KP, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    ARB_CUDA(cudaFuncSetAttribute(k_sweep<KP, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     return ARB_OK;
 }
 
@@ -649,6 +746,8 @@ static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.x_slot_stride = (int64_t)ctx->n_snvs * KP;
     a.n_gather = ctx->n_snvs;
     a.seg_ptr = L.zptr.as<int32_t>();
+    a.seg_mid = L.zmid.as<int32_t>();
+    a.seg_row = L.zrow.as<int32_t>();
     a.stream = L.zstream.as<uint32_t>();
     a.n_rows = ctx->n_cells;
     a.panel_rows = L.panel_rows;
@@ -656,12 +755,16 @@ static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.slot_list = list;
     a.n_active = n_active;
     a.dw = ctx->tab_dw.as<double2>();
+    a.n_pairs = ctx->n_pairs;
     a.tab_n = arb_sweep_table_entries(ctx);
     a.renorm_every = ctx->renorm_every;
     a.out_m = w.pz_m;
     a.out_e = w.pz_e;
     a.out_g = ctx->part_g.as<double>();
-    k_sweep<KP, true><<<n_active * L.np_z, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
+    if (ctx->renorm_every < 8)
+        k_sweep<KP, true, true><<<n_active * L.np_z, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
+    else
+        k_sweep<KP, true, false><<<n_active * L.np_z, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
 }
 
 template <int KP>
@@ -672,6 +775,8 @@ static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.x_slot_stride = (int64_t)ctx->n_cells * KP;
     a.n_gather = ctx->n_cells;
     a.seg_ptr = L.yptr.as<int32_t>();
+    a.seg_mid = L.ymid.as<int32_t>();
+    a.seg_row = L.yrow.as<int32_t>();
     a.stream = L.ystream.as<uint32_t>();
     a.n_rows = ctx->n_snvs;
     a.panel_rows = L.panel_rows;
@@ -679,12 +784,16 @@ static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.slot_list = list;
     a.n_active = n_active;
     a.dw = ctx->tab_dw.as<double2>();
+    a.n_pairs = ctx->n_pairs;
     a.tab_n = arb_sweep_table_entries(ctx);
     a.renorm_every = ctx->renorm_every;
     a.out_m = w.py_m;
     a.out_e = w.py_e;
     a.out_g = nullptr;
-    k_sweep<KP, false><<<n_active * L.np_y, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
+    if (ctx->renorm_every < 8)
+        k_sweep<KP, false, true><<<n_active * L.np_y, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
+    else
+        k_sweep<KP, false, false><<<n_active * L.np_y, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
 }
 
 template <int KP>

@@ -335,65 +335,130 @@ __global__ void k_remap_codes(const int32_t *raw, const int32_t *map, int64_t n,
 // ---------------------------------------------------------------------------------------
 // panel layouts
 // ---------------------------------------------------------------------------------------
-// key of a nonzero in a panelled stream: (panel of the gathered index, row, index in panel)
-__global__ void k_panel_keys(const int32_t *row, const int32_t *col, int64_t nnz, int32_t n_rows,
-                             int32_t panel_rows, uint64_t *key)
+// A panelled stream is cut into segments, one per (panel of the gathered index, row).  Inside
+// a segment the nonzeros of the most frequent pair code (code 0) come first ("A run": the word
+// is the byte offset of the gathered row inside the panel), then the rest ordered by code
+// ("B run": word = code << 16 | index in panel).  Inside a panel the segments are ordered by
+// (A length, B length) descending so that the lane groups of one warp walk segments of
+// (almost always exactly) the same shape; row_id maps a position back to its row.
+__global__ void k_panel_keys(const int32_t *row, const int32_t *col, const uint16_t *code, int64_t nnz,
+                             int32_t n_rows, int32_t panel_rows, uint64_t *key)
 {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= nnz) return;
     const uint64_t panel = (uint64_t)(col[i] / panel_rows), local = (uint64_t)(col[i] % panel_rows);
-    key[i] = (panel * (uint64_t)n_rows + (uint64_t)row[i]) * (uint64_t)panel_rows + local;
+    const uint64_t seg = panel * (uint64_t)n_rows + (uint64_t)row[i];
+    key[i] = (((seg << 16) | (uint64_t)code[i]) << 16) | local;
 }
 
-__global__ void k_panel_stream(const uint64_t *sorted_key, const int32_t *perm, const uint16_t *code,
-                               int64_t nnz, int32_t panel_rows, int64_t n_seg, uint32_t *stream, int32_t *ptr)
+// segment starts in key order + end of every segment's code-0 run
+__global__ void k_seg_bounds(const uint64_t *sorted_key, int64_t nnz, int64_t n_seg, int32_t *start, int32_t *end_a)
 {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= nnz) return;
     const uint64_t k = sorted_key[i];
-    const int64_t seg = (int64_t)(k / (uint64_t)panel_rows);
-    stream[i] = ((uint32_t)code[perm[i]] << 16) | (uint32_t)(k % (uint64_t)panel_rows);
-    // segment pointers: every segment in (previous segment, this one] starts here
-    const int64_t prev = i == 0 ? -1 : (int64_t)(sorted_key[i - 1] / (uint64_t)panel_rows);
-    for (int64_t s = prev + 1; s <= seg; ++s) ptr[s] = (int32_t)i;
+    const int64_t seg = (int64_t)(k >> 32);
+    const int64_t prev = i == 0 ? -1 : (int64_t)(sorted_key[i - 1] >> 32);
+    for (int64_t s = prev + 1; s <= seg; ++s) start[s] = (int32_t)i;
     if (i == nnz - 1)
-        for (int64_t s = seg + 1; s <= n_seg; ++s) ptr[s] = (int32_t)nnz;
+        for (int64_t s = seg + 1; s <= n_seg; ++s) start[s] = (int32_t)nnz;
+    if (((k >> 16) & 0xffffu) == 0) {
+        const bool last = (i == nnz - 1) || ((sorted_key[i + 1] >> 16) != (k >> 16));
+        if (last) end_a[seg] = (int32_t)(i + 1);
+    }
 }
 
-static int build_stream(arb_ctx *ctx, const int32_t *row, const int32_t *col, int32_t n_rows,
-                        int32_t n_cols, int32_t panel_rows, int np, DevBuf &ptr, DevBuf &stream)
+__global__ void k_seg_keys(const int32_t *start, const int32_t *end_a, int64_t n_seg, int32_t n_rows,
+                           uint64_t *key, int32_t *val)
+{
+    int64_t s = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (s >= n_seg) return;
+    const int32_t len = start[s + 1] - start[s];
+    const int32_t la = end_a[s] ? end_a[s] - start[s] : 0, lb = len - la;
+    const uint64_t panel = (uint64_t)(s / n_rows);
+    key[s] = (panel << 40) | ((uint64_t)(0xFFFFF - min(la, 0xFFFFF)) << 20) | (uint64_t)(0xFFFFF - min(lb, 0xFFFFF));
+    val[s] = (int32_t)s;
+}
+
+__global__ void k_seg_place(const int32_t *order, const int32_t *start, const int32_t *end_a, int64_t n_seg,
+                            int32_t n_rows, int32_t *new_len, int32_t *len_a, int32_t *pos_of_seg, int32_t *row_id)
+{
+    int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (p > n_seg) return;
+    if (p == n_seg) { new_len[p] = 0; return; }
+    const int32_t s = order[p];
+    new_len[p] = start[s + 1] - start[s];
+    len_a[p] = end_a[s] ? end_a[s] - start[s] : 0;
+    pos_of_seg[s] = (int32_t)p;
+    row_id[p] = s % n_rows;
+}
+
+__global__ void k_seg_mid(const int32_t *new_start, const int32_t *len_a, int64_t n_seg, int32_t *mid)
+{
+    int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (p < n_seg) mid[p] = new_start[p] + len_a[p];
+}
+
+__global__ void k_panel_scatter(const uint64_t *sorted_key, int64_t nnz, const int32_t *start,
+                                const int32_t *pos_of_seg, const int32_t *new_start, int32_t row_bytes,
+                                uint32_t *stream)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= nnz) return;
+    const uint64_t k = sorted_key[i];
+    const int64_t seg = (int64_t)(k >> 32);
+    const uint32_t code = (uint32_t)((k >> 16) & 0xffffu), local = (uint32_t)(k & 0xffffu);
+    const int64_t dest = (int64_t)new_start[pos_of_seg[seg]] + (i - (int64_t)start[seg]);
+    stream[dest] = code == 0 ? local * (uint32_t)row_bytes : ((code << 16) | local);
+}
+
+static int build_stream(arb_ctx *ctx, const int32_t *row, const int32_t *col, int32_t n_rows, int32_t panel_rows,
+                        int np, int kp, DevBuf &ptr, DevBuf &mid, DevBuf &row_id, DevBuf &stream)
 {
     const int64_t nnz = ctx->nnz, n_seg = (int64_t)np * n_rows;
-    ARB_REQUIRE(n_seg + 1 < (int64_t)INT_MAX, ARB_ERR_UNSUPPORTED, "layout: %lld segments", (long long)n_seg);
-    DevBuf k_in, k_out, v_in, v_out;
+    ARB_REQUIRE(n_seg + 1 < (int64_t)(1 << 30), ARB_ERR_UNSUPPORTED, "layout: %lld segments", (long long)n_seg);
+    DevBuf k_in, k_out, v_in, start, end_a, sk_in, sk_out, sv_in, order, new_len, len_a, pos_of_seg;
     ARB_TRY(k_in.reserve(nnz * 8));
     ARB_TRY(k_out.reserve(nnz * 8));
-    ARB_TRY(v_in.reserve(nnz * 4));
-    ARB_TRY(v_out.reserve(nnz * 4));
+    for (DevBuf *b : {&start, &end_a, &sv_in, &order, &new_len, &len_a, &pos_of_seg}) ARB_TRY(b->reserve((n_seg + 1) * 4));
+    ARB_TRY(sk_in.reserve(n_seg * 8));
+    ARB_TRY(sk_out.reserve(n_seg * 8));
     ARB_TRY(ptr.reserve((n_seg + 1) * 4));
-    ARB_TRY(stream.reserve(nnz * 4));
+    ARB_TRY(mid.reserve((n_seg + 1) * 4));
+    ARB_TRY(row_id.reserve((n_seg + 1) * 4));
+    ARB_TRY(stream.reserve(nnz * 4 + 256));
     cudaStream_t st = ctx->stream;
     const int B = 256;
-    k_panel_keys<<<grid_for(nnz, B), B, 0, st>>>(row, col, nnz, n_rows, panel_rows, k_in.as<uint64_t>());
-    k_iota<<<grid_for(nnz, B), B, 0, st>>>(v_in.as<int32_t>(), nnz);
-    const int end_bit = bits_for((uint64_t)n_seg * (uint64_t)panel_rows);
-    int rc = with_cub(ctx, [&](void *tmp, size_t &bytes) {
-        return cub::DeviceRadixSort::SortPairs(tmp, bytes, k_in.as<uint64_t>(), k_out.as<uint64_t>(),
-                                               v_in.as<int32_t>(), v_out.as<int32_t>(), nnz, 0, end_bit, st);
-    });
-    if (rc == ARB_OK) {
-        k_panel_stream<<<grid_for(nnz, B), B, 0, st>>>(k_out.as<uint64_t>(), v_out.as<int32_t>(),
-                                                       ctx->coo_code.as<uint16_t>(), nnz, panel_rows, n_seg,
-                                                       stream.as<uint32_t>(), ptr.as<int32_t>());
-        cudaError_t e = cudaStreamSynchronize(st);
-        if (e != cudaSuccess) {
-            arb_set_error("layout build: %s", cudaGetErrorString(e));
-            rc = ARB_ERR_CUDA;
-        }
-    }
-    k_in.release(); k_out.release(); v_in.release(); v_out.release();
-    (void)n_cols;
-    return rc;
+    k_panel_keys<<<grid_for(nnz, B), B, 0, st>>>(row, col, ctx->coo_code.as<uint16_t>(), nnz, n_rows, panel_rows,
+                                                 k_in.as<uint64_t>());
+    const int end_bit = std::min(64, 32 + bits_for((uint64_t)n_seg));
+    ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
+        return cub::DeviceRadixSort::SortKeys(tmp, bytes, k_in.as<uint64_t>(), k_out.as<uint64_t>(), nnz, 0, end_bit, st);
+    }));
+    ARB_CUDA(cudaMemsetAsync(end_a.p, 0, (n_seg + 1) * 4, st));
+    k_seg_bounds<<<grid_for(nnz, B), B, 0, st>>>(k_out.as<uint64_t>(), nnz, n_seg, start.as<int32_t>(),
+                                                 end_a.as<int32_t>());
+    k_seg_keys<<<grid_for(n_seg, B), B, 0, st>>>(start.as<int32_t>(), end_a.as<int32_t>(), n_seg, n_rows,
+                                                 sk_in.as<uint64_t>(), sv_in.as<int32_t>());
+    ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
+        return cub::DeviceRadixSort::SortPairs(tmp, bytes, sk_in.as<uint64_t>(), sk_out.as<uint64_t>(),
+                                               sv_in.as<int32_t>(), order.as<int32_t>(), n_seg, 0, 64, st);
+    }));
+    k_seg_place<<<grid_for(n_seg + 1, B), B, 0, st>>>(order.as<int32_t>(), start.as<int32_t>(), end_a.as<int32_t>(),
+                                                      n_seg, n_rows, new_len.as<int32_t>(), len_a.as<int32_t>(),
+                                                      pos_of_seg.as<int32_t>(), row_id.as<int32_t>());
+    ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
+        return cub::DeviceScan::ExclusiveSum(tmp, bytes, new_len.as<int32_t>(), ptr.as<int32_t>(), n_seg + 1, st);
+    }));
+    k_seg_mid<<<grid_for(n_seg, B), B, 0, st>>>(ptr.as<int32_t>(), len_a.as<int32_t>(), n_seg, mid.as<int32_t>());
+    ARB_CUDA(cudaMemsetAsync(stream.p, 0, nnz * 4 + 256, st));
+    k_panel_scatter<<<grid_for(nnz, B), B, 0, st>>>(k_out.as<uint64_t>(), nnz, start.as<int32_t>(),
+                                                    pos_of_seg.as<int32_t>(), ptr.as<int32_t>(), kp * 8,
+                                                    stream.as<uint32_t>());
+    ARB_CUDA(cudaStreamSynchronize(st));
+    for (DevBuf *b : {&k_in, &k_out, &v_in, &start, &end_a, &sk_in, &sk_out, &sv_in, &order, &new_len, &len_a, &pos_of_seg})
+        b->release();
+    return ARB_OK;
 }
 
 // smem budget of the sweep kernel: [panel_rows][KP] doubles + pair table + one mbarrier
@@ -412,10 +477,10 @@ int arb_build_layout(arb_ctx *ctx, int kp)
     L.panel_rows = panel_rows;
     L.np_z = (ctx->n_snvs + panel_rows - 1) / panel_rows;
     L.np_y = (ctx->n_cells + panel_rows - 1) / panel_rows;
-    ARB_TRY(build_stream(ctx, ctx->coo_cell.as<int32_t>(), ctx->coo_snv.as<int32_t>(), ctx->n_cells,
-                         ctx->n_snvs, panel_rows, L.np_z, L.zptr, L.zstream));
-    ARB_TRY(build_stream(ctx, ctx->coo_snv.as<int32_t>(), ctx->coo_cell.as<int32_t>(), ctx->n_snvs,
-                         ctx->n_cells, panel_rows, L.np_y, L.yptr, L.ystream));
+    ARB_TRY(build_stream(ctx, ctx->coo_cell.as<int32_t>(), ctx->coo_snv.as<int32_t>(), ctx->n_cells, panel_rows,
+                         L.np_z, kp, L.zptr, L.zmid, L.zrow, L.zstream));
+    ARB_TRY(build_stream(ctx, ctx->coo_snv.as<int32_t>(), ctx->coo_cell.as<int32_t>(), ctx->n_snvs, panel_rows,
+                         L.np_y, kp, L.yptr, L.ymid, L.yrow, L.ystream));
     L.kp = kp;
     return ARB_OK;
 }
@@ -448,8 +513,8 @@ int arb_refresh_tables(arb_ctx *ctx)
     // factors 1 + d*x lie in [min(1,e^w), max(1,e^w)]: renormalise the running product often
     // enough that it cannot leave the double range (|log2| < 900 between renormalisations)
     const double max_log2 = max_abs_w / 0.6931471805599453;
-    int every = max_log2 > 0 ? (int)floor(900.0 / max_log2) : 16;
-    ctx->renorm_every = std::max(1, std::min(every, 16));
+    int every = max_log2 > 0 ? (int)floor(800.0 / max_log2) : 16;
+    ctx->renorm_every = std::max(1, std::min(every, 16));    // < 8 selects the renormalise-every-factor kernels
     return ARB_OK;
 }
 

@@ -42,19 +42,19 @@ WORKER = textwrap.dedent("""
         assert (qz == idx).all() and (qy == -idx).all() and qz.shape == (4, 3)
     dist.barrier()
     dist.destroy_process_group()
-    print("rank", rank, "ok")
+    open(os.path.join(os.environ["ARB_OUT"], "rank%d.ok" % rank), "w").write("ok")
 """)
 
 
 def test_gloo_world_size_2(tmp_path):
     script = tmp_path / "worker.py"
     script.write_text(WORKER)
-    env = dict(os.environ, ARB_ROOT=ROOT, OMP_NUM_THREADS="1")
+    env = dict(os.environ, ARB_ROOT=ROOT, ARB_OUT=str(tmp_path), OMP_NUM_THREADS="1")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
            "--master-addr", "127.0.0.1", "--master-port", "29533", str(script)]
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=240)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-3000:]
-    assert "rank 0 ok" in res.stdout and "rank 1 ok" in res.stdout
+    assert (tmp_path / "rank0.ok").exists() and (tmp_path / "rank1.ok").exists()
 
 
 def test_single_process_defaults():

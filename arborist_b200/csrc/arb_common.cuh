@@ -66,20 +66,26 @@ struct DevBuf {
     template <class T> T *as() const { return reinterpret_cast<T *>(p); }
 };
 
+#define ARB_SWEEP_WARPS 16    // warps per sweep CTA; the layouts are dealt out to this many warps
+
 // Panelled sparse layout for one padded clone width KP (8, 16 or 32 doubles per row of
 // the gathered operand).  "z": cell-major rows, SNVs cut into panels (q(z) sweep);
-// "y": SNV-major rows, cells cut into panels (q(y) sweep).  Segment p (position inside the
-// panel-major, length-sorted order) spans stream[ptr[p] .. ptr[p+1]); its code-0 run ends
-// at mid[p]; row[p] is the row it belongs to.  See arb_ingest.cu "panel layouts".
+// "y": SNV-major rows, cells cut into panels (q(y) sweep).  Tile slot
+// x = (panel * ARB_SWEEP_WARPS + warp) * tiles_per_warp + u: desc[x] = {first quad, quads in
+// the A region, quads in total, 0}; rows[x * TW + g] = row of the tile's g-th segment or -1;
+// stream = uint4 [quad][TW].  See arb_ingest.cu "panel layouts".
 struct PanelLayout {
     int kp = 0;
-    int panel_rows = 0;      // rows of the gathered operand per panel (<= 65536)
+    int panel_rows = 0;      // rows of the gathered operand per panel
     int np_z = 0, np_y = 0;  // number of panels
-    DevBuf zptr, zmid, zrow, zstream;    // int32 [np_z * n_cells + 1] x3, uint32 [nnz]
-    DevBuf yptr, ymid, yrow, ystream;    // int32 [np_y * n_snvs + 1] x3, uint32 [nnz]
+    int uz = 0, uy = 0;      // tiles per warp per panel
+    int fold_z = 0, fold_y = 0;   // 1: a tile's running product provably stays inside the double range
+    int64_t quads_z = 0, quads_y = 0;   // stream length in quads (x TW x 16 bytes)
+    DevBuf zdesc, zrows, zstream;
+    DevBuf ydesc, yrows, ystream;
     void release()
     {
-        for (DevBuf *b : {&zptr, &zmid, &zrow, &zstream, &yptr, &ymid, &yrow, &ystream}) b->release();
+        for (DevBuf *b : {&zdesc, &zrows, &zstream, &ydesc, &yrows, &ystream}) b->release();
         kp = 0;
     }
 };
@@ -88,7 +94,7 @@ struct FitStats {
     int64_t launches = 0;
     double device_ms = 0, tree_iterations = 0, sweep_ms = 0;
     // per-kernel profile of the last fit (CUDA events on the launching stream)
-    double sweep_z_ms = 0, sweep_y_ms = 0, finish_ms = 0;
+    double sweep_z_ms = 0, sweep_y_ms = 0, finish_ms = 0, finish_z_ms = 0, finish_y_ms = 0;
     double tree_sweeps_z = 0, tree_sweeps_y = 0, launches_z = 0, launches_y = 0, rounds = 0;
 };
 
@@ -118,7 +124,7 @@ struct arb_ctx {
 
     // ---- layouts (index 0: KP 8, 1: KP 16, 2: KP 32) ----------------------------------
     PanelLayout layout[3];
-    int64_t opt_slots = 0, opt_panel_kb = 0, opt_threads = 0;
+    int64_t opt_slots = 0, opt_panel_kb = 0, opt_threads = 0, opt_no_fold = 0;
 
     // ---- fit workspace -----------------------------------------------------------------
     int ws_kp = 0, ws_slots = 0, ws_k = 0;

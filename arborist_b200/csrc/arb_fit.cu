@@ -33,7 +33,7 @@
 int arb_sweep_table_entries(const arb_ctx *ctx);
 int arb_check_table_range(arb_ctx *ctx);
 
-#define SWEEP_THREADS 512
+#define SWEEP_THREADS (ARB_SWEEP_WARPS * 32)
 #define FIN_THREADS 256
 #define FIN_ROWS 256          // rows of q per finishing CTA (fixed: the ELBO reduction order depends on it)
 #define MASK_STRIDE 64        // per tree: 32 column masks (over clusters) + 32 row masks (over clones)
@@ -199,25 +199,25 @@ struct SweepArgs {
     const double *x;           // gathered operand [slot][n_gather][KP]
     int64_t x_slot_stride;     // doubles
     int32_t n_gather;          // rows of the gathered operand
-    const int32_t *seg_ptr;    // [n_panels * n_rows + 1] segment starts (length-sorted positions)
-    const int32_t *seg_mid;    //                          end of the segment's code-0 run
-    const int32_t *seg_row;    //                          row the segment belongs to
-    const uint32_t *stream;    // A run: byte offset of the gathered row; B run: code << 16 | index
-    int32_t n_rows, panel_rows, n_panels;
+    const int4 *desc;          // [n_panels * WARPS * tiles_per_warp] {first quad, A quads, all quads, 0}
+    const int32_t *rows;       // [.. * TW] row of every segment of every tile, -1 = none
+    const uint4 *stream;       // [quad][TW]
+    int32_t n_rows, panel_rows, n_panels, tiles_per_warp;
     const int32_t *slot_list;
     int32_t n_active;
     const double2 *dw;         // per pair code: (d, w)
-    int32_t n_pairs, tab_n, renorm_every;
-    double *out_m;             // [slot][panel][row][KP] mantissa of the running product
-    int32_t *out_e;            //                        its exponent
+    int32_t n_pairs, tab_n, renorm_quads;   // not FOLD: renormalise every this many quads, 0 = after every factor
+    int32_t ks;                // columns kept per row of the partials (K or C rounded up to 4)
+    double *out_m;             // [slot][panel][row][ks] the segment's product (FOLD) or its mantissa
+    int32_t *out_e;            //                        exponent (not FOLD)
     double *out_g;             //                        sum_k w_k x (q(z) sweep only)
 };
 
 // Four clones of one nonzero: two LDS.128 from the staged panel, 4 x (DFMA + DMUL) for the
 // running products and 4 x DFMA for the likelihood accumulators.
-template <bool WITH_G, bool EACH>
+template <bool WITH_G>
 __device__ __forceinline__ void sweep_step(const char *xa_base, const char *xb_base, uint32_t off, double d, double w,
-                                           double (&p)[4], double (&g)[4], int (&e)[4])
+                                           double (&p)[4], double (&g)[4])
 {
     const double2 xa = *reinterpret_cast<const double2 *>(xa_base + off);
     const double2 xb = *reinterpret_cast<const double2 *>(xb_base + off);
@@ -231,21 +231,20 @@ __device__ __forceinline__ void sweep_step(const char *xa_base, const char *xb_b
         g[2] = fma(w, xb.x, g[2]);
         g[3] = fma(w, xb.y, g[3]);
     }
-    if (EACH) {
-#pragma unroll
-        for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
-    }
 }
 
-// One CTA = (tree slot, panel).  Groups of GL = KP/4 lanes walk the panel's segments; lane h of a
-// group owns clones 4h..4h+3 of the segment's row.  The two 16-byte halves a lane reads are
-// swizzled on bit 2 of the lane id so that the eight lanes of a quarter-warp cover all 32 banks.
-template <int KP, bool WITH_G, bool EACH>
-__global__ void __launch_bounds__(SWEEP_THREADS, 1) k_sweep(const SweepArgs a)
+// One CTA = (tree slot, panel); one warp = a run of tiles of that panel (see "panel layouts" in
+// arb_ingest.cu).  GL = KP/4 lanes share a segment, lane h of the group owns clones 4h..4h+3.  The
+// two 16-byte halves a lane reads are swizzled on bit 2 of the lane id so that the eight lanes of
+// a quarter-warp cover all 32 banks.  Every lane of a group loads the same uint4 of four stream
+// words (a warp reads TW*16 contiguous bytes per quad), three quads ahead of the one in use; there
+// are no shuffles, no predicates and no per-segment pointers in the loop.
+template <int KP, bool WITH_G, bool FOLD>
+__global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const SweepArgs a)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     double *xs = reinterpret_cast<double *>(smem_raw);
-    double2 *tab = reinterpret_cast<double2 *>(smem_raw + (size_t)a.panel_rows * KP * 8);
+    double2 *tab = reinterpret_cast<double2 *>(smem_raw + (size_t)(a.panel_rows + 1) * KP * 8);
     uint64_t *mbar = reinterpret_cast<uint64_t *>(tab + a.tab_n);
 
     const int panel = blockIdx.x / a.n_active;
@@ -271,111 +270,101 @@ __global__ void __launch_bounds__(SWEEP_THREADS, 1) k_sweep(const SweepArgs a)
                          ::"r"(dst + off), "l"(src + off), "r"(sz), "r"(bar) : "memory");
         }
     }
-    for (int c = threadIdx.x; c < a.tab_n; c += SWEEP_THREADS) tab[c] = a.dw[c];
+    for (int c = threadIdx.x; c < a.tab_n; c += ARB_SWEEP_WARPS * 32) tab[c] = a.dw[c];
+    if (threadIdx.x < KP) xs[(size_t)a.panel_rows * KP + threadIdx.x] = 0.0;      // the row NULL words point at
     const double2 dw0 = __ldg(a.dw);
-    const double2 dw1 = a.n_pairs > 1 ? __ldg(a.dw + 1) : make_double2(0.0, 0.0);
+
+    constexpr int GL = KP / 4;                     // lanes per segment; each lane owns four clones
+    constexpr int TW = 32 / GL;                    // segments per tile
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int h = lane % GL, grp = lane / GL;
+    const int swz = (lane >> 2) & 1;
+    const int off_a = 4 * h + 2 * swz, off_b = 4 * h + 2 * (1 - swz);       // columns (doubles)
+    const char *xa_base = reinterpret_cast<const char *>(xs + off_a);
+    const char *xb_base = reinterpret_cast<const char *>(xs + off_b);
+    const int U = a.tiles_per_warp;
+    const int64_t x0 = ((int64_t)panel * ARB_SWEEP_WARPS + warp) * U;
+    const int4 *__restrict__ desc = a.desc + x0;
+    const int32_t *__restrict__ rows = a.rows + x0 * TW + grp;
+    const int64_t out0 = ((int64_t)slot * a.n_panels + panel) * a.n_rows;
+    const bool small_tab = a.n_pairs <= a.tab_n;
+    const bool keep = 4 * h < a.ks;
+    const bool each = a.renorm_quads == 0;
+
+    // start the stream before waiting for the panel
+    int4 dn = __ldg(desc);
+    int rown = __ldg(rows);
+    const uint4 *__restrict__ sp = a.stream + (int64_t)dn.x * TW + grp;
+    uint4 w0 = __ldg(sp), w1 = __ldg(sp + TW), w2 = __ldg(sp + 2 * TW);
+    sp += 3 * TW;
+
     __syncthreads();
     asm volatile("{\n\t.reg .pred p;\n\tWAIT_PANEL:\n\t"
                  "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n\t"
                  "@p bra DONE_PANEL;\n\tbra WAIT_PANEL;\n\tDONE_PANEL:\n\t}" ::"r"(bar) : "memory");
 
-    constexpr int GL = KP / 4;                     // lanes per segment; each lane owns four clones
-    constexpr int NG = SWEEP_THREADS / GL;
-    constexpr uint32_t ROW_BYTES = KP * 8;
-    const int lane = threadIdx.x & 31;
-    const int h = threadIdx.x % GL, gid = threadIdx.x / GL;
-    const int swz = (lane >> 2) & 1;
-    const int off_a = 4 * h + 2 * swz, off_b = 4 * h + 2 * (1 - swz);       // columns (doubles)
-    const char *xa_base = reinterpret_cast<const char *>(xs + off_a);
-    const char *xb_base = reinterpret_cast<const char *>(xs + off_b);
-    const int64_t seg0 = (int64_t)panel * a.n_rows;
-    const int64_t out0 = ((int64_t)slot * a.n_panels + panel) * a.n_rows;
-    const int renorm_every = a.renorm_every;
-    const uint32_t *__restrict__ stream = a.stream;
-
-    for (int pos0 = 0; pos0 < a.n_rows; pos0 += NG) {          // warp-uniform trip count
-        const int pos = pos0 + gid;
-        const bool live = pos < a.n_rows;
-        const int k0 = live ? __ldg(a.seg_ptr + seg0 + pos) : 0, km = live ? __ldg(a.seg_mid + seg0 + pos) : 0;
-        const int k1 = live ? __ldg(a.seg_ptr + seg0 + pos + 1) : 0, row = live ? __ldg(a.seg_row + seg0 + pos) : 0;
+    for (int u = 0; u < U; ++u) {
+        const int4 dc = dn;
+        const int row = rown;
+        if (u + 1 < U) {
+            dn = __ldg(desc + u + 1);
+            rown = __ldg(rows + (int64_t)(u + 1) * TW);
+        }
         double p[4] = {1.0, 1.0, 1.0, 1.0}, g[4] = {0.0, 0.0, 0.0, 0.0};
-        int e[4] = {0, 0, 0, 0}, since = 0;
-
-        // Both runs are walked in chunks of GL words (one per lane, broadcast with shuffles).  The
-        // trip counts are made warp-uniform (max over the warp's groups; the layout sorts segments
-        // by shape, so max == min almost always) and shuffles use the full mask: no divergence.
-        // ---- A run: the most frequent (alt,total) pair; d and w live in registers -----------------
-        {
-            const int n_a = km - k0;
-            const int n_max = __reduce_max_sync(0xffffffffu, n_a), n_min = __reduce_min_sync(0xffffffffu, n_a);
-            uint32_t wn = (h < n_a) ? __ldg(stream + k0 + h) : 0u;
-            for (int c = 0; c < n_max; c += GL) {
-                const uint32_t wc = wn;
-                wn = (c + GL + h < n_a) ? __ldg(stream + k0 + c + GL + h) : 0u;
-                if (c + GL <= n_min) {
-#pragma unroll
-                    for (int s = 0; s < GL; ++s) {
-                        const uint32_t off = __shfl_sync(0xffffffffu, wc, s, GL);
-                        sweep_step<WITH_G, EACH>(xa_base, xb_base, off, dw0.x, dw0.y, p, g, e);
-                    }
-                } else {
-                    const int left = n_a - c;
-#pragma unroll
-                    for (int s = 0; s < GL; ++s) {
-                        const uint32_t off = __shfl_sync(0xffffffffu, wc, s, GL);
-                        if (s < left) sweep_step<WITH_G, EACH>(xa_base, xb_base, off, dw0.x, dw0.y, p, g, e);
-                    }
-                }
-                if (!EACH) {
-                    since += GL;
-                    if (since + GL > renorm_every) {
-                        since = 0;
-#pragma unroll
-                        for (int q = 0; q < 4; ++q) renorm(p[q], e[q]);
-                    }
-                }
+        int e[4] = {0, 0, 0, 0};
+        int q = 0, since = 0;
+        // ---- A region: the most frequent (alt,total) pair; d and w live in registers ------------
+        for (; q < dc.y; ++q) {
+            const uint4 w = w0;
+            w0 = w1;
+            w1 = w2;
+            w2 = __ldg(sp);
+            sp += TW;
+            sweep_step<WITH_G>(xa_base, xb_base, w.x, dw0.x, dw0.y, p, g);
+            if (!FOLD && each) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
+            sweep_step<WITH_G>(xa_base, xb_base, w.y, dw0.x, dw0.y, p, g);
+            if (!FOLD && each) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
+            sweep_step<WITH_G>(xa_base, xb_base, w.z, dw0.x, dw0.y, p, g);
+            if (!FOLD && each) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
+            sweep_step<WITH_G>(xa_base, xb_base, w.w, dw0.x, dw0.y, p, g);
+            if (!FOLD && ++since >= a.renorm_quads) {
+                since = 0;
+                for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
             }
         }
-        // ---- B run: every other pair, ordered by code; code 1 from registers, the rest from the table
-        {
-            const int n_b = k1 - km;
-            const int n_max = __reduce_max_sync(0xffffffffu, n_b);
-            uint32_t wn = (h < n_b) ? __ldg(stream + km + h) : 0u;
-            for (int c = 0; c < n_max; c += GL) {
-                const uint32_t wc = wn;
-                wn = (c + GL + h < n_b) ? __ldg(stream + km + c + GL + h) : 0u;
-                const int left = n_b - c;
+        // ---- G region: any pair; (d, w) from the table in shared memory ---------------------------
+        for (; q < dc.z; ++q) {
+            const uint4 w = w0;
+            w0 = w1;
+            w1 = w2;
+            w2 = __ldg(sp);
+            sp += TW;
+            const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
-                for (int s = 0; s < GL; ++s) {
-                    const uint32_t word = __shfl_sync(0xffffffffu, wc, s, GL);
-                    if (s < left) {
-                        const uint32_t code = word >> 16, off = (word & 0xffffu) * ROW_BYTES;
-                        double2 dw = dw1;
-                        if (code != 1u) dw = (code < (uint32_t)a.tab_n) ? tab[code] : __ldg(a.dw + code);
-                        sweep_step<WITH_G, EACH>(xa_base, xb_base, off, dw.x, dw.y, p, g, e);
-                    }
-                }
-                if (!EACH) {
-                    since += GL;
-                    if (since + GL > renorm_every) {
-                        since = 0;
-#pragma unroll
-                        for (int q = 0; q < 4; ++q) renorm(p[q], e[q]);
-                    }
-                }
+            for (int s = 0; s < 4; ++s) {
+                const uint32_t code = ww[s] >> 18, off = ww[s] & 0x3ffffu;
+                const double2 dw = (small_tab || code < (uint32_t)a.tab_n) ? tab[code] : __ldg(a.dw + code);
+                sweep_step<WITH_G>(xa_base, xb_base, off, dw.x, dw.y, p, g);
+                if (!FOLD && each) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
+            }
+            if (!FOLD && ++since >= a.renorm_quads) {
+                since = 0;
+                for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
             }
         }
-#pragma unroll
-        for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
-        if (!live) continue;
-        const int64_t o = (out0 + row) * KP;
-        *reinterpret_cast<double2 *>(a.out_m + o + off_a) = make_double2(p[0], p[1]);
-        *reinterpret_cast<double2 *>(a.out_m + o + off_b) = make_double2(p[2], p[3]);
-        *reinterpret_cast<int2 *>(a.out_e + o + off_a) = make_int2(e[0], e[1]);
-        *reinterpret_cast<int2 *>(a.out_e + o + off_b) = make_int2(e[2], e[3]);
-        if (WITH_G) {
-            *reinterpret_cast<double2 *>(a.out_g + o + off_a) = make_double2(g[0], g[1]);
-            *reinterpret_cast<double2 *>(a.out_g + o + off_b) = make_double2(g[2], g[3]);
+        if (!FOLD) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
+        if (row >= 0 && keep) {
+            const int64_t o = (out0 + row) * a.ks;
+            *reinterpret_cast<double2 *>(a.out_m + o + off_a) = make_double2(p[0], p[1]);
+            *reinterpret_cast<double2 *>(a.out_m + o + off_b) = make_double2(p[2], p[3]);
+            if (!FOLD) {
+                *reinterpret_cast<int2 *>(a.out_e + o + off_a) = make_int2(e[0], e[1]);
+                *reinterpret_cast<int2 *>(a.out_e + o + off_b) = make_int2(e[2], e[3]);
+            }
+            if (WITH_G) {
+                *reinterpret_cast<double2 *>(a.out_g + o + off_a) = make_double2(g[0], g[1]);
+                *reinterpret_cast<double2 *>(a.out_g + o + off_b) = make_double2(g[2], g[3]);
+            }
         }
     }
 }
@@ -388,6 +377,7 @@ struct FinishArgs {
     const int32_t *part_e;
     const double *part_g;
     int32_t n_panels, n_rows, K;
+    int32_t ks;                     // columns per row of the partials
     const int32_t *slot_list;
     const SlotState *st;
     const uint32_t *masks;
@@ -414,13 +404,13 @@ template <int KP> __global__ void __launch_bounds__(FIN_THREADS) k_finish_z(cons
         const bool live = i < a.n_rows;          // uniform per group
         double prod = 1.0, gsum = 0.0;
         int esum = 0;
-        if (live) {
+        if (live && lane < a.ks) {
             for (int p = 0; p < a.n_panels; ++p) {
-                const int64_t o = (((int64_t)slot * a.n_panels + p) * a.n_rows + i) * KP + lane;
-                prod *= a.part_m[o];
-                esum += a.part_e[o];
+                const int64_t o = (((int64_t)slot * a.n_panels + p) * a.n_rows + i) * a.ks + lane;
+                prod *= a.part_m[o];          // prod in [1,2), the partial inside 2^+-1000 (range-proven layout) or in [1,2)
+                if (a.part_e) esum += a.part_e[o];
                 gsum += a.part_g[o];
-                if ((p & 255) == 255) renorm(prod, esum);
+                renorm(prod, esum);
             }
         }
         double logit = (lane < K) ? log(prod) + (double)esum * LN2 : -INFINITY;
@@ -463,12 +453,12 @@ template <int KP> __global__ void __launch_bounds__(FIN_THREADS) k_finish_y(cons
         const bool live = j < a.n_rows;
         double prod = 1.0;
         int esum = 0;
-        if (live) {
+        if (live && lane < a.ks) {
             for (int p = 0; p < a.n_panels; ++p) {
-                const int64_t o = (((int64_t)slot * a.n_panels + p) * a.n_rows + j) * KP + lane;
+                const int64_t o = (((int64_t)slot * a.n_panels + p) * a.n_rows + j) * a.ks + lane;
                 prod *= a.part_m[o];
-                esum += a.part_e[o];
-                if ((p & 255) == 255) renorm(prod, esum);
+                if (a.part_e) esum += a.part_e[o];
+                renorm(prod, esum);
             }
         }
         const bool col = live && lane < C;
@@ -641,8 +631,10 @@ struct FitTarget {                 // where a fit's per-tree results go (all dev
 
 static size_t sweep_smem_bytes(const arb_ctx *ctx, const PanelLayout &L)
 {
-    return (size_t)L.panel_rows * L.kp * 8 + (size_t)arb_sweep_table_entries(ctx) * 16 + 16;
+    return (size_t)(L.panel_rows + 1) * L.kp * 8 + (size_t)arb_sweep_table_entries(ctx) * 16 + 16;
 }
+
+static inline int ks_for(int cols) { return (cols + 3) / 4 * 4; }
 
 template <int KP> static int configure_kernels(const arb_ctx *ctx, const PanelLayout &L)
 {
@@ -663,8 +655,9 @@ static int64_t per_slot_bytes(const arb_ctx *ctx, const PanelLayout &L, int K)
 {
     const int64_t n = ctx->n_cells, m = ctx->n_snvs, kp = L.kp, C = K - 1;
     const int64_t nb = std::max((n + FIN_ROWS - 1) / FIN_ROWS, (m + FIN_ROWS - 1) / FIN_ROWS);
-    return (m * kp + n * kp + n * K + m * C) * 8 + (int64_t)L.np_z * n * kp * 20 + (int64_t)L.np_y * m * kp * 12 +
-           3 * nb * 8 + 64;
+    const int64_t ez = L.fold_z ? 0 : 4, ey = L.fold_y ? 0 : 4;
+    return (m * kp + n * kp + n * K + m * C) * 8 + (int64_t)L.np_z * n * ks_for(K) * (16 + ez) +
+           (int64_t)L.np_y * m * ks_for(C) * (8 + ey) + 3 * nb * 8 + 64;
 }
 
 static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve_bytes, Workspace &ws)
@@ -699,9 +692,10 @@ static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve
         ARB_TRY(ctx->xr.reserve(S * n * kp * 8));
         ARB_TRY(ctx->qz_cur.reserve(S * n * K * 8));
         ARB_TRY(ctx->qy_cur.reserve(S * m * C * 8));
-        ARB_TRY(ctx->part_z.reserve(S * L.np_z * n * kp * 12));      // mantissa (8) + exponent (4)
-        ARB_TRY(ctx->part_g.reserve(S * L.np_z * n * kp * 8));
-        ARB_TRY(ctx->part_y.reserve(S * L.np_y * m * kp * 12));
+        // product (8) [+ exponent (4) when the layout could not prove the range]
+        ARB_TRY(ctx->part_z.reserve(S * L.np_z * n * ks_for(K) * (L.fold_z ? 8 : 12) + 64));
+        ARB_TRY(ctx->part_g.reserve(S * L.np_z * n * ks_for(K) * 8 + 64));
+        ARB_TRY(ctx->part_y.reserve(S * L.np_y * m * ks_for(C) * (L.fold_y ? 8 : 12) + 64));
         ARB_TRY(ctx->red.reserve(S * 3 * ws.nbmax * 8));
         ARB_TRY(ctx->slot_state.reserve(S * sizeof(SlotState) + sizeof(Control) + 64));
         ARB_TRY(ctx->lists.reserve(S * 4 * 4 + 64));
@@ -723,6 +717,7 @@ struct WsPtrs {
 
 static WsPtrs ws_ptrs(arb_ctx *ctx, const PanelLayout &L)
 {
+    const int K = ctx->ws_k, C = K - 1;
     WsPtrs w;
     const int64_t S = ctx->ws_slots;
     w.st = ctx->slot_state.as<SlotState>();
@@ -732,9 +727,9 @@ static WsPtrs ws_ptrs(arb_ctx *ctx, const PanelLayout &L)
     w.list_init = w.list_z + S;
     w.snap_tree = w.list_init + S;
     w.pz_m = ctx->part_z.as<double>();
-    w.pz_e = reinterpret_cast<int32_t *>(w.pz_m + S * L.np_z * ctx->n_cells * L.kp);
+    w.pz_e = L.fold_z ? nullptr : reinterpret_cast<int32_t *>(w.pz_m + S * L.np_z * ctx->n_cells * ks_for(K));
     w.py_m = ctx->part_y.as<double>();
-    w.py_e = reinterpret_cast<int32_t *>(w.py_m + S * L.np_y * ctx->n_snvs * L.kp);
+    w.py_e = L.fold_y ? nullptr : reinterpret_cast<int32_t *>(w.py_m + S * L.np_y * ctx->n_snvs * ks_for(C));
     return w;
 }
 
@@ -745,23 +740,24 @@ static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.x = ctx->xs.as<double>();
     a.x_slot_stride = (int64_t)ctx->n_snvs * KP;
     a.n_gather = ctx->n_snvs;
-    a.seg_ptr = L.zptr.as<int32_t>();
-    a.seg_mid = L.zmid.as<int32_t>();
-    a.seg_row = L.zrow.as<int32_t>();
-    a.stream = L.zstream.as<uint32_t>();
+    a.desc = L.zdesc.as<int4>();
+    a.rows = L.zrows.as<int32_t>();
+    a.stream = L.zstream.as<uint4>();
     a.n_rows = ctx->n_cells;
     a.panel_rows = L.panel_rows;
     a.n_panels = L.np_z;
+    a.tiles_per_warp = L.uz;
+    a.ks = ks_for(ctx->ws_k);
     a.slot_list = list;
     a.n_active = n_active;
     a.dw = ctx->tab_dw.as<double2>();
     a.n_pairs = ctx->n_pairs;
     a.tab_n = arb_sweep_table_entries(ctx);
-    a.renorm_every = ctx->renorm_every;
+    a.renorm_quads = ctx->renorm_every / 4;
     a.out_m = w.pz_m;
     a.out_e = w.pz_e;
     a.out_g = ctx->part_g.as<double>();
-    if (ctx->renorm_every < 8)
+    if (L.fold_z)
         k_sweep<KP, true, true><<<n_active * L.np_z, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
     else
         k_sweep<KP, true, false><<<n_active * L.np_z, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
@@ -774,23 +770,24 @@ static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.x = ctx->xr.as<double>();
     a.x_slot_stride = (int64_t)ctx->n_cells * KP;
     a.n_gather = ctx->n_cells;
-    a.seg_ptr = L.yptr.as<int32_t>();
-    a.seg_mid = L.ymid.as<int32_t>();
-    a.seg_row = L.yrow.as<int32_t>();
-    a.stream = L.ystream.as<uint32_t>();
+    a.desc = L.ydesc.as<int4>();
+    a.rows = L.yrows.as<int32_t>();
+    a.stream = L.ystream.as<uint4>();
     a.n_rows = ctx->n_snvs;
     a.panel_rows = L.panel_rows;
     a.n_panels = L.np_y;
+    a.tiles_per_warp = L.uy;
+    a.ks = ks_for(ctx->ws_k - 1);
     a.slot_list = list;
     a.n_active = n_active;
     a.dw = ctx->tab_dw.as<double2>();
     a.n_pairs = ctx->n_pairs;
     a.tab_n = arb_sweep_table_entries(ctx);
-    a.renorm_every = ctx->renorm_every;
+    a.renorm_quads = ctx->renorm_every / 4;
     a.out_m = w.py_m;
     a.out_e = w.py_e;
     a.out_g = nullptr;
-    if (ctx->renorm_every < 8)
+    if (L.fold_y)
         k_sweep<KP, false, true><<<n_active * L.np_y, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
     else
         k_sweep<KP, false, false><<<n_active * L.np_y, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
@@ -807,6 +804,7 @@ static void launch_finish_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w,
     a.n_panels = L.np_z;
     a.n_rows = ctx->n_cells;
     a.K = ws.K;
+    a.ks = ks_for(ws.K);
     a.slot_list = list;
     a.st = w.st;
     a.masks = masks;
@@ -831,6 +829,7 @@ static void launch_finish_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w,
     a.n_panels = L.np_y;
     a.n_rows = ctx->n_snvs;
     a.K = ws.K;
+    a.ks = ks_for(ws.K - 1);
     a.slot_list = list;
     a.st = w.st;
     a.masks = masks;
@@ -894,11 +893,11 @@ static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, 
         float t = 0;
         if (pending_y) {
             cudaEventElapsedTime(&t, evs[0], evs[1]); stats.sweep_y_ms += t;
-            cudaEventElapsedTime(&t, evs[1], evs[2]); stats.finish_ms += t;
+            cudaEventElapsedTime(&t, evs[1], evs[2]); stats.finish_ms += t; stats.finish_y_ms += t;
         }
         if (pending_z) {
             cudaEventElapsedTime(&t, evs[3], evs[4]); stats.sweep_z_ms += t;
-            cudaEventElapsedTime(&t, evs[4], evs[5]); stats.finish_ms += t;
+            cudaEventElapsedTime(&t, evs[4], evs[5]); stats.finish_ms += t; stats.finish_z_ms += t;
         }
         pending_y = pending_z = false;
     };
@@ -1186,14 +1185,20 @@ ARB_API int arb_last_fit_stats(arb_ctx *ctx, int64_t *kernel_launches, double *d
     return ARB_OK;
 }
 
-// [sweep_z_ms, sweep_y_ms, finish_ms, tree_sweeps_z, tree_sweeps_y, launches_z, launches_y, rounds]
+// [sweep_z_ms, sweep_y_ms, finish_ms, tree_sweeps_z, tree_sweeps_y, launches_z, launches_y, rounds,
+//  finish_z_ms, finish_y_ms, KP, panel_rows, panels_z, panels_y, tiles_per_warp_z, tiles_per_warp_y,
+//  fold_z, fold_y, quads_z, quads_y]
 ARB_API int arb_last_fit_profile(arb_ctx *ctx, double *values, int32_t n_values)
 {
     ARB_REQUIRE(ctx && values && n_values >= 0, ARB_ERR_INVALID, "arb_last_fit_profile: bad argument");
     const FitStats &s = ctx->stats;
-    const double v[8] = {s.sweep_z_ms, s.sweep_y_ms, s.finish_ms, s.tree_sweeps_z, s.tree_sweeps_y,
-                         s.launches_z, s.launches_y, s.rounds};
-    for (int i = 0; i < n_values && i < 8; ++i) values[i] = v[i];
+    PanelLayout none;
+    const PanelLayout &L = ctx->ws_kp ? ctx->layout[kp_index(ctx->ws_kp)] : none;
+    const double v[20] = {s.sweep_z_ms, s.sweep_y_ms, s.finish_ms, s.tree_sweeps_z, s.tree_sweeps_y,
+                          s.launches_z, s.launches_y, s.rounds, s.finish_z_ms, s.finish_y_ms,
+                          (double)L.kp, (double)L.panel_rows, (double)L.np_z, (double)L.np_y, (double)L.uz,
+                          (double)L.uy, (double)L.fold_z, (double)L.fold_y, (double)L.quads_z, (double)L.quads_y};
+    for (int i = 0; i < n_values && i < 20; ++i) values[i] = v[i];
     return ARB_OK;
 }
 

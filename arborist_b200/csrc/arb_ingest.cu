@@ -115,6 +115,11 @@ ARB_API int arb_set_option(arb_ctx *ctx, const char *name, int64_t value)
         for (auto &l : ctx->layout) l.release();
         ctx->ws_kp = 0;                      // partial buffers are sized by the panel count
     } else if (!strcmp(name, "threads")) ctx->opt_threads = value;
+    else if (!strcmp(name, "no_fold")) {
+        ctx->opt_no_fold = value;
+        for (auto &l : ctx->layout) l.release();
+        ctx->ws_kp = 0;
+    }
     else {
         arb_set_error("arb_set_option: unknown option '%s'", name);
         return ARB_ERR_INVALID;
@@ -333,14 +338,22 @@ __global__ void k_remap_codes(const int32_t *raw, const int32_t *map, int64_t n,
 }
 
 // ---------------------------------------------------------------------------------------
-// panel layouts
+// panel layouts ("warp-tile ELL")
 // ---------------------------------------------------------------------------------------
-// A panelled stream is cut into segments, one per (panel of the gathered index, row).  Inside
-// a segment the nonzeros of the most frequent pair code (code 0) come first ("A run": the word
-// is the byte offset of the gathered row inside the panel), then the rest ordered by code
-// ("B run": word = code << 16 | index in panel).  Inside a panel the segments are ordered by
-// (A length, B length) descending so that the lane groups of one warp walk segments of
-// (almost always exactly) the same shape; row_id maps a position back to its row.
+// The stream of one orientation is cut into segments, one per (panel of the gathered index,
+// row).  Inside a segment the nonzeros of the most frequent pair code (code 0) come first,
+// the rest follow ordered by code.  Inside a panel the segments are ordered by (code-0 length,
+// rest length) descending and dealt out in TILES of TW = 128/KP consecutive segments: a tile is
+// what one warp of the sweep kernel works on at a time (GL = KP/4 lanes per segment).  Tile
+// number tau of a panel belongs to warp tau % ARB_SWEEP_WARPS; all tiles of one (panel, warp)
+// are contiguous in memory, in the order the warp visits them, so the warp reads one unbroken
+// stream.  A tile is stored step-major in QUADS: quad q holds steps 4q..4q+3 of every segment
+// of the tile as one uint4 per segment ([quad][segment] -> a warp reads TW*16 contiguous bytes).
+//   A region: the first 4*floor(min code-0 length / 4) steps; every segment has a code-0
+//             nonzero there; word = byte offset of the gathered row inside the staged panel.
+//   G region: the rest, up to the longest segment of the tile; word = code << 18 | byte offset.
+//             Short segments are padded with NULL words (code 0, offset of an all-zero row kept
+//             after the panel): their factor is 1 + d*0 = 1 exactly, so padding needs no predicate.
 __global__ void k_panel_keys(const int32_t *row, const int32_t *col, const uint16_t *code, int64_t nnz,
                              int32_t n_rows, int32_t panel_rows, uint64_t *key)
 {
@@ -380,53 +393,127 @@ __global__ void k_seg_keys(const int32_t *start, const int32_t *end_a, int64_t n
     val[s] = (int32_t)s;
 }
 
-__global__ void k_seg_place(const int32_t *order, const int32_t *start, const int32_t *end_a, int64_t n_seg,
-                            int32_t n_rows, int32_t *new_len, int32_t *len_a, int32_t *pos_of_seg, int32_t *row_id)
+__global__ void k_seg_pos(const int32_t *order, int64_t n_seg, int32_t *pos_of_seg)
 {
     int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (p > n_seg) return;
-    if (p == n_seg) { new_len[p] = 0; return; }
-    const int32_t s = order[p];
-    new_len[p] = start[s + 1] - start[s];
-    len_a[p] = end_a[s] ? end_a[s] - start[s] : 0;
-    pos_of_seg[s] = (int32_t)p;
-    row_id[p] = s % n_rows;
+    if (p < n_seg) pos_of_seg[order[p]] = (int32_t)p;
 }
 
-__global__ void k_seg_mid(const int32_t *new_start, const int32_t *len_a, int64_t n_seg, int32_t *mid)
+// largest |log2| a segment's running product can reach: sum over its nonzeros of the per-code bound
+__global__ void k_seg_expbound(const uint64_t *sorted_key, const int32_t *start, int64_t n_seg,
+                               const float *code_up, const float *code_dn, int32_t *out_bits)
 {
-    int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (p < n_seg) mid[p] = new_start[p] + len_a[p];
+    int64_t s = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    float worst = 0.f;
+    if (s < n_seg) {
+        float up = 0.f, dn = 0.f;
+        for (int32_t i = start[s]; i < start[s + 1]; ++i) {
+            const uint32_t code = (uint32_t)((sorted_key[i] >> 16) & 0xffffu);
+            up += code_up[code];
+            dn += code_dn[code];
+        }
+        worst = fmaxf(up, dn);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) worst = fmaxf(worst, __shfl_xor_sync(0xffffffffu, worst, o));
+    if ((threadIdx.x & 31) == 0 && worst > 0.f) atomicMax(out_bits, __float_as_int(worst));
 }
 
-__global__ void k_panel_scatter(const uint64_t *sorted_key, int64_t nnz, const int32_t *start,
-                                const int32_t *pos_of_seg, const int32_t *new_start, int32_t row_bytes,
-                                uint32_t *stream)
+// slot x = (panel * WARPS + warp) * U + u  <->  tile tau = u * WARPS + warp of that panel
+__global__ void k_tile_shape(const int32_t *order, const int32_t *start, const int32_t *end_a, int32_t n_rows,
+                             int64_t n_slots, int32_t U, int32_t tw, int32_t *nq, int32_t *naq)
+{
+    int64_t x = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (x > n_slots) return;
+    if (x == n_slots) { nq[x] = 0; return; }
+    const int u = (int)(x % U), w = (int)((x / U) % ARB_SWEEP_WARPS);
+    const int64_t panel = x / ((int64_t)U * ARB_SWEEP_WARPS);
+    const int64_t tau = (int64_t)u * ARB_SWEEP_WARPS + w, n_tiles = (n_rows + tw - 1) / tw;
+    int aq = 0, tq = 0;
+    if (tau < n_tiles) {
+        int min_la = INT_MAX, max_len = 0;
+        for (int g = 0; g < tw; ++g) {
+            const int64_t i = tau * tw + g;
+            int la = 0, len = 0;
+            if (i < n_rows) {
+                const int32_t s = order[panel * n_rows + i];
+                len = start[s + 1] - start[s];
+                la = end_a[s] ? end_a[s] - start[s] : 0;
+            }
+            min_la = min(min_la, la);
+            max_len = max(max_len, len);
+        }
+        aq = min_la / 4;
+        tq = aq + (max_len - 4 * aq + 3) / 4;
+    }
+    naq[x] = aq;
+    nq[x] = tq;
+}
+
+__global__ void k_tile_desc(const int32_t *qoff, const int32_t *naq, const int32_t *nq, const int32_t *order,
+                            int32_t n_rows, int64_t n_slots, int32_t U, int32_t tw, int4 *desc, int32_t *rows)
+{
+    int64_t x = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (x >= n_slots) return;
+    desc[x] = make_int4(qoff[x], naq[x], nq[x], 0);
+    const int u = (int)(x % U), w = (int)((x / U) % ARB_SWEEP_WARPS);
+    const int64_t panel = x / ((int64_t)U * ARB_SWEEP_WARPS);
+    const int64_t tau = (int64_t)u * ARB_SWEEP_WARPS + w;
+    for (int g = 0; g < tw; ++g) {
+        const int64_t i = tau * tw + g;
+        rows[x * tw + g] = i < n_rows ? order[panel * n_rows + i] % n_rows : -1;
+    }
+}
+
+__global__ void k_fill_u32(uint32_t *v, int64_t n, uint32_t x)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < n) v[i] = x;
+}
+
+__global__ void k_tile_scatter(const uint64_t *sorted_key, int64_t nnz, const int32_t *start,
+                               const int32_t *pos_of_seg, const int32_t *qoff, const int32_t *naq, int32_t n_rows,
+                               int32_t U, int32_t tw, uint32_t row_bytes, uint32_t *stream)
 {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= nnz) return;
     const uint64_t k = sorted_key[i];
     const int64_t seg = (int64_t)(k >> 32);
     const uint32_t code = (uint32_t)((k >> 16) & 0xffffu), local = (uint32_t)(k & 0xffffu);
-    const int64_t dest = (int64_t)new_start[pos_of_seg[seg]] + (i - (int64_t)start[seg]);
-    stream[dest] = code == 0 ? local * (uint32_t)row_bytes : ((code << 16) | local);
+    const int64_t panel = seg / n_rows, idx = (int64_t)pos_of_seg[seg] - panel * n_rows;
+    const int64_t tau = idx / tw;
+    const int g = (int)(idx % tw), w = (int)(tau % ARB_SWEEP_WARPS), u = (int)(tau / ARB_SWEEP_WARPS);
+    const int64_t x = (panel * ARB_SWEEP_WARPS + w) * U + u;
+    const int32_t t = (int32_t)(i - start[seg]);
+    const uint32_t off = local * row_bytes;
+    const uint32_t word = t < 4 * naq[x] ? off : ((code << 18) | off);
+    stream[(((int64_t)qoff[x] + t / 4) * tw + g) * 4 + (t & 3)] = word;
 }
 
+struct StreamOut {
+    DevBuf *desc, *rows, *stream;
+    int *tiles_per_warp, *fold;
+    int64_t *quads;
+};
+
 static int build_stream(arb_ctx *ctx, const int32_t *row, const int32_t *col, int32_t n_rows, int32_t panel_rows,
-                        int np, int kp, DevBuf &ptr, DevBuf &mid, DevBuf &row_id, DevBuf &stream)
+                        int np, int kp, const float *code_up, const float *code_dn, StreamOut out)
 {
     const int64_t nnz = ctx->nnz, n_seg = (int64_t)np * n_rows;
+    const int tw = 128 / kp;
+    const int U = (int)(((n_rows + tw - 1) / tw + ARB_SWEEP_WARPS - 1) / ARB_SWEEP_WARPS);
+    const int64_t n_slots = (int64_t)np * ARB_SWEEP_WARPS * U;
     ARB_REQUIRE(n_seg + 1 < (int64_t)(1 << 30), ARB_ERR_UNSUPPORTED, "layout: %lld segments", (long long)n_seg);
-    DevBuf k_in, k_out, v_in, start, end_a, sk_in, sk_out, sv_in, order, new_len, len_a, pos_of_seg;
+    DevBuf k_in, k_out, start, end_a, sk_in, sk_out, sv_in, order, pos_of_seg, nq, naq, qoff, bound;
     ARB_TRY(k_in.reserve(nnz * 8));
     ARB_TRY(k_out.reserve(nnz * 8));
-    for (DevBuf *b : {&start, &end_a, &sv_in, &order, &new_len, &len_a, &pos_of_seg}) ARB_TRY(b->reserve((n_seg + 1) * 4));
+    for (DevBuf *b : {&start, &end_a, &sv_in, &order, &pos_of_seg}) ARB_TRY(b->reserve((n_seg + 1) * 4));
+    for (DevBuf *b : {&nq, &naq, &qoff}) ARB_TRY(b->reserve((n_slots + 1) * 4));
     ARB_TRY(sk_in.reserve(n_seg * 8));
     ARB_TRY(sk_out.reserve(n_seg * 8));
-    ARB_TRY(ptr.reserve((n_seg + 1) * 4));
-    ARB_TRY(mid.reserve((n_seg + 1) * 4));
-    ARB_TRY(row_id.reserve((n_seg + 1) * 4));
-    ARB_TRY(stream.reserve(nnz * 4 + 256));
+    ARB_TRY(bound.reserve(4));
+    ARB_TRY(out.desc->reserve(n_slots * 16));
+    ARB_TRY(out.rows->reserve(n_slots * tw * 4));
     cudaStream_t st = ctx->stream;
     const int B = 256;
     k_panel_keys<<<grid_for(nnz, B), B, 0, st>>>(row, col, ctx->coo_code.as<uint16_t>(), nnz, n_rows, panel_rows,
@@ -436,32 +523,52 @@ static int build_stream(arb_ctx *ctx, const int32_t *row, const int32_t *col, in
         return cub::DeviceRadixSort::SortKeys(tmp, bytes, k_in.as<uint64_t>(), k_out.as<uint64_t>(), nnz, 0, end_bit, st);
     }));
     ARB_CUDA(cudaMemsetAsync(end_a.p, 0, (n_seg + 1) * 4, st));
+    ARB_CUDA(cudaMemsetAsync(bound.p, 0, 4, st));
     k_seg_bounds<<<grid_for(nnz, B), B, 0, st>>>(k_out.as<uint64_t>(), nnz, n_seg, start.as<int32_t>(),
                                                  end_a.as<int32_t>());
+    k_seg_expbound<<<grid_for(n_seg, B), B, 0, st>>>(k_out.as<uint64_t>(), start.as<int32_t>(), n_seg, code_up, code_dn,
+                                                    bound.as<int32_t>());
     k_seg_keys<<<grid_for(n_seg, B), B, 0, st>>>(start.as<int32_t>(), end_a.as<int32_t>(), n_seg, n_rows,
                                                  sk_in.as<uint64_t>(), sv_in.as<int32_t>());
     ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
         return cub::DeviceRadixSort::SortPairs(tmp, bytes, sk_in.as<uint64_t>(), sk_out.as<uint64_t>(),
                                                sv_in.as<int32_t>(), order.as<int32_t>(), n_seg, 0, 64, st);
     }));
-    k_seg_place<<<grid_for(n_seg + 1, B), B, 0, st>>>(order.as<int32_t>(), start.as<int32_t>(), end_a.as<int32_t>(),
-                                                      n_seg, n_rows, new_len.as<int32_t>(), len_a.as<int32_t>(),
-                                                      pos_of_seg.as<int32_t>(), row_id.as<int32_t>());
+    k_seg_pos<<<grid_for(n_seg, B), B, 0, st>>>(order.as<int32_t>(), n_seg, pos_of_seg.as<int32_t>());
+    k_tile_shape<<<grid_for(n_slots + 1, B), B, 0, st>>>(order.as<int32_t>(), start.as<int32_t>(), end_a.as<int32_t>(),
+                                                        n_rows, n_slots, U, tw, nq.as<int32_t>(), naq.as<int32_t>());
     ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
-        return cub::DeviceScan::ExclusiveSum(tmp, bytes, new_len.as<int32_t>(), ptr.as<int32_t>(), n_seg + 1, st);
+        return cub::DeviceScan::ExclusiveSum(tmp, bytes, nq.as<int32_t>(), qoff.as<int32_t>(), n_slots + 1, st);
     }));
-    k_seg_mid<<<grid_for(n_seg, B), B, 0, st>>>(ptr.as<int32_t>(), len_a.as<int32_t>(), n_seg, mid.as<int32_t>());
-    ARB_CUDA(cudaMemsetAsync(stream.p, 0, nnz * 4 + 256, st));
-    k_panel_scatter<<<grid_for(nnz, B), B, 0, st>>>(k_out.as<uint64_t>(), nnz, start.as<int32_t>(),
-                                                    pos_of_seg.as<int32_t>(), ptr.as<int32_t>(), kp * 8,
-                                                    stream.as<uint32_t>());
+    int32_t total_q = 0, bound_bits = 0;
+    ARB_CUDA(cudaMemcpyAsync(&total_q, qoff.as<int32_t>() + n_slots, 4, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaMemcpyAsync(&bound_bits, bound.p, 4, cudaMemcpyDeviceToHost, st));
     ARB_CUDA(cudaStreamSynchronize(st));
-    for (DevBuf *b : {&k_in, &k_out, &v_in, &start, &end_a, &sk_in, &sk_out, &sv_in, &order, &new_len, &len_a, &pos_of_seg})
+    float worst;
+    memcpy(&worst, &bound_bits, 4);
+    *out.fold = worst < 1000.f;           // every running product and every partial stays a normal double
+    *out.tiles_per_warp = U;
+    *out.quads = total_q;
+    // the sweep reads three quads ahead of the one it works on: keep that many spare at the end
+    const int64_t n_words = ((int64_t)total_q + 4) * tw * 4;
+    ARB_REQUIRE(n_words < ((int64_t)1 << 31), ARB_ERR_UNSUPPORTED, "layout: stream of %lld words", (long long)n_words);
+    ARB_TRY(out.stream->reserve(n_words * 4));
+    const uint32_t null_word = (uint32_t)panel_rows * (uint32_t)kp * 8u;       // code 0, the zero row
+    k_fill_u32<<<grid_for(n_words, B), B, 0, st>>>(out.stream->as<uint32_t>(), n_words, null_word);
+    k_tile_scatter<<<grid_for(nnz, B), B, 0, st>>>(k_out.as<uint64_t>(), nnz, start.as<int32_t>(),
+                                                   pos_of_seg.as<int32_t>(), qoff.as<int32_t>(), naq.as<int32_t>(),
+                                                   n_rows, U, tw, (uint32_t)kp * 8u, out.stream->as<uint32_t>());
+    k_tile_desc<<<grid_for(n_slots, B), B, 0, st>>>(qoff.as<int32_t>(), naq.as<int32_t>(), nq.as<int32_t>(),
+                                                   order.as<int32_t>(), n_rows, n_slots, U, tw, out.desc->as<int4>(),
+                                                   out.rows->as<int32_t>());
+    ARB_CUDA(cudaStreamSynchronize(st));
+    ARB_CUDA(cudaGetLastError());
+    for (DevBuf *b : {&k_in, &k_out, &start, &end_a, &sk_in, &sk_out, &sv_in, &order, &pos_of_seg, &nq, &naq, &qoff, &bound})
         b->release();
     return ARB_OK;
 }
 
-// smem budget of the sweep kernel: [panel_rows][KP] doubles + pair table + one mbarrier
+// smem budget of the sweep kernel: [panel_rows + 1][KP] doubles + pair table + one mbarrier
 int arb_sweep_table_entries(const arb_ctx *ctx) { return std::min<int>(ctx->n_pairs, 512); }
 
 int arb_build_layout(arb_ctx *ctx, int kp)
@@ -469,18 +576,37 @@ int arb_build_layout(arb_ctx *ctx, int kp)
     PanelLayout &L = ctx->layout[kp_index(kp)];
     if (L.kp == kp) return ARB_OK;
     ARB_REQUIRE(ctx->ingested, ARB_ERR_INVALID, "no matrix ingested");
+    ARB_REQUIRE(ctx->n_pairs <= 16384, ARB_ERR_UNSUPPORTED, "%d distinct (alt,total) pairs: the stream word holds 14 bits",
+                ctx->n_pairs);
     size_t budget = ctx->smem_optin - 1024 - (size_t)arb_sweep_table_entries(ctx) * 16;
     if (ctx->opt_panel_kb > 0) budget = std::min<size_t>(budget, (size_t)ctx->opt_panel_kb * 1024);
-    int panel_rows = (int)(budget / ((size_t)kp * 8));
-    panel_rows = std::min(panel_rows, 65536) / 32 * 32;
+    int panel_rows = (int)(budget / ((size_t)kp * 8)) - 1;        // one more row of zeros for the padding words
+    panel_rows = std::min(panel_rows, 65504) / 32 * 32;
     ARB_REQUIRE(panel_rows >= 32, ARB_ERR_INVALID, "panel budget too small");
     L.panel_rows = panel_rows;
     L.np_z = (ctx->n_snvs + panel_rows - 1) / panel_rows;
     L.np_y = (ctx->n_cells + panel_rows - 1) / panel_rows;
+    // per-code bounds on |log2(1 + d x)|, x in [0,1], with a little slack for rounding
+    std::vector<float> up(ctx->n_pairs), dn(ctx->n_pairs);
+    for (int c = 0; c < ctx->n_pairs; ++c) {
+        const double w = ctx->tab_lp[c] - ctx->tab_la[c];
+        up[c] = (float)(std::max(0.0, w) / 0.6931471805599453 * 1.001 + 1e-3);
+        dn[c] = (float)(std::max(0.0, -w) / 0.6931471805599453 * 1.001 + 1e-3);
+    }
+    DevBuf d_up, d_dn;
+    ARB_TRY(d_up.reserve(up.size() * 4));
+    ARB_TRY(d_dn.reserve(dn.size() * 4));
+    ARB_CUDA(cudaMemcpyAsync(d_up.p, up.data(), up.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+    ARB_CUDA(cudaMemcpyAsync(d_dn.p, dn.data(), dn.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
     ARB_TRY(build_stream(ctx, ctx->coo_cell.as<int32_t>(), ctx->coo_snv.as<int32_t>(), ctx->n_cells, panel_rows,
-                         L.np_z, kp, L.zptr, L.zmid, L.zrow, L.zstream));
+                         L.np_z, kp, d_up.as<float>(), d_dn.as<float>(),
+                         StreamOut{&L.zdesc, &L.zrows, &L.zstream, &L.uz, &L.fold_z, &L.quads_z}));
     ARB_TRY(build_stream(ctx, ctx->coo_snv.as<int32_t>(), ctx->coo_cell.as<int32_t>(), ctx->n_snvs, panel_rows,
-                         L.np_y, kp, L.yptr, L.ymid, L.yrow, L.ystream));
+                         L.np_y, kp, d_up.as<float>(), d_dn.as<float>(),
+                         StreamOut{&L.ydesc, &L.yrows, &L.ystream, &L.uy, &L.fold_y, &L.quads_y}));
+    d_up.release();
+    d_dn.release();
+    if (ctx->opt_no_fold) L.fold_z = L.fold_y = 0;
     L.kp = kp;
     return ARB_OK;
 }
@@ -510,11 +636,12 @@ int arb_refresh_tables(arb_ctx *ctx)
         if (ctx->pair_count[c] > 0 && fabs(w) > max_abs_w) max_abs_w = fabs(w);
     }
     ctx->sum_la = s;
-    // factors 1 + d*x lie in [min(1,e^w), max(1,e^w)]: renormalise the running product often
-    // enough that it cannot leave the double range (|log2| < 900 between renormalisations)
+    // factors 1 + d*x lie in [min(1,e^w), max(1,e^w)]: where the layout has no range proof the sweep
+    // renormalises its running products every renorm_every factors (|log2| < 900 in between);
+    // renorm_every / 4 quads, 0 = after every factor
     const double max_log2 = max_abs_w / 0.6931471805599453;
-    int every = max_log2 > 0 ? (int)floor(800.0 / max_log2) : 16;
-    ctx->renorm_every = std::max(1, std::min(every, 16));    // < 8 selects the renormalise-every-factor kernels
+    int every = max_log2 > 0 ? (int)floor(900.0 / max_log2) : 256;
+    ctx->renorm_every = std::max(1, std::min(every, 256));
     return ARB_OK;
 }
 
@@ -877,6 +1004,9 @@ ARB_API int arb_set_loglik_table(arb_ctx *ctx, int32_t n_pairs, const double *lo
     ctx->tab_lp.assign(log_present, log_present + n_pairs);
     ctx->tab_la.assign(log_absent, log_absent + n_pairs);
     ctx->single_tree = -1;
+    // the layouts carry a range proof made with the old table: rebuild them at the next fit
+    for (auto &l : ctx->layout) l.release();
+    ctx->ws_kp = 0;
     return arb_refresh_tables(ctx);
 }
 

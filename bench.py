@@ -269,7 +269,7 @@ def run_gpu_arm(args):
     dev_ms = wall = 0.0
     launches = 0
     prof = dict(sweep_z_ms=0.0, sweep_y_ms=0.0, finish_ms=0.0, tree_sweeps_z=0.0, tree_sweeps_y=0.0,
-                launches_z=0.0, launches_y=0.0, rounds=0.0)
+                launches_z=0.0, launches_y=0.0, rounds=0.0, finish_z_ms=0.0, finish_y_ms=0.0)
     tree_iters = 0.0
     t_wall0 = time.perf_counter()
     for _ in range(args.steps):
@@ -317,7 +317,10 @@ def run_gpu_arm(args):
                        "note": "tree-iterations x B_iter / step time, per GPU"},
         "kernel_share_of_step": {"sweep_z": prof["sweep_z_ms"] / (dev_ms if world == 1 else max(dev_ms, 1e-9)),
                                  "sweep_y": prof["sweep_y_ms"] / max(dev_ms, 1e-9),
-                                 "finish": prof["finish_ms"] / max(dev_ms, 1e-9)},
+                                 "finish_z": prof["finish_z_ms"] / max(dev_ms, 1e-9),
+                                 "finish_y": prof["finish_y_ms"] / max(dev_ms, 1e-9)},
+        "layout": {k: int(pf[k]) for k in ("kp", "panel_rows", "panels_z", "panels_y", "tiles_per_warp_z",
+                                            "tiles_per_warp_y", "fold_z", "fold_y", "quads_z", "quads_y")},
     }
 
     # ---- end to end through arborist(...) with host DataFrames ---------------------------------------

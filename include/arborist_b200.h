@@ -150,7 +150,9 @@ int arb_last_fit_stats(arb_ctx *ctx, int64_t *kernel_launches, double *device_ms
                        double *tree_iterations, double *sweep_ms);
 /* per-kernel profile of the last arb_fit_* call, measured with CUDA events on the context's
  * stream: values[0..7] = q(z) sweep ms, q(y) sweep ms, finishing kernels ms, tree-sweeps done
- * by the q(z) / q(y) sweep launches, number of q(z) / q(y) sweep launches, rounds */
+ * by the q(z) / q(y) sweep launches, number of q(z) / q(y) sweep launches, rounds;
+ * values[8..19] = q(z) / q(y) finishing ms, then the layout in use: KP, rows per panel, panels
+ * (z, y), tiles per warp (z, y), range-proof flags (z, y), stream quads (z, y) */
 int arb_last_fit_profile(arb_ctx *ctx, double *values, int32_t n_values);
 /* tuning knobs: "slots" (trees in flight), "panel_kb" (panel bytes cap), "threads"; returns ARB_ERR_INVALID
  * for unknown names */

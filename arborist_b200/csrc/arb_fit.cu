@@ -208,9 +208,9 @@ struct SweepArgs {
     const double2 *dw;         // per pair code: (d, w)
     int32_t n_pairs, tab_n, renorm_quads;   // not FOLD: renormalise every this many quads, 0 = after every factor
     int32_t ks;                // columns kept per row of the partials (K or C rounded up to 4)
-    double *out_m;             // [slot][panel][row][ks] the segment's product (FOLD) or its mantissa
-    int32_t *out_e;            //                        exponent (not FOLD)
-    double *out_g;             //                        sum_k w_k x (q(z) sweep only)
+    double *out_m;             // [slot][panel][row][ks] the segment's product (FOLD) or its mantissa; the q(z)
+                               // sweep interleaves {product, sum_k w_k x} per column
+    int32_t *out_e;            // [slot][panel][row][ks] exponent (not FOLD)
 };
 
 // Four clones of one nonzero: two LDS.128 from the staged panel, 4 x (DFMA + DMUL) for the
@@ -286,8 +286,11 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const SweepAr
     const int64_t x0 = ((int64_t)panel * ARB_SWEEP_WARPS + warp) * U;
     const int4 *__restrict__ desc = a.desc + x0;
     const int32_t *__restrict__ rows = a.rows + x0 * TW + grp;
+    constexpr int RW = WITH_G ? 2 : 1;             // doubles per column of a partial row
     const int64_t out0 = ((int64_t)slot * a.n_panels + panel) * a.n_rows;
-    const bool small_tab = a.n_pairs <= a.tab_n;
+    const uint32_t out_stride = (uint32_t)a.ks * 8u * RW;
+    char *out_a = reinterpret_cast<char *>(a.out_m) + (out0 * a.ks + off_a) * 8 * RW;
+    int32_t *oute_a = FOLD ? nullptr : a.out_e + out0 * a.ks + off_a;
     const bool keep = 4 * h < a.ks;
     const bool each = a.renorm_quads == 0;
 
@@ -306,76 +309,98 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const SweepAr
     for (int u = 0; u < U; ++u) {
         const int4 dc = dn;
         const int row = rown;
-        if (u + 1 < U) {
-            dn = __ldg(desc + u + 1);
-            rown = __ldg(rows + (int64_t)(u + 1) * TW);
-        }
+        // next tile's descriptor (the arrays carry one spare slot at the end)
+        ++desc;
+        rows += TW;
+        dn = __ldg(desc);
+        rown = __ldg(rows);
         double p[4] = {1.0, 1.0, 1.0, 1.0}, g[4] = {0.0, 0.0, 0.0, 0.0};
         int e[4] = {0, 0, 0, 0};
-        int q = 0, since = 0;
+        int since = 0;
+        // one quad = four steps of every segment of the tile; WC is consumed, then refilled three quads ahead
+#define ARB_QUAD_A(WC)                                                                          \
+    {                                                                                           \
+        const uint4 w = WC;                                                                     \
+        WC = __ldg(sp);                                                                         \
+        sp += TW;                                                                               \
+        sweep_step<WITH_G>(xa_base, xb_base, w.x, dw0.x, dw0.y, p, g);                          \
+        if (!FOLD && each) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);                      \
+        sweep_step<WITH_G>(xa_base, xb_base, w.y, dw0.x, dw0.y, p, g);                          \
+        if (!FOLD && each) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);                      \
+        sweep_step<WITH_G>(xa_base, xb_base, w.z, dw0.x, dw0.y, p, g);                          \
+        if (!FOLD && each) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);                      \
+        sweep_step<WITH_G>(xa_base, xb_base, w.w, dw0.x, dw0.y, p, g);                          \
+        if (!FOLD && ++since >= a.renorm_quads) {                                               \
+            since = 0;                                                                          \
+            for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);                                     \
+        }                                                                                       \
+    }
+#define ARB_QUAD_G(WC)                                                                          \
+    {                                                                                           \
+        const uint32_t ww[4] = {WC.x, WC.y, WC.z, WC.w};                                        \
+        WC = __ldg(sp);                                                                         \
+        sp += TW;                                                                               \
+        _Pragma("unroll") for (int s = 0; s < 4; ++s) {                                         \
+            const uint32_t code = ww[s] >> 18, off = ww[s] & 0x3ffffu;                          \
+            const double2 dw = (FOLD || code < (uint32_t)a.tab_n) ? tab[code] : __ldg(a.dw + code); \
+            sweep_step<WITH_G>(xa_base, xb_base, off, dw.x, dw.y, p, g);                        \
+            if (!FOLD && each) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);                  \
+        }                                                                                       \
+        if (!FOLD && ++since >= a.renorm_quads) {                                               \
+            since = 0;                                                                          \
+            for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);                                     \
+        }                                                                                       \
+    }
+#define ARB_ROT1 { const uint4 t = w0; w0 = w1; w1 = w2; w2 = t; }
+#define ARB_ROT2 { const uint4 t = w2; w2 = w1; w1 = w0; w0 = t; }
         // ---- A region: the most frequent (alt,total) pair; d and w live in registers ------------
-        for (; q < dc.y; ++q) {
-            const uint4 w = w0;
-            w0 = w1;
-            w1 = w2;
-            w2 = __ldg(sp);
-            sp += TW;
-            sweep_step<WITH_G>(xa_base, xb_base, w.x, dw0.x, dw0.y, p, g);
-            if (!FOLD && each) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
-            sweep_step<WITH_G>(xa_base, xb_base, w.y, dw0.x, dw0.y, p, g);
-            if (!FOLD && each) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
-            sweep_step<WITH_G>(xa_base, xb_base, w.z, dw0.x, dw0.y, p, g);
-            if (!FOLD && each) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
-            sweep_step<WITH_G>(xa_base, xb_base, w.w, dw0.x, dw0.y, p, g);
-            if (!FOLD && ++since >= a.renorm_quads) {
-                since = 0;
-                for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
-            }
+        {
+            int q = dc.y;
+            for (; q >= 3; q -= 3) { ARB_QUAD_A(w0) ARB_QUAD_A(w1) ARB_QUAD_A(w2) }
+            if (q == 1) { ARB_QUAD_A(w0) ARB_ROT1 }
+            else if (q == 2) { ARB_QUAD_A(w0) ARB_QUAD_A(w1) ARB_ROT2 }
         }
         // ---- G region: any pair; (d, w) from the table in shared memory ---------------------------
-        for (; q < dc.z; ++q) {
-            const uint4 w = w0;
-            w0 = w1;
-            w1 = w2;
-            w2 = __ldg(sp);
-            sp += TW;
-            const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
-#pragma unroll
-            for (int s = 0; s < 4; ++s) {
-                const uint32_t code = ww[s] >> 18, off = ww[s] & 0x3ffffu;
-                const double2 dw = (small_tab || code < (uint32_t)a.tab_n) ? tab[code] : __ldg(a.dw + code);
-                sweep_step<WITH_G>(xa_base, xb_base, off, dw.x, dw.y, p, g);
-                if (!FOLD && each) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
-            }
-            if (!FOLD && ++since >= a.renorm_quads) {
-                since = 0;
-                for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
-            }
+        {
+            int q = dc.z - dc.y;
+            for (; q >= 3; q -= 3) { ARB_QUAD_G(w0) ARB_QUAD_G(w1) ARB_QUAD_G(w2) }
+            if (q == 1) { ARB_QUAD_G(w0) ARB_ROT1 }
+            else if (q == 2) { ARB_QUAD_G(w0) ARB_QUAD_G(w1) ARB_ROT2 }
         }
+#undef ARB_QUAD_A
+#undef ARB_QUAD_G
+#undef ARB_ROT1
+#undef ARB_ROT2
         if (!FOLD) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
         if (row >= 0 && keep) {
-            const int64_t o = (out0 + row) * a.ks;
-            *reinterpret_cast<double2 *>(a.out_m + o + off_a) = make_double2(p[0], p[1]);
-            *reinterpret_cast<double2 *>(a.out_m + o + off_b) = make_double2(p[2], p[3]);
-            if (!FOLD) {
-                *reinterpret_cast<int2 *>(a.out_e + o + off_a) = make_int2(e[0], e[1]);
-                *reinterpret_cast<int2 *>(a.out_e + o + off_b) = make_int2(e[2], e[3]);
-            }
+            // partial row: q(z) {m, g} per column, q(y) m; this lane's pair (off_a, off_a+1), the other pair
+            // sits at the same address with bit (16 * RW) flipped
+            char *pa = out_a + (int64_t)row * out_stride;
+            char *pb = reinterpret_cast<char *>(reinterpret_cast<uintptr_t>(pa) ^ (uintptr_t)(16 * RW));
             if (WITH_G) {
-                *reinterpret_cast<double2 *>(a.out_g + o + off_a) = make_double2(g[0], g[1]);
-                *reinterpret_cast<double2 *>(a.out_g + o + off_b) = make_double2(g[2], g[3]);
+                reinterpret_cast<double2 *>(pa)[0] = make_double2(p[0], g[0]);
+                reinterpret_cast<double2 *>(pa)[1] = make_double2(p[1], g[1]);
+                reinterpret_cast<double2 *>(pb)[0] = make_double2(p[2], g[2]);
+                reinterpret_cast<double2 *>(pb)[1] = make_double2(p[3], g[3]);
+            } else {
+                reinterpret_cast<double2 *>(pa)[0] = make_double2(p[0], p[1]);
+                reinterpret_cast<double2 *>(pb)[0] = make_double2(p[2], p[3]);
+            }
+            if (!FOLD) {
+                int32_t *ea = oute_a + (int64_t)row * a.ks;
+                *reinterpret_cast<int2 *>(ea) = make_int2(e[0], e[1]);
+                *reinterpret_cast<int2 *>(ea + (off_b - off_a)) = make_int2(e[2], e[3]);
             }
         }
     }
 }
 
 // ---------------------------------------------------------------------------------------
-// finishing kernels: combine the panel partials, softmax, ELBO pieces, next gathered operand
+// finishing kernel: combine the panel partials, softmax, ELBO pieces, next gathered operand
 // ---------------------------------------------------------------------------------------
 struct FinishArgs {
-    const double *part_m;
-    const int32_t *part_e;
-    const double *part_g;
+    const double *part_m;           // [slot][panel][row][ks] ({m, g} interleaved for q(z))
+    const int32_t *part_e;          // exponents, null for range-proven (folded) partials
     int32_t n_panels, n_rows, K;
     int32_t ks;                     // columns per row of the partials
     const int32_t *slot_list;
@@ -389,95 +414,146 @@ struct FinishArgs {
     int32_t given_q;                // elbo_terms hook: take q from q_cur instead of the softmax
 };
 
-// q(z): A.py:245-250 (softmax), A.py:268-273 (entropy), likelihood term, R rows
-template <int KP> __global__ void __launch_bounds__(FIN_THREADS) k_finish_z(const FinishArgs a)
+// The end of a row: A.py:245-250 softmax + A.py:268-273 entropy + likelihood term + R rows (q(z)),
+// A.py:373-375 (+ log prior) softmax + A.py:293-299 KL + S rows (q(y)).  A row lives in the GL = KP/4
+// lanes of a group, lane h holds columns 4h..4h+3.  Executed by whole warps (shuffles); only memory
+// accesses are guarded.  Masked sums run in ascending source order (deterministic, tree-independent).
+template <int KP, bool IS_Z>
+__device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int64_t row, bool rowok, int h,
+                                           const uint32_t (&omask)[4], const double (&p)[4], const int (&e)[4],
+                                           const double (&g)[4], double &acc1, double &acc2)
 {
-    __shared__ double sh[FIN_THREADS / 32];
-    const int K = a.K, C = K - 1, lane = threadIdx.x % KP, g = threadIdx.x / KP;
-    constexpr int NG = FIN_THREADS / KP;
-    const int slot = a.slot_list[blockIdx.y];
-    const uint32_t *mk = a.masks + (int64_t)a.st[slot].tree * MASK_STRIDE;
-    const uint32_t rm = lane < C ? mk[32 + lane] : 0u;
-    double lik = 0.0, ent = 0.0;
-    for (int it = 0; it < FIN_ROWS / NG; ++it) {
-        const int64_t i = (int64_t)blockIdx.x * FIN_ROWS + it * NG + g;
-        const bool live = i < a.n_rows;          // uniform per group
-        double prod = 1.0, gsum = 0.0;
-        int esum = 0;
-        if (live && lane < a.ks) {
-            for (int p = 0; p < a.n_panels; ++p) {
-                const int64_t o = (((int64_t)slot * a.n_panels + p) * a.n_rows + i) * a.ks + lane;
-                prod *= a.part_m[o];          // prod in [1,2), the partial inside 2^+-1000 (range-proven layout) or in [1,2)
-                if (a.part_e) esum += a.part_e[o];
-                gsum += a.part_g[o];
-                renorm(prod, esum);
-            }
-        }
-        double logit = (lane < K) ? log(prod) + (double)esum * LN2 : -INFINITY;
-        const double mx = group_max<KP>(logit);
-        double q = (lane < K) ? exp(logit - mx) : 0.0;
-        const double s = group_sum<KP>(q);
-        q = q / s;
-        if (a.given_q) q = (live && lane < K) ? a.q_cur[((int64_t)slot * a.n_rows + i) * K + lane] : 0.0;
-        const double r = masked_sum<KP>(q, rm, K);
-        if (live) {
-            if (lane < K) {
-                if (!a.given_q) a.q_cur[((int64_t)slot * a.n_rows + i) * K + lane] = q;
-                lik += q * gsum;
-                if (q > 0.0) ent -= q * log(q + 1e-12);
-            }
-            a.x_next[((int64_t)slot * a.n_rows + i) * KP + lane] = r;
+    constexpr int GL = KP / 4;
+    const int K = a.K, C = K - 1, ncol = IS_Z ? K : C;
+    const int64_t qbase = ((int64_t)slot * a.n_rows + row) * ncol;
+    double logit[4];
+    bool v[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        v[c] = 4 * h + c < ncol;
+        double l = log(p[c]) + (double)e[c] * LN2;
+        if (!IS_Z && v[c] && rowok) l += a.logq0[row * C + 4 * h + c];
+        logit[c] = v[c] ? l : -INFINITY;
+    }
+    double mx = fmax(fmax(logit[0], logit[1]), fmax(logit[2], logit[3]));
+#pragma unroll
+    for (int o = GL / 2; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o, GL));
+    double q[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) q[c] = v[c] ? exp(logit[c] - mx) : 0.0;
+    double s = (q[0] + q[1]) + (q[2] + q[3]);
+#pragma unroll
+    for (int o = GL / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o, GL);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) q[c] = q[c] / s;
+    if (IS_Z && a.given_q) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) q[c] = (v[c] && rowok) ? a.q_cur[qbase + 4 * h + c] : 0.0;
+    }
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+    for (int b = 0; b < KP; ++b) {
+        if (b < ncol) {
+            const double xb = __shfl_sync(0xffffffffu, q[b & 3], b >> 2, GL);
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+                if ((omask[c] >> b) & 1u) acc[c] += xb;
         }
     }
-    const double t_lik = block_sum(lik, sh);
-    const double t_ent = block_sum(ent, sh);
-    if (threadIdx.x == 0) {
-        double *red = a.red + (int64_t)slot * 3 * a.nbmax;
-        red[blockIdx.x] = t_lik;
-        red[a.nbmax + blockIdx.x] = t_ent;
+    if (rowok) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            if (v[c]) {
+                if (!(IS_Z && a.given_q)) a.q_cur[qbase + 4 * h + c] = q[c];
+                if (IS_Z) {
+                    acc1 += q[c] * g[c];
+                    if (q[c] > 0.0) acc2 -= q[c] * log(q[c] + 1e-12);
+                } else {
+                    acc1 += q[c] * (log(q[c] + 1e-12) - a.logq0e[row * C + 4 * h + c]);
+                }
+            }
+        }
+        double2 *xn = reinterpret_cast<double2 *>(a.x_next + ((int64_t)slot * a.n_rows + row) * KP + 4 * h);
+        xn[0] = make_double2(acc[0], acc[1]);
+        xn[1] = make_double2(acc[2], acc[3]);
     }
 }
 
-// q(y): A.py:373-375 (+ log prior, softmax), A.py:293-299 (KL), S rows
-template <int KP> __global__ void __launch_bounds__(FIN_THREADS) k_finish_y(const FinishArgs a)
+#define FIN_WARPS (FIN_THREADS / 32)
+
+// grid (row blocks of FIN_ROWS, active slots); a warp takes TW = 128/KP rows at a time
+template <int KP, bool IS_Z> __global__ void __launch_bounds__(FIN_THREADS) k_finish(const FinishArgs a)
 {
-    __shared__ double sh[FIN_THREADS / 32];
-    const int K = a.K, C = K - 1, lane = threadIdx.x % KP, g = threadIdx.x / KP;
-    constexpr int NG = FIN_THREADS / KP;
+    __shared__ double sh[FIN_WARPS];
+    constexpr int GL = KP / 4, TW = 32 / GL, RW = IS_Z ? 2 : 1;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int h = lane % GL, grp = lane / GL;
     const int slot = a.slot_list[blockIdx.y];
-    const uint32_t *mk = a.masks + (int64_t)a.st[slot].tree * MASK_STRIDE;
-    const uint32_t cm = lane < K ? mk[lane] : 0u;
-    double kl = 0.0;
-    for (int it = 0; it < FIN_ROWS / NG; ++it) {
-        const int64_t j = (int64_t)blockIdx.x * FIN_ROWS + it * NG + g;
-        const bool live = j < a.n_rows;
-        double prod = 1.0;
-        int esum = 0;
-        if (live && lane < a.ks) {
-            for (int p = 0; p < a.n_panels; ++p) {
-                const int64_t o = (((int64_t)slot * a.n_panels + p) * a.n_rows + j) * a.ks + lane;
-                prod *= a.part_m[o];
-                if (a.part_e) esum += a.part_e[o];
-                renorm(prod, esum);
+    const int np = a.n_panels;
+    const bool keep = 4 * h < a.ks;
+    uint32_t omask[4];
+    {
+        const uint32_t *mk = a.masks + (int64_t)a.st[slot].tree * MASK_STRIDE + (IS_Z ? 32 : 0);
+        const int n_out = IS_Z ? a.K - 1 : a.K;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) omask[c] = 4 * h + c < n_out ? mk[4 * h + c] : 0u;
+    }
+    const int64_t panel_stride = (int64_t)a.n_rows * a.ks;          // columns between panels
+    double acc1 = 0.0, acc2 = 0.0;
+    for (int it = 0; it < FIN_ROWS / (FIN_WARPS * TW); ++it) {
+        const int64_t row = (int64_t)blockIdx.x * FIN_ROWS + (it * FIN_WARPS + warp) * TW + grp;
+        const bool rowok = row < a.n_rows;
+        const bool mine = rowok && keep;
+        double p[4] = {1.0, 1.0, 1.0, 1.0}, g[4] = {0.0, 0.0, 0.0, 0.0};
+        int e[4] = {0, 0, 0, 0};
+        if (mine) {
+            const int64_t o0 = ((int64_t)slot * np * a.n_rows + row) * a.ks + 4 * h;
+            const double2 *src = reinterpret_cast<const double2 *>(a.part_m + o0 * RW);
+            const int64_t pstep = panel_stride * RW / 2;            // in double2
+#pragma unroll 2
+            for (int pn = 0; pn < np; ++pn) {
+                double m[4];
+                if (IS_Z) {
+                    const double2 v0 = __ldcs(src), v1 = __ldcs(src + 1), v2 = __ldcs(src + 2), v3 = __ldcs(src + 3);
+                    m[0] = v0.x; m[1] = v1.x; m[2] = v2.x; m[3] = v3.x;
+                    g[0] += v0.y; g[1] += v1.y; g[2] += v2.y; g[3] += v3.y;
+                } else {
+                    const double2 v0 = __ldcs(src), v1 = __ldcs(src + 1);
+                    m[0] = v0.x; m[1] = v0.y; m[2] = v1.x; m[3] = v1.y;
+                }
+                src += pstep;
+                // split every partial (positive, normal: 2^+-1000 at most) into mantissa and exponent with
+                // integer ops; the mantissa product stays below 2^np, far inside the double range
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const int hi = __double2hiint(m[c]);
+                    e[c] += (hi >> 20) - 1023;
+                    p[c] *= __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(m[c]));
+                }
+                if ((pn & 255) == 255)
+                    for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
+            }
+            if (a.part_e) {
+                const int4 *se = reinterpret_cast<const int4 *>(a.part_e + o0);
+                for (int pn = 0; pn < np; ++pn) {
+                    const int4 v = __ldcs(se + pn * (panel_stride / 4));
+                    e[0] += v.x; e[1] += v.y; e[2] += v.z; e[3] += v.w;
+                }
             }
         }
-        const bool col = live && lane < C;
-        double logit = col ? a.logq0[j * C + lane] + (log(prod) + (double)esum * LN2) : -INFINITY;
-        const double mx = group_max<KP>(logit);
-        double q = col ? exp(logit - mx) : 0.0;
-        const double s = group_sum<KP>(q);
-        q = q / s;
-        const double sv = masked_sum<KP>(q, cm, C);
-        if (live) {
-            if (lane < C) {
-                a.q_cur[((int64_t)slot * a.n_rows + j) * C + lane] = q;
-                kl += q * (log(q + 1e-12) - a.logq0e[j * C + lane]);
-            }
-            a.x_next[((int64_t)slot * a.n_rows + j) * KP + lane] = sv;
+        finish_row<KP, IS_Z>(a, slot, rowok ? row : 0, rowok, h, omask, p, e, g, acc1, acc2);
+    }
+    const double t1 = block_sum(acc1, sh);
+    const double t2 = block_sum(acc2, sh);
+    if (threadIdx.x == 0) {
+        double *red = a.red + (int64_t)slot * 3 * a.nbmax;
+        if (IS_Z) {
+            red[blockIdx.x] = t1;
+            red[a.nbmax + blockIdx.x] = t2;
+        } else {
+            red[2 * a.nbmax + blockIdx.x] = t1;
         }
     }
-    const double t_kl = block_sum(kl, sh);
-    if (threadIdx.x == 0) a.red[(int64_t)slot * 3 * a.nbmax + 2 * a.nbmax + blockIdx.x] = t_kl;
 }
 
 // entropy / KL of given matrices (kernel-level hook)
@@ -693,8 +769,7 @@ static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve
         ARB_TRY(ctx->qz_cur.reserve(S * n * K * 8));
         ARB_TRY(ctx->qy_cur.reserve(S * m * C * 8));
         // product (8) [+ exponent (4) when the layout could not prove the range]
-        ARB_TRY(ctx->part_z.reserve(S * L.np_z * n * ks_for(K) * (L.fold_z ? 8 : 12) + 64));
-        ARB_TRY(ctx->part_g.reserve(S * L.np_z * n * ks_for(K) * 8 + 64));
+        ARB_TRY(ctx->part_z.reserve(S * L.np_z * n * ks_for(K) * (L.fold_z ? 16 : 20) + 64));
         ARB_TRY(ctx->part_y.reserve(S * L.np_y * m * ks_for(C) * (L.fold_y ? 8 : 12) + 64));
         ARB_TRY(ctx->red.reserve(S * 3 * ws.nbmax * 8));
         ARB_TRY(ctx->slot_state.reserve(S * sizeof(SlotState) + sizeof(Control) + 64));
@@ -727,7 +802,7 @@ static WsPtrs ws_ptrs(arb_ctx *ctx, const PanelLayout &L)
     w.list_init = w.list_z + S;
     w.snap_tree = w.list_init + S;
     w.pz_m = ctx->part_z.as<double>();
-    w.pz_e = L.fold_z ? nullptr : reinterpret_cast<int32_t *>(w.pz_m + S * L.np_z * ctx->n_cells * ks_for(K));
+    w.pz_e = L.fold_z ? nullptr : reinterpret_cast<int32_t *>(w.pz_m + 2 * S * L.np_z * ctx->n_cells * ks_for(K));
     w.py_m = ctx->part_y.as<double>();
     w.py_e = L.fold_y ? nullptr : reinterpret_cast<int32_t *>(w.py_m + S * L.np_y * ctx->n_snvs * ks_for(C));
     return w;
@@ -756,7 +831,6 @@ static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.renorm_quads = ctx->renorm_every / 4;
     a.out_m = w.pz_m;
     a.out_e = w.pz_e;
-    a.out_g = ctx->part_g.as<double>();
     if (L.fold_z)
         k_sweep<KP, true, true><<<n_active * L.np_z, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
     else
@@ -786,7 +860,6 @@ static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.renorm_quads = ctx->renorm_every / 4;
     a.out_m = w.py_m;
     a.out_e = w.py_e;
-    a.out_g = nullptr;
     if (L.fold_y)
         k_sweep<KP, false, true><<<n_active * L.np_y, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
     else
@@ -800,7 +873,6 @@ static void launch_finish_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w,
     FinishArgs a;
     a.part_m = w.pz_m;
     a.part_e = w.pz_e;
-    a.part_g = ctx->part_g.as<double>();
     a.n_panels = L.np_z;
     a.n_rows = ctx->n_cells;
     a.K = ws.K;
@@ -815,7 +887,7 @@ static void launch_finish_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w,
     a.red = ctx->red.as<double>();
     a.nbmax = ws.nbmax;
     a.given_q = given_q;
-    k_finish_z<KP><<<dim3(ws.nbz, n_active), FIN_THREADS, 0, ctx->stream>>>(a);
+    k_finish<KP, true><<<dim3(ws.nbz, n_active), FIN_THREADS, 0, ctx->stream>>>(a);
 }
 
 template <int KP>
@@ -825,7 +897,6 @@ static void launch_finish_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w,
     FinishArgs a;
     a.part_m = w.py_m;
     a.part_e = w.py_e;
-    a.part_g = nullptr;
     a.n_panels = L.np_y;
     a.n_rows = ctx->n_snvs;
     a.K = ws.K;
@@ -840,7 +911,7 @@ static void launch_finish_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w,
     a.red = ctx->red.as<double>();
     a.nbmax = ws.nbmax;
     a.given_q = 0;
-    k_finish_y<KP><<<dim3(ws.nby, n_active), FIN_THREADS, 0, ctx->stream>>>(a);
+    k_finish<KP, false><<<dim3(ws.nby, n_active), FIN_THREADS, 0, ctx->stream>>>(a);
 }
 
 template <int KP>

@@ -490,6 +490,8 @@ __global__ void k_tile_scatter(const uint64_t *sorted_key, int64_t nnz, const in
     stream[(((int64_t)qoff[x] + t / 4) * tw + g) * 4 + (t & 3)] = word;
 }
 
+int arb_sweep_table_entries(const arb_ctx *ctx);
+
 struct StreamOut {
     DevBuf *desc, *rows, *stream;
     int *tiles_per_warp, *fold;
@@ -512,8 +514,10 @@ static int build_stream(arb_ctx *ctx, const int32_t *row, const int32_t *col, in
     ARB_TRY(sk_in.reserve(n_seg * 8));
     ARB_TRY(sk_out.reserve(n_seg * 8));
     ARB_TRY(bound.reserve(4));
-    ARB_TRY(out.desc->reserve(n_slots * 16));
-    ARB_TRY(out.rows->reserve(n_slots * tw * 4));
+    ARB_TRY(out.desc->reserve((n_slots + 1) * 16));          // one spare slot: the sweep prefetches past the end
+    ARB_TRY(out.rows->reserve((n_slots + 1) * tw * 4));
+    ARB_CUDA(cudaMemsetAsync(out.desc->p, 0, (n_slots + 1) * 16, ctx->stream));
+    ARB_CUDA(cudaMemsetAsync(out.rows->p, 0xff, (n_slots + 1) * tw * 4, ctx->stream));
     cudaStream_t st = ctx->stream;
     const int B = 256;
     k_panel_keys<<<grid_for(nnz, B), B, 0, st>>>(row, col, ctx->coo_code.as<uint16_t>(), nnz, n_rows, panel_rows,
@@ -546,7 +550,7 @@ static int build_stream(arb_ctx *ctx, const int32_t *row, const int32_t *col, in
     ARB_CUDA(cudaStreamSynchronize(st));
     float worst;
     memcpy(&worst, &bound_bits, 4);
-    *out.fold = worst < 1000.f;           // every running product and every partial stays a normal double
+    *out.fold = worst < 1000.f && ctx->n_pairs <= arb_sweep_table_entries(ctx);           // every running product and every partial stays a normal double
     *out.tiles_per_warp = U;
     *out.quads = total_q;
     // the sweep reads three quads ahead of the one it works on: keep that many spare at the end

@@ -142,7 +142,10 @@ struct arb_ctx {
 };
 
 static inline int kp_index(int kp) { return kp == 8 ? 0 : kp == 16 ? 1 : 2; }
-static inline int kp_for(int n_clones) { return n_clones <= 8 ? 8 : n_clones <= 16 ? 16 : 32; }
+// The sweeps always run on 16-column packed rows ("virtual slots", arb_fit.cu): the columns of the
+// trees in flight are laid side by side in units of four, so no lane works on a padding column.
+#define ARB_VW 16
+static inline int kp_for(int) { return ARB_VW; }
 
 // ---- internal entry points shared between translation units ---------------------------
 int arb_build_layout(arb_ctx *ctx, int kp);                       // arb_ingest.cu

@@ -102,31 +102,38 @@ __global__ void k_masks_from_presence(const uint8_t *__restrict__ presence, int3
 }
 
 // ---------------------------------------------------------------------------------------
-// masked sums over a KP-lane group: out(lane c) = sum_{b: mask_c bit b} v(lane b)
-// fixed ascending order => deterministic and independent of the tree shape
+// Column packing ("virtual slots").  The sweep kernel works on rows of ARB_VW = 16 doubles
+// (one 128-byte shared-memory wavefront per nonzero).  A tree needs kc = 4*ceil(cols/4) columns
+// (cols = K for S rows / q(z), K-1 for R rows / q(y)); instead of padding every tree to 16,
+// the trees active in a sweep are laid side by side in units of four columns ("chunks"):
+// the tree at position `pos` of the sweep's list owns chunks pos*kc/4 .. (pos+1)*kc/4 - 1 of
+// the flat chunk axis, chunk q lives in virtual slot q/4 at columns 4*(q%4)...  The sweep
+// never learns which tree a column belongs to; the seeding and finishing kernels address
+// the packed operand / partial rows through packed_off().
 // ---------------------------------------------------------------------------------------
-template <int KP> __device__ __forceinline__ double masked_sum(double v, uint32_t mask, int n_src)
+__device__ __forceinline__ int64_t packed_off(int pos, int chunks_per_tree, int h, int64_t rows_per_slot, int64_t row)
 {
-    double acc = 0.0;
-    for (int b = 0; b < n_src; ++b) {
-        const double x = __shfl_sync(0xffffffffu, v, b, KP);
-        if ((mask >> b) & 1u) acc += x;
+    const int q = pos * chunks_per_tree + h;                 // flat chunk index
+    return ((int64_t)(q >> 2) * rows_per_slot + row) * ARB_VW + (q & 3) * 4;
+}
+
+// masked sums of a row spread over GL lanes, lane h holding columns 4h..4h+3:
+// acc[c] = sum over source columns b < n_src with bit b of omask[c] set, in ascending b
+// (fixed order => deterministic and independent of the tree shape).  Whole warps only.
+template <int GL>
+__device__ __forceinline__ void masked_rows(const double (&q)[4], const uint32_t (&omask)[4], int n_src,
+                                            double (&acc)[4])
+{
+    acc[0] = acc[1] = acc[2] = acc[3] = 0.0;
+#pragma unroll
+    for (int b = 0; b < 4 * GL; ++b) {
+        if (b < n_src) {
+            const double xb = __shfl_sync(0xffffffffu, q[b & 3], b >> 2, GL);
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+                if ((omask[c] >> b) & 1u) acc[c] += xb;
+        }
     }
-    return acc;
-}
-
-template <int KP> __device__ __forceinline__ double group_max(double v)
-{
-#pragma unroll
-    for (int o = KP / 2; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o, KP));
-    return v;
-}
-
-template <int KP> __device__ __forceinline__ double group_sum(double v)
-{
-#pragma unroll
-    for (int o = KP / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o, KP);
-    return v;
 }
 
 // fixed-order block reduction of per-thread partial sums; result valid in thread 0
@@ -143,42 +150,66 @@ __device__ __forceinline__ double block_sum(double v, double *sh)
     return s;
 }
 
-// ---------------------------------------------------------------------------------------
-// seed: S rows from a q(y) matrix (the prior for a tree's first pass, A.py:733-743)
-// ---------------------------------------------------------------------------------------
-template <int KP>
-__global__ void k_seed_s(const double *__restrict__ q_src, int64_t src_slot_stride, const int32_t *__restrict__ slots,
-                         const SlotState *__restrict__ st, const uint32_t *__restrict__ masks, int32_t m, int32_t K,
-                         double *__restrict__ xs, double *__restrict__ qy_cur, int copy_q)
+#define SEED_THREADS 256
+
+// S rows (packed, at the tree's position in this round's q(z) list) from a q(y) matrix: the prior
+// for a tree's first pass (A.py:733-743), or an explicit q(y) for the kernel-level hooks.
+// grid (row blocks, trees in `list`)
+template <int GL>
+__global__ void __launch_bounds__(SEED_THREADS)
+k_seed_s(const double *__restrict__ q_src, int64_t src_slot_stride, const int32_t *__restrict__ list,
+         const int32_t *__restrict__ pos_z, const SlotState *__restrict__ st, const uint32_t *__restrict__ masks,
+         int32_t m, int32_t K, double *__restrict__ xs, double *__restrict__ qy_cur, int copy_q)
 {
-    const int C = K - 1, lane = threadIdx.x % KP;
-    const int slot = slots[blockIdx.y];
+    const int C = K - 1, h = threadIdx.x % GL;
+    const int slot = list[blockIdx.y], pos = pos_z[slot];
     const uint32_t *mk = masks + (int64_t)st[slot].tree * MASK_STRIDE;
-    const uint32_t cm = lane < K ? mk[lane] : 0u;
-    const int64_t j = (int64_t)blockIdx.x * (blockDim.x / KP) + threadIdx.x / KP;
+    uint32_t omask[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) omask[c] = 4 * h + c < K ? mk[4 * h + c] : 0u;
+    const int64_t j = (int64_t)blockIdx.x * (SEED_THREADS / GL) + threadIdx.x / GL;
     const bool live = j < m;
     const double *src = q_src + (int64_t)slot * src_slot_stride;
-    const double q = (live && lane < C) ? src[j * C + lane] : 0.0;
-    const double s = masked_sum<KP>(q, cm, C);
+    double q[4], acc[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) q[c] = (live && 4 * h + c < C) ? src[j * C + 4 * h + c] : 0.0;
+    masked_rows<GL>(q, omask, C, acc);
     if (live) {
-        xs[((int64_t)slot * m + j) * KP + lane] = s;
-        if (copy_q && lane < C) qy_cur[((int64_t)slot * m + j) * C + lane] = q;
+        if (4 * h < K) {
+            double2 *xn = reinterpret_cast<double2 *>(xs + packed_off(pos, (K + 3) / 4, h, m, j));
+            xn[0] = make_double2(acc[0], acc[1]);
+            xn[1] = make_double2(acc[2], acc[3]);
+        }
+        if (copy_q)
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+                if (4 * h + c < C) qy_cur[((int64_t)slot * m + j) * C + 4 * h + c] = q[c];
     }
 }
 
-// R rows from a q(z) matrix (kernel-level hook only; the fit gets R from k_finish_z)
-template <int KP>
-__global__ void k_seed_r(const double *__restrict__ qz, int32_t slot, const SlotState *__restrict__ st,
-                         const uint32_t *__restrict__ masks, int32_t n, int32_t K, double *__restrict__ xr)
+// R rows (packed, at the tree's position in this round's q(y) list) from the tree's current q(z)
+template <int GL>
+__global__ void __launch_bounds__(SEED_THREADS)
+k_seed_r(const double *__restrict__ qz_cur, const int32_t *__restrict__ list, const SlotState *__restrict__ st,
+         const uint32_t *__restrict__ masks, int32_t n, int32_t K, double *__restrict__ xr)
 {
-    const int C = K - 1, lane = threadIdx.x % KP;
-    const uint32_t *mk = masks + (int64_t)st[slot].tree * MASK_STRIDE;
-    const uint32_t rm = lane < C ? mk[32 + lane] : 0u;
-    const int64_t i = (int64_t)blockIdx.x * (blockDim.x / KP) + threadIdx.x / KP;
+    const int C = K - 1, h = threadIdx.x % GL;
+    const int slot = list[blockIdx.y], pos = blockIdx.y;
+    const uint32_t *mk = masks + (int64_t)st[slot].tree * MASK_STRIDE + 32;
+    uint32_t omask[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) omask[c] = 4 * h + c < C ? mk[4 * h + c] : 0u;
+    const int64_t i = (int64_t)blockIdx.x * (SEED_THREADS / GL) + threadIdx.x / GL;
     const bool live = i < n;
-    const double q = (live && lane < K) ? qz[((int64_t)slot * n + i) * K + lane] : 0.0;
-    const double r = masked_sum<KP>(q, rm, K);
-    if (live) xr[((int64_t)slot * n + i) * KP + lane] = r;
+    double q[4], acc[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) q[c] = (live && 4 * h + c < K) ? qz_cur[((int64_t)slot * n + i) * K + 4 * h + c] : 0.0;
+    masked_rows<GL>(q, omask, K, acc);
+    if (live && 4 * h < C) {
+        double2 *xn = reinterpret_cast<double2 *>(xr + packed_off(pos, (C + 3) / 4, h, n, i));
+        xn[0] = make_double2(acc[0], acc[1]);
+        xn[1] = make_double2(acc[2], acc[3]);
+    }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -196,21 +227,19 @@ __device__ __forceinline__ void renorm(double &p, int &e)
 }
 
 struct SweepArgs {
-    const double *x;           // gathered operand [slot][n_gather][KP]
-    int64_t x_slot_stride;     // doubles
+    const double *x;           // gathered operand, packed: [virtual slot][n_gather][KP]
+    int64_t x_slot_stride;     // doubles per virtual slot
     int32_t n_gather;          // rows of the gathered operand
     const int4 *desc;          // [n_panels * WARPS * tiles_per_warp] {first quad, A quads, all quads, 0}
     const int32_t *rows;       // [.. * TW] row of every segment of every tile, -1 = none
     const uint4 *stream;       // [quad][TW]
     int32_t n_rows, panel_rows, n_panels, tiles_per_warp;
-    const int32_t *slot_list;
-    int32_t n_active;
+    int32_t n_vslots;          // virtual slots in this launch (grid = n_vslots * n_panels)
     const double2 *dw;         // per pair code: (d, w)
     int32_t n_pairs, tab_n, renorm_quads;   // not FOLD: renormalise every this many quads, 0 = after every factor
-    int32_t ks;                // columns kept per row of the partials (K or C rounded up to 4)
-    double *out_m;             // [slot][panel][row][ks] the segment's product (FOLD) or its mantissa; the q(z)
+    double *out_m;             // [vslot][panel][row][KP] the segment's product (FOLD) or its mantissa; the q(z)
                                // sweep interleaves {product, sum_k w_k x} per column
-    int32_t *out_e;            // [slot][panel][row][ks] exponent (not FOLD)
+    int32_t *out_e;            // [vslot][panel][row][KP] exponent (not FOLD)
 };
 
 // Four clones of one nonzero: two LDS.128 from the staged panel, 4 x (DFMA + DMUL) for the
@@ -247,8 +276,8 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const SweepAr
     double2 *tab = reinterpret_cast<double2 *>(smem_raw + (size_t)(a.panel_rows + 1) * KP * 8);
     uint64_t *mbar = reinterpret_cast<uint64_t *>(tab + a.tab_n);
 
-    const int panel = blockIdx.x / a.n_active;
-    const int slot = a.slot_list[blockIdx.x % a.n_active];
+    const int panel = blockIdx.x / a.n_vslots;
+    const int slot = blockIdx.x % a.n_vslots;            // virtual slot: 16 packed columns of the active trees
     const int row0 = panel * a.panel_rows;
     const int cnt_rows = min(a.panel_rows, a.n_gather - row0);
     const uint32_t bytes = (uint32_t)cnt_rows * KP * 8u;
@@ -288,10 +317,9 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const SweepAr
     const int32_t *__restrict__ rows = a.rows + x0 * TW + grp;
     constexpr int RW = WITH_G ? 2 : 1;             // doubles per column of a partial row
     const int64_t out0 = ((int64_t)slot * a.n_panels + panel) * a.n_rows;
-    const uint32_t out_stride = (uint32_t)a.ks * 8u * RW;
-    char *out_a = reinterpret_cast<char *>(a.out_m) + (out0 * a.ks + off_a) * 8 * RW;
-    int32_t *oute_a = FOLD ? nullptr : a.out_e + out0 * a.ks + off_a;
-    const bool keep = 4 * h < a.ks;
+    const uint32_t out_stride = (uint32_t)KP * 8u * RW;
+    char *out_a = reinterpret_cast<char *>(a.out_m) + (out0 * KP + off_a) * 8 * RW;
+    int32_t *oute_a = FOLD ? nullptr : a.out_e + out0 * KP + off_a;
     const bool each = a.renorm_quads == 0;
 
     // start the stream before waiting for the panel
@@ -372,7 +400,7 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const SweepAr
 #undef ARB_ROT1
 #undef ARB_ROT2
         if (!FOLD) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
-        if (row >= 0 && keep) {
+        if (row >= 0) {
             // partial row: q(z) {m, g} per column, q(y) m; this lane's pair (off_a, off_a+1), the other pair
             // sits at the same address with bit (16 * RW) flipped
             char *pa = out_a + (int64_t)row * out_stride;
@@ -387,7 +415,7 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const SweepAr
                 reinterpret_cast<double2 *>(pb)[0] = make_double2(p[2], p[3]);
             }
             if (!FOLD) {
-                int32_t *ea = oute_a + (int64_t)row * a.ks;
+                int32_t *ea = oute_a + (int64_t)row * KP;
                 *reinterpret_cast<int2 *>(ea) = make_int2(e[0], e[1]);
                 *reinterpret_cast<int2 *>(ea + (off_b - off_a)) = make_int2(e[2], e[3]);
             }
@@ -399,31 +427,30 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const SweepAr
 // finishing kernel: combine the panel partials, softmax, ELBO pieces, next gathered operand
 // ---------------------------------------------------------------------------------------
 struct FinishArgs {
-    const double *part_m;           // [slot][panel][row][ks] ({m, g} interleaved for q(z))
+    const double *part_m;           // [vslot][panel][row][16] ({m, g} interleaved for q(z)), packed columns
     const int32_t *part_e;          // exponents, null for range-proven (folded) partials
     int32_t n_panels, n_rows, K;
-    int32_t ks;                     // columns per row of the partials
-    const int32_t *slot_list;
+    const int32_t *slot_list;       // position in the sweep's list -> tree slot
+    const int32_t *pos_out;         // q(y) only: tree slot -> position in this round's q(z) list
     const SlotState *st;
     const uint32_t *masks;
     const double *logq0, *logq0e;   // q(y) only: log prior, log(prior + 1e-12)
     double *q_cur;                  // [slot][row][K or C]
-    double *x_next;                 // [slot][row][KP]  R (after q_z) or S (after q_y)
+    double *x_next;                 // q(y) only: packed S rows for the q(z) sweep of the same round
     double *red;                    // [slot][3][nbmax]: lik, entropy, kl partial sums per CTA
     int32_t nbmax;
     int32_t given_q;                // elbo_terms hook: take q from q_cur instead of the softmax
 };
 
-// The end of a row: A.py:245-250 softmax + A.py:268-273 entropy + likelihood term + R rows (q(z)),
-// A.py:373-375 (+ log prior) softmax + A.py:293-299 KL + S rows (q(y)).  A row lives in the GL = KP/4
+// The end of a row: A.py:245-250 softmax + A.py:268-273 entropy + likelihood term (q(z)),
+// A.py:373-375 (+ log prior) softmax + A.py:293-299 KL + S rows (q(y)).  A row lives in the GL
 // lanes of a group, lane h holds columns 4h..4h+3.  Executed by whole warps (shuffles); only memory
 // accesses are guarded.  Masked sums run in ascending source order (deterministic, tree-independent).
-template <int KP, bool IS_Z>
-__device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int64_t row, bool rowok, int h,
+template <int GL, bool IS_Z>
+__device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int pos_out, int64_t row, bool rowok, int h,
                                            const uint32_t (&omask)[4], const double (&p)[4], const int (&e)[4],
                                            const double (&g)[4], double &acc1, double &acc2)
 {
-    constexpr int GL = KP / 4;
     const int K = a.K, C = K - 1, ncol = IS_Z ? K : C;
     const int64_t qbase = ((int64_t)slot * a.n_rows + row) * ncol;
     double logit[4];
@@ -451,15 +478,7 @@ __device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int64_
         for (int c = 0; c < 4; ++c) q[c] = (v[c] && rowok) ? a.q_cur[qbase + 4 * h + c] : 0.0;
     }
     double acc[4] = {0.0, 0.0, 0.0, 0.0};
-#pragma unroll
-    for (int b = 0; b < KP; ++b) {
-        if (b < ncol) {
-            const double xb = __shfl_sync(0xffffffffu, q[b & 3], b >> 2, GL);
-#pragma unroll
-            for (int c = 0; c < 4; ++c)
-                if ((omask[c] >> b) & 1u) acc[c] += xb;
-        }
-    }
+    if (!IS_Z) masked_rows<GL>(q, omask, ncol, acc);          // S rows of the new q(y)
     if (rowok) {
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
@@ -473,32 +492,35 @@ __device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int64_
                 }
             }
         }
-        double2 *xn = reinterpret_cast<double2 *>(a.x_next + ((int64_t)slot * a.n_rows + row) * KP + 4 * h);
-        xn[0] = make_double2(acc[0], acc[1]);
-        xn[1] = make_double2(acc[2], acc[3]);
+        if (!IS_Z && 4 * h < K) {
+            double2 *xn = reinterpret_cast<double2 *>(a.x_next + packed_off(pos_out, (K + 3) / 4, h, a.n_rows, row));
+            xn[0] = make_double2(acc[0], acc[1]);
+            xn[1] = make_double2(acc[2], acc[3]);
+        }
     }
 }
 
 #define FIN_WARPS (FIN_THREADS / 32)
 
-// grid (row blocks of FIN_ROWS, active slots); a warp takes TW = 128/KP rows at a time
-template <int KP, bool IS_Z> __global__ void __launch_bounds__(FIN_THREADS) k_finish(const FinishArgs a)
+// grid (row blocks of FIN_ROWS, trees of the sweep's list); a warp takes TW = 32/GL rows at a time
+template <int GL, bool IS_Z> __global__ void __launch_bounds__(FIN_THREADS) k_finish(const FinishArgs a)
 {
     __shared__ double sh[FIN_WARPS];
-    constexpr int GL = KP / 4, TW = 32 / GL, RW = IS_Z ? 2 : 1;
+    constexpr int TW = 32 / GL, RW = IS_Z ? 2 : 1;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int h = lane % GL, grp = lane / GL;
-    const int slot = a.slot_list[blockIdx.y];
+    const int pos = blockIdx.y, slot = a.slot_list[pos];
     const int np = a.n_panels;
-    const bool keep = 4 * h < a.ks;
-    uint32_t omask[4];
-    {
-        const uint32_t *mk = a.masks + (int64_t)a.st[slot].tree * MASK_STRIDE + (IS_Z ? 32 : 0);
-        const int n_out = IS_Z ? a.K - 1 : a.K;
+    const int ncol = IS_Z ? a.K : a.K - 1, chunks = (ncol + 3) / 4;
+    const bool keep = h < chunks;
+    const int pos_out = IS_Z ? 0 : a.pos_out[slot];
+    uint32_t omask[4] = {0u, 0u, 0u, 0u};
+    if (!IS_Z) {
+        const uint32_t *mk = a.masks + (int64_t)a.st[slot].tree * MASK_STRIDE;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) omask[c] = 4 * h + c < n_out ? mk[4 * h + c] : 0u;
+        for (int c = 0; c < 4; ++c) omask[c] = 4 * h + c < a.K ? mk[4 * h + c] : 0u;
     }
-    const int64_t panel_stride = (int64_t)a.n_rows * a.ks;          // columns between panels
+    const int64_t panel_stride = (int64_t)a.n_rows * ARB_VW;        // columns between panels
     double acc1 = 0.0, acc2 = 0.0;
     for (int it = 0; it < FIN_ROWS / (FIN_WARPS * TW); ++it) {
         const int64_t row = (int64_t)blockIdx.x * FIN_ROWS + (it * FIN_WARPS + warp) * TW + grp;
@@ -507,7 +529,9 @@ template <int KP, bool IS_Z> __global__ void __launch_bounds__(FIN_THREADS) k_fi
         double p[4] = {1.0, 1.0, 1.0, 1.0}, g[4] = {0.0, 0.0, 0.0, 0.0};
         int e[4] = {0, 0, 0, 0};
         if (mine) {
-            const int64_t o0 = ((int64_t)slot * np * a.n_rows + row) * a.ks + 4 * h;
+            // this lane's chunk of the packed partial rows: [vslot][panel][row][16]
+            const int q = pos * chunks + h;
+            const int64_t o0 = ((int64_t)(q >> 2) * np * a.n_rows + row) * ARB_VW + (q & 3) * 4;
             const double2 *src = reinterpret_cast<const double2 *>(a.part_m + o0 * RW);
             const int64_t pstep = panel_stride * RW / 2;            // in double2
 #pragma unroll 2
@@ -541,7 +565,7 @@ template <int KP, bool IS_Z> __global__ void __launch_bounds__(FIN_THREADS) k_fi
                 }
             }
         }
-        finish_row<KP, IS_Z>(a, slot, rowok ? row : 0, rowok, h, omask, p, e, g, acc1, acc2);
+        finish_row<GL, IS_Z>(a, slot, pos_out, rowok ? row : 0, rowok, h, omask, p, e, g, acc1, acc2);
     }
     const double t1 = block_sum(acc1, sh);
     const double t2 = block_sum(acc2, sh);
@@ -574,7 +598,7 @@ __global__ void k_entropy_kl(const double *qz, int64_t nz, const double *qy, con
 // the per-tree state machine (A.py:745-816) and slot scheduling
 // ---------------------------------------------------------------------------------------
 __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict__ red, int32_t *list_y,
-                          int32_t *list_z, int32_t *list_init, int32_t *snap_tree, double *elbo_out,
+                          int32_t *list_z, int32_t *list_init, int32_t *pos_z, int32_t *snap_tree, double *elbo_out,
                           int32_t *iters_out, double *trace, int first_call)
 {
     const int n_slots = ctl->n_slots, nbmax = ctl->nbmax;
@@ -637,7 +661,10 @@ __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict_
             } else if (z.phase == PH_ITER) {
                 list_y[ny++] = s;
             }
-            if (z.phase != PH_EMPTY) list_z[nz++] = s;
+            if (z.phase != PH_EMPTY) {
+                pos_z[s] = nz;                                // packed position in this round's q(z) sweep
+                list_z[nz++] = s;
+            }
         }
         ctl->next_tree = next;
         ctl->n_y = ny;
@@ -710,15 +737,18 @@ static size_t sweep_smem_bytes(const arb_ctx *ctx, const PanelLayout &L)
     return (size_t)(L.panel_rows + 1) * L.kp * 8 + (size_t)arb_sweep_table_entries(ctx) * 16 + 16;
 }
 
-static inline int ks_for(int cols) { return (cols + 3) / 4 * 4; }
+static inline int chunks_for(int cols) { return (cols + 3) / 4; }              // 4-column chunks per tree
+static inline int64_t vslots_for(int64_t trees, int cols) { return (trees * chunks_for(cols) + 3) / 4; }
+// lanes per row in the seeding / finishing kernels: power of two covering ceil(K/4) chunks
+static inline int gl_for(int K) { const int c = chunks_for(K); return c <= 1 ? 1 : c <= 2 ? 2 : c <= 4 ? 4 : 8; }
 
-template <int KP> static int configure_kernels(const arb_ctx *ctx, const PanelLayout &L)
+static int configure_kernels(const arb_ctx *ctx, const PanelLayout &L)
 {
     const int smem = (int)sweep_smem_bytes(ctx, L);
-    ARB_CUDA(cudaFuncSetAttribute(k_sweep<KP, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    ARB_CUDA(cudaFuncSetAttribute(k_sweep<KP, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    ARB_CUDA(cudaFuncSetAttribute(k_sweep<KP, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    ARB_CUDA(cudaFuncSetAttribute(k_sweep<KP, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    ARB_CUDA(cudaFuncSetAttribute(k_sweep<ARB_VW, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    ARB_CUDA(cudaFuncSetAttribute(k_sweep<ARB_VW, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    ARB_CUDA(cudaFuncSetAttribute(k_sweep<ARB_VW, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    ARB_CUDA(cudaFuncSetAttribute(k_sweep<ARB_VW, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     return ARB_OK;
 }
 
@@ -727,13 +757,15 @@ struct Workspace {
     int64_t per_slot_bytes;
 };
 
+// bytes one more tree in flight costs (packed buffers grow by kc/16 of a virtual slot per tree)
 static int64_t per_slot_bytes(const arb_ctx *ctx, const PanelLayout &L, int K)
 {
-    const int64_t n = ctx->n_cells, m = ctx->n_snvs, kp = L.kp, C = K - 1;
+    const int64_t n = ctx->n_cells, m = ctx->n_snvs, C = K - 1;
+    const int64_t kcz = 4 * chunks_for(K), kcy = 4 * chunks_for(C);
     const int64_t nb = std::max((n + FIN_ROWS - 1) / FIN_ROWS, (m + FIN_ROWS - 1) / FIN_ROWS);
     const int64_t ez = L.fold_z ? 0 : 4, ey = L.fold_y ? 0 : 4;
-    return (m * kp + n * kp + n * K + m * C) * 8 + (int64_t)L.np_z * n * ks_for(K) * (16 + ez) +
-           (int64_t)L.np_y * m * ks_for(C) * (8 + ey) + 3 * nb * 8 + 64;
+    return (m * kcz + n * kcy + n * K + m * C) * 8 + (int64_t)L.np_z * n * kcz * (16 + ez) +
+           (int64_t)L.np_y * m * kcy * (8 + ey) + 3 * nb * 8 + 64;
 }
 
 static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve_bytes, Workspace &ws)
@@ -758,22 +790,28 @@ static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve
         ctx->ws_slots = 0;
         size_t free_b = 0, total_b = 0;
         ARB_CUDA(cudaMemGetInfo(&free_b, &total_b));
-        const int64_t usable = (int64_t)(free_b * 0.90) - reserve_bytes;
+        // one virtual slot of slack for the rounding of the packed buffers
+        const int64_t slack = (m + n) * ARB_VW * 8 + ((int64_t)L.np_z * n * 20 + (int64_t)L.np_y * m * 12) * ARB_VW;
+        const int64_t usable = (int64_t)(free_b * 0.90) - reserve_bytes - slack;
         const int64_t fit = usable / ws.per_slot_bytes;
         ARB_REQUIRE(fit >= 1, ARB_ERR_NOMEM, "not enough device memory for one tree slot (%lld bytes needed, %lld usable)",
                     (long long)ws.per_slot_bytes, (long long)usable);
         n_slots = (int)std::min<int64_t>(n_slots, fit);
-        const int64_t S = n_slots;
-        ARB_TRY(ctx->xs.reserve(S * m * kp * 8));
-        ARB_TRY(ctx->xr.reserve(S * n * kp * 8));
+        const int64_t S = n_slots, vz = vslots_for(S, K), vy = vslots_for(S, C);
+        ARB_TRY(ctx->xs.reserve(vz * m * ARB_VW * 8));
+        ARB_TRY(ctx->xr.reserve(vy * n * ARB_VW * 8));
+        // columns past the last tree of a sweep are never read back, but the sweep multiplies through
+        // them: keep them finite (stale S / R values or zero)
+        ARB_CUDA(cudaMemsetAsync(ctx->xs.p, 0, vz * m * ARB_VW * 8, ctx->stream));
+        ARB_CUDA(cudaMemsetAsync(ctx->xr.p, 0, vy * n * ARB_VW * 8, ctx->stream));
         ARB_TRY(ctx->qz_cur.reserve(S * n * K * 8));
         ARB_TRY(ctx->qy_cur.reserve(S * m * C * 8));
         // product (8) [+ exponent (4) when the layout could not prove the range]
-        ARB_TRY(ctx->part_z.reserve(S * L.np_z * n * ks_for(K) * (L.fold_z ? 16 : 20) + 64));
-        ARB_TRY(ctx->part_y.reserve(S * L.np_y * m * ks_for(C) * (L.fold_y ? 8 : 12) + 64));
+        ARB_TRY(ctx->part_z.reserve(vz * L.np_z * n * ARB_VW * (L.fold_z ? 16 : 20) + 64));
+        ARB_TRY(ctx->part_y.reserve(vy * L.np_y * m * ARB_VW * (L.fold_y ? 8 : 12) + 64));
         ARB_TRY(ctx->red.reserve(S * 3 * ws.nbmax * 8));
         ARB_TRY(ctx->slot_state.reserve(S * sizeof(SlotState) + sizeof(Control) + 64));
-        ARB_TRY(ctx->lists.reserve(S * 4 * 4 + 64));
+        ARB_TRY(ctx->lists.reserve(S * 5 * 4 + 64));
         ctx->ws_kp = kp;
         ctx->ws_k = K;
         ctx->ws_slots = n_slots;
@@ -785,7 +823,7 @@ static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve
 struct WsPtrs {
     SlotState *st;
     Control *ctl;
-    int32_t *list_y, *list_z, *list_init, *snap_tree;
+    int32_t *list_y, *list_z, *list_init, *pos_z, *snap_tree;
     double *pz_m, *py_m;
     int32_t *pz_e, *py_e;
 };
@@ -794,26 +832,27 @@ static WsPtrs ws_ptrs(arb_ctx *ctx, const PanelLayout &L)
 {
     const int K = ctx->ws_k, C = K - 1;
     WsPtrs w;
-    const int64_t S = ctx->ws_slots;
+    const int64_t S = ctx->ws_slots, vz = vslots_for(S, K), vy = vslots_for(S, C);
     w.st = ctx->slot_state.as<SlotState>();
     w.ctl = reinterpret_cast<Control *>(reinterpret_cast<char *>(ctx->slot_state.p) + S * sizeof(SlotState));
     w.list_y = ctx->lists.as<int32_t>();
     w.list_z = w.list_y + S;
     w.list_init = w.list_z + S;
-    w.snap_tree = w.list_init + S;
+    w.pos_z = w.list_init + S;
+    w.snap_tree = w.pos_z + S;
     w.pz_m = ctx->part_z.as<double>();
-    w.pz_e = L.fold_z ? nullptr : reinterpret_cast<int32_t *>(w.pz_m + 2 * S * L.np_z * ctx->n_cells * ks_for(K));
+    w.pz_e = L.fold_z ? nullptr : reinterpret_cast<int32_t *>(w.pz_m + 2 * vz * L.np_z * ctx->n_cells * ARB_VW);
     w.py_m = ctx->part_y.as<double>();
-    w.py_e = L.fold_y ? nullptr : reinterpret_cast<int32_t *>(w.py_m + S * L.np_y * ctx->n_snvs * ks_for(C));
+    w.py_e = L.fold_y ? nullptr : reinterpret_cast<int32_t *>(w.py_m + vy * L.np_y * ctx->n_snvs * ARB_VW);
     return w;
 }
 
-template <int KP>
-static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, const int32_t *list, int n_active)
+// q(z) sweep over the packed S rows of the first n_trees entries of this round's q(z) list
+static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, int n_trees)
 {
     SweepArgs a;
     a.x = ctx->xs.as<double>();
-    a.x_slot_stride = (int64_t)ctx->n_snvs * KP;
+    a.x_slot_stride = (int64_t)ctx->n_snvs * ARB_VW;
     a.n_gather = ctx->n_snvs;
     a.desc = L.zdesc.as<int4>();
     a.rows = L.zrows.as<int32_t>();
@@ -822,27 +861,25 @@ static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.panel_rows = L.panel_rows;
     a.n_panels = L.np_z;
     a.tiles_per_warp = L.uz;
-    a.ks = ks_for(ctx->ws_k);
-    a.slot_list = list;
-    a.n_active = n_active;
+    a.n_vslots = (int)vslots_for(n_trees, ctx->ws_k);
     a.dw = ctx->tab_dw.as<double2>();
     a.n_pairs = ctx->n_pairs;
     a.tab_n = arb_sweep_table_entries(ctx);
     a.renorm_quads = ctx->renorm_every / 4;
     a.out_m = w.pz_m;
     a.out_e = w.pz_e;
+    const int grid = a.n_vslots * L.np_z;
     if (L.fold_z)
-        k_sweep<KP, true, true><<<n_active * L.np_z, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
+        k_sweep<ARB_VW, true, true><<<grid, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
     else
-        k_sweep<KP, true, false><<<n_active * L.np_z, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
+        k_sweep<ARB_VW, true, false><<<grid, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
 }
 
-template <int KP>
-static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, const int32_t *list, int n_active)
+static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, int n_trees)
 {
     SweepArgs a;
     a.x = ctx->xr.as<double>();
-    a.x_slot_stride = (int64_t)ctx->n_cells * KP;
+    a.x_slot_stride = (int64_t)ctx->n_cells * ARB_VW;
     a.n_gather = ctx->n_cells;
     a.desc = L.ydesc.as<int4>();
     a.rows = L.yrows.as<int32_t>();
@@ -851,22 +888,21 @@ static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.panel_rows = L.panel_rows;
     a.n_panels = L.np_y;
     a.tiles_per_warp = L.uy;
-    a.ks = ks_for(ctx->ws_k - 1);
-    a.slot_list = list;
-    a.n_active = n_active;
+    a.n_vslots = (int)vslots_for(n_trees, ctx->ws_k - 1);
     a.dw = ctx->tab_dw.as<double2>();
     a.n_pairs = ctx->n_pairs;
     a.tab_n = arb_sweep_table_entries(ctx);
     a.renorm_quads = ctx->renorm_every / 4;
     a.out_m = w.py_m;
     a.out_e = w.py_e;
+    const int grid = a.n_vslots * L.np_y;
     if (L.fold_y)
-        k_sweep<KP, false, true><<<n_active * L.np_y, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
+        k_sweep<ARB_VW, false, true><<<grid, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
     else
-        k_sweep<KP, false, false><<<n_active * L.np_y, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
+        k_sweep<ARB_VW, false, false><<<grid, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
 }
 
-template <int KP>
+template <int GL>
 static void launch_finish_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, const Workspace &ws,
                             const uint32_t *masks, const int32_t *list, int n_active, int given_q)
 {
@@ -876,21 +912,21 @@ static void launch_finish_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w,
     a.n_panels = L.np_z;
     a.n_rows = ctx->n_cells;
     a.K = ws.K;
-    a.ks = ks_for(ws.K);
     a.slot_list = list;
+    a.pos_out = nullptr;
     a.st = w.st;
     a.masks = masks;
     a.logq0 = nullptr;
     a.logq0e = nullptr;
     a.q_cur = ctx->qz_cur.as<double>();
-    a.x_next = ctx->xr.as<double>();
+    a.x_next = nullptr;
     a.red = ctx->red.as<double>();
     a.nbmax = ws.nbmax;
     a.given_q = given_q;
-    k_finish<KP, true><<<dim3(ws.nbz, n_active), FIN_THREADS, 0, ctx->stream>>>(a);
+    k_finish<GL, true><<<dim3(ws.nbz, n_active), FIN_THREADS, 0, ctx->stream>>>(a);
 }
 
-template <int KP>
+template <int GL>
 static void launch_finish_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, const Workspace &ws,
                             const uint32_t *masks, const int32_t *list, int n_active)
 {
@@ -900,8 +936,8 @@ static void launch_finish_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w,
     a.n_panels = L.np_y;
     a.n_rows = ctx->n_snvs;
     a.K = ws.K;
-    a.ks = ks_for(ws.K - 1);
     a.slot_list = list;
+    a.pos_out = w.pos_z;
     a.st = w.st;
     a.masks = masks;
     a.logq0 = ctx->logq0.as<double>();
@@ -911,26 +947,34 @@ static void launch_finish_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w,
     a.red = ctx->red.as<double>();
     a.nbmax = ws.nbmax;
     a.given_q = 0;
-    k_finish<KP, false><<<dim3(ws.nby, n_active), FIN_THREADS, 0, ctx->stream>>>(a);
+    k_finish<GL, false><<<dim3(ws.nby, n_active), FIN_THREADS, 0, ctx->stream>>>(a);
 }
 
-template <int KP>
+template <int GL>
 static void launch_seed_s(arb_ctx *ctx, const WsPtrs &w, const uint32_t *masks, const double *q_src,
                           int64_t src_stride, const int32_t *list, int n_active, int K, int copy_q)
 {
-    const int rows_per_block = 256 / KP;
-    k_seed_s<KP><<<dim3(grid_for(ctx->n_snvs, rows_per_block), n_active), 256, 0, ctx->stream>>>(
-        q_src, src_stride, list, w.st, masks, ctx->n_snvs, K, ctx->xs.as<double>(), ctx->qy_cur.as<double>(), copy_q);
+    k_seed_s<GL><<<dim3(grid_for(ctx->n_snvs, SEED_THREADS / GL), n_active), SEED_THREADS, 0, ctx->stream>>>(
+        q_src, src_stride, list, w.pos_z, w.st, masks, ctx->n_snvs, K, ctx->xs.as<double>(), ctx->qy_cur.as<double>(),
+        copy_q);
+}
+
+template <int GL>
+static void launch_seed_r(arb_ctx *ctx, const WsPtrs &w, const uint32_t *masks, const int32_t *list, int n_active,
+                          int K)
+{
+    k_seed_r<GL><<<dim3(grid_for(ctx->n_cells, SEED_THREADS / GL), n_active), SEED_THREADS, 0, ctx->stream>>>(
+        ctx->qz_cur.as<double>(), list, w.st, masks, ctx->n_cells, K, ctx->xr.as<double>());
 }
 
 // one fit of n_trees trees whose masks are on the device
-template <int KP>
+template <int GL>
 static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, const FitTarget &tg, int64_t reserve)
 {
     Workspace ws;
     ARB_TRY(ensure_workspace(ctx, K, std::min(n_trees, 1024), reserve, ws));
-    const PanelLayout &L = ctx->layout[kp_index(KP)];
-    ARB_TRY(configure_kernels<KP>(ctx, L));
+    const PanelLayout &L = ctx->layout[kp_index(ws.kp)];
+    ARB_TRY(configure_kernels(ctx, L));
     const WsPtrs w = ws_ptrs(ctx, L);
     cudaStream_t st = ctx->stream;
     const int64_t nz = (int64_t)ctx->n_cells * K, ny = (int64_t)ctx->n_snvs * (K - 1);
@@ -955,8 +999,8 @@ static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, 
     for (auto &e : evs) ARB_CUDA(cudaEventCreate(&e));
     ARB_CUDA(cudaEventRecord(ev0, st));
     FitStats stats;
-    k_control<<<1, 256, 0, st>>>(w.ctl, w.st, ctx->red.as<double>(), w.list_y, w.list_z, w.list_init, w.snap_tree,
-                                 tg.elbo, tg.iters, tg.trace, 1);
+    k_control<<<1, 256, 0, st>>>(w.ctl, w.st, ctx->red.as<double>(), w.list_y, w.list_z, w.list_init, w.pos_z,
+                                 w.snap_tree, tg.elbo, tg.iters, tg.trace, 1);
     stats.launches++;
     int rc = ARB_OK;
     bool pending_y = false, pending_z = false;
@@ -984,29 +1028,30 @@ static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, 
         if (h.n_z == 0) break;
         stats.rounds += 1;
         if (h.n_init > 0) {
-            launch_seed_s<KP>(ctx, w, tg.masks, ctx->q0.as<double>(), 0, w.list_init, h.n_init, K, 1);
+            launch_seed_s<GL>(ctx, w, tg.masks, ctx->q0.as<double>(), 0, w.list_init, h.n_init, K, 1);
             stats.launches++;
         }
         if (h.n_y > 0) {
+            launch_seed_r<GL>(ctx, w, tg.masks, w.list_y, h.n_y, K);
             cudaEventRecord(evs[0], st);
-            launch_sweep_y<KP>(ctx, L, w, w.list_y, h.n_y);
+            launch_sweep_y(ctx, L, w, h.n_y);
             cudaEventRecord(evs[1], st);
-            launch_finish_y<KP>(ctx, L, w, ws, tg.masks, w.list_y, h.n_y);
+            launch_finish_y<GL>(ctx, L, w, ws, tg.masks, w.list_y, h.n_y);
             cudaEventRecord(evs[2], st);
-            stats.launches += 2;
+            stats.launches += 3;
             stats.launches_y += 1;
             stats.tree_sweeps_y += h.n_y;
             pending_y = true;
         }
         cudaEventRecord(evs[3], st);
-        launch_sweep_z<KP>(ctx, L, w, w.list_z, h.n_z);
+        launch_sweep_z(ctx, L, w, h.n_z);
         cudaEventRecord(evs[4], st);
-        launch_finish_z<KP>(ctx, L, w, ws, tg.masks, w.list_z, h.n_z, 0);
+        launch_finish_z<GL>(ctx, L, w, ws, tg.masks, w.list_z, h.n_z, 0);
         cudaEventRecord(evs[5], st);
         stats.launches_z += 1;
         stats.tree_sweeps_z += h.n_z;
         pending_z = true;
-        k_control<<<1, 256, 0, st>>>(w.ctl, w.st, ctx->red.as<double>(), w.list_y, w.list_z, w.list_init,
+        k_control<<<1, 256, 0, st>>>(w.ctl, w.st, ctx->red.as<double>(), w.list_y, w.list_z, w.list_init, w.pos_z,
                                      w.snap_tree, tg.elbo, tg.iters, tg.trace, 0);
         stats.launches += 3;
         if (tg.best_qz) {
@@ -1038,10 +1083,11 @@ static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, 
 static int fit_dispatch(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, const FitTarget &tg,
                         int64_t reserve)
 {
-    switch (kp_for(K)) {
-    case 8: return fit_core<8>(ctx, n_trees, K, max_iter, tol, tg, reserve);
-    case 16: return fit_core<16>(ctx, n_trees, K, max_iter, tol, tg, reserve);
-    default: return fit_core<32>(ctx, n_trees, K, max_iter, tol, tg, reserve);
+    switch (gl_for(K)) {
+    case 1: return fit_core<1>(ctx, n_trees, K, max_iter, tol, tg, reserve);
+    case 2: return fit_core<2>(ctx, n_trees, K, max_iter, tol, tg, reserve);
+    case 4: return fit_core<4>(ctx, n_trees, K, max_iter, tol, tg, reserve);
+    default: return fit_core<8>(ctx, n_trees, K, max_iter, tol, tg, reserve);
     }
 }
 
@@ -1351,11 +1397,7 @@ static int hook_setup(arb_ctx *ctx, int K, const uint8_t *presence, HookEnv &env
     ARB_TRY(ensure_workspace(ctx, K, 1, 0, env.ws));
     env.L = &ctx->layout[kp_index(env.ws.kp)];
     env.w = ws_ptrs(ctx, *env.L);
-    switch (env.ws.kp) {
-    case 8: ARB_TRY(configure_kernels<8>(ctx, *env.L)); break;
-    case 16: ARB_TRY(configure_kernels<16>(ctx, *env.L)); break;
-    default: ARB_TRY(configure_kernels<32>(ctx, *env.L)); break;
-    }
+    ARB_TRY(configure_kernels(ctx, *env.L));
     const int C = K - 1;
     DevBuf d_p;
     ARB_TRY(d_p.reserve((size_t)C * K));
@@ -1367,8 +1409,9 @@ static int hook_setup(arb_ctx *ctx, int K, const uint8_t *presence, HookEnv &env
     s0.tree = 0;
     s0.phase = PH_INIT;
     ARB_CUDA(cudaMemcpyAsync(env.w.st, &s0, sizeof s0, cudaMemcpyHostToDevice, ctx->stream));
-    int32_t zero = 0;
+    int32_t zero = 0;                   // the one tree sits in slot 0 at packed position 0
     ARB_CUDA(cudaMemcpyAsync(env.w.list_z, &zero, 4, cudaMemcpyHostToDevice, ctx->stream));
+    ARB_CUDA(cudaMemcpyAsync(env.w.pos_z, &zero, 4, cudaMemcpyHostToDevice, ctx->stream));
     env.list0 = env.w.list_z;
     ARB_CUDA(cudaStreamSynchronize(ctx->stream));
     d_p.release();
@@ -1376,11 +1419,12 @@ static int hook_setup(arb_ctx *ctx, int K, const uint8_t *presence, HookEnv &env
     return ARB_OK;
 }
 
-#define KP_SWITCH(kp, ...)                                  \
-    switch (kp) {                                           \
-    case 8: { constexpr int KPV = 8; __VA_ARGS__; } break;   \
-    case 16: { constexpr int KPV = 16; __VA_ARGS__; } break; \
-    default: { constexpr int KPV = 32; __VA_ARGS__; } break; \
+#define GL_SWITCH(K, ...)                                  \
+    switch (gl_for(K)) {                                   \
+    case 1: { constexpr int GLV = 1; __VA_ARGS__; } break;  \
+    case 2: { constexpr int GLV = 2; __VA_ARGS__; } break;  \
+    case 4: { constexpr int GLV = 4; __VA_ARGS__; } break;  \
+    default: { constexpr int GLV = 8; __VA_ARGS__; } break; \
     }
 
 ARB_API int arb_qz_update(arb_ctx *ctx, int32_t n_clones, const uint8_t *presence, const double *q_y, double *q_z)
@@ -1391,10 +1435,10 @@ ARB_API int arb_qz_update(arb_ctx *ctx, int32_t n_clones, const uint8_t *presenc
     const int K = n_clones, C = K - 1;
     const uint32_t *mk = ctx->masks.as<uint32_t>();
     ARB_CUDA(cudaMemcpyAsync(ctx->qy_cur.p, q_y, (size_t)ctx->n_snvs * C * 8, cudaMemcpyHostToDevice, ctx->stream));
-    KP_SWITCH(env.ws.kp, {
-        launch_seed_s<KPV>(ctx, env.w, mk, ctx->qy_cur.as<double>(), (int64_t)ctx->n_snvs * C, env.list0, 1, K, 0);
-        launch_sweep_z<KPV>(ctx, *env.L, env.w, env.list0, 1);
-        launch_finish_z<KPV>(ctx, *env.L, env.w, env.ws, mk, env.list0, 1, 0);
+    GL_SWITCH(K, {
+        launch_seed_s<GLV>(ctx, env.w, mk, ctx->qy_cur.as<double>(), (int64_t)ctx->n_snvs * C, env.list0, 1, K, 0);
+        launch_sweep_z(ctx, *env.L, env.w, 1);
+        launch_finish_z<GLV>(ctx, *env.L, env.w, env.ws, mk, env.list0, 1, 0);
     });
     ARB_CUDA(cudaMemcpyAsync(q_z, ctx->qz_cur.p, (size_t)ctx->n_cells * K * 8, cudaMemcpyDeviceToHost, ctx->stream));
     ARB_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -1412,11 +1456,10 @@ ARB_API int arb_qy_update(arb_ctx *ctx, int32_t n_clones, const uint8_t *presenc
     const int K = n_clones, C = K - 1;
     const uint32_t *mk = ctx->masks.as<uint32_t>();
     ARB_CUDA(cudaMemcpyAsync(ctx->qz_cur.p, q_z, (size_t)ctx->n_cells * K * 8, cudaMemcpyHostToDevice, ctx->stream));
-    KP_SWITCH(env.ws.kp, {
-        k_seed_r<KPV><<<grid_for(ctx->n_cells, 256 / KPV), 256, 0, ctx->stream>>>(
-            ctx->qz_cur.as<double>(), 0, env.w.st, mk, ctx->n_cells, K, ctx->xr.as<double>());
-        launch_sweep_y<KPV>(ctx, *env.L, env.w, env.list0, 1);
-        launch_finish_y<KPV>(ctx, *env.L, env.w, env.ws, mk, env.list0, 1);
+    GL_SWITCH(K, {
+        launch_seed_r<GLV>(ctx, env.w, mk, env.list0, 1, K);
+        launch_sweep_y(ctx, *env.L, env.w, 1);
+        launch_finish_y<GLV>(ctx, *env.L, env.w, env.ws, mk, env.list0, 1);
     });
     ARB_CUDA(cudaMemcpyAsync(q_y, ctx->qy_cur.p, (size_t)ctx->n_snvs * C * 8, cudaMemcpyDeviceToHost, ctx->stream));
     ARB_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -1437,10 +1480,10 @@ ARB_API int arb_elbo_terms(arb_ctx *ctx, int32_t n_clones, const uint8_t *presen
     const uint32_t *mk = ctx->masks.as<uint32_t>();
     ARB_CUDA(cudaMemcpyAsync(ctx->qy_cur.p, q_y, ny * 8, cudaMemcpyHostToDevice, ctx->stream));
     ARB_CUDA(cudaMemcpyAsync(ctx->qz_cur.p, q_z, nz * 8, cudaMemcpyHostToDevice, ctx->stream));
-    KP_SWITCH(env.ws.kp, {
-        launch_seed_s<KPV>(ctx, env.w, mk, ctx->qy_cur.as<double>(), ny, env.list0, 1, K, 0);
-        launch_sweep_z<KPV>(ctx, *env.L, env.w, env.list0, 1);
-        launch_finish_z<KPV>(ctx, *env.L, env.w, env.ws, mk, env.list0, 1, 1);
+    GL_SWITCH(K, {
+        launch_seed_s<GLV>(ctx, env.w, mk, ctx->qy_cur.as<double>(), ny, env.list0, 1, K, 0);
+        launch_sweep_z(ctx, *env.L, env.w, 1);
+        launch_finish_z<GLV>(ctx, *env.L, env.w, env.ws, mk, env.list0, 1, 1);
     });
     DevBuf out;
     ARB_TRY(out.reserve(16));

@@ -6,6 +6,6 @@ never a CPU fallback.
 """
 from .utils import read_trees  # noqa: F401
 from .treefit import TreeFit  # noqa: F401
-from .arborist import arborist, run_variational_inference  # noqa: F401
+from .arborist import arborist, run_variational_inference, run_simple_max_likelihood  # noqa: F401
 
 __version__ = "0.1.0"

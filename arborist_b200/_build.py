@@ -34,7 +34,7 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
     nvcc = nvcc_path()
     if nvcc is None:
         raise RuntimeError("nvcc not found: cannot build libarborist_b200.so")
-    cmd = [nvcc, *NVCC_FLAGS, *SOURCES, "-o", LIB]
+    cmd = [nvcc, *NVCC_FLAGS, *os.environ.get("ARB_NVCC_EXTRA", "").split(), *SOURCES, "-o", LIB]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
     res = subprocess.run(cmd, cwd=CSRC, capture_output=True, text=True)

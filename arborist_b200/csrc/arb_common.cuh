@@ -66,6 +66,7 @@ struct DevBuf {
     template <class T> T *as() const { return reinterpret_cast<T *>(p); }
 };
 
+#define ARB_MAX_GROUPS 4
 #define ARB_SWEEP_WARPS 16    // warps per sweep CTA; the layouts are dealt out to this many warps
 
 // Panelled sparse layout for one padded clone width KP (8, 16 or 32 doubles per row of
@@ -95,7 +96,7 @@ struct FitStats {
     double device_ms = 0, tree_iterations = 0, sweep_ms = 0;
     // per-kernel profile of the last fit (CUDA events on the launching stream)
     double sweep_z_ms = 0, sweep_y_ms = 0, finish_ms = 0, finish_z_ms = 0, finish_y_ms = 0;
-    double tree_sweeps_z = 0, tree_sweeps_y = 0, launches_z = 0, launches_y = 0, rounds = 0;
+    double tree_sweeps_z = 0, tree_sweeps_y = 0, launches_z = 0, launches_y = 0, rounds = 0, groups = 0;
 };
 
 struct arb_ctx {
@@ -120,14 +121,20 @@ struct arb_ctx {
 
     // ---- prior ---------------------------------------------------------------------
     int32_t n_clusters = 0;
-    DevBuf q0, logq0, logq0e;             // [m, C]: q, log q (-inf for 0), log(q + 1e-12)
+    DevBuf q0, logq0, logq0e, q0_hard;    // [m, C]: q, log q (-inf for 0), log(q + 1e-12), one-hot argmax of q
 
     // ---- layouts (index 0: KP 8, 1: KP 16, 2: KP 32) ----------------------------------
     PanelLayout layout[3];
-    int64_t opt_slots = 0, opt_panel_kb = 0, opt_threads = 0, opt_no_fold = 0;
+    int64_t opt_slots = 0, opt_panel_kb = 0, opt_threads = 0, opt_no_fold = 0, opt_groups = 0;
 
     // ---- fit workspace -----------------------------------------------------------------
-    int ws_kp = 0, ws_slots = 0, ws_k = 0;
+    // The slots are split into `ws_groups` stream groups of `ws_sg` slots; every group runs its own
+    // rounds on its own stream, so one group's finishing kernels (HBM-bound) overlap another group's
+    // sweeps (shared-memory-pipe-bound).
+    int ws_kp = 0, ws_slots = 0, ws_k = 0, ws_groups = 0, ws_sg = 0;
+    cudaStream_t gstream[ARB_MAX_GROUPS] = {};
+    cudaEvent_t gevent[ARB_MAX_GROUPS][8] = {};   // 6 profile events, control-ready, done
+    void *h_ctl = nullptr;                        // pinned host copies of the groups' Control blocks
     DevBuf xs, xr, qz_cur, qy_cur, part_z, part_g, part_y, red, slot_state, lists, masks;
     // results of the last fit
     int32_t fit_trees = 0, fit_k = 0, fit_max_iter = 0, fit_mode = 0;

@@ -33,6 +33,14 @@
 int arb_sweep_table_entries(const arb_ctx *ctx);
 int arb_check_table_range(arb_ctx *ctx);
 
+// Partial rows of the q(y) sweep are stored as 16-byte pieces [k][h] (see the end of k_sweep); measured on
+// B200 at config 3 (scripts/ab_layout.sh): q(y) finishing kernel -9 %; the same order for the q(z) partial
+// rows made its finishing kernel 32 % slower (chunks no longer cover whole sectors), so q(z) keeps chunks
+// contiguous.  bit 0: q(y), bit 1: q(z).
+#ifndef ARB_PIECE_LAYOUT
+#define ARB_PIECE_LAYOUT 1
+#endif
+#define ARB_PIECES(with_g) ((ARB_PIECE_LAYOUT >> ((with_g) ? 1 : 0)) & 1)
 #define SWEEP_THREADS (ARB_SWEEP_WARPS * 32)
 #define FIN_THREADS 256
 #define FIN_ROWS 256          // rows of q per finishing CTA (fixed: the ELBO reduction order depends on it)
@@ -46,11 +54,15 @@ struct SlotState {
     double best;
 };
 
+// One Control per stream group: the group owns slots slot0 .. slot0+n_slots-1 and fits trees
+// next_tree, next_tree + tree_step, ... (static interleaving of the tree set over the groups).
 struct Control {
-    int32_t next_tree, n_trees, n_slots, max_iter;
+    int32_t next_tree, n_trees, tree_step, max_iter;
+    int32_t slot0, n_slots, n_done, keep;
     double tol, sum_la;
-    int32_t n_y, n_z, n_init, n_done;
-    int32_t nbz, nby, nbmax, keep;
+    int32_t n_y, n_z, n_init, mode;
+    int32_t nbz, nby, nbmax, pad1;
+    int32_t pad2[16];              // 128 bytes
 };
 
 static inline int grid_for(int64_t n, int block) { return (int)std::max<int64_t>(1, (n + block - 1) / block); }
@@ -318,7 +330,8 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const SweepAr
     constexpr int RW = WITH_G ? 2 : 1;             // doubles per column of a partial row
     const int64_t out0 = ((int64_t)slot * a.n_panels + panel) * a.n_rows;
     const uint32_t out_stride = (uint32_t)KP * 8u * RW;
-    char *out_a = reinterpret_cast<char *>(a.out_m) + (out0 * KP + off_a) * 8 * RW;
+    constexpr bool PIECES = ARB_PIECES(WITH_G);
+    char *out_a = reinterpret_cast<char *>(a.out_m) + (PIECES ? out0 * KP * 8 * RW + h * 16 : (out0 * KP + off_a) * 8 * RW);
     int32_t *oute_a = FOLD ? nullptr : a.out_e + out0 * KP + off_a;
     const bool each = a.renorm_quads == 0;
 
@@ -401,6 +414,23 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const SweepAr
 #undef ARB_ROT2
         if (!FOLD) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
         if (row >= 0) {
+            if (PIECES) {
+            // partial row stored as 16-byte pieces [k][h] (k = piece of the lane's chunk, h = lane of the group):
+            // one store instruction writes 64 contiguous bytes per row.  q(z): piece k = {m, g} of column 4h+k
+            // (4 pieces); q(y): piece k = m of columns 4h+2k, 4h+2k+1 (2 pieces).  This lane holds columns
+            // 4h+2swz.. in p[0..1] and 4h+2(1-swz).. in p[2..3].
+            char *pr = out_a + (int64_t)row * out_stride;
+            if (WITH_G) {
+                double2 *lo = reinterpret_cast<double2 *>(pr + swz * 128), *hi = reinterpret_cast<double2 *>(pr + (1 - swz) * 128);
+                lo[0] = make_double2(p[0], g[0]);
+                lo[4] = make_double2(p[1], g[1]);
+                hi[0] = make_double2(p[2], g[2]);
+                hi[4] = make_double2(p[3], g[3]);
+            } else {
+                *reinterpret_cast<double2 *>(pr + swz * 64) = make_double2(p[0], p[1]);
+                *reinterpret_cast<double2 *>(pr + (1 - swz) * 64) = make_double2(p[2], p[3]);
+            }
+            } else {
             // partial row: q(z) {m, g} per column, q(y) m; this lane's pair (off_a, off_a+1), the other pair
             // sits at the same address with bit (16 * RW) flipped
             char *pa = out_a + (int64_t)row * out_stride;
@@ -413,6 +443,7 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const SweepAr
             } else {
                 reinterpret_cast<double2 *>(pa)[0] = make_double2(p[0], p[1]);
                 reinterpret_cast<double2 *>(pb)[0] = make_double2(p[2], p[3]);
+            }
             }
             if (!FOLD) {
                 int32_t *ea = oute_a + (int64_t)row * KP;
@@ -446,7 +477,7 @@ struct FinishArgs {
 // A.py:373-375 (+ log prior) softmax + A.py:293-299 KL + S rows (q(y)).  A row lives in the GL
 // lanes of a group, lane h holds columns 4h..4h+3.  Executed by whole warps (shuffles); only memory
 // accesses are guarded.  Masked sums run in ascending source order (deterministic, tree-independent).
-template <int GL, bool IS_Z>
+template <int GL, bool IS_Z, bool HARD>
 __device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int pos_out, int64_t row, bool rowok, int h,
                                            const uint32_t (&omask)[4], const double (&p)[4], const int (&e)[4],
                                            const double (&g)[4], double &acc1, double &acc2)
@@ -479,6 +510,31 @@ __device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int po
     }
     double acc[4] = {0.0, 0.0, 0.0, 0.0};
     if (!IS_Z) masked_rows<GL>(q, omask, ncol, acc);          // S rows of the new q(y)
+    if (IS_Z && HARD) {
+        // hard-assignment mode (A.py:596, 662-674): the likelihood term of the row's MAP clone (first maximum
+        // of q(z), like numpy's argmax); the soft q(z) is still what the caller gets back
+        double bv = -1.0;
+        int bi = 0;
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+            if (v[c] && q[c] > bv) { bv = q[c]; bi = 4 * h + c; }
+#pragma unroll
+        for (int o = GL / 2; o > 0; o >>= 1) {
+            const double ov = __shfl_xor_sync(0xffffffffu, bv, o, GL);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o, GL);
+            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+        }
+        if (rowok) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                if (v[c]) {
+                    if (!a.given_q) a.q_cur[qbase + 4 * h + c] = q[c];
+                    if (bi == 4 * h + c) acc1 += g[c];
+                }
+            }
+        }
+        return;
+    }
     if (rowok) {
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
@@ -503,7 +559,8 @@ __device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int po
 #define FIN_WARPS (FIN_THREADS / 32)
 
 // grid (row blocks of FIN_ROWS, trees of the sweep's list); a warp takes TW = 32/GL rows at a time
-template <int GL, bool IS_Z> __global__ void __launch_bounds__(FIN_THREADS) k_finish(const FinishArgs a)
+template <int GL, bool IS_Z, bool HARD>
+__global__ void __launch_bounds__(FIN_THREADS) k_finish(const FinishArgs a)
 {
     __shared__ double sh[FIN_WARPS];
     constexpr int TW = 32 / GL, RW = IS_Z ? 2 : 1;
@@ -529,20 +586,24 @@ template <int GL, bool IS_Z> __global__ void __launch_bounds__(FIN_THREADS) k_fi
         double p[4] = {1.0, 1.0, 1.0, 1.0}, g[4] = {0.0, 0.0, 0.0, 0.0};
         int e[4] = {0, 0, 0, 0};
         if (mine) {
-            // this lane's chunk of the packed partial rows: [vslot][panel][row][16]
+            // this lane's chunk of the packed partial rows: [vslot][panel][row][16 columns]
             const int q = pos * chunks + h;
             const int64_t o0 = ((int64_t)(q >> 2) * np * a.n_rows + row) * ARB_VW + (q & 3) * 4;
-            const double2 *src = reinterpret_cast<const double2 *>(a.part_m + o0 * RW);
+            // pieces [k][h]: 4 double2 between a chunk's pieces; else the chunk is contiguous
+            constexpr bool PIECES = ARB_PIECES(IS_Z);
+            constexpr int PS = PIECES ? 4 : 1;
+            const double2 *src = PIECES ? reinterpret_cast<const double2 *>(a.part_m + (o0 - (q & 3) * 4) * RW) + (q & 3)
+                                        : reinterpret_cast<const double2 *>(a.part_m + o0 * RW);
             const int64_t pstep = panel_stride * RW / 2;            // in double2
 #pragma unroll 2
             for (int pn = 0; pn < np; ++pn) {
                 double m[4];
                 if (IS_Z) {
-                    const double2 v0 = __ldcs(src), v1 = __ldcs(src + 1), v2 = __ldcs(src + 2), v3 = __ldcs(src + 3);
+                    const double2 v0 = __ldcs(src), v1 = __ldcs(src + PS), v2 = __ldcs(src + 2 * PS), v3 = __ldcs(src + 3 * PS);
                     m[0] = v0.x; m[1] = v1.x; m[2] = v2.x; m[3] = v3.x;
                     g[0] += v0.y; g[1] += v1.y; g[2] += v2.y; g[3] += v3.y;
                 } else {
-                    const double2 v0 = __ldcs(src), v1 = __ldcs(src + 1);
+                    const double2 v0 = __ldcs(src), v1 = __ldcs(src + PS);
                     m[0] = v0.x; m[1] = v0.y; m[2] = v1.x; m[3] = v1.y;
                 }
                 src += pstep;
@@ -565,7 +626,7 @@ template <int GL, bool IS_Z> __global__ void __launch_bounds__(FIN_THREADS) k_fi
                 }
             }
         }
-        finish_row<GL, IS_Z>(a, slot, pos_out, rowok ? row : 0, rowok, h, omask, p, e, g, acc1, acc2);
+        finish_row<GL, IS_Z, HARD>(a, slot, pos_out, rowok ? row : 0, rowok, h, omask, p, e, g, acc1, acc2);
     }
     const double t1 = block_sum(acc1, sh);
     const double t2 = block_sum(acc2, sh);
@@ -601,9 +662,10 @@ __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict_
                           int32_t *list_z, int32_t *list_init, int32_t *pos_z, int32_t *snap_tree, double *elbo_out,
                           int32_t *iters_out, double *trace, int first_call)
 {
-    const int n_slots = ctl->n_slots, nbmax = ctl->nbmax;
+    // st, red, pos_z, snap_tree are indexed by global slot; the three lists belong to this group
+    const int s0 = ctl->slot0, s1 = s0 + ctl->n_slots, nbmax = ctl->nbmax;
     if (!first_call) {
-        for (int s = threadIdx.x; s < n_slots; s += blockDim.x) {
+        for (int s = s0 + threadIdx.x; s < s1; s += blockDim.x) {
             SlotState z = st[s];
             int snap = -1;
             if (z.phase != PH_EMPTY) {
@@ -613,14 +675,15 @@ __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict_
                 for (int b = 0; b < ctl->nbz; ++b) ent += r[nbmax + b];
                 bool done;
                 if (z.phase == PH_INIT) {
-                    const double elbo = lik + ent - 0.0;      // KL(q_y0 || q_y0) = 0 (A.py:750-759)
+                    // KL(q_y0 || q_y0) = 0 (A.py:750-759); hard-assignment mode returns the likelihood (A.py:664-676)
+                    const double elbo = ctl->mode == ARB_MODE_ML ? lik : lik + ent - 0.0;
                     z.best = elbo;
                     z.iter = 0;
                     z.converged = 0;
                     z.phase = PH_ITER;
                     snap = z.tree;                            // A.py:762-763
                     if (trace) trace[(int64_t)z.tree * (ctl->max_iter + 1)] = elbo;
-                    done = ctl->max_iter == 0;
+                    done = ctl->max_iter == 0 || ctl->mode == ARB_MODE_ML;
                 } else {
                     for (int b = 0; b < ctl->nby; ++b) kl += r[2 * nbmax + b];
                     const double elbo = lik + ent - kl;       // A.py:801-803
@@ -648,10 +711,11 @@ __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict_
     __syncthreads();
     if (threadIdx.x == 0) {
         int ny = 0, nz = 0, ni = 0, next = ctl->next_tree;
-        for (int s = 0; s < n_slots; ++s) {
+        for (int s = s0; s < s1; ++s) {
             SlotState z = st[s];
             if (z.phase == PH_EMPTY && next < ctl->n_trees) {
-                z.tree = next++;
+                z.tree = next;
+                next += ctl->tree_step;
                 z.phase = PH_INIT;
                 z.iter = 0;
                 z.converged = 0;
@@ -676,9 +740,9 @@ __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict_
 // A.py:762-763 / 809-810: keep the posteriors of the best iterate
 __global__ void k_snapshot(const int32_t *__restrict__ snap_tree, const double *__restrict__ qz_cur,
                            const double *__restrict__ qy_cur, int64_t nz, int64_t ny, double *__restrict__ best_qz,
-                           double *__restrict__ best_qy)
+                           double *__restrict__ best_qy, int slot0)
 {
-    const int slot = blockIdx.y, tree = snap_tree[slot];
+    const int slot = slot0 + blockIdx.y, tree = snap_tree[slot];
     if (tree < 0) return;
     const double *sz = qz_cur + (int64_t)slot * nz, *sy = qy_cur + (int64_t)slot * ny;
     double *dz = best_qz + (int64_t)tree * nz, *dy = best_qy + (int64_t)tree * ny;
@@ -721,6 +785,18 @@ __global__ void k_prior_logs(const double *__restrict__ q0, int64_t n, double *_
     lqe[i] = log(q0[i] + 1e-12);                      // A.py:296
 }
 
+// hard_assign_q of the prior (A.py:572-595): 1 at the row's first maximum, 0 elsewhere
+__global__ void k_prior_hard(const double *__restrict__ q0, int32_t m, int32_t C, double *__restrict__ qh)
+{
+    const int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (j >= m) return;
+    const double *r = q0 + j * C;
+    int best = 0;
+    for (int c = 1; c < C; ++c)
+        if (r[c] > r[best]) best = c;
+    for (int c = 0; c < C; ++c) qh[j * C + c] = c == best ? 1.0 : 0.0;
+}
+
 // ---------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------
@@ -753,7 +829,7 @@ static int configure_kernels(const arb_ctx *ctx, const PanelLayout &L)
 }
 
 struct Workspace {
-    int kp, K, n_slots, nbz, nby, nbmax;
+    int kp, K, n_slots, groups, sg, nbz, nby, nbmax;
     int64_t per_slot_bytes;
 };
 
@@ -766,6 +842,17 @@ static int64_t per_slot_bytes(const arb_ctx *ctx, const PanelLayout &L, int K)
     const int64_t ez = L.fold_z ? 0 : 4, ey = L.fold_y ? 0 : 4;
     return (m * kcz + n * kcy + n * K + m * C) * 8 + (int64_t)L.np_z * n * kcz * (16 + ez) +
            (int64_t)L.np_y * m * kcy * (8 + ey) + 3 * nb * 8 + 64;
+}
+
+// stream groups for a fit with `slots` trees in flight: enough trees per group to fill the machine
+static int groups_for(const arb_ctx *ctx, int slots)
+{
+    // default: one group.  More groups let one group's finishing kernels run under another group's sweeps,
+    // but both kinds of kernel are limited by the same L1/shared-memory pipe, so on B200 the overlap
+    // measured 2.5 % slower at config 3 (profiles/r1i_summary.md); the option is kept for other shapes.
+    int g = ctx->opt_groups > 0 ? (int)ctx->opt_groups : 1;
+    while (g > 1 && slots / g < 1) --g;
+    return std::max(1, std::min(g, ARB_MAX_GROUPS));
 }
 
 static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve_bytes, Workspace &ws)
@@ -782,22 +869,28 @@ static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve
     ws.per_slot_bytes = per_slot_bytes(ctx, L, K);
     int n_slots = want_slots;
     if (ctx->opt_slots > 0) n_slots = (int)std::min<int64_t>(n_slots, ctx->opt_slots);
-    if (!(ctx->ws_kp == kp && ctx->ws_k == K && ctx->ws_slots >= n_slots)) {
+    int G = groups_for(ctx, n_slots);
+    int sg = (n_slots + G - 1) / G;
+    if (!(ctx->ws_kp == kp && ctx->ws_k == K && ctx->ws_groups >= G && ctx->ws_sg >= sg)) {
         // release first so the free-memory query sees what we can really use
         for (DevBuf *b : {&ctx->xs, &ctx->xr, &ctx->qz_cur, &ctx->qy_cur, &ctx->part_z, &ctx->part_g, &ctx->part_y,
                           &ctx->red, &ctx->slot_state, &ctx->lists})
             b->release();
-        ctx->ws_slots = 0;
+        ctx->ws_slots = ctx->ws_groups = ctx->ws_sg = 0;
         size_t free_b = 0, total_b = 0;
         ARB_CUDA(cudaMemGetInfo(&free_b, &total_b));
-        // one virtual slot of slack for the rounding of the packed buffers
-        const int64_t slack = (m + n) * ARB_VW * 8 + ((int64_t)L.np_z * n * 20 + (int64_t)L.np_y * m * 12) * ARB_VW;
+        // one virtual slot of slack per group for the rounding of the packed buffers
+        const int64_t slack = G * ((m + n) * ARB_VW * 8 + ((int64_t)L.np_z * n * 20 + (int64_t)L.np_y * m * 12) * ARB_VW);
         const int64_t usable = (int64_t)(free_b * 0.90) - reserve_bytes - slack;
         const int64_t fit = usable / ws.per_slot_bytes;
         ARB_REQUIRE(fit >= 1, ARB_ERR_NOMEM, "not enough device memory for one tree slot (%lld bytes needed, %lld usable)",
                     (long long)ws.per_slot_bytes, (long long)usable);
-        n_slots = (int)std::min<int64_t>(n_slots, fit);
-        const int64_t S = n_slots, vz = vslots_for(S, K), vy = vslots_for(S, C);
+        if (fit < n_slots) {
+            n_slots = (int)fit;
+            G = groups_for(ctx, n_slots);
+            sg = n_slots / G;
+        }
+        const int64_t S = (int64_t)G * sg, vz = G * vslots_for(sg, K), vy = G * vslots_for(sg, C);
         ARB_TRY(ctx->xs.reserve(vz * m * ARB_VW * 8));
         ARB_TRY(ctx->xr.reserve(vy * n * ARB_VW * 8));
         // columns past the last tree of a sweep are never read back, but the sweep multiplies through
@@ -810,48 +903,75 @@ static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve
         ARB_TRY(ctx->part_z.reserve(vz * L.np_z * n * ARB_VW * (L.fold_z ? 16 : 20) + 64));
         ARB_TRY(ctx->part_y.reserve(vy * L.np_y * m * ARB_VW * (L.fold_y ? 8 : 12) + 64));
         ARB_TRY(ctx->red.reserve(S * 3 * ws.nbmax * 8));
-        ARB_TRY(ctx->slot_state.reserve(S * sizeof(SlotState) + sizeof(Control) + 64));
+        ARB_TRY(ctx->slot_state.reserve(S * sizeof(SlotState) + ARB_MAX_GROUPS * sizeof(Control) + 64));
         ARB_TRY(ctx->lists.reserve(S * 5 * 4 + 64));
         ctx->ws_kp = kp;
         ctx->ws_k = K;
-        ctx->ws_slots = n_slots;
+        ctx->ws_groups = G;
+        ctx->ws_sg = sg;
+        ctx->ws_slots = (int)S;
     }
-    ws.n_slots = std::min(n_slots, ctx->ws_slots);
+    // a fit may use fewer groups / slots per group than the workspace holds
+    ws.groups = std::min(G, ctx->ws_groups);
+    ws.sg = std::min(sg, ctx->ws_sg);
+    ws.n_slots = ws.groups * ws.sg;
+    for (int g = 0; g < ws.groups; ++g) {
+        if (!ctx->gstream[g]) ARB_CUDA(cudaStreamCreateWithFlags(&ctx->gstream[g], cudaStreamNonBlocking));
+        for (int i = 0; i < 8; ++i)
+            if (!ctx->gevent[g][i])
+                ARB_CUDA(i < 6 ? cudaEventCreate(&ctx->gevent[g][i])
+                               : cudaEventCreateWithFlags(&ctx->gevent[g][i], cudaEventDisableTiming));
+    }
+    if (!ctx->h_ctl) ARB_CUDA(cudaMallocHost(&ctx->h_ctl, ARB_MAX_GROUPS * sizeof(Control)));
     return ARB_OK;
 }
 
+// device pointers of one stream group: its slots, its lists and its regions of the packed buffers
 struct WsPtrs {
-    SlotState *st;
-    Control *ctl;
-    int32_t *list_y, *list_z, *list_init, *pos_z, *snap_tree;
-    double *pz_m, *py_m;
+    int slot0, n_slots;
+    cudaStream_t stream;
+    SlotState *st;                       // [all slots]
+    Control *ctl;                        // this group's
+    int32_t *list_y, *list_z, *list_init;        // this group's (entries are global slot ids)
+    int32_t *pos_z, *snap_tree;          // [all slots]
+    double *xs, *xr, *pz_m, *py_m;       // this group's regions
     int32_t *pz_e, *py_e;
 };
 
-static WsPtrs ws_ptrs(arb_ctx *ctx, const PanelLayout &L)
+static WsPtrs ws_ptrs(arb_ctx *ctx, const PanelLayout &L, int g, cudaStream_t stream)
 {
     const int K = ctx->ws_k, C = K - 1;
     WsPtrs w;
-    const int64_t S = ctx->ws_slots, vz = vslots_for(S, K), vy = vslots_for(S, C);
+    const int64_t S = ctx->ws_slots, G = ctx->ws_groups, sg = ctx->ws_sg;
+    const int64_t vz = vslots_for(sg, K), vy = vslots_for(sg, C);          // per group
+    const int64_t n = ctx->n_cells, m = ctx->n_snvs;
+    w.slot0 = (int)(g * sg);
+    w.n_slots = (int)sg;
+    w.stream = stream;
     w.st = ctx->slot_state.as<SlotState>();
-    w.ctl = reinterpret_cast<Control *>(reinterpret_cast<char *>(ctx->slot_state.p) + S * sizeof(SlotState));
-    w.list_y = ctx->lists.as<int32_t>();
-    w.list_z = w.list_y + S;
-    w.list_init = w.list_z + S;
-    w.pos_z = w.list_init + S;
-    w.snap_tree = w.pos_z + S;
-    w.pz_m = ctx->part_z.as<double>();
-    w.pz_e = L.fold_z ? nullptr : reinterpret_cast<int32_t *>(w.pz_m + 2 * vz * L.np_z * ctx->n_cells * ARB_VW);
-    w.py_m = ctx->part_y.as<double>();
-    w.py_e = L.fold_y ? nullptr : reinterpret_cast<int32_t *>(w.py_m + vy * L.np_y * ctx->n_snvs * ARB_VW);
+    w.ctl = reinterpret_cast<Control *>(reinterpret_cast<char *>(ctx->slot_state.p) + S * sizeof(SlotState)) + g;
+    int32_t *lists = ctx->lists.as<int32_t>();
+    w.list_y = lists + w.slot0;
+    w.list_z = lists + S + w.slot0;
+    w.list_init = lists + 2 * S + w.slot0;
+    w.pos_z = lists + 3 * S;
+    w.snap_tree = lists + 4 * S;
+    w.xs = ctx->xs.as<double>() + g * vz * m * ARB_VW;
+    w.xr = ctx->xr.as<double>() + g * vy * n * ARB_VW;
+    double *pz = ctx->part_z.as<double>(), *py = ctx->part_y.as<double>();
+    const int64_t pz_cols = vz * L.np_z * n * ARB_VW, py_cols = vy * L.np_y * m * ARB_VW;   // per group
+    w.pz_m = pz + g * 2 * pz_cols;
+    w.pz_e = L.fold_z ? nullptr : reinterpret_cast<int32_t *>(pz + G * 2 * pz_cols) + g * pz_cols;
+    w.py_m = py + g * py_cols;
+    w.py_e = L.fold_y ? nullptr : reinterpret_cast<int32_t *>(py + G * py_cols) + g * py_cols;
     return w;
 }
 
-// q(z) sweep over the packed S rows of the first n_trees entries of this round's q(z) list
+// q(z) sweep over the packed S rows of the first n_trees entries of the group's q(z) list
 static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, int n_trees)
 {
     SweepArgs a;
-    a.x = ctx->xs.as<double>();
+    a.x = w.xs;
     a.x_slot_stride = (int64_t)ctx->n_snvs * ARB_VW;
     a.n_gather = ctx->n_snvs;
     a.desc = L.zdesc.as<int4>();
@@ -870,15 +990,15 @@ static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.out_e = w.pz_e;
     const int grid = a.n_vslots * L.np_z;
     if (L.fold_z)
-        k_sweep<ARB_VW, true, true><<<grid, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
+        k_sweep<ARB_VW, true, true><<<grid, SWEEP_THREADS, sweep_smem_bytes(ctx, L), w.stream>>>(a);
     else
-        k_sweep<ARB_VW, true, false><<<grid, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
+        k_sweep<ARB_VW, true, false><<<grid, SWEEP_THREADS, sweep_smem_bytes(ctx, L), w.stream>>>(a);
 }
 
 static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, int n_trees)
 {
     SweepArgs a;
-    a.x = ctx->xr.as<double>();
+    a.x = w.xr;
     a.x_slot_stride = (int64_t)ctx->n_cells * ARB_VW;
     a.n_gather = ctx->n_cells;
     a.desc = L.ydesc.as<int4>();
@@ -897,14 +1017,14 @@ static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.out_e = w.py_e;
     const int grid = a.n_vslots * L.np_y;
     if (L.fold_y)
-        k_sweep<ARB_VW, false, true><<<grid, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
+        k_sweep<ARB_VW, false, true><<<grid, SWEEP_THREADS, sweep_smem_bytes(ctx, L), w.stream>>>(a);
     else
-        k_sweep<ARB_VW, false, false><<<grid, SWEEP_THREADS, sweep_smem_bytes(ctx, L), ctx->stream>>>(a);
+        k_sweep<ARB_VW, false, false><<<grid, SWEEP_THREADS, sweep_smem_bytes(ctx, L), w.stream>>>(a);
 }
 
 template <int GL>
 static void launch_finish_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, const Workspace &ws,
-                            const uint32_t *masks, const int32_t *list, int n_active, int given_q)
+                            const uint32_t *masks, const int32_t *list, int n_active, int given_q, int hard)
 {
     FinishArgs a;
     a.part_m = w.pz_m;
@@ -923,7 +1043,10 @@ static void launch_finish_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w,
     a.red = ctx->red.as<double>();
     a.nbmax = ws.nbmax;
     a.given_q = given_q;
-    k_finish<GL, true><<<dim3(ws.nbz, n_active), FIN_THREADS, 0, ctx->stream>>>(a);
+    if (hard)
+        k_finish<GL, true, true><<<dim3(ws.nbz, n_active), FIN_THREADS, 0, w.stream>>>(a);
+    else
+        k_finish<GL, true, false><<<dim3(ws.nbz, n_active), FIN_THREADS, 0, w.stream>>>(a);
 }
 
 template <int GL>
@@ -943,132 +1066,168 @@ static void launch_finish_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w,
     a.logq0 = ctx->logq0.as<double>();
     a.logq0e = ctx->logq0e.as<double>();
     a.q_cur = ctx->qy_cur.as<double>();
-    a.x_next = ctx->xs.as<double>();
+    a.x_next = w.xs;
     a.red = ctx->red.as<double>();
     a.nbmax = ws.nbmax;
     a.given_q = 0;
-    k_finish<GL, false><<<dim3(ws.nby, n_active), FIN_THREADS, 0, ctx->stream>>>(a);
+    k_finish<GL, false, false><<<dim3(ws.nby, n_active), FIN_THREADS, 0, w.stream>>>(a);
 }
 
 template <int GL>
 static void launch_seed_s(arb_ctx *ctx, const WsPtrs &w, const uint32_t *masks, const double *q_src,
                           int64_t src_stride, const int32_t *list, int n_active, int K, int copy_q)
 {
-    k_seed_s<GL><<<dim3(grid_for(ctx->n_snvs, SEED_THREADS / GL), n_active), SEED_THREADS, 0, ctx->stream>>>(
-        q_src, src_stride, list, w.pos_z, w.st, masks, ctx->n_snvs, K, ctx->xs.as<double>(), ctx->qy_cur.as<double>(),
-        copy_q);
+    k_seed_s<GL><<<dim3(grid_for(ctx->n_snvs, SEED_THREADS / GL), n_active), SEED_THREADS, 0, w.stream>>>(
+        q_src, src_stride, list, w.pos_z, w.st, masks, ctx->n_snvs, K, w.xs, ctx->qy_cur.as<double>(), copy_q);
 }
 
 template <int GL>
 static void launch_seed_r(arb_ctx *ctx, const WsPtrs &w, const uint32_t *masks, const int32_t *list, int n_active,
                           int K)
 {
-    k_seed_r<GL><<<dim3(grid_for(ctx->n_cells, SEED_THREADS / GL), n_active), SEED_THREADS, 0, ctx->stream>>>(
-        ctx->qz_cur.as<double>(), list, w.st, masks, ctx->n_cells, K, ctx->xr.as<double>());
+    k_seed_r<GL><<<dim3(grid_for(ctx->n_cells, SEED_THREADS / GL), n_active), SEED_THREADS, 0, w.stream>>>(
+        ctx->qz_cur.as<double>(), list, w.st, masks, ctx->n_cells, K, w.xr);
 }
 
-// one fit of n_trees trees whose masks are on the device
+// One fit of n_trees trees whose masks are on the device.  The slots are split into stream groups;
+// every group advances its own trees round by round on its own stream (k_control -> seeds -> q(y)
+// sweep + finish -> q(z) sweep + finish -> k_control ...), the host only reads the group's three list
+// lengths between rounds.  While the host waits for one group, the other groups' rounds are queued,
+// so their finishing / seeding / control kernels run underneath this group's sweeps.
 template <int GL>
-static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, const FitTarget &tg, int64_t reserve)
+static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, int mode, const FitTarget &tg,
+                    int64_t reserve)
 {
     Workspace ws;
     ARB_TRY(ensure_workspace(ctx, K, std::min(n_trees, 1024), reserve, ws));
     const PanelLayout &L = ctx->layout[kp_index(ws.kp)];
     ARB_TRY(configure_kernels(ctx, L));
-    const WsPtrs w = ws_ptrs(ctx, L);
-    cudaStream_t st = ctx->stream;
+    const int G = ws.groups;
+    const bool hard = mode == ARB_MODE_ML;
     const int64_t nz = (int64_t)ctx->n_cells * K, ny = (int64_t)ctx->n_snvs * (K - 1);
-
-    Control h;
-    memset(&h, 0, sizeof h);
-    h.n_trees = n_trees;
-    h.n_slots = ws.n_slots;
-    h.max_iter = max_iter;
-    h.tol = tol;
-    h.sum_la = ctx->sum_la;
-    h.nbz = ws.nbz;
-    h.nby = ws.nby;
-    h.nbmax = ws.nbmax;
-    h.keep = tg.best_qz != nullptr;
-    ARB_CUDA(cudaMemsetAsync(w.st, 0, (size_t)ctx->ws_slots * sizeof(SlotState), st));
-    ARB_CUDA(cudaMemcpyAsync(w.ctl, &h, sizeof h, cudaMemcpyHostToDevice, st));
-
-    cudaEvent_t ev0, ev1, evs[6];
+    cudaStream_t main = ctx->stream;
+    WsPtrs w[ARB_MAX_GROUPS];
+    Control *h = reinterpret_cast<Control *>(ctx->h_ctl);
+    ARB_CUDA(cudaMemsetAsync(ctx->slot_state.p, 0, (size_t)ctx->ws_slots * sizeof(SlotState), main));
+    for (int g = 0; g < G; ++g) {
+        w[g] = ws_ptrs(ctx, L, g, ctx->gstream[g]);
+        w[g].n_slots = ws.sg;
+        Control &c = h[g];
+        memset(&c, 0, sizeof c);
+        c.next_tree = g;
+        c.tree_step = G;
+        c.n_trees = n_trees;
+        c.slot0 = w[g].slot0;
+        c.n_slots = ws.sg;
+        c.max_iter = max_iter;
+        c.tol = tol;
+        c.sum_la = ctx->sum_la;
+        c.nbz = ws.nbz;
+        c.nby = ws.nby;
+        c.nbmax = ws.nbmax;
+        c.keep = tg.best_qz != nullptr;
+        c.mode = mode;
+        ARB_CUDA(cudaMemcpyAsync(w[g].ctl, &c, sizeof c, cudaMemcpyHostToDevice, main));
+    }
+    cudaEvent_t ev0, ev1;
     ARB_CUDA(cudaEventCreate(&ev0));
     ARB_CUDA(cudaEventCreate(&ev1));
-    for (auto &e : evs) ARB_CUDA(cudaEventCreate(&e));
-    ARB_CUDA(cudaEventRecord(ev0, st));
+    ARB_CUDA(cudaEventRecord(ev0, main));
+    // the pinned Control blocks are reused for the read-backs: the uploads above must have left them
+    ARB_CUDA(cudaStreamSynchronize(main));
     FitStats stats;
-    k_control<<<1, 256, 0, st>>>(w.ctl, w.st, ctx->red.as<double>(), w.list_y, w.list_z, w.list_init, w.pos_z,
-                                 w.snap_tree, tg.elbo, tg.iters, tg.trace, 1);
-    stats.launches++;
-    int rc = ARB_OK;
-    bool pending_y = false, pending_z = false;
-    auto collect = [&]() {               // events of the previous round are complete after the sync
-        float t = 0;
-        if (pending_y) {
-            cudaEventElapsedTime(&t, evs[0], evs[1]); stats.sweep_y_ms += t;
-            cudaEventElapsedTime(&t, evs[1], evs[2]); stats.finish_ms += t; stats.finish_y_ms += t;
-        }
-        if (pending_z) {
-            cudaEventElapsedTime(&t, evs[3], evs[4]); stats.sweep_z_ms += t;
-            cudaEventElapsedTime(&t, evs[4], evs[5]); stats.finish_ms += t; stats.finish_z_ms += t;
-        }
-        pending_y = pending_z = false;
+    bool active[ARB_MAX_GROUPS] = {}, pending_y[ARB_MAX_GROUPS] = {}, pending_z[ARB_MAX_GROUPS] = {};
+    auto control = [&](int g, int first) {
+        const WsPtrs &p = w[g];
+        k_control<<<1, 256, 0, p.stream>>>(p.ctl, p.st, ctx->red.as<double>(), p.list_y, p.list_z, p.list_init,
+                                          p.pos_z, p.snap_tree, tg.elbo, tg.iters, tg.trace, first);
+        cudaMemcpyAsync(&h[g], p.ctl, sizeof(Control), cudaMemcpyDeviceToHost, p.stream);
+        cudaEventRecord(ctx->gevent[g][6], p.stream);
+        stats.launches++;
     };
-    for (;;) {
-        cudaError_t e = cudaMemcpyAsync(&h, w.ctl, sizeof h, cudaMemcpyDeviceToHost, st);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-        if (e != cudaSuccess) {
-            arb_set_error("fit round: %s", cudaGetErrorString(e));
-            rc = ARB_ERR_CUDA;
-            break;
-        }
-        collect();
-        if (h.n_z == 0) break;
-        stats.rounds += 1;
-        if (h.n_init > 0) {
-            launch_seed_s<GL>(ctx, w, tg.masks, ctx->q0.as<double>(), 0, w.list_init, h.n_init, K, 1);
-            stats.launches++;
-        }
-        if (h.n_y > 0) {
-            launch_seed_r<GL>(ctx, w, tg.masks, w.list_y, h.n_y, K);
-            cudaEventRecord(evs[0], st);
-            launch_sweep_y(ctx, L, w, h.n_y);
-            cudaEventRecord(evs[1], st);
-            launch_finish_y<GL>(ctx, L, w, ws, tg.masks, w.list_y, h.n_y);
-            cudaEventRecord(evs[2], st);
-            stats.launches += 3;
-            stats.launches_y += 1;
-            stats.tree_sweeps_y += h.n_y;
-            pending_y = true;
-        }
-        cudaEventRecord(evs[3], st);
-        launch_sweep_z(ctx, L, w, h.n_z);
-        cudaEventRecord(evs[4], st);
-        launch_finish_z<GL>(ctx, L, w, ws, tg.masks, w.list_z, h.n_z, 0);
-        cudaEventRecord(evs[5], st);
-        stats.launches_z += 1;
-        stats.tree_sweeps_z += h.n_z;
-        pending_z = true;
-        k_control<<<1, 256, 0, st>>>(w.ctl, w.st, ctx->red.as<double>(), w.list_y, w.list_z, w.list_init, w.pos_z,
-                                     w.snap_tree, tg.elbo, tg.iters, tg.trace, 0);
-        stats.launches += 3;
-        if (tg.best_qz) {
-            k_snapshot<<<dim3(16, ws.n_slots), 256, 0, st>>>(w.snap_tree, ctx->qz_cur.as<double>(),
-                                                            ctx->qy_cur.as<double>(), nz, ny, tg.best_qz, tg.best_qy);
-            stats.launches++;
+    for (int g = 0; g < G; ++g) {
+        active[g] = true;
+        control(g, 1);
+    }
+    int rc = ARB_OK, n_active = G;
+    while (n_active > 0 && rc == ARB_OK) {
+        for (int g = 0; g < G && rc == ARB_OK; ++g) {
+            if (!active[g]) continue;
+            const WsPtrs &p = w[g];
+            cudaEvent_t *evs = ctx->gevent[g];
+            cudaError_t e = cudaEventSynchronize(evs[6]);
+            if (e != cudaSuccess) {
+                arb_set_error("fit round: %s", cudaGetErrorString(e));
+                rc = ARB_ERR_CUDA;
+                break;
+            }
+            const Control c = h[g];
+            if (c.n_z == 0) {
+                active[g] = false;
+                --n_active;
+            }
+            // the events of the group's previous round precede its control kernel in the stream
+            float t = 0;
+            if (pending_y[g]) {
+                cudaEventElapsedTime(&t, evs[0], evs[1]); stats.sweep_y_ms += t;
+                cudaEventElapsedTime(&t, evs[1], evs[2]); stats.finish_ms += t; stats.finish_y_ms += t;
+            }
+            if (pending_z[g]) {
+                cudaEventElapsedTime(&t, evs[3], evs[4]); stats.sweep_z_ms += t;
+                cudaEventElapsedTime(&t, evs[4], evs[5]); stats.finish_ms += t; stats.finish_z_ms += t;
+            }
+            pending_y[g] = pending_z[g] = false;
+            if (!active[g]) continue;
+            stats.rounds += 1;
+            if (c.n_init > 0) {
+                launch_seed_s<GL>(ctx, p, tg.masks, hard ? ctx->q0_hard.as<double>() : ctx->q0.as<double>(), 0,
+                                  p.list_init, c.n_init, K, 1);
+                stats.launches++;
+            }
+            if (c.n_y > 0) {
+                launch_seed_r<GL>(ctx, p, tg.masks, p.list_y, c.n_y, K);
+                cudaEventRecord(evs[0], p.stream);
+                launch_sweep_y(ctx, L, p, c.n_y);
+                cudaEventRecord(evs[1], p.stream);
+                launch_finish_y<GL>(ctx, L, p, ws, tg.masks, p.list_y, c.n_y);
+                cudaEventRecord(evs[2], p.stream);
+                stats.launches += 3;
+                stats.launches_y += 1;
+                stats.tree_sweeps_y += c.n_y;
+                pending_y[g] = true;
+            }
+            cudaEventRecord(evs[3], p.stream);
+            launch_sweep_z(ctx, L, p, c.n_z);
+            cudaEventRecord(evs[4], p.stream);
+            launch_finish_z<GL>(ctx, L, p, ws, tg.masks, p.list_z, c.n_z, 0, hard);
+            cudaEventRecord(evs[5], p.stream);
+            stats.launches += 2;
+            stats.launches_z += 1;
+            stats.tree_sweeps_z += c.n_z;
+            pending_z[g] = true;
+            control(g, 0);
+            if (tg.best_qz) {
+                k_snapshot<<<dim3(16, ws.sg), 256, 0, p.stream>>>(p.snap_tree, ctx->qz_cur.as<double>(),
+                                                                 ctx->qy_cur.as<double>(), nz, ny, tg.best_qz,
+                                                                 tg.best_qy, p.slot0);
+                stats.launches++;
+            }
         }
     }
-    cudaEventRecord(ev1, st);
+    // join the groups into the context's stream
+    for (int g = 0; g < G; ++g) {
+        cudaEventRecord(ctx->gevent[g][7], w[g].stream);
+        cudaStreamWaitEvent(main, ctx->gevent[g][7], 0);
+    }
+    cudaEventRecord(ev1, main);
     cudaEventSynchronize(ev1);
     float ms = 0;
     cudaEventElapsedTime(&ms, ev0, ev1);
     cudaEventDestroy(ev0);
     cudaEventDestroy(ev1);
-    for (auto &e : evs) cudaEventDestroy(e);
     stats.sweep_ms = stats.sweep_z_ms + stats.sweep_y_ms;
     stats.device_ms = ms;
+    stats.groups = G;
     ctx->stats = stats;
     if (rc == ARB_OK) {
         cudaError_t e = cudaGetLastError();
@@ -1080,14 +1239,14 @@ static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, 
     return rc;
 }
 
-static int fit_dispatch(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, const FitTarget &tg,
+static int fit_dispatch(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, int mode, const FitTarget &tg,
                         int64_t reserve)
 {
     switch (gl_for(K)) {
-    case 1: return fit_core<1>(ctx, n_trees, K, max_iter, tol, tg, reserve);
-    case 2: return fit_core<2>(ctx, n_trees, K, max_iter, tol, tg, reserve);
-    case 4: return fit_core<4>(ctx, n_trees, K, max_iter, tol, tg, reserve);
-    default: return fit_core<8>(ctx, n_trees, K, max_iter, tol, tg, reserve);
+    case 1: return fit_core<1>(ctx, n_trees, K, max_iter, tol, mode, tg, reserve);
+    case 2: return fit_core<2>(ctx, n_trees, K, max_iter, tol, mode, tg, reserve);
+    case 4: return fit_core<4>(ctx, n_trees, K, max_iter, tol, mode, tg, reserve);
+    default: return fit_core<8>(ctx, n_trees, K, max_iter, tol, mode, tg, reserve);
     }
 }
 
@@ -1106,8 +1265,7 @@ static int check_ready(arb_ctx *ctx, int K, const char *who)
 static int run_fit(arb_ctx *ctx, int32_t n_trees, int32_t K, int32_t max_iter, double tol, int32_t mode,
                    int32_t keep, double *elbo, int32_t *iters, double *elbo_trace)
 {
-    ARB_REQUIRE(mode == ARB_MODE_VI, ARB_ERR_UNSUPPORTED,
-                "mode %d: only ARB_MODE_VI is implemented in this release", mode);
+    ARB_REQUIRE(mode == ARB_MODE_VI || mode == ARB_MODE_ML, ARB_ERR_INVALID, "unknown fit mode %d", mode);
     ARB_REQUIRE(max_iter >= 0, ARB_ERR_INVALID, "max_iter=%d", max_iter);
     cudaStream_t st = ctx->stream;
     const int64_t nz = (int64_t)ctx->n_cells * K, ny = (int64_t)ctx->n_snvs * (K - 1);
@@ -1138,7 +1296,7 @@ static int run_fit(arb_ctx *ctx, int32_t n_trees, int32_t K, int32_t max_iter, d
     }
     ctx->fit_trees = 0;
     ctx->single_tree = -1;
-    ARB_TRY(fit_dispatch(ctx, n_trees, K, max_iter, tol, tg, reserve));
+    ARB_TRY(fit_dispatch(ctx, n_trees, K, max_iter, tol, mode, tg, reserve));
     ARB_CUDA(cudaMemcpyAsync(elbo, tg.elbo, (size_t)n_trees * 8, cudaMemcpyDeviceToHost, st));
     ARB_CUDA(cudaMemcpyAsync(iters, tg.iters, (size_t)n_trees * 4, cudaMemcpyDeviceToHost, st));
     if (elbo_trace) ARB_CUDA(cudaMemcpyAsync(elbo_trace, tg.trace, trace_n * 8, cudaMemcpyDeviceToHost, st));
@@ -1237,7 +1395,7 @@ static int locate_fit(arb_ctx *ctx, int32_t t, const double **qz, const double *
         tg.best_qz = ctx->single_qz.as<double>();
         tg.best_qy = ctx->single_qy.as<double>();
         const FitStats keep_stats = ctx->stats;
-        int rc = fit_dispatch(ctx, 1, K, ctx->fit_max_iter, ctx->fit_tol, tg, 0);
+        int rc = fit_dispatch(ctx, 1, K, ctx->fit_max_iter, ctx->fit_tol, ctx->fit_mode, tg, 0);
         ctx->stats = keep_stats;
         tmp.release();
         ARB_TRY(rc);
@@ -1304,18 +1462,19 @@ ARB_API int arb_last_fit_stats(arb_ctx *ctx, int64_t *kernel_launches, double *d
 
 // [sweep_z_ms, sweep_y_ms, finish_ms, tree_sweeps_z, tree_sweeps_y, launches_z, launches_y, rounds,
 //  finish_z_ms, finish_y_ms, KP, panel_rows, panels_z, panels_y, tiles_per_warp_z, tiles_per_warp_y,
-//  fold_z, fold_y, quads_z, quads_y]
+//  fold_z, fold_y, quads_z, quads_y, stream groups]
 ARB_API int arb_last_fit_profile(arb_ctx *ctx, double *values, int32_t n_values)
 {
     ARB_REQUIRE(ctx && values && n_values >= 0, ARB_ERR_INVALID, "arb_last_fit_profile: bad argument");
     const FitStats &s = ctx->stats;
     PanelLayout none;
     const PanelLayout &L = ctx->ws_kp ? ctx->layout[kp_index(ctx->ws_kp)] : none;
-    const double v[20] = {s.sweep_z_ms, s.sweep_y_ms, s.finish_ms, s.tree_sweeps_z, s.tree_sweeps_y,
+    const double v[21] = {s.sweep_z_ms, s.sweep_y_ms, s.finish_ms, s.tree_sweeps_z, s.tree_sweeps_y,
                           s.launches_z, s.launches_y, s.rounds, s.finish_z_ms, s.finish_y_ms,
                           (double)L.kp, (double)L.panel_rows, (double)L.np_z, (double)L.np_y, (double)L.uz,
-                          (double)L.uy, (double)L.fold_z, (double)L.fold_y, (double)L.quads_z, (double)L.quads_y};
-    for (int i = 0; i < n_values && i < 20; ++i) values[i] = v[i];
+                          (double)L.uy, (double)L.fold_z, (double)L.fold_y, (double)L.quads_z, (double)L.quads_y,
+                          s.groups};
+    for (int i = 0; i < n_values && i < 21; ++i) values[i] = v[i];
     return ARB_OK;
 }
 
@@ -1327,8 +1486,11 @@ static int finish_prior(arb_ctx *ctx, int32_t C)
     const int64_t n = (int64_t)ctx->n_snvs * C;
     ARB_TRY(ctx->logq0.reserve(n * 8));
     ARB_TRY(ctx->logq0e.reserve(n * 8));
+    ARB_TRY(ctx->q0_hard.reserve(n * 8));
     k_prior_logs<<<grid_for(n, 256), 256, 0, ctx->stream>>>(ctx->q0.as<double>(), n, ctx->logq0.as<double>(),
                                                            ctx->logq0e.as<double>());
+    k_prior_hard<<<grid_for(ctx->n_snvs, 256), 256, 0, ctx->stream>>>(ctx->q0.as<double>(), ctx->n_snvs, C,
+                                                                     ctx->q0_hard.as<double>());
     ARB_CUDA(cudaStreamSynchronize(ctx->stream));
     ctx->n_clusters = C;
     ctx->single_tree = -1;
@@ -1396,7 +1558,7 @@ static int hook_setup(arb_ctx *ctx, int K, const uint8_t *presence, HookEnv &env
     ARB_CUDA(cudaSetDevice(ctx->device));
     ARB_TRY(ensure_workspace(ctx, K, 1, 0, env.ws));
     env.L = &ctx->layout[kp_index(env.ws.kp)];
-    env.w = ws_ptrs(ctx, *env.L);
+    env.w = ws_ptrs(ctx, *env.L, 0, ctx->stream);
     ARB_TRY(configure_kernels(ctx, *env.L));
     const int C = K - 1;
     DevBuf d_p;
@@ -1438,7 +1600,7 @@ ARB_API int arb_qz_update(arb_ctx *ctx, int32_t n_clones, const uint8_t *presenc
     GL_SWITCH(K, {
         launch_seed_s<GLV>(ctx, env.w, mk, ctx->qy_cur.as<double>(), (int64_t)ctx->n_snvs * C, env.list0, 1, K, 0);
         launch_sweep_z(ctx, *env.L, env.w, 1);
-        launch_finish_z<GLV>(ctx, *env.L, env.w, env.ws, mk, env.list0, 1, 0);
+        launch_finish_z<GLV>(ctx, *env.L, env.w, env.ws, mk, env.list0, 1, 0, 0);
     });
     ARB_CUDA(cudaMemcpyAsync(q_z, ctx->qz_cur.p, (size_t)ctx->n_cells * K * 8, cudaMemcpyDeviceToHost, ctx->stream));
     ARB_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -1483,7 +1645,7 @@ ARB_API int arb_elbo_terms(arb_ctx *ctx, int32_t n_clones, const uint8_t *presen
     GL_SWITCH(K, {
         launch_seed_s<GLV>(ctx, env.w, mk, ctx->qy_cur.as<double>(), ny, env.list0, 1, K, 0);
         launch_sweep_z(ctx, *env.L, env.w, 1);
-        launch_finish_z<GLV>(ctx, *env.L, env.w, env.ws, mk, env.list0, 1, 1);
+        launch_finish_z<GLV>(ctx, *env.L, env.w, env.ws, mk, env.list0, 1, 1, 0);
     });
     DevBuf out;
     ARB_TRY(out.reserve(16));

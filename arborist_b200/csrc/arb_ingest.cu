@@ -94,13 +94,18 @@ ARB_API int arb_ctx_destroy(arb_ctx *ctx)
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     DevBuf *bufs[] = {&ctx->coo_cell, &ctx->coo_snv, &ctx->coo_code, &ctx->cell_order,
-                      &ctx->snv_order, &ctx->tab_dw, &ctx->q0, &ctx->logq0, &ctx->logq0e,
+                      &ctx->snv_order, &ctx->tab_dw, &ctx->q0, &ctx->logq0, &ctx->logq0e, &ctx->q0_hard,
                       &ctx->xs, &ctx->xr, &ctx->qz_cur, &ctx->qy_cur, &ctx->part_z, &ctx->part_g,
                       &ctx->part_y, &ctx->red, &ctx->slot_state, &ctx->lists, &ctx->masks,
                       &ctx->best_qz, &ctx->best_qy, &ctx->d_elbo, &ctx->d_iters, &ctx->d_trace,
                       &ctx->tree_masks, &ctx->single_qz, &ctx->single_qy, &ctx->scratch};
     for (DevBuf *b : bufs) b->release();
     for (auto &l : ctx->layout) l.release();
+    for (int g = 0; g < ARB_MAX_GROUPS; ++g) {
+        if (ctx->gstream[g]) cudaStreamDestroy(ctx->gstream[g]);
+        for (auto &e : ctx->gevent[g]) if (e) cudaEventDestroy(e);
+    }
+    if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
     return ARB_OK;
@@ -115,6 +120,11 @@ ARB_API int arb_set_option(arb_ctx *ctx, const char *name, int64_t value)
         for (auto &l : ctx->layout) l.release();
         ctx->ws_kp = 0;                      // partial buffers are sized by the panel count
     } else if (!strcmp(name, "threads")) ctx->opt_threads = value;
+    else if (!strcmp(name, "groups")) {
+        ARB_REQUIRE(value >= 0 && value <= ARB_MAX_GROUPS, ARB_ERR_INVALID, "arb_set_option: groups=%lld outside 0..%d",
+                    (long long)value, ARB_MAX_GROUPS);
+        ctx->opt_groups = value;
+    }
     else if (!strcmp(name, "no_fold")) {
         ctx->opt_no_fold = value;
         for (auto &l : ctx->layout) l.release();

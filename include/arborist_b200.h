@@ -148,14 +148,16 @@ int arb_elbo_terms(arb_ctx *ctx, int32_t n_clones, const uint8_t *presence, cons
  * CAVI tree-iterations it executed (initial pass = half an iteration) */
 int arb_last_fit_stats(arb_ctx *ctx, int64_t *kernel_launches, double *device_ms,
                        double *tree_iterations, double *sweep_ms);
-/* per-kernel profile of the last arb_fit_* call, measured with CUDA events on the context's
- * stream: values[0..7] = q(z) sweep ms, q(y) sweep ms, finishing kernels ms, tree-sweeps done
+/* per-kernel profile of the last arb_fit_* call, measured with CUDA events on the launching
+ * streams (with more than one stream group the kernels of different groups overlap, so the
+ * per-kernel times are not exclusive; set option "groups" to 1 for exclusive times): values[0..7] = q(z) sweep ms, q(y) sweep ms, finishing kernels ms, tree-sweeps done
  * by the q(z) / q(y) sweep launches, number of q(z) / q(y) sweep launches, rounds;
  * values[8..19] = q(z) / q(y) finishing ms, then the layout in use: KP, rows per panel, panels
- * (z, y), tiles per warp (z, y), range-proof flags (z, y), stream quads (z, y) */
+ * (z, y), tiles per warp (z, y), range-proof flags (z, y), stream quads (z, y); values[20] = stream
+ * groups used */
 int arb_last_fit_profile(arb_ctx *ctx, double *values, int32_t n_values);
-/* tuning knobs: "slots" (trees in flight), "panel_kb" (panel bytes cap), "threads"; returns ARB_ERR_INVALID
- * for unknown names */
+/* tuning knobs: "slots" (trees in flight), "groups" (stream groups the slots are split into, 0 = default,
+ * at most 4), "panel_kb" (panel bytes cap), "threads", "no_fold"; returns ARB_ERR_INVALID for unknown names */
 int arb_set_option(arb_ctx *ctx, const char *name, int64_t value);
 
 #ifdef __cplusplus

@@ -236,6 +236,74 @@ def test_seam_run_variational_inference(eng_mod):
         np.testing.assert_allclose(qy, g["q_y"][t], rtol=Q_RTOL, atol=Q_ATOL)
 
 
+@pytest.mark.parametrize("name", SMALL)
+def test_seam_run_simple_max_likelihood(eng_mod, name):
+    """Hard-assignment mode behind the same 13-argument seam (A.py:598-676): likelihood under the
+    MAP cluster of the prior and the MAP clone of q(z); returns the soft q(z) and the one-hot q(y)."""
+    from arborist_b200 import run_simple_max_likelihood
+    g = load_golden(name)
+    n, m, K = int(g["n_cells"]), int(g["n_snvs"]), int(g["n_clones"])
+    lik, qz, qy = run_simple_max_likelihood(
+        g["presence"][0], g["ll_cs"], g["ll_ss"], g["cell_idx_ss"], g["snv_idx_cs"], n, m, K,
+        g["q_y_init"], g["cell_ptr"], g["snv_ptr"])
+    assert lik == pytest.approx(float(g["ml_lik"]), rel=ELBO_RTOL)
+    np.testing.assert_allclose(qz, g["ml_qz"], rtol=Q_RTOL, atol=Q_ATOL)
+    assert np.array_equal(qy, g["ml_qy"])                      # one-hot: bit-exact
+    assert_map_equal(qz, g["ml_qz"])
+
+
+def test_ml_mode_batched_matches_oracle(eng_mod):
+    """ARB_MODE_ML over a whole candidate set in one call vs the oracle's per-tree hard scorer."""
+    from oracle import oracle as orc
+    g = load_golden("small")
+    n, m, K = int(g["n_cells"]), int(g["n_snvs"]), int(g["n_clones"])
+    e, _, _ = _coo_engine(eng_mod, g)
+    e.set_prior(g["q_y_init"])
+    P = np.ascontiguousarray(g["presence"] != 0, np.uint8)
+    lik, iters = e.fit(presence=P, n_clones=K, max_iter=10, tolerance=1.0, mode="ml", keep_posteriors="all")
+    assert np.all(iters == 0)
+    want = []
+    for t in range(P.shape[0]):
+        l, qz, qy = orc.run_simple_max_likelihood(
+            g["presence"][t], g["ll_cs"], g["ll_ss"], g["cell_idx_ss"], g["snv_idx_cs"], n, m, K,
+            g["q_y_init"], g["cell_ptr"], g["snv_ptr"])
+        want.append(l)
+        gz, gy = e.get_fit(t)
+        np.testing.assert_allclose(gz, qz, rtol=Q_RTOL, atol=Q_ATOL)
+        assert np.array_equal(gy, qy)
+    want = np.array(want)
+    np.testing.assert_allclose(lik, want, rtol=ELBO_RTOL)
+    assert np.array_equal(np.argsort(-lik, kind="stable"), np.argsort(-want, kind="stable"))
+    e.close()
+
+
+def test_stream_groups_do_not_change_bits(eng_mod):
+    """The slots are split into stream groups whose rounds overlap on the device; the split must not
+    change a single bit of any result (ELBOs, iteration counts, posteriors)."""
+    from arborist_b200.arborist import add_normal_clone, prepare_trees
+    g = load_golden("small")
+    e, _, _ = _coo_engine(eng_mod, g)
+    e.set_prior(g["q_y_init"])
+    trees, _, _ = golden_frames(g)
+    c2i, _, parents, _, normal = prepare_trees(add_normal_clone(trees))
+    K = len(c2i)
+    e.set_option("groups", 1)
+    ref = e.fit(parents=parents, n_clones=K, normal_idx=normal, max_iter=25, tolerance=1.0, keep_posteriors="all")
+    assert e.last_fit_profile()["groups"] == 1
+    ref_q = [e.get_fit(t) for t in range(len(parents))]
+    for groups, slots in ((2, 0), (3, 0), (4, 0), (4, 5), (2, 3)):
+        e.set_option("groups", groups)
+        e.set_option("slots", slots)
+        got = e.fit(parents=parents, n_clones=K, normal_idx=normal, max_iter=25, tolerance=1.0,
+                    keep_posteriors="all")
+        assert e.last_fit_profile()["groups"] == min(groups, slots or groups)
+        assert np.array_equal(got[0], ref[0]) and np.array_equal(got[1], ref[1])
+        for t in (0, len(parents) - 1):
+            qz, qy = e.get_fit(t)
+            assert np.array_equal(qz, ref_q[t][0]) and np.array_equal(qy, ref_q[t][1])
+    e.close()
+
+
 def test_slot_count_and_duplicates_do_not_change_bits(eng_mod):
     """Determinism: results are independent of how many trees are in flight, and duplicate
     trees get bit-identical ELBOs (the reference has both properties)."""

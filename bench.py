@@ -154,7 +154,11 @@ class CpuArm:
         from oracle import oracle as orc
 
         self.orc, self.iters, self.trees, self.tps = orc, iters, trees, trees_per_step
-        self.cores = orc.lib().orc_max_threads()
+        # every core this process may run on (torchrun exports OMP_NUM_THREADS=1: do not inherit that)
+        try:
+            self.cores = len(os.sched_getaffinity(0))
+        except AttributeError:
+            self.cores = os.cpu_count() or 1
         orc.lib().orc_set_threads(self.cores)
         self.prob = orc.prepare(trees[:1], d.read_counts_frame(), d.clusters_frame(), alpha=RUN["alpha"],
                                 gamma=RUN["gamma"], add_normal=True)

@@ -81,6 +81,7 @@ struct PanelLayout {
     int np_z = 0, np_y = 0;  // number of panels
     int uz = 0, uy = 0;      // tiles per warp per panel
     int fold_z = 0, fold_y = 0;   // 1: a tile's running product provably stays inside the double range
+    int w16 = 0;                  // 1: 16-bit stream words {row | code << 11} (<= 32 pair codes, < 2048 panel rows)
     int64_t quads_z = 0, quads_y = 0;   // stream length in quads (x TW x 16 bytes)
     DevBuf zdesc, zrows, zstream;
     DevBuf ydesc, yrows, ystream;
@@ -125,7 +126,7 @@ struct arb_ctx {
 
     // ---- layouts (index 0: KP 8, 1: KP 16, 2: KP 32) ----------------------------------
     PanelLayout layout[3];
-    int64_t opt_slots = 0, opt_panel_kb = 0, opt_threads = 0, opt_no_fold = 0, opt_groups = 0;
+    int64_t opt_slots = 0, opt_panel_kb = 0, opt_threads = 0, opt_no_fold = 0, opt_groups = 0, opt_w32 = 0;
 
     // ---- fit workspace -----------------------------------------------------------------
     // The slots are split into `ws_groups` stream groups of `ws_sg` slots; every group runs its own

@@ -244,7 +244,7 @@ struct SweepArgs {
     int32_t n_gather;          // rows of the gathered operand
     const int4 *desc;          // [n_panels * WARPS * tiles_per_warp] {first quad, A quads, all quads, 0}
     const int32_t *rows;       // [.. * TW] row of every segment of every tile, -1 = none
-    const uint4 *stream;       // [quad][TW]
+    const void *stream;        // [quad][TW] of uint4 (32-bit words) or uint2 (16-bit words, W16)
     int32_t n_rows, panel_rows, n_panels, tiles_per_warp;
     int32_t n_vslots;          // virtual slots in this launch (grid = n_vslots * n_panels)
     const double2 *dw;         // per pair code: (d, w)
@@ -280,7 +280,20 @@ __device__ __forceinline__ void sweep_step(const char *xa_base, const char *xb_b
 // a quarter-warp cover all 32 banks.  Every lane of a group loads the same uint4 of four stream
 // words (a warp reads TW*16 contiguous bytes per quad), three quads ahead of the one in use; there
 // are no shuffles, no predicates and no per-segment pointers in the loop.
-template <int KP, bool WITH_G, bool FOLD>
+template <bool W16> struct StreamQuad { typedef uint4 type; };
+template <> struct StreamQuad<true> { typedef uint2 type; };
+// the four stream words of a quad as {byte offset of the gathered row | code << 18}
+__device__ __forceinline__ void quad_words(const uint4 &q, uint32_t (&w)[4]) { w[0] = q.x; w[1] = q.y; w[2] = q.z; w[3] = q.w; }
+// 16-bit words {row | code << 11}; rows are 128 bytes (ARB_VW doubles), so word << 7 is the 32-bit form
+__device__ __forceinline__ void quad_words(const uint2 &q, uint32_t (&w)[4])
+{
+    w[0] = (q.x << 7) & 0x7fff80u;
+    w[1] = (q.x >> 9) & 0x7fff80u;
+    w[2] = (q.y << 7) & 0x7fff80u;
+    w[3] = (q.y >> 9) & 0x7fff80u;
+}
+
+template <int KP, bool WITH_G, bool FOLD, bool W16>
 __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const SweepArgs a)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -338,8 +351,9 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const SweepAr
     // start the stream before waiting for the panel
     int4 dn = __ldg(desc);
     int rown = __ldg(rows);
-    const uint4 *__restrict__ sp = a.stream + (int64_t)dn.x * TW + grp;
-    uint4 w0 = __ldg(sp), w1 = __ldg(sp + TW), w2 = __ldg(sp + 2 * TW);
+    typedef typename StreamQuad<W16>::type Quad;
+    const Quad *__restrict__ sp = reinterpret_cast<const Quad *>(a.stream) + (int64_t)dn.x * TW + grp;
+    Quad w0 = __ldg(sp), w1 = __ldg(sp + TW), w2 = __ldg(sp + 2 * TW);
     sp += 3 * TW;
 
     __syncthreads();
@@ -361,16 +375,17 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const SweepAr
         // one quad = four steps of every segment of the tile; WC is consumed, then refilled three quads ahead
 #define ARB_QUAD_A(WC)                                                                          \
     {                                                                                           \
-        const uint4 w = WC;                                                                     \
+        uint32_t w[4];                                                                          \
+        quad_words(WC, w);                                                                      \
         WC = __ldg(sp);                                                                         \
         sp += TW;                                                                               \
-        sweep_step<WITH_G>(xa_base, xb_base, w.x, dw0.x, dw0.y, p, g);                          \
+        sweep_step<WITH_G>(xa_base, xb_base, w[0], dw0.x, dw0.y, p, g);                         \
         if (!FOLD && each) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);                      \
-        sweep_step<WITH_G>(xa_base, xb_base, w.y, dw0.x, dw0.y, p, g);                          \
+        sweep_step<WITH_G>(xa_base, xb_base, w[1], dw0.x, dw0.y, p, g);                         \
         if (!FOLD && each) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);                      \
-        sweep_step<WITH_G>(xa_base, xb_base, w.z, dw0.x, dw0.y, p, g);                          \
+        sweep_step<WITH_G>(xa_base, xb_base, w[2], dw0.x, dw0.y, p, g);                         \
         if (!FOLD && each) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);                      \
-        sweep_step<WITH_G>(xa_base, xb_base, w.w, dw0.x, dw0.y, p, g);                          \
+        sweep_step<WITH_G>(xa_base, xb_base, w[3], dw0.x, dw0.y, p, g);                         \
         if (!FOLD && ++since >= a.renorm_quads) {                                               \
             since = 0;                                                                          \
             for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);                                     \
@@ -378,7 +393,8 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const SweepAr
     }
 #define ARB_QUAD_G(WC)                                                                          \
     {                                                                                           \
-        const uint32_t ww[4] = {WC.x, WC.y, WC.z, WC.w};                                        \
+        uint32_t ww[4];                                                                         \
+        quad_words(WC, ww);                                                                     \
         WC = __ldg(sp);                                                                         \
         sp += TW;                                                                               \
         _Pragma("unroll") for (int s = 0; s < 4; ++s) {                                         \
@@ -392,8 +408,8 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const SweepAr
             for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);                                     \
         }                                                                                       \
     }
-#define ARB_ROT1 { const uint4 t = w0; w0 = w1; w1 = w2; w2 = t; }
-#define ARB_ROT2 { const uint4 t = w2; w2 = w1; w1 = w0; w0 = t; }
+#define ARB_ROT1 { const Quad t = w0; w0 = w1; w1 = w2; w2 = t; }
+#define ARB_ROT2 { const Quad t = w2; w2 = w1; w1 = w0; w0 = t; }
         // ---- A region: the most frequent (alt,total) pair; d and w live in registers ------------
         {
             int q = dc.y;
@@ -821,10 +837,12 @@ static inline int gl_for(int K) { const int c = chunks_for(K); return c <= 1 ? 1
 static int configure_kernels(const arb_ctx *ctx, const PanelLayout &L)
 {
     const int smem = (int)sweep_smem_bytes(ctx, L);
-    ARB_CUDA(cudaFuncSetAttribute(k_sweep<ARB_VW, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    ARB_CUDA(cudaFuncSetAttribute(k_sweep<ARB_VW, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    ARB_CUDA(cudaFuncSetAttribute(k_sweep<ARB_VW, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    ARB_CUDA(cudaFuncSetAttribute(k_sweep<ARB_VW, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+#define ARB_SET_SMEM(G, F, W) \
+    ARB_CUDA(cudaFuncSetAttribute(k_sweep<ARB_VW, G, F, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem))
+    ARB_SET_SMEM(true, false, false); ARB_SET_SMEM(false, false, false); ARB_SET_SMEM(true, true, false);
+    ARB_SET_SMEM(false, true, false); ARB_SET_SMEM(true, false, true); ARB_SET_SMEM(false, false, true);
+    ARB_SET_SMEM(true, true, true); ARB_SET_SMEM(false, true, true);
+#undef ARB_SET_SMEM
     return ARB_OK;
 }
 
@@ -967,6 +985,18 @@ static WsPtrs ws_ptrs(arb_ctx *ctx, const PanelLayout &L, int g, cudaStream_t st
     return w;
 }
 
+template <bool WITH_G>
+static void launch_sweep(const SweepArgs &a, int grid, int fold, int w16, size_t smem, cudaStream_t st)
+{
+    if (fold) {
+        if (w16) k_sweep<ARB_VW, WITH_G, true, true><<<grid, SWEEP_THREADS, smem, st>>>(a);
+        else k_sweep<ARB_VW, WITH_G, true, false><<<grid, SWEEP_THREADS, smem, st>>>(a);
+    } else {
+        if (w16) k_sweep<ARB_VW, WITH_G, false, true><<<grid, SWEEP_THREADS, smem, st>>>(a);
+        else k_sweep<ARB_VW, WITH_G, false, false><<<grid, SWEEP_THREADS, smem, st>>>(a);
+    }
+}
+
 // q(z) sweep over the packed S rows of the first n_trees entries of the group's q(z) list
 static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, int n_trees)
 {
@@ -976,7 +1006,7 @@ static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.n_gather = ctx->n_snvs;
     a.desc = L.zdesc.as<int4>();
     a.rows = L.zrows.as<int32_t>();
-    a.stream = L.zstream.as<uint4>();
+    a.stream = L.zstream.p;
     a.n_rows = ctx->n_cells;
     a.panel_rows = L.panel_rows;
     a.n_panels = L.np_z;
@@ -989,10 +1019,7 @@ static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.out_m = w.pz_m;
     a.out_e = w.pz_e;
     const int grid = a.n_vslots * L.np_z;
-    if (L.fold_z)
-        k_sweep<ARB_VW, true, true><<<grid, SWEEP_THREADS, sweep_smem_bytes(ctx, L), w.stream>>>(a);
-    else
-        k_sweep<ARB_VW, true, false><<<grid, SWEEP_THREADS, sweep_smem_bytes(ctx, L), w.stream>>>(a);
+    launch_sweep<true>(a, grid, L.fold_z, L.w16, sweep_smem_bytes(ctx, L), w.stream);
 }
 
 static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, int n_trees)
@@ -1003,7 +1030,7 @@ static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.n_gather = ctx->n_cells;
     a.desc = L.ydesc.as<int4>();
     a.rows = L.yrows.as<int32_t>();
-    a.stream = L.ystream.as<uint4>();
+    a.stream = L.ystream.p;
     a.n_rows = ctx->n_snvs;
     a.panel_rows = L.panel_rows;
     a.n_panels = L.np_y;
@@ -1016,10 +1043,7 @@ static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.out_m = w.py_m;
     a.out_e = w.py_e;
     const int grid = a.n_vslots * L.np_y;
-    if (L.fold_y)
-        k_sweep<ARB_VW, false, true><<<grid, SWEEP_THREADS, sweep_smem_bytes(ctx, L), w.stream>>>(a);
-    else
-        k_sweep<ARB_VW, false, false><<<grid, SWEEP_THREADS, sweep_smem_bytes(ctx, L), w.stream>>>(a);
+    launch_sweep<false>(a, grid, L.fold_y, L.w16, sweep_smem_bytes(ctx, L), w.stream);
 }
 
 template <int GL>
@@ -1462,19 +1486,19 @@ ARB_API int arb_last_fit_stats(arb_ctx *ctx, int64_t *kernel_launches, double *d
 
 // [sweep_z_ms, sweep_y_ms, finish_ms, tree_sweeps_z, tree_sweeps_y, launches_z, launches_y, rounds,
 //  finish_z_ms, finish_y_ms, KP, panel_rows, panels_z, panels_y, tiles_per_warp_z, tiles_per_warp_y,
-//  fold_z, fold_y, quads_z, quads_y, stream groups]
+//  fold_z, fold_y, quads_z, quads_y, stream groups, 16-bit stream words]
 ARB_API int arb_last_fit_profile(arb_ctx *ctx, double *values, int32_t n_values)
 {
     ARB_REQUIRE(ctx && values && n_values >= 0, ARB_ERR_INVALID, "arb_last_fit_profile: bad argument");
     const FitStats &s = ctx->stats;
     PanelLayout none;
     const PanelLayout &L = ctx->ws_kp ? ctx->layout[kp_index(ctx->ws_kp)] : none;
-    const double v[21] = {s.sweep_z_ms, s.sweep_y_ms, s.finish_ms, s.tree_sweeps_z, s.tree_sweeps_y,
+    const double v[22] = {s.sweep_z_ms, s.sweep_y_ms, s.finish_ms, s.tree_sweeps_z, s.tree_sweeps_y,
                           s.launches_z, s.launches_y, s.rounds, s.finish_z_ms, s.finish_y_ms,
                           (double)L.kp, (double)L.panel_rows, (double)L.np_z, (double)L.np_y, (double)L.uz,
                           (double)L.uy, (double)L.fold_z, (double)L.fold_y, (double)L.quads_z, (double)L.quads_y,
-                          s.groups};
-    for (int i = 0; i < n_values && i < 21; ++i) values[i] = v[i];
+                          s.groups, (double)L.w16};
+    for (int i = 0; i < n_values && i < 22; ++i) values[i] = v[i];
     return ARB_OK;
 }
 

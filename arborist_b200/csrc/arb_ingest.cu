@@ -125,6 +125,11 @@ ARB_API int arb_set_option(arb_ctx *ctx, const char *name, int64_t value)
                     (long long)value, ARB_MAX_GROUPS);
         ctx->opt_groups = value;
     }
+    else if (!strcmp(name, "w32")) {          // force 32-bit stream words
+        ctx->opt_w32 = value;
+        for (auto &l : ctx->layout) l.release();
+        ctx->ws_kp = 0;
+    }
     else if (!strcmp(name, "no_fold")) {
         ctx->opt_no_fold = value;
         for (auto &l : ctx->layout) l.release();
@@ -481,9 +486,12 @@ __global__ void k_fill_u32(uint32_t *v, int64_t n, uint32_t x)
     if (i < n) v[i] = x;
 }
 
+// W16: 16-bit words {row in panel | code << 11} (the sweep shifts them left by 7 = log2 of the 128-byte row);
+// else 32-bit words {byte offset of the row | code << 18}
+template <bool W16>
 __global__ void k_tile_scatter(const uint64_t *sorted_key, int64_t nnz, const int32_t *start,
                                const int32_t *pos_of_seg, const int32_t *qoff, const int32_t *naq, int32_t n_rows,
-                               int32_t U, int32_t tw, uint32_t row_bytes, uint32_t *stream)
+                               int32_t U, int32_t tw, uint32_t row_bytes, void *stream)
 {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= nnz) return;
@@ -495,9 +503,20 @@ __global__ void k_tile_scatter(const uint64_t *sorted_key, int64_t nnz, const in
     const int g = (int)(idx % tw), w = (int)(tau % ARB_SWEEP_WARPS), u = (int)(tau / ARB_SWEEP_WARPS);
     const int64_t x = (panel * ARB_SWEEP_WARPS + w) * U + u;
     const int32_t t = (int32_t)(i - start[seg]);
-    const uint32_t off = local * row_bytes;
-    const uint32_t word = t < 4 * naq[x] ? off : ((code << 18) | off);
-    stream[(((int64_t)qoff[x] + t / 4) * tw + g) * 4 + (t & 3)] = word;
+    const bool in_a = t < 4 * naq[x];
+    const int64_t at = (((int64_t)qoff[x] + t / 4) * tw + g) * 4 + (t & 3);
+    if (W16) {
+        reinterpret_cast<uint16_t *>(stream)[at] = (uint16_t)(in_a ? local : ((code << 11) | local));
+    } else {
+        const uint32_t off = local * row_bytes;
+        reinterpret_cast<uint32_t *>(stream)[at] = in_a ? off : ((code << 18) | off);
+    }
+}
+
+__global__ void k_fill_u16(uint16_t *v, int64_t n, uint16_t x)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < n) v[i] = x;
 }
 
 int arb_sweep_table_entries(const arb_ctx *ctx);
@@ -509,7 +528,7 @@ struct StreamOut {
 };
 
 static int build_stream(arb_ctx *ctx, const int32_t *row, const int32_t *col, int32_t n_rows, int32_t panel_rows,
-                        int np, int kp, const float *code_up, const float *code_dn, StreamOut out)
+                        int np, int kp, int w16, const float *code_up, const float *code_dn, StreamOut out)
 {
     const int64_t nnz = ctx->nnz, n_seg = (int64_t)np * n_rows;
     const int tw = 128 / kp;
@@ -566,12 +585,19 @@ static int build_stream(arb_ctx *ctx, const int32_t *row, const int32_t *col, in
     // the sweep reads three quads ahead of the one it works on: keep that many spare at the end
     const int64_t n_words = ((int64_t)total_q + 4) * tw * 4;
     ARB_REQUIRE(n_words < ((int64_t)1 << 31), ARB_ERR_UNSUPPORTED, "layout: stream of %lld words", (long long)n_words);
-    ARB_TRY(out.stream->reserve(n_words * 4));
-    const uint32_t null_word = (uint32_t)panel_rows * (uint32_t)kp * 8u;       // code 0, the zero row
-    k_fill_u32<<<grid_for(n_words, B), B, 0, st>>>(out.stream->as<uint32_t>(), n_words, null_word);
-    k_tile_scatter<<<grid_for(nnz, B), B, 0, st>>>(k_out.as<uint64_t>(), nnz, start.as<int32_t>(),
-                                                   pos_of_seg.as<int32_t>(), qoff.as<int32_t>(), naq.as<int32_t>(),
-                                                   n_rows, U, tw, (uint32_t)kp * 8u, out.stream->as<uint32_t>());
+    ARB_TRY(out.stream->reserve(n_words * (w16 ? 2 : 4)));
+    if (w16) {
+        k_fill_u16<<<grid_for(n_words, B), B, 0, st>>>(out.stream->as<uint16_t>(), n_words, (uint16_t)panel_rows);   // code 0, the zero row
+        k_tile_scatter<true><<<grid_for(nnz, B), B, 0, st>>>(k_out.as<uint64_t>(), nnz, start.as<int32_t>(),
+                                                             pos_of_seg.as<int32_t>(), qoff.as<int32_t>(),
+                                                             naq.as<int32_t>(), n_rows, U, tw, (uint32_t)kp * 8u, out.stream->p);
+    } else {
+        const uint32_t null_word = (uint32_t)panel_rows * (uint32_t)kp * 8u;       // code 0, the zero row
+        k_fill_u32<<<grid_for(n_words, B), B, 0, st>>>(out.stream->as<uint32_t>(), n_words, null_word);
+        k_tile_scatter<false><<<grid_for(nnz, B), B, 0, st>>>(k_out.as<uint64_t>(), nnz, start.as<int32_t>(),
+                                                              pos_of_seg.as<int32_t>(), qoff.as<int32_t>(),
+                                                              naq.as<int32_t>(), n_rows, U, tw, (uint32_t)kp * 8u, out.stream->p);
+    }
     k_tile_desc<<<grid_for(n_slots, B), B, 0, st>>>(qoff.as<int32_t>(), naq.as<int32_t>(), nq.as<int32_t>(),
                                                    order.as<int32_t>(), n_rows, n_slots, U, tw, out.desc->as<int4>(),
                                                    out.rows->as<int32_t>());
@@ -600,6 +626,8 @@ int arb_build_layout(arb_ctx *ctx, int kp)
     L.panel_rows = panel_rows;
     L.np_z = (ctx->n_snvs + panel_rows - 1) / panel_rows;
     L.np_y = (ctx->n_cells + panel_rows - 1) / panel_rows;
+    // 16-bit stream words when the row (11 bits, the zero row included) and the pair code (5 bits) fit
+    L.w16 = kp == ARB_VW && panel_rows < 2048 && ctx->n_pairs <= 32 && !ctx->opt_w32;
     // per-code bounds on |log2(1 + d x)|, x in [0,1], with a little slack for rounding
     std::vector<float> up(ctx->n_pairs), dn(ctx->n_pairs);
     for (int c = 0; c < ctx->n_pairs; ++c) {
@@ -613,10 +641,10 @@ int arb_build_layout(arb_ctx *ctx, int kp)
     ARB_CUDA(cudaMemcpyAsync(d_up.p, up.data(), up.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
     ARB_CUDA(cudaMemcpyAsync(d_dn.p, dn.data(), dn.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
     ARB_TRY(build_stream(ctx, ctx->coo_cell.as<int32_t>(), ctx->coo_snv.as<int32_t>(), ctx->n_cells, panel_rows,
-                         L.np_z, kp, d_up.as<float>(), d_dn.as<float>(),
+                         L.np_z, kp, L.w16, d_up.as<float>(), d_dn.as<float>(),
                          StreamOut{&L.zdesc, &L.zrows, &L.zstream, &L.uz, &L.fold_z, &L.quads_z}));
     ARB_TRY(build_stream(ctx, ctx->coo_snv.as<int32_t>(), ctx->coo_cell.as<int32_t>(), ctx->n_snvs, panel_rows,
-                         L.np_y, kp, d_up.as<float>(), d_dn.as<float>(),
+                         L.np_y, kp, L.w16, d_up.as<float>(), d_dn.as<float>(),
                          StreamOut{&L.ydesc, &L.yrows, &L.ystream, &L.uy, &L.fold_y, &L.quads_y}));
     d_up.release();
     d_dn.release();

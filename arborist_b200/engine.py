@@ -296,12 +296,12 @@ class Engine:
                     sweep_ms=sw.value)
 
     def last_fit_profile(self):
-        v = np.zeros(21)
-        _check(self._lib.arb_last_fit_profile(self._h, v, 21))
+        v = np.zeros(22)
+        _check(self._lib.arb_last_fit_profile(self._h, v, 22))
         keys = ("sweep_z_ms", "sweep_y_ms", "finish_ms", "tree_sweeps_z", "tree_sweeps_y",
                 "launches_z", "launches_y", "rounds", "finish_z_ms", "finish_y_ms", "kp", "panel_rows",
                 "panels_z", "panels_y", "tiles_per_warp_z", "tiles_per_warp_y", "fold_z", "fold_y",
-                "quads_z", "quads_y", "groups")
+                "quads_z", "quads_y", "groups", "w16")
         return dict(zip(keys, v.tolist()))
 
     def set_option(self, name, value):

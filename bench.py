@@ -43,6 +43,10 @@ RUN = dict(alpha=0.001, gamma=0.7, max_iter=25, tolerance=1.0)      # CLI defaul
 # measured by the GPU arm; used only to express the CPU sample (a few iterations of one tree)
 # in the metric's unit.  See BASELINE.md section 5.
 MEAN_TREE_ITERS = {"config3": 17.84, "config2": 12.8}
+# DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) per tree-sweep of the two sweep kernels, from the
+# one `ncu --set full` capture summarised in profiles/r1h_full_summary.md (config 3 only; per launch the
+# kernel moves this times the tree-sweeps of the launch).
+NCU_DRAM_BYTES_PER_TREE_SWEEP = {"config3": {"z": 24.73e6, "y": 12.20e6}}
 
 
 def parse_args():
@@ -321,7 +325,11 @@ def run_gpu_arm(args):
         "kernel": "k_sweep<KP,true> (q(z) sweep + E[log lik] accumulators)", "bound": "hbm",
         "achieved": ach_z, "peak": peak, "unit": "GB/s", "frac": ach_z / peak,
         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
-        "traffic": None,
+        "traffic": (NCU_DRAM_BYTES_PER_TREE_SWEEP[cfg.name]["z"] * prof["tree_sweeps_z"] / lz
+                    if cfg.name in NCU_DRAM_BYTES_PER_TREE_SWEEP else None),
+        "traffic_source": "ncu --set full, profiles/r1h_full_summary.md: 24.73 MB of DRAM traffic per tree-sweep "
+                          "x tree-sweeps per launch (bytes per launch, like the algorithmic figure: "
+                          "algorithmic_bytes_per_tree_sweep x tree_sweeps_per_launch)",
         "algorithmic_bytes_per_tree_sweep": b_z, "tree_sweeps_per_launch": prof["tree_sweeps_z"] / lz,
         "avg_launch_ms": prof["sweep_z_ms"] / lz,
         "qy_sweep": {"achieved": ach_y, "frac": ach_y / peak, "algorithmic_bytes_per_tree_sweep": b_y,
@@ -334,7 +342,7 @@ def run_gpu_arm(args):
                                  "finish_z": prof["finish_z_ms"] / max(dev_ms, 1e-9),
                                  "finish_y": prof["finish_y_ms"] / max(dev_ms, 1e-9)},
         "layout": {k: int(pf[k]) for k in ("kp", "panel_rows", "panels_z", "panels_y", "tiles_per_warp_z",
-                                            "tiles_per_warp_y", "fold_z", "fold_y", "quads_z", "quads_y")},
+                                            "tiles_per_warp_y", "fold_z", "fold_y", "quads_z", "quads_y", "w16")},
     }
 
     # ---- end to end through arborist(...) with host DataFrames ---------------------------------------

@@ -154,10 +154,10 @@ int arb_last_fit_stats(arb_ctx *ctx, int64_t *kernel_launches, double *device_ms
  * by the q(z) / q(y) sweep launches, number of q(z) / q(y) sweep launches, rounds;
  * values[8..19] = q(z) / q(y) finishing ms, then the layout in use: KP, rows per panel, panels
  * (z, y), tiles per warp (z, y), range-proof flags (z, y), stream quads (z, y); values[20] = stream
- * groups used */
+ * groups used, values[21] = 1 when the sparse stream uses 16-bit words */
 int arb_last_fit_profile(arb_ctx *ctx, double *values, int32_t n_values);
 /* tuning knobs: "slots" (trees in flight), "groups" (stream groups the slots are split into, 0 = default,
- * at most 4), "panel_kb" (panel bytes cap), "threads", "no_fold"; returns ARB_ERR_INVALID for unknown names */
+ * at most 4), "panel_kb" (panel bytes cap), "threads", "no_fold", "w32" (force 32-bit stream words); returns ARB_ERR_INVALID for unknown names */
 int arb_set_option(arb_ctx *ctx, const char *name, int64_t value);
 
 #ifdef __cplusplus

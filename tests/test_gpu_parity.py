@@ -304,6 +304,27 @@ def test_stream_groups_do_not_change_bits(eng_mod):
     e.close()
 
 
+def test_stream_word_width_does_not_change_bits(eng_mod):
+    """16-bit stream words {row | code << 11} (used when they fit) and the 32-bit form drive the same arithmetic."""
+    from arborist_b200.arborist import add_normal_clone, prepare_trees
+    g = load_golden("small")
+    e, _, _ = _coo_engine(eng_mod, g)
+    e.set_prior(g["q_y_init"])
+    trees, _, _ = golden_frames(g)
+    c2i, _, parents, _, normal = prepare_trees(add_normal_clone(trees))
+    K = len(c2i)
+    ref = e.fit(parents=parents, n_clones=K, normal_idx=normal, max_iter=25, tolerance=1.0, keep_posteriors="all")
+    assert e.last_fit_profile()["w16"] == 1
+    ref_q = e.get_fit(2)
+    e.set_option("w32", 1)
+    got = e.fit(parents=parents, n_clones=K, normal_idx=normal, max_iter=25, tolerance=1.0, keep_posteriors="all")
+    assert e.last_fit_profile()["w16"] == 0
+    assert np.array_equal(got[0], ref[0]) and np.array_equal(got[1], ref[1])
+    qz, qy = e.get_fit(2)
+    assert np.array_equal(qz, ref_q[0]) and np.array_equal(qy, ref_q[1])
+    e.close()
+
+
 def test_slot_count_and_duplicates_do_not_change_bits(eng_mod):
     """Determinism: results are independent of how many trees are in flight, and duplicate
     trees get bit-identical ELBOs (the reference has both properties)."""

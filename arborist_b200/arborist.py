@@ -65,11 +65,18 @@ def add_normal_clone(candidate_trees):
     """Prepend a normal clone ``min(nodes) - 1`` above each tree's root (A.py:860-882)."""
     out = []
     for edges in candidate_trees:
-        _, nodes = _digraph_edge_order(edges)
-        kids = {v for _, v in edges}
-        root = [n for n in nodes if n not in kids][0]
+        # one pass: node / successor order as nx.DiGraph(edges) keeps it, then the extra edge last
+        nodes, succ, kids = {}, {}, set()
+        for u, v in edges:
+            nodes.setdefault(u, None)
+            nodes.setdefault(v, None)
+            succ.setdefault(u, {}).setdefault(v, None)
+            kids.add(v)
+        root = next(n for n in nodes if n not in kids)
         normal = min(nodes) - 1
-        out.append(_digraph_edge_order(edges, extra=(normal, root))[0])
+        nodes.setdefault(normal, None)
+        succ.setdefault(normal, {}).setdefault(root, None)
+        out.append([(u, v) for u in nodes for v in succ.get(u, ())])
     return out
 
 

@@ -40,26 +40,31 @@ void arb_set_error(const char *fmt, ...);
     } while (0)
 
 // ---- device buffer with size tracking -----------------------------------------------
+// Released allocations go to a process-wide pool (arb_ingest.cu) instead of back to the driver: a
+// service that calls arborist(...) repeatedly on same-shaped inputs would otherwise spend tens of
+// milliseconds per call in cudaMalloc / cudaFree of its ~50 GB workspace.  ARB_POOL=0 disables it,
+// arb_pool_trim() empties it.
+void *arb_pool_alloc(size_t n, size_t *got);       // nullptr on failure (error already set)
+void arb_pool_free(void *p, size_t n);
+size_t arb_pool_bytes(int device);                 // bytes parked in the pool for this device
+
 struct DevBuf {
     void *p = nullptr;
     size_t bytes = 0;
     int reserve(size_t n) {          // grows only; contents are NOT preserved
         if (n <= bytes && p) return ARB_OK;
-        if (p) cudaFree(p);
+        if (p) arb_pool_free(p, bytes);
         p = nullptr;
         bytes = 0;
         if (n == 0) return ARB_OK;
-        cudaError_t e = cudaMalloc(&p, n);
-        if (e != cudaSuccess) {
-            arb_set_error("cudaMalloc(%zu bytes): %s", n, cudaGetErrorString(e));
-            cudaGetLastError();
-            return ARB_ERR_NOMEM;
-        }
-        bytes = n;
+        size_t got = 0;
+        p = arb_pool_alloc(n, &got);
+        if (!p) return ARB_ERR_NOMEM;
+        bytes = got;
         return ARB_OK;
     }
     void release() {
-        if (p) cudaFree(p);
+        if (p) arb_pool_free(p, bytes);
         p = nullptr;
         bytes = 0;
     }

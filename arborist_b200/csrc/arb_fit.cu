@@ -897,6 +897,7 @@ static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve
         ctx->ws_slots = ctx->ws_groups = ctx->ws_sg = 0;
         size_t free_b = 0, total_b = 0;
         ARB_CUDA(cudaMemGetInfo(&free_b, &total_b));
+        free_b += arb_pool_bytes(ctx->device);            // parked allocations are ours to reuse
         // one virtual slot of slack per group for the rounding of the packed buffers
         const int64_t slack = G * ((m + n) * ARB_VW * 8 + ((int64_t)L.np_z * n * 20 + (int64_t)L.np_y * m * 12) * ARB_VW);
         const int64_t usable = (int64_t)(free_b * 0.90) - reserve_bytes - slack;
@@ -1387,6 +1388,7 @@ ARB_API int arb_posterior_bytes(arb_ctx *ctx, int32_t n_trees, int32_t n_clones,
     if (free_bytes) {
         size_t f = 0, t = 0;
         ARB_CUDA(cudaMemGetInfo(&f, &t));
+        f += arb_pool_bytes(ctx->device);
         *free_bytes = (int64_t)f + (int64_t)ctx->best_qz.bytes + (int64_t)ctx->best_qy.bytes;
     }
     return ARB_OK;

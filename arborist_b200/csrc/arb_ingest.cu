@@ -39,6 +39,111 @@ void arb_set_error(const char *fmt, ...)
 }
 
 ARB_API const char *arb_last_error(void) { return g_last_error.c_str(); }
+
+// ---------------------------------------------------------------------------------------
+// device allocation pool (see DevBuf in arb_common.cuh)
+// ---------------------------------------------------------------------------------------
+#include <mutex>
+struct PoolBlock { void *p; size_t bytes; int device; };
+static std::mutex g_pool_mu;
+static std::vector<PoolBlock> g_pool;
+static int pool_enabled()
+{
+    static int on = -1;
+    if (on < 0) {
+        const char *e = getenv("ARB_POOL");
+        on = !(e && e[0] == '0');
+    }
+    return on;
+}
+
+static void pool_flush_locked(int device)
+{
+    for (size_t i = 0; i < g_pool.size();) {
+        if (g_pool[i].device == device) {
+            cudaFree(g_pool[i].p);
+            g_pool[i] = g_pool.back();
+            g_pool.pop_back();
+        } else {
+            ++i;
+        }
+    }
+}
+
+void *arb_pool_alloc(size_t n, size_t *got)
+{
+    int device = 0;
+    cudaGetDevice(&device);
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    // best fit among the parked blocks of this device, at most 12.5 % larger than asked
+    int best = -1;
+    for (size_t i = 0; i < g_pool.size(); ++i)
+        if (g_pool[i].device == device && g_pool[i].bytes >= n && g_pool[i].bytes <= n + n / 8 + 4096 &&
+            (best < 0 || g_pool[i].bytes < g_pool[best].bytes))
+            best = (int)i;
+    if (best >= 0) {
+        void *p = g_pool[best].p;
+        *got = g_pool[best].bytes;
+        g_pool[best] = g_pool.back();
+        g_pool.pop_back();
+        return p;
+    }
+    void *p = nullptr;
+    cudaError_t e = cudaMalloc(&p, n);
+    if (e != cudaSuccess) {              // give the parked memory back to the driver and try again
+        cudaGetLastError();
+        pool_flush_locked(device);
+        e = cudaMalloc(&p, n);
+    }
+    if (e != cudaSuccess) {
+        arb_set_error("cudaMalloc(%zu bytes): %s", n, cudaGetErrorString(e));
+        cudaGetLastError();
+        return nullptr;
+    }
+    *got = n;
+    return p;
+}
+
+void arb_pool_free(void *p, size_t n)
+{
+    if (!p) return;
+    if (!pool_enabled()) {
+        cudaFree(p);
+        return;
+    }
+    int device = 0;
+    cudaGetDevice(&device);
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    g_pool.push_back(PoolBlock{p, n, device});
+}
+
+size_t arb_pool_bytes(int device)
+{
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    size_t t = 0;
+    for (const PoolBlock &b : g_pool)
+        if (b.device == device) t += b.bytes;
+    return t;
+}
+
+ARB_API int arb_pool_trim(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return ARB_OK; }
+    int cur = 0;
+    cudaGetDevice(&cur);
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    for (int d = 0; d < n; ++d) {
+        bool any = false;
+        for (const PoolBlock &b : g_pool) any |= b.device == d;
+        if (!any) continue;
+        cudaSetDevice(d);
+        pool_flush_locked(d);
+    }
+    cudaSetDevice(cur);
+    return ARB_OK;
+}
+
 ARB_API int arb_abi_version(void) { return ARB_ABI_VERSION; }
 
 ARB_API int arb_device_count(int *count)

@@ -72,6 +72,7 @@ _SIGNATURES = {
                                      C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "arb_last_fit_profile": (C.c_int, [_ctx, _f64p, C.c_int32]),
     "arb_set_option": (C.c_int, [_ctx, C.c_char_p, C.c_int64]),
+    "arb_pool_trim": (C.c_int, []),
 }
 
 
@@ -101,6 +102,11 @@ def load_library():
 def _check(status):
     if status != 0:
         raise ArboristError(status, load_library().arb_last_error().decode("utf-8", "replace"))
+
+
+def trim_pool() -> None:
+    """Return the device memory parked in the library's allocation pool to the driver."""
+    _check(load_library().arb_pool_trim())
 
 
 def device_count() -> int:

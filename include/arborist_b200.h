@@ -159,6 +159,12 @@ int arb_last_fit_profile(arb_ctx *ctx, double *values, int32_t n_values);
 /* tuning knobs: "slots" (trees in flight), "groups" (stream groups the slots are split into, 0 = default,
  * at most 4), "panel_kb" (panel bytes cap), "threads", "no_fold", "w32" (force 32-bit stream words); returns ARB_ERR_INVALID for unknown names */
 int arb_set_option(arb_ctx *ctx, const char *name, int64_t value);
+/* Device allocations released by a context (arb_ctx_destroy, workspace resizes) are parked in a
+ * process-wide pool and handed to the next context that asks for a buffer of about that size, so
+ * repeated arborist(...) calls do not pay cudaMalloc / cudaFree for the workspace every time.
+ * arb_pool_trim returns everything parked to the driver; ARB_POOL=0 in the environment disables
+ * the pool. */
+int arb_pool_trim(void);
 
 #ifdef __cplusplus
 }

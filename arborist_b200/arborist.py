@@ -198,14 +198,18 @@ def ingest_read_counts(eng, read_counts, snv_clusters, cluster_to_idx, alpha, ga
     """A.py:1034-1069 on the device: upload the long-format table as integer codes, build the
     sparse matrix and the prior there.  Returns ``(cell_ids, snv_ids)`` in row/column order.
 
-    Host work is the first-appearance factorisation of the two id columns (A.py:851-855, on
-    the UNFILTERED table); the zero-alt filter (A.py:1034-1041), re-indexing, dictionary
+    The first-appearance factorisation of the two id columns (A.py:851-855, on the UNFILTERED
+    table) runs on the device when the ids are int64, on the host (pandas) otherwise; the zero-alt filter (A.py:1034-1041), re-indexing, dictionary
     coding and the cell-major / SNV-major layouts are built by ``arb_ingest_coo``.
     """
-    snv_codes, snv_uniques = pd.factorize(read_counts["snv"].to_numpy(), use_na_sentinel=True)
-    cell_codes, cell_uniques = pd.factorize(read_counts["cell"].to_numpy(), use_na_sentinel=False)
-    eng.ingest_coo(cell_codes, snv_codes, read_counts["alt"].to_numpy(),
-                   read_counts["total"].to_numpy(), len(cell_uniques), len(snv_uniques), alpha)
+    cols = [read_counts[c].to_numpy() for c in ("cell", "snv", "alt", "total")]
+    if all(a.dtype == np.int64 for a in cols):
+        # integer ids: the factorisation runs on the device too (arb_ingest_ids)
+        cell_uniques, snv_uniques = eng.ingest_ids(*cols, alpha)
+    else:
+        snv_codes, snv_uniques = pd.factorize(cols[1], use_na_sentinel=True)
+        cell_codes, cell_uniques = pd.factorize(cols[0], use_na_sentinel=False)
+        eng.ingest_coo(cell_codes, snv_codes, cols[2], cols[3], len(cell_uniques), len(snv_uniques), alpha)
     _install_scipy_table(eng, alpha)
     cell_order, snv_order = eng.orders()
     cell_ids = np.asarray(cell_uniques)[cell_order]

@@ -117,6 +117,8 @@ struct arb_ctx {
     int64_t nnz = 0;
     DevBuf coo_cell, coo_snv, coo_code;   // int32, int32, uint16
     DevBuf cell_order, snv_order;         // int32 (coo ingest)
+    DevBuf cell_uniques, snv_uniques;     // int64 ids in first-appearance order (arb_ingest_ids)
+    int32_t n_cell_uniques = 0, n_snv_uniques = 0;
     std::vector<int32_t> pair_alt, pair_total;
     std::vector<int64_t> pair_count;
     std::vector<double> tab_lp, tab_la;   // host copies of the table

@@ -203,7 +203,8 @@ ARB_API int arb_ctx_destroy(arb_ctx *ctx)
                       &ctx->xs, &ctx->xr, &ctx->qz_cur, &ctx->qy_cur, &ctx->part_z, &ctx->part_g,
                       &ctx->part_y, &ctx->red, &ctx->slot_state, &ctx->lists, &ctx->masks,
                       &ctx->best_qz, &ctx->best_qy, &ctx->d_elbo, &ctx->d_iters, &ctx->d_trace,
-                      &ctx->tree_masks, &ctx->single_qz, &ctx->single_qy, &ctx->scratch};
+                      &ctx->tree_masks, &ctx->single_qz, &ctx->single_qy, &ctx->scratch, &ctx->cell_uniques,
+                      &ctx->snv_uniques};
     for (DevBuf *b : bufs) b->release();
     for (auto &l : ctx->layout) l.release();
     for (int g = 0; g < ARB_MAX_GROUPS; ++g) {
@@ -855,6 +856,10 @@ static int finish_canonical(arb_ctx *ctx, DevBuf &key, const uint16_t *code)
 // ---------------------------------------------------------------------------------------
 // arb_ingest_coo
 // ---------------------------------------------------------------------------------------
+// the table as device-resident first-appearance codes (d_cell, d_snv, d_alt, d_tot: int32 [n_rows], consumed)
+static int ingest_device_codes(arb_ctx *ctx, int64_t n_rows, DevBuf &d_cell, DevBuf &d_snv, DevBuf &d_alt, DevBuf &d_tot,
+                               int32_t n_cell_codes, int32_t n_snv_codes, double alpha);
+
 ARB_API int arb_ingest_coo(arb_ctx *ctx, int64_t n_rows, const int32_t *cell_code, const int32_t *snv_code,
                            const int32_t *alt, const int32_t *total, int32_t n_cell_codes,
                            int32_t n_snv_codes, double alpha)
@@ -864,21 +869,30 @@ ARB_API int arb_ingest_coo(arb_ctx *ctx, int64_t n_rows, const int32_t *cell_cod
                 (long long)n_rows);
     ARB_REQUIRE(n_cell_codes > 0 && n_snv_codes > 0, ARB_ERR_INVALID, "arb_ingest_coo: empty code space");
     ARB_CUDA(cudaSetDevice(ctx->device));
+    ctx->n_cell_uniques = ctx->n_snv_uniques = 0;
+    cudaStream_t st = ctx->stream;
+    DevBuf d_cell, d_snv, d_alt, d_tot;
+    for (DevBuf *b : {&d_cell, &d_snv, &d_alt, &d_tot}) ARB_TRY(b->reserve(n_rows * 4));
+    ARB_CUDA(cudaMemcpyAsync(d_cell.p, cell_code, n_rows * 4, cudaMemcpyHostToDevice, st));
+    ARB_CUDA(cudaMemcpyAsync(d_snv.p, snv_code, n_rows * 4, cudaMemcpyHostToDevice, st));
+    ARB_CUDA(cudaMemcpyAsync(d_alt.p, alt, n_rows * 4, cudaMemcpyHostToDevice, st));
+    ARB_CUDA(cudaMemcpyAsync(d_tot.p, total, n_rows * 4, cudaMemcpyHostToDevice, st));
+    return ingest_device_codes(ctx, n_rows, d_cell, d_snv, d_alt, d_tot, n_cell_codes, n_snv_codes, alpha);
+}
+
+static int ingest_device_codes(arb_ctx *ctx, int64_t n_rows, DevBuf &d_cell, DevBuf &d_snv, DevBuf &d_alt, DevBuf &d_tot,
+                               int32_t n_cell_codes, int32_t n_snv_codes, double alpha)
+{
     reset_matrix(ctx);
     cudaStream_t st = ctx->stream;
     const int B = 256;
-    DevBuf d_cell, d_snv, d_alt, d_tot, alt_sum, keep, snv_new, row_keep, row_pos, first, iota, sfirst, scell,
-        cell_new, counters;
-    for (DevBuf *b : {&d_cell, &d_snv, &d_alt, &d_tot, &row_keep, &row_pos}) ARB_TRY(b->reserve(n_rows * 4));
+    DevBuf alt_sum, keep, snv_new, row_keep, row_pos, first, iota, sfirst, scell, cell_new, counters;
+    for (DevBuf *b : {&row_keep, &row_pos}) ARB_TRY(b->reserve(n_rows * 4));
     ARB_TRY(alt_sum.reserve((size_t)n_snv_codes * 8));
     ARB_TRY(keep.reserve((size_t)n_snv_codes * 4));
     ARB_TRY(snv_new.reserve((size_t)n_snv_codes * 4));
     for (DevBuf *b : {&first, &iota, &sfirst, &scell, &cell_new}) ARB_TRY(b->reserve((size_t)n_cell_codes * 4));
     ARB_TRY(counters.reserve(64));
-    ARB_CUDA(cudaMemcpyAsync(d_cell.p, cell_code, n_rows * 4, cudaMemcpyHostToDevice, st));
-    ARB_CUDA(cudaMemcpyAsync(d_snv.p, snv_code, n_rows * 4, cudaMemcpyHostToDevice, st));
-    ARB_CUDA(cudaMemcpyAsync(d_alt.p, alt, n_rows * 4, cudaMemcpyHostToDevice, st));
-    ARB_CUDA(cudaMemcpyAsync(d_tot.p, total, n_rows * 4, cudaMemcpyHostToDevice, st));
     ARB_CUDA(cudaMemsetAsync(alt_sum.p, 0, (size_t)n_snv_codes * 8, st));
     ARB_CUDA(cudaMemsetAsync(counters.p, 0, 64, st));
 
@@ -1003,6 +1017,137 @@ ARB_API int arb_ingest_coo(arb_ctx *ctx, int64_t n_rows, const int32_t *cell_cod
     ARB_TRY(arb_refresh_tables(ctx));
     ctx->ingested = true;
     ctx->from_coo = true;
+    return ARB_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// arb_ingest_ids: the long table with raw 64-bit integer ids; the first-appearance factorisation
+// of the two id columns (pandas unique / factorize order, A.py:851-855) is done on the device
+// ---------------------------------------------------------------------------------------
+__global__ void k_narrow_i64(const int64_t *src, int64_t n, int32_t *dst, int32_t *bad)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int64_t v = src[i];
+    if (v < 0 || v > INT_MAX) atomicExch(bad, 1);
+    dst[i] = (int32_t)v;
+}
+
+__global__ void k_head_flags(const uint64_t *sorted, int64_t n, int32_t *flag)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < n) flag[i] = (i == 0 || sorted[i] != sorted[i - 1]) ? 1 : 0;
+}
+
+// group g (ids in ascending order) first appears at row first[g]
+__global__ void k_group_first(const int32_t *flag, const int32_t *gidx, const int32_t *row, int64_t n, int32_t *first)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < n && flag[i]) first[gidx[i] - 1] = row[i]; // the sort is stable: the head holds the smallest row
+}
+
+__global__ void k_group_rank(const int32_t *group_by_first, int32_t n_groups, int32_t *code_of_group)
+{
+    int32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < n_groups) code_of_group[group_by_first[r]] = r;
+}
+
+__global__ void k_scatter_codes(const uint64_t *sorted, const int32_t *flag, const int32_t *gidx, const int32_t *row,
+                                const int32_t *code_of_group, int64_t n, int32_t *code, int64_t *uniques)
+{
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int32_t c = code_of_group[gidx[i] - 1];
+    code[row[i]] = c;
+    if (flag[i]) uniques[c] = (int64_t)sorted[i];
+}
+
+// codes[row] = index of ids[row] in first-appearance order; uniques[code] = id
+static int device_factorize(arb_ctx *ctx, const DevBuf &ids, int64_t n, DevBuf &codes, DevBuf &uniques, int32_t *n_codes)
+{
+    cudaStream_t st = ctx->stream;
+    const int B = 256;
+    DevBuf sorted, row_in, row_out, flag, gidx, first, gi, sfirst, gsorted, cog;
+    ARB_TRY(sorted.reserve(n * 8));
+    for (DevBuf *b : {&row_in, &row_out, &flag, &gidx}) ARB_TRY(b->reserve(n * 4));
+    k_iota<<<grid_for(n, B), B, 0, st>>>(row_in.as<int32_t>(), n);
+    ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
+        return cub::DeviceRadixSort::SortPairs(tmp, bytes, ids.as<uint64_t>(), sorted.as<uint64_t>(), row_in.as<int32_t>(),
+                                               row_out.as<int32_t>(), n, 0, 64, st);
+    }));
+    k_head_flags<<<grid_for(n, B), B, 0, st>>>(sorted.as<uint64_t>(), n, flag.as<int32_t>());
+    ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
+        return cub::DeviceScan::InclusiveSum(tmp, bytes, flag.as<int32_t>(), gidx.as<int32_t>(), n, st);
+    }));
+    int32_t ng = 0;                      // gidx[i] = 1 + group of element i (groups in ascending id order)
+    ARB_CUDA(cudaMemcpyAsync(&ng, gidx.as<int32_t>() + n - 1, 4, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaStreamSynchronize(st));
+    for (DevBuf *b : {&first, &gi, &sfirst, &gsorted, &cog}) ARB_TRY(b->reserve((size_t)ng * 4));
+    ARB_TRY(uniques.reserve((size_t)ng * 8));
+    ARB_TRY(codes.reserve(n * 4));
+    k_group_first<<<grid_for(n, B), B, 0, st>>>(flag.as<int32_t>(), gidx.as<int32_t>(), row_out.as<int32_t>(), n,
+                                                first.as<int32_t>());
+    k_iota<<<grid_for(ng, B), B, 0, st>>>(gi.as<int32_t>(), ng);
+    ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
+        return cub::DeviceRadixSort::SortPairs(tmp, bytes, first.as<int32_t>(), sfirst.as<int32_t>(), gi.as<int32_t>(),
+                                               gsorted.as<int32_t>(), ng, 0, 32, st);
+    }));
+    k_group_rank<<<grid_for(ng, B), B, 0, st>>>(gsorted.as<int32_t>(), ng, cog.as<int32_t>());
+    k_scatter_codes<<<grid_for(n, B), B, 0, st>>>(sorted.as<uint64_t>(), flag.as<int32_t>(), gidx.as<int32_t>(),
+                                                  row_out.as<int32_t>(), cog.as<int32_t>(), n, codes.as<int32_t>(),
+                                                  uniques.as<int64_t>());
+    ARB_CUDA(cudaStreamSynchronize(st));
+    for (DevBuf *b : {&sorted, &row_in, &row_out, &flag, &gidx, &first, &gi, &sfirst, &gsorted, &cog}) b->release();
+    *n_codes = ng;
+    return ARB_OK;
+}
+
+ARB_API int arb_ingest_ids(arb_ctx *ctx, int64_t n_rows, const int64_t *cell_id, const int64_t *snv_id,
+                           const int64_t *alt, const int64_t *total, double alpha, int32_t *n_cell_ids,
+                           int32_t *n_snv_ids)
+{
+    ARB_REQUIRE(ctx && cell_id && snv_id && alt && total, ARB_ERR_INVALID, "arb_ingest_ids: null argument");
+    ARB_REQUIRE(n_rows > 0 && n_rows < (int64_t)INT_MAX, ARB_ERR_INVALID, "arb_ingest_ids: n_rows=%lld",
+                (long long)n_rows);
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const int B = 256;
+    DevBuf raw, d_cell, d_snv, d_alt, d_tot, bad;
+    ARB_TRY(raw.reserve(n_rows * 8));
+    ARB_TRY(bad.reserve(4));
+    ARB_CUDA(cudaMemsetAsync(bad.p, 0, 4, st));
+    ARB_TRY(d_alt.reserve(n_rows * 4));
+    ARB_TRY(d_tot.reserve(n_rows * 4));
+    ARB_CUDA(cudaMemcpyAsync(raw.p, alt, n_rows * 8, cudaMemcpyHostToDevice, st));
+    k_narrow_i64<<<grid_for(n_rows, B), B, 0, st>>>(raw.as<int64_t>(), n_rows, d_alt.as<int32_t>(), bad.as<int32_t>());
+    ARB_CUDA(cudaMemcpyAsync(raw.p, total, n_rows * 8, cudaMemcpyHostToDevice, st));
+    k_narrow_i64<<<grid_for(n_rows, B), B, 0, st>>>(raw.as<int64_t>(), n_rows, d_tot.as<int32_t>(), bad.as<int32_t>());
+    int32_t h_bad = 0;
+    ARB_CUDA(cudaMemcpyAsync(&h_bad, bad.p, 4, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaMemcpyAsync(raw.p, cell_id, n_rows * 8, cudaMemcpyHostToDevice, st));
+    ARB_CUDA(cudaStreamSynchronize(st));
+    ARB_REQUIRE(!h_bad, ARB_ERR_INVALID, "arb_ingest_ids: alt / total outside 0..2^31-1");
+    int32_t nc = 0, ns = 0;
+    ARB_TRY(device_factorize(ctx, raw, n_rows, d_cell, ctx->cell_uniques, &nc));
+    ARB_CUDA(cudaMemcpyAsync(raw.p, snv_id, n_rows * 8, cudaMemcpyHostToDevice, st));
+    ARB_TRY(device_factorize(ctx, raw, n_rows, d_snv, ctx->snv_uniques, &ns));
+    raw.release();
+    bad.release();
+    ctx->n_cell_uniques = nc;
+    ctx->n_snv_uniques = ns;
+    if (n_cell_ids) *n_cell_ids = nc;
+    if (n_snv_ids) *n_snv_ids = ns;
+    return ingest_device_codes(ctx, n_rows, d_cell, d_snv, d_alt, d_tot, nc, ns, alpha);
+}
+
+ARB_API int arb_get_id_uniques(arb_ctx *ctx, int64_t *cell_uniques, int64_t *snv_uniques)
+{
+    ARB_REQUIRE(ctx && ctx->n_cell_uniques > 0, ARB_ERR_INVALID, "arb_get_id_uniques: no arb_ingest_ids table");
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    if (cell_uniques)
+        ARB_CUDA(cudaMemcpy(cell_uniques, ctx->cell_uniques.p, (size_t)ctx->n_cell_uniques * 8, cudaMemcpyDeviceToHost));
+    if (snv_uniques)
+        ARB_CUDA(cudaMemcpy(snv_uniques, ctx->snv_uniques.p, (size_t)ctx->n_snv_uniques * 8, cudaMemcpyDeviceToHost));
     return ARB_OK;
 }
 

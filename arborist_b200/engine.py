@@ -19,6 +19,7 @@ _LIB = None
 
 _i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
 _f64p = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
+_i64p = np.ctypeslib.ndpointer(dtype=np.int64, flags="C_CONTIGUOUS")
 _u8p = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
 _ctx = C.c_void_p
 _opt = C.c_void_p           # optional pointer arguments are passed as raw addresses
@@ -44,6 +45,9 @@ _SIGNATURES = {
     "arb_ctx_destroy": (C.c_int, [_ctx]),
     "arb_ingest_coo": (C.c_int, [_ctx, C.c_int64, _i32p, _i32p, _i32p, _i32p, C.c_int32, C.c_int32,
                                  C.c_double]),
+    "arb_ingest_ids": (C.c_int, [_ctx, C.c_int64, _i64p, _i64p, _i64p, _i64p, C.c_double,
+                                 C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    "arb_get_id_uniques": (C.c_int, [_ctx, _i64p, _i64p]),
     "arb_ingest_csr": (C.c_int, [_ctx, C.c_int32, C.c_int32, C.c_int64, _i32p, _i32p, _f64p]),
     "arb_get_dims": (C.c_int, [_ctx, C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
@@ -160,6 +164,16 @@ class Engine:
         _check(self._lib.arb_ingest_coo(self._h, cell_codes.shape[0], cell_codes, snv_codes,
                                         _i32(alt64), _i32(tot64), int(n_cell_codes),
                                         int(n_snv_codes), float(alpha)))
+
+    def ingest_ids(self, cell_ids, snv_ids, alt, total, alpha):
+        """Long table with int64 ids; the first-appearance factorisation runs on the device.
+        Returns ``(cell_uniques, snv_uniques)`` (ids in code order, like ``pd.factorize``)."""
+        arrs = [np.ascontiguousarray(a, dtype=np.int64) for a in (cell_ids, snv_ids, alt, total)]
+        nc, ns = C.c_int32(), C.c_int32()
+        _check(self._lib.arb_ingest_ids(self._h, len(arrs[0]), *arrs, float(alpha), C.byref(nc), C.byref(ns)))
+        cu, su = np.empty(nc.value, np.int64), np.empty(ns.value, np.int64)
+        _check(self._lib.arb_get_id_uniques(self._h, cu, su))
+        return cu, su
 
     def ingest_csr(self, cell_ptr, snv_idx, log_likes, n_cells, n_snvs):
         snv_idx = _i32(snv_idx)

@@ -366,10 +366,12 @@ def run_gpu_arm(args):
         barrier()
         e2e_wall = max_over_ranks(time.perf_counter() - t0)
         e2e = {"value": T * steps / e2e_wall, "unit": "trees/s",
-               "h2d_bytes_per_step": int(16 * len(rc) + 4 * m + 4 * my_parents.size + 16 * n_pairs),
+               # the four int64 columns of the table (ids are factorised on the device), prior labels, parent
+               # vectors, scipy's log-pmf table
+               "h2d_bytes_per_step": int(32 * len(rc) + 4 * m + 4 * my_parents.size + 16 * n_pairs),
                "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * e2e_wall / steps,
-               "note": "arborist(trees, read_counts_df, clusters_df): host id factorisation, H2D of the COO "
-                       "table, device ingest + layouts, batched fit, ELBO gather, ranking, D2H of ELBOs / "
+               "note": "arborist(trees, read_counts_df, clusters_df): H2D of the long table (int64 columns), device "
+                       "id factorisation + ingest + layouts, batched fit, ELBO gather, ranking, D2H of ELBOs / "
                        "iteration counts / index orders / the best tree's q_z and q_y; host wall clock"}
 
     # ---- CPU baseline (rank 0, N = 1) ------------------------------------------------------------------

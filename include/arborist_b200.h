@@ -68,6 +68,15 @@ int arb_ctx_destroy(arb_ctx *ctx);
 int arb_ingest_coo(arb_ctx *ctx, int64_t n_rows, const int32_t *cell_code,
                    const int32_t *snv_code, const int32_t *alt, const int32_t *total,
                    int32_t n_cell_codes, int32_t n_snv_codes, double alpha);
+/* The same ingest for tables whose ids are 64-bit integers: the first-appearance
+ * factorisation of the two id columns (pandas `unique` / `factorize` order, A.py:851-855) is done
+ * on the device as well (stable radix sort by id, first row of every id, rank of the first rows),
+ * then everything arb_ingest_coo does.  alt / total are int64 as pandas holds them.  The distinct
+ * ids in code order come back through arb_get_id_uniques ([*n_cell_ids] / [*n_snv_ids] int64). */
+int arb_ingest_ids(arb_ctx *ctx, int64_t n_rows, const int64_t *cell_id, const int64_t *snv_id,
+                   const int64_t *alt, const int64_t *total, double alpha, int32_t *n_cell_ids,
+                   int32_t *n_snv_ids);
+int arb_get_id_uniques(arb_ctx *ctx, int64_t *cell_uniques, int64_t *snv_uniques);
 
 /* Seam-level ingest from the reference's own arrays (the arguments of run(...),
  * A.py:1093-1107): CSR pointer, SNV index per entry, interleaved [log_present,

@@ -304,6 +304,47 @@ def test_stream_groups_do_not_change_bits(eng_mod):
     e.close()
 
 
+def test_device_factorisation_matches_pandas(eng_mod):
+    """arb_ingest_ids (ids factorised on the device) vs pd.factorize + arb_ingest_coo: same id order, same
+    matrix, and a table with string ids (host path) gives the same ELBOs as its integer twin."""
+    import pandas as pd
+    from arborist_b200 import arborist
+    rng = np.random.default_rng(7)
+    n = 20000
+    cell = rng.integers(-50, 400, n) * 1000003          # negative and large ids, many repeats
+    snv = rng.integers(0, 900, n) * 7 + 10**12
+    key = np.unique(np.stack([cell, snv], 1), axis=0)
+    rng.shuffle(key)
+    cell, snv = key[:, 0].copy(), key[:, 1].copy()
+    total = 1 + rng.poisson(0.3, len(cell))
+    alt = rng.binomial(total, 0.3)
+    e = eng_mod.Engine()
+    cu, su = e.ingest_ids(cell, snv, alt, total, 0.001)
+    cc, cu_ref = pd.factorize(cell)
+    sc, su_ref = pd.factorize(snv)
+    assert np.array_equal(cu, cu_ref) and np.array_equal(su, su_ref)
+    ptr_a, idx_a, ll_a = e.export_sparse()
+    orders_a = e.orders()
+    e2 = eng_mod.Engine()
+    e2.ingest_coo(cc, sc, alt, total, len(cu_ref), len(su_ref), 0.001)
+    ptr_b, idx_b, ll_b = e2.export_sparse()
+    assert np.array_equal(ptr_a, ptr_b) and np.array_equal(idx_a, idx_b) and np.array_equal(ll_a, ll_b)
+    assert all(np.array_equal(a, b) for a, b in zip(orders_a, e2.orders()))
+    e.close(); e2.close()
+    # API level: integer ids (device path) vs the same table with string ids (host path)
+    g = load_golden("small")
+    trees, rc, cl = golden_frames(g)
+    lik_i, best_i, _ = arborist(trees, rc, cl, max_iter=25, add_normal=True)
+    rc_s = rc.assign(cell=rc["cell"].map(lambda v: f"c{v}"), snv=rc["snv"].map(lambda v: f"s{v}"))
+    cl_s = cl.copy()
+    cl_s[cl_s.columns[0]] = cl_s[cl_s.columns[0]].map(lambda v: f"s{v}")
+    lik_s, best_s, _ = arborist(trees, rc_s, cl_s, max_iter=25, add_normal=True)
+    assert [lik_i[t] for t in range(len(trees))] == [lik_s[t] for t in range(len(trees))]
+    assert best_i.tree_idx == best_s.tree_idx
+    assert np.array_equal(best_i.q_z, best_s.q_z)
+    assert [f"c{c}" for c in best_i.cell_to_idx] == list(best_s.cell_to_idx)
+
+
 def test_stream_word_width_does_not_change_bits(eng_mod):
     """16-bit stream words {row | code << 11} (used when they fit) and the 32-bit form drive the same arithmetic."""
     from arborist_b200.arborist import add_normal_clone, prepare_trees

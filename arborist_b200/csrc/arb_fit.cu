@@ -518,8 +518,9 @@ __device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int po
     double s = (q[0] + q[1]) + (q[2] + q[3]);
 #pragma unroll
     for (int o = GL / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o, GL);
+    const double inv_s = 1.0 / s;                 // one division per row (A.py:169 divides every entry)
 #pragma unroll
-    for (int c = 0; c < 4; ++c) q[c] = q[c] / s;
+    for (int c = 0; c < 4; ++c) q[c] = q[c] * inv_s;
     if (IS_Z && a.given_q) {
 #pragma unroll
         for (int c = 0; c < 4; ++c) q[c] = (v[c] && rowok) ? a.q_cur[qbase + 4 * h + c] : 0.0;
@@ -576,7 +577,7 @@ __device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int po
 
 // grid (row blocks of FIN_ROWS, trees of the sweep's list); a warp takes TW = 32/GL rows at a time
 template <int GL, bool IS_Z, bool HARD>
-__global__ void __launch_bounds__(FIN_THREADS) k_finish(const FinishArgs a)
+__global__ void __launch_bounds__(FIN_THREADS, 4) k_finish(const FinishArgs a)
 {
     __shared__ double sh[FIN_WARPS];
     constexpr int TW = 32 / GL, RW = IS_Z ? 2 : 1;
@@ -611,20 +612,9 @@ __global__ void __launch_bounds__(FIN_THREADS) k_finish(const FinishArgs a)
             const double2 *src = PIECES ? reinterpret_cast<const double2 *>(a.part_m + (o0 - (q & 3) * 4) * RW) + (q & 3)
                                         : reinterpret_cast<const double2 *>(a.part_m + o0 * RW);
             const int64_t pstep = panel_stride * RW / 2;            // in double2
-#pragma unroll 2
-            for (int pn = 0; pn < np; ++pn) {
-                double m[4];
-                if (IS_Z) {
-                    const double2 v0 = __ldcs(src), v1 = __ldcs(src + PS), v2 = __ldcs(src + 2 * PS), v3 = __ldcs(src + 3 * PS);
-                    m[0] = v0.x; m[1] = v1.x; m[2] = v2.x; m[3] = v3.x;
-                    g[0] += v0.y; g[1] += v1.y; g[2] += v2.y; g[3] += v3.y;
-                } else {
-                    const double2 v0 = __ldcs(src), v1 = __ldcs(src + PS);
-                    m[0] = v0.x; m[1] = v0.y; m[2] = v1.x; m[3] = v1.y;
-                }
-                src += pstep;
-                // split every partial (positive, normal: 2^+-1000 at most) into mantissa and exponent with
-                // integer ops; the mantissa product stays below 2^np, far inside the double range
+            // split every partial (positive, normal: 2^+-1000 at most) into mantissa and exponent with integer
+            // ops; the mantissa product stays below 2^np, far inside the double range
+            auto fold_in = [&](const double (&m)[4], int pn) {
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
                     const int hi = __double2hiint(m[c]);
@@ -633,6 +623,35 @@ __global__ void __launch_bounds__(FIN_THREADS) k_finish(const FinishArgs a)
                 }
                 if ((pn & 255) == 255)
                     for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
+            };
+            if (IS_Z) {
+                // HBM-bound (23 MB of partial rows per tree): the loads of panel pn+1 are issued before the
+                // partials of panel pn are consumed
+                double2 cur[4], nxt[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) cur[k] = __ldcs(src + k * PS);
+#pragma unroll 2
+                for (int pn = 0; pn < np; ++pn) {
+                    src += pstep;
+                    if (pn + 1 < np) {
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) nxt[k] = __ldcs(src + k * PS);
+                    }
+                    const double m[4] = {cur[0].x, cur[1].x, cur[2].x, cur[3].x};
+                    g[0] += cur[0].y; g[1] += cur[1].y; g[2] += cur[2].y; g[3] += cur[3].y;
+                    fold_in(m, pn);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) cur[k] = nxt[k];
+                }
+            } else {
+                // issue-bound (three fp64 transcendentals per entry): the plain loop has the fewest instructions
+#pragma unroll 2
+                for (int pn = 0; pn < np; ++pn) {
+                    const double2 v0 = __ldcs(src), v1 = __ldcs(src + PS);
+                    const double m[4] = {v0.x, v0.y, v1.x, v1.y};
+                    src += pstep;
+                    fold_in(m, pn);
+                }
             }
             if (a.part_e) {
                 const int4 *se = reinterpret_cast<const int4 *>(a.part_e + o0);

@@ -4,6 +4,8 @@ from the unmodified reference and against the CPU oracle on fresh seeded inputs.
 Tolerances (BASELINE.json north_star): tree ranking, iteration counts and MAP assignments
 bit-exact; ELBOs and posteriors within 1e-6 relative in fp64 -- the tests ask for 1e-9
 (observed ~1e-13) so a regression shows long before the contract is at risk."""
+import os
+
 import numpy as np
 import pandas as pd
 import pytest
@@ -460,3 +462,32 @@ def test_config3_properties_at_full_shape(eng_mod):
         if t < 22:
             assert lik[t] == pytest.approx(float(g["elbo"][k]), rel=ELBO_RTOL)
     del eng
+
+
+def test_cli_outputs_match_reference(eng_mod, tmp_path, capsys):
+    """CLI level: the command line of the reference's main() (A.py:1133-1191)
+    replayed through arborist_b200.arborist.main on the same input files; every output file is diffed
+    against what the unmodified reference wrote (tests/golden/cli_tiny/expected, oracle/gen_cli_golden.py)."""
+    import pandas as pd
+    sys_path = os.path.join(os.path.dirname(__file__), "..", "oracle")
+    import sys
+    sys.path.insert(0, sys_path)
+    try:
+        import gen_cli_golden as gc
+    finally:
+        sys.path.remove(sys_path)
+    from arborist_b200.arborist import main
+    indir = os.path.join(os.path.dirname(__file__), "golden", "cli_tiny")
+    exp = os.path.join(indir, "expected")
+    main(gc.command_line(indir, str(tmp_path)))
+    out = capsys.readouterr().out
+    assert "Arborist complete!" in out and "Tree 4" in out and "ELBO: -345.43" in out
+    got, want = pd.read_csv(tmp_path / "ranking.csv"), pd.read_csv(os.path.join(exp, "ranking.csv"))
+    assert list(got.columns) == list(want.columns) and list(got["tree_idx"]) == list(want["tree_idx"])
+    np.testing.assert_allclose(got["elbo"], want["elbo"], rtol=ELBO_RTOL)
+    for name in ("cell_assign.csv", "snv_assign.csv", "tree.txt"):          # discrete outputs: byte-identical
+        assert open(tmp_path / name).read() == open(os.path.join(exp, name)).read(), name
+    for name in ("q_z.csv", "q_y.csv"):
+        g, w = pd.read_csv(tmp_path / name), pd.read_csv(os.path.join(exp, name))
+        assert list(g.columns) == list(w.columns) and list(g["id"]) == list(w["id"])
+        np.testing.assert_allclose(g.iloc[:, 1:].to_numpy(), w.iloc[:, 1:].to_numpy(), rtol=Q_RTOL, atol=Q_ATOL)

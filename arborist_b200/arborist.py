@@ -27,7 +27,7 @@ import numpy as np
 import pandas as pd
 
 from .treefit import TreeFit
-from .utils import read_trees, visualize_tree
+from .utils import read_read_counts, read_trees, visualize_tree
 
 __all__ = ["arborist", "run_variational_inference", "run_simple_max_likelihood", "main",
            "parse_arguments", "add_normal_clone", "tree_to_clone_set", "prepare_trees",
@@ -449,7 +449,7 @@ def parse_arguments(argv=None) -> argparse.Namespace:
 
 def main(argv=None):
     args = parse_arguments(argv)
-    read_counts = pd.read_csv(args.read_counts)
+    read_counts = read_read_counts(args.read_counts)      # CSV as upstream; also Parquet / Feather / npz
     snv_clusters = pd.read_csv(args.snv_clusters, header=None, names=["snv", "cluster"])
     candidate_trees = read_trees(args.trees, sep=args.edge_delim)
 

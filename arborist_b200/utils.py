@@ -7,7 +7,7 @@ unavailable instead of breaking ``import arborist_b200``.
 """
 from __future__ import annotations
 
-__all__ = ["read_trees", "visualize_tree", "write_trees"]
+__all__ = ["read_trees", "read_read_counts", "visualize_tree", "write_trees"]
 
 
 def read_trees(file_path, sep=" "):
@@ -32,6 +32,33 @@ def read_trees(file_path, sep=" "):
     if cur:
         trees.append(cur)
     return trees
+
+
+def read_read_counts(path):
+    """The long-format read-count table (columns ``snv, cell, alt, total``) as a DataFrame.
+
+    The reference reads a CSV (``pd.read_csv``, A.py:1135), which at 10^8 rows takes minutes and
+    becomes the floor of a run once the fit is on the GPU.  Besides CSV
+    this accepts the same four columns as Parquet / Feather (pyarrow) or as an ``.npz`` of four
+    arrays; integer id columns then go to the device as they are (``arb_ingest_ids``)."""
+    import pandas as pd
+
+    low = str(path).lower()
+    if low.endswith((".parquet", ".pq")):
+        df = pd.read_parquet(path)
+    elif low.endswith((".feather", ".arrow")):
+        df = pd.read_feather(path)
+    elif low.endswith(".npz"):
+        import numpy as np
+
+        with np.load(path, allow_pickle=False) as z:
+            df = pd.DataFrame({c: z[c] for c in ("snv", "cell", "alt", "total")})
+    else:
+        return pd.read_csv(path)
+    missing = [c for c in ("snv", "cell", "alt", "total") if c not in df.columns]
+    if missing:
+        raise ValueError(f"{path}: missing column(s) {missing}")
+    return df
 
 
 def write_trees(trees, file_path, sep=" "):

@@ -155,3 +155,22 @@ def test_synth_generator_is_seed_stable():
     assert np.array_equal(a.alt, b.alt) and a.trees == b.trees
     g = load_golden("tiny")
     assert np.array_equal(a.snv, g["rc_snv"]) and np.array_equal(a.alt, g["rc_alt"])
+
+
+def test_read_read_counts_formats(tmp_path):
+    """the read-count table as CSV (the reference's format, A.py:1135), Parquet,
+    Feather or npz gives the same DataFrame."""
+    import pandas as pd
+    from arborist_b200.utils import read_read_counts
+    from arborist_b200 import synth
+    rc = synth.generate(synth.CONFIGS["tiny"]).read_counts_frame()
+    rc.to_csv(tmp_path / "rc.csv", index=False)
+    rc.to_parquet(tmp_path / "rc.parquet")
+    rc.to_feather(tmp_path / "rc.feather")
+    np.savez(tmp_path / "rc.npz", **{c: rc[c].to_numpy() for c in rc.columns})
+    for name in ("rc.csv", "rc.parquet", "rc.feather", "rc.npz"):
+        got = read_read_counts(str(tmp_path / name))
+        pd.testing.assert_frame_equal(got[list(rc.columns)], rc, check_dtype=True)
+    np.savez(tmp_path / "bad.npz", snv=rc["snv"].to_numpy())
+    with pytest.raises((ValueError, KeyError)):
+        read_read_counts(str(tmp_path / "bad.npz"))

@@ -82,7 +82,12 @@ struct DevBuf {
 // stream = uint4 [quad][TW].  See arb_ingest.cu "panel layouts".
 struct PanelLayout {
     int kp = 0;
-    int panel_rows = 0;      // rows of the gathered operand per panel
+    int panel_rows = 0;      // max(prz, pry): sizes the shared-memory panel
+    // Panels are INTERLEAVED: gathered index c belongs to panel c % np and is row c / np of it, so the
+    // nonzeros of a row spread evenly over the panels whatever the id order of the input (first-appearance
+    // indices put the cells of the first SNVs next to each other).  The gathered operand is stored in that
+    // order: row arb_perm(c, np, pr) of [np * pr] rows per virtual slot, every panel one contiguous block.
+    int prz = 0, pry = 0;    // rows per panel of the q(z) sweep (S rows of SNVs) / the q(y) sweep (R rows of cells)
     int np_z = 0, np_y = 0;  // number of panels
     int uz = 0, uy = 0;      // tiles per warp per panel
     int fold_z = 0, fold_y = 0;   // 1: a tile's running product provably stays inside the double range
@@ -156,6 +161,7 @@ struct arb_ctx {
     DevBuf scratch;                       // cub temp storage
 };
 
+__host__ __device__ static inline int64_t arb_perm(int64_t c, int np, int pr) { return (c % np) * (int64_t)pr + c / np; }
 static inline int kp_index(int kp) { return kp == 8 ? 0 : kp == 16 ? 1 : 2; }
 // The sweeps always run on 16-column packed rows ("virtual slots", arb_fit.cu): the columns of the
 // trees in flight are laid side by side in units of four, so no lane works on a padding column.

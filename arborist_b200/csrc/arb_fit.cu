@@ -171,7 +171,7 @@ template <int GL>
 __global__ void __launch_bounds__(SEED_THREADS)
 k_seed_s(const double *__restrict__ q_src, int64_t src_slot_stride, const int32_t *__restrict__ list,
          const int32_t *__restrict__ pos_z, const SlotState *__restrict__ st, const uint32_t *__restrict__ masks,
-         int32_t m, int32_t K, double *__restrict__ xs, double *__restrict__ qy_cur, int copy_q)
+         int32_t m, int32_t K, double *__restrict__ xs, double *__restrict__ qy_cur, int copy_q, int np, int pr)
 {
     const int C = K - 1, h = threadIdx.x % GL;
     const int slot = list[blockIdx.y], pos = pos_z[slot];
@@ -188,7 +188,7 @@ k_seed_s(const double *__restrict__ q_src, int64_t src_slot_stride, const int32_
     masked_rows<GL>(q, omask, C, acc);
     if (live) {
         if (4 * h < K) {
-            double2 *xn = reinterpret_cast<double2 *>(xs + packed_off(pos, (K + 3) / 4, h, m, j));
+            double2 *xn = reinterpret_cast<double2 *>(xs + packed_off(pos, (K + 3) / 4, h, (int64_t)np * pr, arb_perm(j, np, pr)));
             xn[0] = make_double2(acc[0], acc[1]);
             xn[1] = make_double2(acc[2], acc[3]);
         }
@@ -203,7 +203,7 @@ k_seed_s(const double *__restrict__ q_src, int64_t src_slot_stride, const int32_
 template <int GL>
 __global__ void __launch_bounds__(SEED_THREADS)
 k_seed_r(const double *__restrict__ qz_cur, const int32_t *__restrict__ list, const SlotState *__restrict__ st,
-         const uint32_t *__restrict__ masks, int32_t n, int32_t K, double *__restrict__ xr)
+         const uint32_t *__restrict__ masks, int32_t n, int32_t K, double *__restrict__ xr, int np, int pr)
 {
     const int C = K - 1, h = threadIdx.x % GL;
     const int slot = list[blockIdx.y], pos = blockIdx.y;
@@ -218,7 +218,7 @@ k_seed_r(const double *__restrict__ qz_cur, const int32_t *__restrict__ list, co
     for (int c = 0; c < 4; ++c) q[c] = (live && 4 * h + c < K) ? qz_cur[((int64_t)slot * n + i) * K + 4 * h + c] : 0.0;
     masked_rows<GL>(q, omask, K, acc);
     if (live && 4 * h < C) {
-        double2 *xn = reinterpret_cast<double2 *>(xr + packed_off(pos, (C + 3) / 4, h, n, i));
+        double2 *xn = reinterpret_cast<double2 *>(xr + packed_off(pos, (C + 3) / 4, h, (int64_t)np * pr, arb_perm(i, np, pr)));
         xn[0] = make_double2(acc[0], acc[1]);
         xn[1] = make_double2(acc[2], acc[3]);
     }
@@ -239,9 +239,10 @@ __device__ __forceinline__ void renorm(double &p, int &e)
 }
 
 struct SweepArgs {
-    const double *x;           // gathered operand, packed: [virtual slot][n_gather][KP]
+    const double *x;           // gathered operand, packed: [virtual slot][n_gather][KP], rows in interleaved
+                               // panel order (arb_perm): panel p = rows p * panel_rows .. of the slot
     int64_t x_slot_stride;     // doubles per virtual slot
-    int32_t n_gather;          // rows of the gathered operand
+    int32_t n_gather;          // rows of the gathered operand per slot = n_panels * panel_rows (padded)
     const int4 *desc;          // [n_panels * WARPS * tiles_per_warp] {first quad, A quads, all quads, 0}
     const int32_t *rows;       // [.. * TW] row of every segment of every tile, -1 = none
     const void *stream;        // [quad][TW] of uint4 (32-bit words) or uint2 (16-bit words, W16)
@@ -484,6 +485,7 @@ struct FinishArgs {
     const double *logq0, *logq0e;   // q(y) only: log prior, log(prior + 1e-12)
     double *q_cur;                  // [slot][row][K or C]
     double *x_next;                 // q(y) only: packed S rows for the q(z) sweep of the same round
+    int32_t xn_np, xn_pr;           // panels / rows per panel of that sweep (interleaved row order)
     double *red;                    // [slot][3][nbmax]: lik, entropy, kl partial sums per CTA
     int32_t nbmax;
     int32_t given_q;                // elbo_terms hook: take q from q_cur instead of the softmax
@@ -566,7 +568,8 @@ __device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int po
             }
         }
         if (!IS_Z && 4 * h < K) {
-            double2 *xn = reinterpret_cast<double2 *>(a.x_next + packed_off(pos_out, (K + 3) / 4, h, a.n_rows, row));
+            double2 *xn = reinterpret_cast<double2 *>(a.x_next + packed_off(pos_out, (K + 3) / 4, h, (int64_t)a.xn_np * a.xn_pr,
+                                                                          arb_perm(row, a.xn_np, a.xn_pr)));
             xn[0] = make_double2(acc[0], acc[1]);
             xn[1] = make_double2(acc[2], acc[3]);
         }
@@ -877,7 +880,8 @@ static int64_t per_slot_bytes(const arb_ctx *ctx, const PanelLayout &L, int K)
     const int64_t kcz = 4 * chunks_for(K), kcy = 4 * chunks_for(C);
     const int64_t nb = std::max((n + FIN_ROWS - 1) / FIN_ROWS, (m + FIN_ROWS - 1) / FIN_ROWS);
     const int64_t ez = L.fold_z ? 0 : 4, ey = L.fold_y ? 0 : 4;
-    return (m * kcz + n * kcy + n * K + m * C) * 8 + (int64_t)L.np_z * n * kcz * (16 + ez) +
+    const int64_t mg = (int64_t)L.np_z * L.prz, ng = (int64_t)L.np_y * L.pry;      // padded gathered rows
+    return (mg * kcz + ng * kcy + n * K + m * C) * 8 + (int64_t)L.np_z * n * kcz * (16 + ez) +
            (int64_t)L.np_y * m * kcy * (8 + ey) + 3 * nb * 8 + 64;
 }
 
@@ -918,7 +922,8 @@ static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve
         ARB_CUDA(cudaMemGetInfo(&free_b, &total_b));
         free_b += arb_pool_bytes(ctx->device);            // parked allocations are ours to reuse
         // one virtual slot of slack per group for the rounding of the packed buffers
-        const int64_t slack = G * ((m + n) * ARB_VW * 8 + ((int64_t)L.np_z * n * 20 + (int64_t)L.np_y * m * 12) * ARB_VW);
+        const int64_t mg = (int64_t)L.np_z * L.prz, ng = (int64_t)L.np_y * L.pry;
+        const int64_t slack = G * ((mg + ng) * ARB_VW * 8 + ((int64_t)L.np_z * n * 20 + (int64_t)L.np_y * m * 12) * ARB_VW);
         const int64_t usable = (int64_t)(free_b * 0.90) - reserve_bytes - slack;
         const int64_t fit = usable / ws.per_slot_bytes;
         ARB_REQUIRE(fit >= 1, ARB_ERR_NOMEM, "not enough device memory for one tree slot (%lld bytes needed, %lld usable)",
@@ -929,12 +934,12 @@ static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve
             sg = n_slots / G;
         }
         const int64_t S = (int64_t)G * sg, vz = G * vslots_for(sg, K), vy = G * vslots_for(sg, C);
-        ARB_TRY(ctx->xs.reserve(vz * m * ARB_VW * 8));
-        ARB_TRY(ctx->xr.reserve(vy * n * ARB_VW * 8));
+        ARB_TRY(ctx->xs.reserve(vz * mg * ARB_VW * 8));
+        ARB_TRY(ctx->xr.reserve(vy * ng * ARB_VW * 8));
         // columns past the last tree of a sweep are never read back, but the sweep multiplies through
         // them: keep them finite (stale S / R values or zero)
-        ARB_CUDA(cudaMemsetAsync(ctx->xs.p, 0, vz * m * ARB_VW * 8, ctx->stream));
-        ARB_CUDA(cudaMemsetAsync(ctx->xr.p, 0, vy * n * ARB_VW * 8, ctx->stream));
+        ARB_CUDA(cudaMemsetAsync(ctx->xs.p, 0, vz * mg * ARB_VW * 8, ctx->stream));
+        ARB_CUDA(cudaMemsetAsync(ctx->xr.p, 0, vy * ng * ARB_VW * 8, ctx->stream));
         ARB_TRY(ctx->qz_cur.reserve(S * n * K * 8));
         ARB_TRY(ctx->qy_cur.reserve(S * m * C * 8));
         // product (8) [+ exponent (4) when the layout could not prove the range]
@@ -994,8 +999,8 @@ static WsPtrs ws_ptrs(arb_ctx *ctx, const PanelLayout &L, int g, cudaStream_t st
     w.list_init = lists + 2 * S + w.slot0;
     w.pos_z = lists + 3 * S;
     w.snap_tree = lists + 4 * S;
-    w.xs = ctx->xs.as<double>() + g * vz * m * ARB_VW;
-    w.xr = ctx->xr.as<double>() + g * vy * n * ARB_VW;
+    w.xs = ctx->xs.as<double>() + g * vz * ((int64_t)L.np_z * L.prz) * ARB_VW;
+    w.xr = ctx->xr.as<double>() + g * vy * ((int64_t)L.np_y * L.pry) * ARB_VW;
     double *pz = ctx->part_z.as<double>(), *py = ctx->part_y.as<double>();
     const int64_t pz_cols = vz * L.np_z * n * ARB_VW, py_cols = vy * L.np_y * m * ARB_VW;   // per group
     w.pz_m = pz + g * 2 * pz_cols;
@@ -1022,13 +1027,13 @@ static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
 {
     SweepArgs a;
     a.x = w.xs;
-    a.x_slot_stride = (int64_t)ctx->n_snvs * ARB_VW;
-    a.n_gather = ctx->n_snvs;
+    a.x_slot_stride = (int64_t)L.np_z * L.prz * ARB_VW;
+    a.n_gather = L.np_z * L.prz;
     a.desc = L.zdesc.as<int4>();
     a.rows = L.zrows.as<int32_t>();
     a.stream = L.zstream.p;
     a.n_rows = ctx->n_cells;
-    a.panel_rows = L.panel_rows;
+    a.panel_rows = L.prz;
     a.n_panels = L.np_z;
     a.tiles_per_warp = L.uz;
     a.n_vslots = (int)vslots_for(n_trees, ctx->ws_k);
@@ -1046,13 +1051,13 @@ static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
 {
     SweepArgs a;
     a.x = w.xr;
-    a.x_slot_stride = (int64_t)ctx->n_cells * ARB_VW;
-    a.n_gather = ctx->n_cells;
+    a.x_slot_stride = (int64_t)L.np_y * L.pry * ARB_VW;
+    a.n_gather = L.np_y * L.pry;
     a.desc = L.ydesc.as<int4>();
     a.rows = L.yrows.as<int32_t>();
     a.stream = L.ystream.p;
     a.n_rows = ctx->n_snvs;
-    a.panel_rows = L.panel_rows;
+    a.panel_rows = L.pry;
     a.n_panels = L.np_y;
     a.tiles_per_warp = L.uy;
     a.n_vslots = (int)vslots_for(n_trees, ctx->ws_k - 1);
@@ -1084,6 +1089,7 @@ static void launch_finish_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w,
     a.logq0e = nullptr;
     a.q_cur = ctx->qz_cur.as<double>();
     a.x_next = nullptr;
+    a.xn_np = a.xn_pr = 1;
     a.red = ctx->red.as<double>();
     a.nbmax = ws.nbmax;
     a.given_q = given_q;
@@ -1111,6 +1117,8 @@ static void launch_finish_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w,
     a.logq0e = ctx->logq0e.as<double>();
     a.q_cur = ctx->qy_cur.as<double>();
     a.x_next = w.xs;
+    a.xn_np = L.np_z;
+    a.xn_pr = L.prz;
     a.red = ctx->red.as<double>();
     a.nbmax = ws.nbmax;
     a.given_q = 0;
@@ -1122,7 +1130,8 @@ static void launch_seed_s(arb_ctx *ctx, const WsPtrs &w, const uint32_t *masks, 
                           int64_t src_stride, const int32_t *list, int n_active, int K, int copy_q)
 {
     k_seed_s<GL><<<dim3(grid_for(ctx->n_snvs, SEED_THREADS / GL), n_active), SEED_THREADS, 0, w.stream>>>(
-        q_src, src_stride, list, w.pos_z, w.st, masks, ctx->n_snvs, K, w.xs, ctx->qy_cur.as<double>(), copy_q);
+        q_src, src_stride, list, w.pos_z, w.st, masks, ctx->n_snvs, K, w.xs, ctx->qy_cur.as<double>(), copy_q,
+        ctx->layout[kp_index(ctx->ws_kp)].np_z, ctx->layout[kp_index(ctx->ws_kp)].prz);
 }
 
 template <int GL>
@@ -1130,7 +1139,8 @@ static void launch_seed_r(arb_ctx *ctx, const WsPtrs &w, const uint32_t *masks, 
                           int K)
 {
     k_seed_r<GL><<<dim3(grid_for(ctx->n_cells, SEED_THREADS / GL), n_active), SEED_THREADS, 0, w.stream>>>(
-        ctx->qz_cur.as<double>(), list, w.st, masks, ctx->n_cells, K, w.xr);
+        ctx->qz_cur.as<double>(), list, w.st, masks, ctx->n_cells, K, w.xr, ctx->layout[kp_index(ctx->ws_kp)].np_y,
+        ctx->layout[kp_index(ctx->ws_kp)].pry);
 }
 
 // One fit of n_trees trees whose masks are on the device.  The slots are split into stream groups;

@@ -476,11 +476,12 @@ __global__ void k_remap_codes(const int32_t *raw, const int32_t *map, int64_t n,
 //             Short segments are padded with NULL words (code 0, offset of an all-zero row kept
 //             after the panel): their factor is 1 + d*0 = 1 exactly, so padding needs no predicate.
 __global__ void k_panel_keys(const int32_t *row, const int32_t *col, const uint16_t *code, int64_t nnz,
-                             int32_t n_rows, int32_t panel_rows, uint64_t *key)
+                             int32_t n_rows, int32_t np, uint64_t *key)
 {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= nnz) return;
-    const uint64_t panel = (uint64_t)(col[i] / panel_rows), local = (uint64_t)(col[i] % panel_rows);
+    // interleaved panels (PanelLayout in arb_common.cuh)
+    const uint64_t panel = (uint64_t)(col[i] % np), local = (uint64_t)(col[i] / np);
     const uint64_t seg = panel * (uint64_t)n_rows + (uint64_t)row[i];
     key[i] = (((seg << 16) | (uint64_t)code[i]) << 16) | local;
 }
@@ -655,7 +656,7 @@ static int build_stream(arb_ctx *ctx, const int32_t *row, const int32_t *col, in
     ARB_CUDA(cudaMemsetAsync(out.rows->p, 0xff, (n_slots + 1) * tw * 4, ctx->stream));
     cudaStream_t st = ctx->stream;
     const int B = 256;
-    k_panel_keys<<<grid_for(nnz, B), B, 0, st>>>(row, col, ctx->coo_code.as<uint16_t>(), nnz, n_rows, panel_rows,
+    k_panel_keys<<<grid_for(nnz, B), B, 0, st>>>(row, col, ctx->coo_code.as<uint16_t>(), nnz, n_rows, np,
                                                  k_in.as<uint64_t>());
     const int end_bit = std::min(64, 32 + bits_for((uint64_t)n_seg));
     ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
@@ -729,11 +730,14 @@ int arb_build_layout(arb_ctx *ctx, int kp)
     int panel_rows = (int)(budget / ((size_t)kp * 8)) - 1;        // one more row of zeros for the padding words
     panel_rows = std::min(panel_rows, 65504) / 32 * 32;
     ARB_REQUIRE(panel_rows >= 32, ARB_ERR_INVALID, "panel budget too small");
-    L.panel_rows = panel_rows;
     L.np_z = (ctx->n_snvs + panel_rows - 1) / panel_rows;
     L.np_y = (ctx->n_cells + panel_rows - 1) / panel_rows;
+    // equal panels: ceil(rows / panels) rows each
+    L.prz = (ctx->n_snvs + L.np_z - 1) / L.np_z;
+    L.pry = (ctx->n_cells + L.np_y - 1) / L.np_y;
+    L.panel_rows = std::max(L.prz, L.pry);
     // 16-bit stream words when the row (11 bits, the zero row included) and the pair code (5 bits) fit
-    L.w16 = kp == ARB_VW && panel_rows < 2048 && ctx->n_pairs <= 32 && !ctx->opt_w32;
+    L.w16 = kp == ARB_VW && L.panel_rows < 2048 && ctx->n_pairs <= 32 && !ctx->opt_w32;
     // per-code bounds on |log2(1 + d x)|, x in [0,1], with a little slack for rounding
     std::vector<float> up(ctx->n_pairs), dn(ctx->n_pairs);
     for (int c = 0; c < ctx->n_pairs; ++c) {
@@ -746,10 +750,10 @@ int arb_build_layout(arb_ctx *ctx, int kp)
     ARB_TRY(d_dn.reserve(dn.size() * 4));
     ARB_CUDA(cudaMemcpyAsync(d_up.p, up.data(), up.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
     ARB_CUDA(cudaMemcpyAsync(d_dn.p, dn.data(), dn.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
-    ARB_TRY(build_stream(ctx, ctx->coo_cell.as<int32_t>(), ctx->coo_snv.as<int32_t>(), ctx->n_cells, panel_rows,
+    ARB_TRY(build_stream(ctx, ctx->coo_cell.as<int32_t>(), ctx->coo_snv.as<int32_t>(), ctx->n_cells, L.prz,
                          L.np_z, kp, L.w16, d_up.as<float>(), d_dn.as<float>(),
                          StreamOut{&L.zdesc, &L.zrows, &L.zstream, &L.uz, &L.fold_z, &L.quads_z}));
-    ARB_TRY(build_stream(ctx, ctx->coo_snv.as<int32_t>(), ctx->coo_cell.as<int32_t>(), ctx->n_snvs, panel_rows,
+    ARB_TRY(build_stream(ctx, ctx->coo_snv.as<int32_t>(), ctx->coo_cell.as<int32_t>(), ctx->n_snvs, L.pry,
                          L.np_y, kp, L.w16, d_up.as<float>(), d_dn.as<float>(),
                          StreamOut{&L.ydesc, &L.yrows, &L.ystream, &L.uy, &L.fold_y, &L.quads_y}));
     d_up.release();

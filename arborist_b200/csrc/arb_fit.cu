@@ -49,9 +49,13 @@ int arb_check_table_range(arb_ctx *ctx);
 
 enum { PH_EMPTY = 0, PH_INIT = 1, PH_ITER = 2 };
 
+// q(z) / q(y) of a slot live in two planes: `cur` holds the current iterate, `bestb` the best one so far
+// (A.py:762-763, 808-811 copy the arrays; here the next iterate is simply written to the plane that is
+// not the best one, and the best plane is copied out once, when the tree is done).
 struct SlotState {
     int32_t tree, phase, iter, converged;
     double best;
+    int32_t cur, bestb;
 };
 
 // One Control per stream group: the group owns slots slot0 .. slot0+n_slots-1 and fits trees
@@ -171,7 +175,8 @@ template <int GL>
 __global__ void __launch_bounds__(SEED_THREADS)
 k_seed_s(const double *__restrict__ q_src, int64_t src_slot_stride, const int32_t *__restrict__ list,
          const int32_t *__restrict__ pos_z, const SlotState *__restrict__ st, const uint32_t *__restrict__ masks,
-         int32_t m, int32_t K, double *__restrict__ xs, double *__restrict__ qy_cur, int copy_q, int np, int pr)
+         int32_t m, int32_t K, double *__restrict__ xs, double *__restrict__ qy_cur, int copy_q, int np, int pr,
+         int64_t plane_slots)
 {
     const int C = K - 1, h = threadIdx.x % GL;
     const int slot = list[blockIdx.y], pos = pos_z[slot];
@@ -195,7 +200,7 @@ k_seed_s(const double *__restrict__ q_src, int64_t src_slot_stride, const int32_
         if (copy_q)
 #pragma unroll
             for (int c = 0; c < 4; ++c)
-                if (4 * h + c < C) qy_cur[((int64_t)slot * m + j) * C + 4 * h + c] = q[c];
+                if (4 * h + c < C) qy_cur[(((1 - st[slot].bestb) * plane_slots + slot) * m + j) * C + 4 * h + c] = q[c];
     }
 }
 
@@ -203,7 +208,8 @@ k_seed_s(const double *__restrict__ q_src, int64_t src_slot_stride, const int32_
 template <int GL>
 __global__ void __launch_bounds__(SEED_THREADS)
 k_seed_r(const double *__restrict__ qz_cur, const int32_t *__restrict__ list, const SlotState *__restrict__ st,
-         const uint32_t *__restrict__ masks, int32_t n, int32_t K, double *__restrict__ xr, int np, int pr)
+         const uint32_t *__restrict__ masks, int32_t n, int32_t K, double *__restrict__ xr, int np, int pr,
+         int64_t plane_slots)
 {
     const int C = K - 1, h = threadIdx.x % GL;
     const int slot = list[blockIdx.y], pos = blockIdx.y;
@@ -215,7 +221,7 @@ k_seed_r(const double *__restrict__ qz_cur, const int32_t *__restrict__ list, co
     const bool live = i < n;
     double q[4], acc[4];
 #pragma unroll
-    for (int c = 0; c < 4; ++c) q[c] = (live && 4 * h + c < K) ? qz_cur[((int64_t)slot * n + i) * K + 4 * h + c] : 0.0;
+    for (int c = 0; c < 4; ++c) q[c] = (live && 4 * h + c < K) ? qz_cur[((st[slot].cur * plane_slots + slot) * n + i) * K + 4 * h + c] : 0.0;
     masked_rows<GL>(q, omask, K, acc);
     if (live && 4 * h < C) {
         double2 *xn = reinterpret_cast<double2 *>(xr + packed_off(pos, (C + 3) / 4, h, (int64_t)np * pr, arb_perm(i, np, pr)));
@@ -483,7 +489,8 @@ struct FinishArgs {
     const SlotState *st;
     const uint32_t *masks;
     const double *logq0, *logq0e;   // q(y) only: log prior, log(prior + 1e-12)
-    double *q_cur;                  // [slot][row][K or C]
+    double *q_cur;                  // [plane][slot][row][K or C]; the iterate goes to plane 1 - st[slot].bestb
+    int64_t plane_slots;            // slots per plane
     double *x_next;                 // q(y) only: packed S rows for the q(z) sweep of the same round
     int32_t xn_np, xn_pr;           // panels / rows per panel of that sweep (interleaved row order)
     double *red;                    // [slot][3][nbmax]: lik, entropy, kl partial sums per CTA
@@ -501,7 +508,7 @@ __device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int po
                                            const double (&g)[4], double &acc1, double &acc2)
 {
     const int K = a.K, C = K - 1, ncol = IS_Z ? K : C;
-    const int64_t qbase = ((int64_t)slot * a.n_rows + row) * ncol;
+    const int64_t qbase = (((1 - a.st[slot].bestb) * a.plane_slots + slot) * a.n_rows + row) * ncol;
     double logit[4];
     bool v[4];
 #pragma unroll
@@ -707,6 +714,8 @@ __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict_
             SlotState z = st[s];
             int snap = -1;
             if (z.phase != PH_EMPTY) {
+                const int wr = 1 - z.bestb;                    // the plane this round's q(y) / q(z) went to
+                z.cur = wr;
                 const double *r = red + (int64_t)s * 3 * nbmax;
                 double lik = ctl->sum_la, ent = 0.0, kl = 0.0;
                 for (int b = 0; b < ctl->nbz; ++b) lik += r[b];
@@ -719,7 +728,7 @@ __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict_
                     z.iter = 0;
                     z.converged = 0;
                     z.phase = PH_ITER;
-                    snap = z.tree;                            // A.py:762-763
+                    z.bestb = wr;                             // A.py:762-763
                     if (trace) trace[(int64_t)z.tree * (ctl->max_iter + 1)] = elbo;
                     done = ctl->max_iter == 0 || ctl->mode == ARB_MODE_ML;
                 } else {
@@ -727,8 +736,8 @@ __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict_
                     const double elbo = lik + ent - kl;       // A.py:801-803
                     if (trace) trace[(int64_t)z.tree * (ctl->max_iter + 1) + z.iter + 1] = elbo;
                     if (fabs(elbo - z.best) < ctl->tol) z.converged = 1;      // A.py:805 (vs BEST)
-                    if (elbo > z.best) {                                       // A.py:808
-                        snap = z.tree;
+                    if (elbo > z.best) {                                       // A.py:808-811
+                        z.bestb = wr;
                         z.best = elbo;
                     }
                     z.iter += 1;
@@ -737,6 +746,7 @@ __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict_
                 if (done) {
                     elbo_out[z.tree] = z.best;
                     iters_out[z.tree] = z.iter;
+                    snap = z.tree * 2 + z.bestb;              // k_snapshot copies the best plane out
                     z.phase = PH_EMPTY;
                     z.tree = -1;
                     atomicAdd(&ctl->n_done, 1);
@@ -758,6 +768,8 @@ __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict_
                 z.iter = 0;
                 z.converged = 0;
                 z.best = 0.0;
+                z.cur = 0;
+                z.bestb = 1;                                  // nothing kept yet: the first pass writes plane 0
                 st[s] = z;
                 list_init[ni++] = s;
             } else if (z.phase == PH_ITER) {
@@ -775,14 +787,15 @@ __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict_
     }
 }
 
-// A.py:762-763 / 809-810: keep the posteriors of the best iterate
+// A.py:816: the posteriors of a finished tree's best iterate leave the slot (snap = 2 * tree + plane)
 __global__ void k_snapshot(const int32_t *__restrict__ snap_tree, const double *__restrict__ qz_cur,
                            const double *__restrict__ qy_cur, int64_t nz, int64_t ny, double *__restrict__ best_qz,
-                           double *__restrict__ best_qy, int slot0)
+                           double *__restrict__ best_qy, int slot0, int64_t plane_slots)
 {
-    const int slot = slot0 + blockIdx.y, tree = snap_tree[slot];
-    if (tree < 0) return;
-    const double *sz = qz_cur + (int64_t)slot * nz, *sy = qy_cur + (int64_t)slot * ny;
+    const int slot = slot0 + blockIdx.y, snap = snap_tree[slot];
+    if (snap < 0) return;
+    const int tree = snap >> 1, b = snap & 1;
+    const double *sz = qz_cur + (b * plane_slots + slot) * nz, *sy = qy_cur + (b * plane_slots + slot) * ny;
     double *dz = best_qz + (int64_t)tree * nz, *dy = best_qy + (int64_t)tree * ny;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nz; i += stride) dz[i] = sz[i];
@@ -881,7 +894,7 @@ static int64_t per_slot_bytes(const arb_ctx *ctx, const PanelLayout &L, int K)
     const int64_t nb = std::max((n + FIN_ROWS - 1) / FIN_ROWS, (m + FIN_ROWS - 1) / FIN_ROWS);
     const int64_t ez = L.fold_z ? 0 : 4, ey = L.fold_y ? 0 : 4;
     const int64_t mg = (int64_t)L.np_z * L.prz, ng = (int64_t)L.np_y * L.pry;      // padded gathered rows
-    return (mg * kcz + ng * kcy + n * K + m * C) * 8 + (int64_t)L.np_z * n * kcz * (16 + ez) +
+    return (mg * kcz + ng * kcy + 2 * (n * K + m * C)) * 8 + (int64_t)L.np_z * n * kcz * (16 + ez) +
            (int64_t)L.np_y * m * kcy * (8 + ey) + 3 * nb * 8 + 64;
 }
 
@@ -940,8 +953,8 @@ static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve
         // them: keep them finite (stale S / R values or zero)
         ARB_CUDA(cudaMemsetAsync(ctx->xs.p, 0, vz * mg * ARB_VW * 8, ctx->stream));
         ARB_CUDA(cudaMemsetAsync(ctx->xr.p, 0, vy * ng * ARB_VW * 8, ctx->stream));
-        ARB_TRY(ctx->qz_cur.reserve(S * n * K * 8));
-        ARB_TRY(ctx->qy_cur.reserve(S * m * C * 8));
+        ARB_TRY(ctx->qz_cur.reserve(2 * S * n * K * 8));      // two planes (SlotState)
+        ARB_TRY(ctx->qy_cur.reserve(2 * S * m * C * 8));
         // product (8) [+ exponent (4) when the layout could not prove the range]
         ARB_TRY(ctx->part_z.reserve(vz * L.np_z * n * ARB_VW * (L.fold_z ? 16 : 20) + 64));
         ARB_TRY(ctx->part_y.reserve(vy * L.np_y * m * ARB_VW * (L.fold_y ? 8 : 12) + 64));
@@ -1088,6 +1101,7 @@ static void launch_finish_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w,
     a.logq0 = nullptr;
     a.logq0e = nullptr;
     a.q_cur = ctx->qz_cur.as<double>();
+    a.plane_slots = ctx->ws_slots;
     a.x_next = nullptr;
     a.xn_np = a.xn_pr = 1;
     a.red = ctx->red.as<double>();
@@ -1116,6 +1130,7 @@ static void launch_finish_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w,
     a.logq0 = ctx->logq0.as<double>();
     a.logq0e = ctx->logq0e.as<double>();
     a.q_cur = ctx->qy_cur.as<double>();
+    a.plane_slots = ctx->ws_slots;
     a.x_next = w.xs;
     a.xn_np = L.np_z;
     a.xn_pr = L.prz;
@@ -1131,7 +1146,7 @@ static void launch_seed_s(arb_ctx *ctx, const WsPtrs &w, const uint32_t *masks, 
 {
     k_seed_s<GL><<<dim3(grid_for(ctx->n_snvs, SEED_THREADS / GL), n_active), SEED_THREADS, 0, w.stream>>>(
         q_src, src_stride, list, w.pos_z, w.st, masks, ctx->n_snvs, K, w.xs, ctx->qy_cur.as<double>(), copy_q,
-        ctx->layout[kp_index(ctx->ws_kp)].np_z, ctx->layout[kp_index(ctx->ws_kp)].prz);
+        ctx->layout[kp_index(ctx->ws_kp)].np_z, ctx->layout[kp_index(ctx->ws_kp)].prz, (int64_t)ctx->ws_slots);
 }
 
 template <int GL>
@@ -1140,7 +1155,7 @@ static void launch_seed_r(arb_ctx *ctx, const WsPtrs &w, const uint32_t *masks, 
 {
     k_seed_r<GL><<<dim3(grid_for(ctx->n_cells, SEED_THREADS / GL), n_active), SEED_THREADS, 0, w.stream>>>(
         ctx->qz_cur.as<double>(), list, w.st, masks, ctx->n_cells, K, w.xr, ctx->layout[kp_index(ctx->ws_kp)].np_y,
-        ctx->layout[kp_index(ctx->ws_kp)].pry);
+        ctx->layout[kp_index(ctx->ws_kp)].pry, (int64_t)ctx->ws_slots);
 }
 
 // One fit of n_trees trees whose masks are on the device.  The slots are split into stream groups;
@@ -1263,7 +1278,7 @@ static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, 
             if (tg.best_qz) {
                 k_snapshot<<<dim3(16, ws.sg), 256, 0, p.stream>>>(p.snap_tree, ctx->qz_cur.as<double>(),
                                                                  ctx->qy_cur.as<double>(), nz, ny, tg.best_qz,
-                                                                 tg.best_qy, p.slot0);
+                                                                 tg.best_qy, p.slot0, (int64_t)ctx->ws_slots);
                 stats.launches++;
             }
         }
@@ -1625,6 +1640,8 @@ static int hook_setup(arb_ctx *ctx, int K, const uint8_t *presence, HookEnv &env
     memset(&s0, 0, sizeof s0);
     s0.tree = 0;
     s0.phase = PH_INIT;
+    s0.cur = 0;                         // explicit posteriors are read from / written to plane 0
+    s0.bestb = 1;
     ARB_CUDA(cudaMemcpyAsync(env.w.st, &s0, sizeof s0, cudaMemcpyHostToDevice, ctx->stream));
     int32_t zero = 0;                   // the one tree sits in slot 0 at packed position 0
     ARB_CUDA(cudaMemcpyAsync(env.w.list_z, &zero, 4, cudaMemcpyHostToDevice, ctx->stream));

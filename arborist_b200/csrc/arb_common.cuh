@@ -128,6 +128,7 @@ struct arb_ctx {
     std::vector<int64_t> pair_count;
     std::vector<double> tab_lp, tab_la;   // host copies of the table
     DevBuf tab_dw;                        // double2 [n_pairs]: (expm1(lp-la), lp-la)
+    std::vector<double> h_dw;             // host copy of tab_dw (d, w interleaved)
     double sum_la = 0;                    // sum over nonzeros of log_absent
     int renorm_every = 16;
     double alpha = 0;

@@ -41,6 +41,9 @@ int arb_check_table_range(arb_ctx *ctx);
 #define ARB_PIECE_LAYOUT 1
 #endif
 #define ARB_PIECES(with_g) ((ARB_PIECE_LAYOUT >> ((with_g) ? 1 : 0)) & 1)
+#ifndef ARB_TABC
+#define ARB_TABC 1
+#endif
 #define SWEEP_THREADS (ARB_SWEEP_WARPS * 32)
 #define FIN_THREADS 256
 #define FIN_ROWS 256          // rows of q per finishing CTA (fixed: the ELBO reduction order depends on it)
@@ -259,6 +262,8 @@ struct SweepArgs {
     double *out_m;             // [vslot][panel][row][KP] the segment's product (FOLD) or its mantissa; the q(z)
                                // sweep interleaves {product, sum_k w_k x} per column
     int32_t *out_e;            // [vslot][panel][row][KP] exponent (not FOLD)
+    double2 tabc[32];          // W16 (<= 32 pair codes): the (d, w) table in the kernel's constant bank, so the
+                               // look-ups of the G region stay off the shared-memory pipe
 };
 
 // Four clones of one nonzero: two LDS.128 from the staged panel, 4 x (DFMA + DMUL) for the
@@ -301,7 +306,7 @@ __device__ __forceinline__ void quad_words(const uint2 &q, uint32_t (&w)[4])
 }
 
 template <int KP, bool WITH_G, bool FOLD, bool W16>
-__global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const SweepArgs a)
+__global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const __grid_constant__ SweepArgs a)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     double *xs = reinterpret_cast<double *>(smem_raw);
@@ -406,7 +411,8 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const SweepAr
         sp += TW;                                                                               \
         _Pragma("unroll") for (int s = 0; s < 4; ++s) {                                         \
             const uint32_t code = ww[s] >> 18, off = ww[s] & 0x3ffffu;                          \
-            const double2 dw = (FOLD || code < (uint32_t)a.tab_n) ? tab[code] : __ldg(a.dw + code); \
+            const double2 dw = ARB_TABC && W16 ? a.tabc[code]                                   \
+                               : (FOLD || code < (uint32_t)a.tab_n) ? tab[code] : __ldg(a.dw + code); \
             sweep_step<WITH_G>(xa_base, xb_base, off, dw.x, dw.y, p, g);                        \
             if (!FOLD && each) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);                  \
         }                                                                                       \
@@ -1023,6 +1029,13 @@ static WsPtrs ws_ptrs(arb_ctx *ctx, const PanelLayout &L, int g, cudaStream_t st
     return w;
 }
 
+static void fill_tabc(const arb_ctx *ctx, SweepArgs &a)
+{
+    memset(a.tabc, 0, sizeof a.tabc);
+    const int n = std::min<int>(32, (int)ctx->h_dw.size() / 2);
+    for (int c = 0; c < n; ++c) a.tabc[c] = make_double2(ctx->h_dw[2 * c], ctx->h_dw[2 * c + 1]);
+}
+
 template <bool WITH_G>
 static void launch_sweep(const SweepArgs &a, int grid, int fold, int w16, size_t smem, cudaStream_t st)
 {
@@ -1056,6 +1069,7 @@ static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.renorm_quads = ctx->renorm_every / 4;
     a.out_m = w.pz_m;
     a.out_e = w.pz_e;
+    fill_tabc(ctx, a);
     const int grid = a.n_vslots * L.np_z;
     launch_sweep<true>(a, grid, L.fold_z, L.w16, sweep_smem_bytes(ctx, L), w.stream);
 }
@@ -1080,6 +1094,7 @@ static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.renorm_quads = ctx->renorm_every / 4;
     a.out_m = w.py_m;
     a.out_e = w.py_e;
+    fill_tabc(ctx, a);
     const int grid = a.n_vslots * L.np_y;
     launch_sweep<false>(a, grid, L.fold_y, L.w16, sweep_smem_bytes(ctx, L), w.stream);
 }

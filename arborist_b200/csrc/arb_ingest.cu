@@ -777,6 +777,8 @@ int arb_refresh_tables(arb_ctx *ctx)
     ARB_CUDA(cudaMemcpyAsync(la.p, ctx->tab_la.data(), (size_t)n * 8, cudaMemcpyHostToDevice, ctx->stream));
     k_table_derive<<<grid_for(n, 128), 128, 0, ctx->stream>>>(lp.as<double>(), la.as<double>(), n,
                                                              ctx->tab_dw.as<double2>());
+    ctx->h_dw.resize((size_t)n * 2);             // the device's own doubles, for the kernels' constant-bank copy
+    ARB_CUDA(cudaMemcpyAsync(ctx->h_dw.data(), ctx->tab_dw.p, (size_t)n * 16, cudaMemcpyDeviceToHost, ctx->stream));
     ARB_CUDA(cudaStreamSynchronize(ctx->stream));
     lp.release();
     la.release();

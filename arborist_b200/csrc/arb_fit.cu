@@ -41,6 +41,8 @@ int arb_check_table_range(arb_ctx *ctx);
 #define ARB_PIECE_LAYOUT 1
 #endif
 #define ARB_PIECES(with_g) ((ARB_PIECE_LAYOUT >> ((with_g) ? 1 : 0)) & 1)
+// partial rows are written once and read once by the finishing kernel: streaming stores
+#define ARB_ST(p, v) __stcs((p), (v))
 #ifndef ARB_TABC
 #define ARB_TABC 1
 #endif
@@ -451,13 +453,13 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const __grid_
             char *pr = out_a + (int64_t)row * out_stride;
             if (WITH_G) {
                 double2 *lo = reinterpret_cast<double2 *>(pr + swz * 128), *hi = reinterpret_cast<double2 *>(pr + (1 - swz) * 128);
-                lo[0] = make_double2(p[0], g[0]);
-                lo[4] = make_double2(p[1], g[1]);
-                hi[0] = make_double2(p[2], g[2]);
-                hi[4] = make_double2(p[3], g[3]);
+                ARB_ST(lo + 0, make_double2(p[0], g[0]));
+                ARB_ST(lo + 4, make_double2(p[1], g[1]));
+                ARB_ST(hi + 0, make_double2(p[2], g[2]));
+                ARB_ST(hi + 4, make_double2(p[3], g[3]));
             } else {
-                *reinterpret_cast<double2 *>(pr + swz * 64) = make_double2(p[0], p[1]);
-                *reinterpret_cast<double2 *>(pr + (1 - swz) * 64) = make_double2(p[2], p[3]);
+                ARB_ST(reinterpret_cast<double2 *>(pr + swz * 64), make_double2(p[0], p[1]));
+                ARB_ST(reinterpret_cast<double2 *>(pr + (1 - swz) * 64), make_double2(p[2], p[3]));
             }
             } else {
             // partial row: q(z) {m, g} per column, q(y) m; this lane's pair (off_a, off_a+1), the other pair
@@ -465,13 +467,13 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const __grid_
             char *pa = out_a + (int64_t)row * out_stride;
             char *pb = reinterpret_cast<char *>(reinterpret_cast<uintptr_t>(pa) ^ (uintptr_t)(16 * RW));
             if (WITH_G) {
-                reinterpret_cast<double2 *>(pa)[0] = make_double2(p[0], g[0]);
-                reinterpret_cast<double2 *>(pa)[1] = make_double2(p[1], g[1]);
-                reinterpret_cast<double2 *>(pb)[0] = make_double2(p[2], g[2]);
-                reinterpret_cast<double2 *>(pb)[1] = make_double2(p[3], g[3]);
+                ARB_ST(reinterpret_cast<double2 *>(pa) + 0, make_double2(p[0], g[0]));
+                ARB_ST(reinterpret_cast<double2 *>(pa) + 1, make_double2(p[1], g[1]));
+                ARB_ST(reinterpret_cast<double2 *>(pb) + 0, make_double2(p[2], g[2]));
+                ARB_ST(reinterpret_cast<double2 *>(pb) + 1, make_double2(p[3], g[3]));
             } else {
-                reinterpret_cast<double2 *>(pa)[0] = make_double2(p[0], p[1]);
-                reinterpret_cast<double2 *>(pb)[0] = make_double2(p[2], p[3]);
+                ARB_ST(reinterpret_cast<double2 *>(pa) + 0, make_double2(p[0], p[1]));
+                ARB_ST(reinterpret_cast<double2 *>(pb) + 0, make_double2(p[2], p[3]));
             }
             }
             if (!FOLD) {

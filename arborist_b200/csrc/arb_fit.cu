@@ -43,6 +43,18 @@ int arb_check_table_range(arb_ctx *ctx);
 #define ARB_PIECES(with_g) ((ARB_PIECE_LAYOUT >> ((with_g) ? 1 : 0)) & 1)
 // partial rows are written once and read once by the finishing kernel: streaming stores
 #define ARB_ST(p, v) __stcs((p), (v))
+// The stream is loaded three quads ahead of its use.  Pulling the line into L1 further ahead
+// (prefetch.global.L1, ARB_PF_QUADS = 6 / 12 / 24 quads) was measured 1 % SLOWER at config 3: the
+// long-scoreboard stalls on the stream words are covered by the other warps, and the prefetches cost
+// L1 cycles on the pipe that bounds the kernel.  Off by default.
+#ifndef ARB_PF_QUADS
+#define ARB_PF_QUADS 0
+#endif
+#if ARB_PF_QUADS > 0
+#define ARB_PREFETCH(sp) asm volatile("prefetch.global.L1 [%0];" ::"l"((sp) + ARB_PF_QUADS * TW));
+#else
+#define ARB_PREFETCH(sp)
+#endif
 #ifndef ARB_TABC
 #define ARB_TABC 1
 #endif
@@ -392,6 +404,7 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const __grid_
         uint32_t w[4];                                                                          \
         quad_words(WC, w);                                                                      \
         WC = __ldg(sp);                                                                         \
+        ARB_PREFETCH(sp)                                                                        \
         sp += TW;                                                                               \
         sweep_step<WITH_G>(xa_base, xb_base, w[0], dw0.x, dw0.y, p, g);                         \
         if (!FOLD && each) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);                      \
@@ -410,6 +423,7 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const __grid_
         uint32_t ww[4];                                                                         \
         quad_words(WC, ww);                                                                     \
         WC = __ldg(sp);                                                                         \
+        ARB_PREFETCH(sp)                                                                        \
         sp += TW;                                                                               \
         _Pragma("unroll") for (int s = 0; s < 4; ++s) {                                         \
             const uint32_t code = ww[s] >> 18, off = ww[s] & 0x3ffffu;                          \

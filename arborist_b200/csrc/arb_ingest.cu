@@ -690,7 +690,7 @@ static int build_stream(arb_ctx *ctx, const int32_t *row, const int32_t *col, in
     *out.tiles_per_warp = U;
     *out.quads = total_q;
     // the sweep reads three quads ahead of the one it works on: keep that many spare at the end
-    const int64_t n_words = ((int64_t)total_q + 4) * tw * 4;
+    const int64_t n_words = ((int64_t)total_q + 4 + 64) * tw * 4;     // + room for the L1 prefetch distance
     ARB_REQUIRE(n_words < ((int64_t)1 << 31), ARB_ERR_UNSUPPORTED, "layout: stream of %lld words", (long long)n_words);
     ARB_TRY(out.stream->reserve(n_words * (w16 ? 2 : 4)));
     if (w16) {

@@ -150,18 +150,20 @@ __device__ __forceinline__ int64_t packed_off(int pos, int chunks_per_tree, int 
     return ((int64_t)(q >> 2) * rows_per_slot + row) * ARB_VW + (q & 3) * 4;
 }
 
-// masked sums of a row spread over GL lanes, lane h holding columns 4h..4h+3:
+// Rows of q live in GL = ceil(K/4) consecutive lanes (any GL in 1..8; a warp holds TW = 32/GL rows, its last
+// 32 - TW*GL lanes idle), lane h of the group holding columns 4h..4h+3.  `base` = first lane of the group.
+// masked sums of a row spread over GL lanes:
 // acc[c] = sum over source columns b < n_src with bit b of omask[c] set, in ascending b
 // (fixed order => deterministic and independent of the tree shape).  Whole warps only.
 template <int GL>
-__device__ __forceinline__ void masked_rows(const double (&q)[4], const uint32_t (&omask)[4], int n_src,
+__device__ __forceinline__ void masked_rows(const double (&q)[4], const uint32_t (&omask)[4], int n_src, int base,
                                             double (&acc)[4])
 {
     acc[0] = acc[1] = acc[2] = acc[3] = 0.0;
 #pragma unroll
     for (int b = 0; b < 4 * GL; ++b) {
         if (b < n_src) {
-            const double xb = __shfl_sync(0xffffffffu, q[b & 3], b >> 2, GL);
+            const double xb = __shfl_sync(0xffffffffu, q[b & 3], base + (b >> 2));
 #pragma unroll
             for (int c = 0; c < 4; ++c)
                 if ((omask[c] >> b) & 1u) acc[c] += xb;
@@ -185,6 +187,22 @@ __device__ __forceinline__ double block_sum(double v, double *sh)
 
 #define SEED_THREADS 256
 
+// lane -> (row group of the warp, lane within the group); the lanes past the last whole group idle but keep
+// shuffling with the last group
+template <int GL> struct RowLanes {
+    static constexpr int TW = 32 / GL;
+    int grp, h, base;
+    bool active;
+    __device__ __forceinline__ RowLanes()
+    {
+        const int lane = threadIdx.x & 31, g0 = lane / GL;
+        active = g0 < TW;
+        grp = active ? g0 : TW - 1;
+        h = lane - g0 * GL;
+        base = grp * GL;
+    }
+};
+
 // S rows (packed, at the tree's position in this round's q(z) list) from a q(y) matrix: the prior
 // for a tree's first pass (A.py:733-743), or an explicit q(y) for the kernel-level hooks.
 // grid (row blocks, trees in `list`)
@@ -195,19 +213,20 @@ k_seed_s(const double *__restrict__ q_src, int64_t src_slot_stride, const int32_
          int32_t m, int32_t K, double *__restrict__ xs, double *__restrict__ qy_cur, int copy_q, int np, int pr,
          int64_t plane_slots)
 {
-    const int C = K - 1, h = threadIdx.x % GL;
+    const RowLanes<GL> rl;
+    const int C = K - 1, h = rl.h;
     const int slot = list[blockIdx.y], pos = pos_z[slot];
     const uint32_t *mk = masks + (int64_t)st[slot].tree * MASK_STRIDE;
     uint32_t omask[4];
 #pragma unroll
     for (int c = 0; c < 4; ++c) omask[c] = 4 * h + c < K ? mk[4 * h + c] : 0u;
-    const int64_t j = (int64_t)blockIdx.x * (SEED_THREADS / GL) + threadIdx.x / GL;
-    const bool live = j < m;
+    const int64_t j = ((int64_t)blockIdx.x * (SEED_THREADS / 32) + (threadIdx.x >> 5)) * rl.TW + rl.grp;
+    const bool live = rl.active && j < m;
     const double *src = q_src + (int64_t)slot * src_slot_stride;
     double q[4], acc[4];
 #pragma unroll
     for (int c = 0; c < 4; ++c) q[c] = (live && 4 * h + c < C) ? src[j * C + 4 * h + c] : 0.0;
-    masked_rows<GL>(q, omask, C, acc);
+    masked_rows<GL>(q, omask, C, rl.base, acc);
     if (live) {
         if (4 * h < K) {
             double2 *xn = reinterpret_cast<double2 *>(xs + packed_off(pos, (K + 3) / 4, h, (int64_t)np * pr, arb_perm(j, np, pr)));
@@ -228,18 +247,19 @@ k_seed_r(const double *__restrict__ qz_cur, const int32_t *__restrict__ list, co
          const uint32_t *__restrict__ masks, int32_t n, int32_t K, double *__restrict__ xr, int np, int pr,
          int64_t plane_slots)
 {
-    const int C = K - 1, h = threadIdx.x % GL;
+    const RowLanes<GL> rl;
+    const int C = K - 1, h = rl.h;
     const int slot = list[blockIdx.y], pos = blockIdx.y;
     const uint32_t *mk = masks + (int64_t)st[slot].tree * MASK_STRIDE + 32;
     uint32_t omask[4];
 #pragma unroll
     for (int c = 0; c < 4; ++c) omask[c] = 4 * h + c < C ? mk[4 * h + c] : 0u;
-    const int64_t i = (int64_t)blockIdx.x * (SEED_THREADS / GL) + threadIdx.x / GL;
-    const bool live = i < n;
+    const int64_t i = ((int64_t)blockIdx.x * (SEED_THREADS / 32) + (threadIdx.x >> 5)) * rl.TW + rl.grp;
+    const bool live = rl.active && i < n;
     double q[4], acc[4];
 #pragma unroll
     for (int c = 0; c < 4; ++c) q[c] = (live && 4 * h + c < K) ? qz_cur[((st[slot].cur * plane_slots + slot) * n + i) * K + 4 * h + c] : 0.0;
-    masked_rows<GL>(q, omask, K, acc);
+    masked_rows<GL>(q, omask, K, rl.base, acc);
     if (live && 4 * h < C) {
         double2 *xn = reinterpret_cast<double2 *>(xr + packed_off(pos, (C + 3) / 4, h, (int64_t)np * pr, arb_perm(i, np, pr)));
         xn[0] = make_double2(acc[0], acc[1]);
@@ -526,7 +546,7 @@ struct FinishArgs {
 // accesses are guarded.  Masked sums run in ascending source order (deterministic, tree-independent).
 template <int GL, bool IS_Z, bool HARD>
 __device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int pos_out, int64_t row, bool rowok, int h,
-                                           const uint32_t (&omask)[4], const double (&p)[4], const int (&e)[4],
+                                           int base, const uint32_t (&omask)[4], const double (&p)[4], const int (&e)[4],
                                            const double (&g)[4], double &acc1, double &acc2)
 {
     const int K = a.K, C = K - 1, ncol = IS_Z ? K : C;
@@ -541,14 +561,28 @@ __device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int po
         logit[c] = v[c] ? l : -INFINITY;
     }
     double mx = fmax(fmax(logit[0], logit[1]), fmax(logit[2], logit[3]));
+    constexpr bool POW2 = (GL & (GL - 1)) == 0;    // butterflies inside aligned groups, else gather the group
+    if (POW2) {
 #pragma unroll
-    for (int o = GL / 2; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o, GL));
+        for (int o = GL / 2; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o, GL));
+    } else {
+        const double mine = mx;
+#pragma unroll
+        for (int k = 0; k < GL; ++k) mx = fmax(mx, __shfl_sync(0xffffffffu, mine, base + k));
+    }
     double q[4];
 #pragma unroll
     for (int c = 0; c < 4; ++c) q[c] = v[c] ? exp(logit[c] - mx) : 0.0;
     double s = (q[0] + q[1]) + (q[2] + q[3]);
+    if (POW2) {
 #pragma unroll
-    for (int o = GL / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o, GL);
+        for (int o = GL / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o, GL);
+    } else {
+        const double mine = s;                    // same order on every lane of the group: same bits
+        s = __shfl_sync(0xffffffffu, mine, base);
+#pragma unroll
+        for (int k = 1; k < GL; ++k) s += __shfl_sync(0xffffffffu, mine, base + k);
+    }
     const double inv_s = 1.0 / s;                 // one division per row (A.py:169 divides every entry)
 #pragma unroll
     for (int c = 0; c < 4; ++c) q[c] = q[c] * inv_s;
@@ -557,7 +591,7 @@ __device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int po
         for (int c = 0; c < 4; ++c) q[c] = (v[c] && rowok) ? a.q_cur[qbase + 4 * h + c] : 0.0;
     }
     double acc[4] = {0.0, 0.0, 0.0, 0.0};
-    if (!IS_Z) masked_rows<GL>(q, omask, ncol, acc);          // S rows of the new q(y)
+    if (!IS_Z) masked_rows<GL>(q, omask, ncol, base, acc);    // S rows of the new q(y)
     if (IS_Z && HARD) {
         // hard-assignment mode (A.py:596, 662-674): the likelihood term of the row's MAP clone (first maximum
         // of q(z), like numpy's argmax); the soft q(z) is still what the caller gets back
@@ -566,10 +600,12 @@ __device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int po
 #pragma unroll
         for (int c = 0; c < 4; ++c)
             if (v[c] && q[c] > bv) { bv = q[c]; bi = 4 * h + c; }
+        const double bv0 = bv;
+        const int bi0 = bi;
 #pragma unroll
-        for (int o = GL / 2; o > 0; o >>= 1) {
-            const double ov = __shfl_xor_sync(0xffffffffu, bv, o, GL);
-            const int oi = __shfl_xor_sync(0xffffffffu, bi, o, GL);
+        for (int k = 0; k < GL; ++k) {                // every lane scans the group in column order
+            const double ov = __shfl_sync(0xffffffffu, bv0, base + k);
+            const int oi = __shfl_sync(0xffffffffu, bi0, base + k);
             if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
         }
         if (rowok) {
@@ -613,8 +649,9 @@ __global__ void __launch_bounds__(FIN_THREADS, 4) k_finish(const FinishArgs a)
 {
     __shared__ double sh[FIN_WARPS];
     constexpr int TW = 32 / GL, RW = IS_Z ? 2 : 1;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int h = lane % GL, grp = lane / GL;
+    const RowLanes<GL> rl;
+    const int warp = threadIdx.x >> 5;
+    const int h = rl.h, grp = rl.grp;
     const int pos = blockIdx.y, slot = a.slot_list[pos];
     const int np = a.n_panels;
     const int ncol = IS_Z ? a.K : a.K - 1, chunks = (ncol + 3) / 4;
@@ -628,9 +665,10 @@ __global__ void __launch_bounds__(FIN_THREADS, 4) k_finish(const FinishArgs a)
     }
     const int64_t panel_stride = (int64_t)a.n_rows * ARB_VW;        // columns between panels
     double acc1 = 0.0, acc2 = 0.0;
-    for (int it = 0; it < FIN_ROWS / (FIN_WARPS * TW); ++it) {
-        const int64_t row = (int64_t)blockIdx.x * FIN_ROWS + (it * FIN_WARPS + warp) * TW + grp;
-        const bool rowok = row < a.n_rows;
+    for (int it = 0; it < (FIN_ROWS + FIN_WARPS * TW - 1) / (FIN_WARPS * TW); ++it) {
+        const int lr = (it * FIN_WARPS + warp) * TW + grp;             // row of this CTA's block of FIN_ROWS
+        const int64_t row = (int64_t)blockIdx.x * FIN_ROWS + lr;
+        const bool rowok = rl.active && lr < FIN_ROWS && row < a.n_rows;
         const bool mine = rowok && keep;
         double p[4] = {1.0, 1.0, 1.0, 1.0}, g[4] = {0.0, 0.0, 0.0, 0.0};
         int e[4] = {0, 0, 0, 0};
@@ -693,7 +731,7 @@ __global__ void __launch_bounds__(FIN_THREADS, 4) k_finish(const FinishArgs a)
                 }
             }
         }
-        finish_row<GL, IS_Z, HARD>(a, slot, pos_out, rowok ? row : 0, rowok, h, omask, p, e, g, acc1, acc2);
+        finish_row<GL, IS_Z, HARD>(a, slot, pos_out, rowok ? row : 0, rowok, h, rl.base, omask, p, e, g, acc1, acc2);
     }
     const double t1 = block_sum(acc1, sh);
     const double t2 = block_sum(acc2, sh);
@@ -889,7 +927,7 @@ static size_t sweep_smem_bytes(const arb_ctx *ctx, const PanelLayout &L)
 static inline int chunks_for(int cols) { return (cols + 3) / 4; }              // 4-column chunks per tree
 static inline int64_t vslots_for(int64_t trees, int cols) { return (trees * chunks_for(cols) + 3) / 4; }
 // lanes per row in the seeding / finishing kernels: power of two covering ceil(K/4) chunks
-static inline int gl_for(int K) { const int c = chunks_for(K); return c <= 1 ? 1 : c <= 2 ? 2 : c <= 4 ? 4 : 8; }
+static inline int gl_for(int K) { return chunks_for(K); }          // 1..8, need not be a power of two
 
 static int configure_kernels(const arb_ctx *ctx, const PanelLayout &L)
 {
@@ -1175,7 +1213,7 @@ template <int GL>
 static void launch_seed_s(arb_ctx *ctx, const WsPtrs &w, const uint32_t *masks, const double *q_src,
                           int64_t src_stride, const int32_t *list, int n_active, int K, int copy_q)
 {
-    k_seed_s<GL><<<dim3(grid_for(ctx->n_snvs, SEED_THREADS / GL), n_active), SEED_THREADS, 0, w.stream>>>(
+    k_seed_s<GL><<<dim3(grid_for(ctx->n_snvs, (SEED_THREADS / 32) * (32 / GL)), n_active), SEED_THREADS, 0, w.stream>>>(
         q_src, src_stride, list, w.pos_z, w.st, masks, ctx->n_snvs, K, w.xs, ctx->qy_cur.as<double>(), copy_q,
         ctx->layout[kp_index(ctx->ws_kp)].np_z, ctx->layout[kp_index(ctx->ws_kp)].prz, (int64_t)ctx->ws_slots);
 }
@@ -1184,7 +1222,7 @@ template <int GL>
 static void launch_seed_r(arb_ctx *ctx, const WsPtrs &w, const uint32_t *masks, const int32_t *list, int n_active,
                           int K)
 {
-    k_seed_r<GL><<<dim3(grid_for(ctx->n_cells, SEED_THREADS / GL), n_active), SEED_THREADS, 0, w.stream>>>(
+    k_seed_r<GL><<<dim3(grid_for(ctx->n_cells, (SEED_THREADS / 32) * (32 / GL)), n_active), SEED_THREADS, 0, w.stream>>>(
         ctx->qz_cur.as<double>(), list, w.st, masks, ctx->n_cells, K, w.xr, ctx->layout[kp_index(ctx->ws_kp)].np_y,
         ctx->layout[kp_index(ctx->ws_kp)].pry, (int64_t)ctx->ws_slots);
 }
@@ -1345,7 +1383,11 @@ static int fit_dispatch(arb_ctx *ctx, int n_trees, int K, int max_iter, double t
     switch (gl_for(K)) {
     case 1: return fit_core<1>(ctx, n_trees, K, max_iter, tol, mode, tg, reserve);
     case 2: return fit_core<2>(ctx, n_trees, K, max_iter, tol, mode, tg, reserve);
+    case 3: return fit_core<3>(ctx, n_trees, K, max_iter, tol, mode, tg, reserve);
     case 4: return fit_core<4>(ctx, n_trees, K, max_iter, tol, mode, tg, reserve);
+    case 5: return fit_core<5>(ctx, n_trees, K, max_iter, tol, mode, tg, reserve);
+    case 6: return fit_core<6>(ctx, n_trees, K, max_iter, tol, mode, tg, reserve);
+    case 7: return fit_core<7>(ctx, n_trees, K, max_iter, tol, mode, tg, reserve);
     default: return fit_core<8>(ctx, n_trees, K, max_iter, tol, mode, tg, reserve);
     }
 }
@@ -1688,7 +1730,11 @@ static int hook_setup(arb_ctx *ctx, int K, const uint8_t *presence, HookEnv &env
     switch (gl_for(K)) {                                   \
     case 1: { constexpr int GLV = 1; __VA_ARGS__; } break;  \
     case 2: { constexpr int GLV = 2; __VA_ARGS__; } break;  \
+    case 3: { constexpr int GLV = 3; __VA_ARGS__; } break;  \
     case 4: { constexpr int GLV = 4; __VA_ARGS__; } break;  \
+    case 5: { constexpr int GLV = 5; __VA_ARGS__; } break;  \
+    case 6: { constexpr int GLV = 6; __VA_ARGS__; } break;  \
+    case 7: { constexpr int GLV = 7; __VA_ARGS__; } break;  \
     default: { constexpr int GLV = 8; __VA_ARGS__; } break; \
     }
 

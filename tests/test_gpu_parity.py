@@ -418,6 +418,28 @@ def test_against_oracle_on_fresh_inputs(eng_mod):
             assert_map_equal(fits[t].q_y, ofits[t][2])
 
 
+@pytest.mark.parametrize("n_clones", [3, 4, 10, 13, 14, 17, 20, 21, 25, 29, 32])
+def test_clone_counts_against_oracle(eng_mod, n_clones):
+    """Every lanes-per-row width of the seeding / finishing kernels (ceil(K/4) = 1..8 lanes, a power of two or
+    not) and the column packing that goes with it, against the CPU oracle on a small seeded workload."""
+    from arborist_b200 import arborist, synth
+    from oracle import oracle as orc
+    cfg = synth.SynthConfig(f"k{n_clones}", 150, 400, n_clones, 5, seed=7000 + n_clones, coverage=0.08,
+                            min_proportion=0.01)
+    d = synth.generate(cfg)
+    rc, cl = d.read_counts_frame(), d.clusters_frame()
+    lik, best, fits = arborist(d.trees, rc, cl, max_iter=6, tolerance=1.0, add_normal=True)
+    olik, obest, ofits, _ = orc.arborist_oracle(d.trees, rc, cl, max_iter=6, tolerance=1.0, add_normal=True)
+    assert best.tree_idx == obest
+    for t in range(len(d.trees)):
+        assert lik[t] == pytest.approx(olik[t], rel=ELBO_RTOL)
+        assert arborist.last_stats["iters"][t] == ofits[t][3]
+        np.testing.assert_allclose(fits[t].q_z, ofits[t][1], rtol=Q_RTOL, atol=Q_ATOL)
+        np.testing.assert_allclose(fits[t].q_y, ofits[t][2], rtol=Q_RTOL, atol=Q_ATOL)
+        assert_map_equal(fits[t].q_z, ofits[t][1])
+        assert_map_equal(fits[t].q_y, ofits[t][2])
+
+
 def test_non_forest_presence_and_errors(eng_mod):
     """Inputs that are not forests go through explicit genotype matrices; bad input is an error,
     not a fallback."""

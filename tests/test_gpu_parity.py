@@ -365,6 +365,19 @@ def test_stream_word_width_does_not_change_bits(eng_mod):
     assert np.array_equal(got[0], ref[0]) and np.array_equal(got[1], ref[1])
     qz, qy = e.get_fit(2)
     assert np.array_equal(qz, ref_q[0]) and np.array_equal(qy, ref_q[1])
+    # the exponent-peeling variants of the sweep (used when a layout cannot prove that its running products
+    # stay inside the double range) with both word widths: same iteration counts, ELBOs within rounding
+    for w32 in (0, 1):
+        e.set_option("w32", w32)
+        e.set_option("no_fold", 1)
+        got = e.fit(parents=parents, n_clones=K, normal_idx=normal, max_iter=25, tolerance=1.0, keep_posteriors="all")
+        pf = e.last_fit_profile()
+        assert pf["fold_z"] == 0 and pf["fold_y"] == 0 and pf["w16"] == 1 - w32
+        np.testing.assert_allclose(got[0], ref[0], rtol=1e-12)
+        assert np.array_equal(got[1], ref[1])
+        qz, qy = e.get_fit(2)
+        np.testing.assert_allclose(qz, ref_q[0], rtol=1e-9, atol=1e-300)
+        np.testing.assert_allclose(qy, ref_q[1], rtol=1e-9, atol=1e-300)
     e.close()
 
 

@@ -72,7 +72,9 @@ struct DevBuf {
 };
 
 #define ARB_MAX_GROUPS 4
+#ifndef ARB_SWEEP_WARPS
 #define ARB_SWEEP_WARPS 16    // warps per sweep CTA; the layouts are dealt out to this many warps
+#endif
 
 // Panelled sparse layout for one padded clone width KP (8, 16 or 32 doubles per row of
 // the gathered operand).  "z": cell-major rows, SNVs cut into panels (q(z) sweep);

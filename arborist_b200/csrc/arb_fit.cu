@@ -55,6 +55,9 @@ int arb_check_table_range(arb_ctx *ctx);
 #else
 #define ARB_PREFETCH(sp)
 #endif
+#ifndef ARB_ST256
+#define ARB_ST256 1
+#endif
 #ifndef ARB_TABC
 #define ARB_TABC 1
 #endif
@@ -501,10 +504,16 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const __grid_
             char *pa = out_a + (int64_t)row * out_stride;
             char *pb = reinterpret_cast<char *>(reinterpret_cast<uintptr_t>(pa) ^ (uintptr_t)(16 * RW));
             if (WITH_G) {
+#if ARB_ST256
+                // two 256-bit streaming stores (sm_100: st.global.v4.f64) instead of four 128-bit ones
+                asm volatile("st.global.cs.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(pa), "d"(p[0]), "d"(g[0]), "d"(p[1]), "d"(g[1]) : "memory");
+                asm volatile("st.global.cs.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(pb), "d"(p[2]), "d"(g[2]), "d"(p[3]), "d"(g[3]) : "memory");
+#else
                 ARB_ST(reinterpret_cast<double2 *>(pa) + 0, make_double2(p[0], g[0]));
                 ARB_ST(reinterpret_cast<double2 *>(pa) + 1, make_double2(p[1], g[1]));
                 ARB_ST(reinterpret_cast<double2 *>(pb) + 0, make_double2(p[2], g[2]));
                 ARB_ST(reinterpret_cast<double2 *>(pb) + 1, make_double2(p[3], g[3]));
+#endif
             } else {
                 ARB_ST(reinterpret_cast<double2 *>(pa) + 0, make_double2(p[0], p[1]));
                 ARB_ST(reinterpret_cast<double2 *>(pb) + 0, make_double2(p[2], p[3]));

@@ -33,12 +33,13 @@
 int arb_sweep_table_entries(const arb_ctx *ctx);
 int arb_check_table_range(arb_ctx *ctx);
 
-// Partial rows of the q(y) sweep are stored as 16-byte pieces [k][h] (see the end of k_sweep); measured on
-// B200 at config 3 (scripts/ab_layout.sh): q(y) finishing kernel -9 %; the same order for the q(z) partial
-// rows made its finishing kernel 32 % slower (chunks no longer cover whole sectors), so q(z) keeps chunks
-// contiguous.  bit 0: q(y), bit 1: q(z).
+// Layout of a partial row.  Default (0): every lane's chunk is contiguous (q(y): 32 bytes = one 256-bit store /
+// load, q(z): 64 bytes = two), which is what the finishing kernels read best.  Bits 0 / 1 switch the q(y) / q(z)
+// partial rows to 16-byte pieces [k][h] (one store instruction then writes 64 contiguous bytes per row); measured on
+// B200 at config 3 (scripts/ab_layout.sh, exp_y256.sh): with 128-bit accesses pieces helped q(y) (-9 % on its
+// finishing kernel) and hurt q(z) (+32 %); with 256-bit accesses the contiguous chunks win for both.
 #ifndef ARB_PIECE_LAYOUT
-#define ARB_PIECE_LAYOUT 1
+#define ARB_PIECE_LAYOUT 0
 #endif
 #define ARB_PIECES(with_g) ((ARB_PIECE_LAYOUT >> ((with_g) ? 1 : 0)) & 1)
 // partial rows are written once and read once by the finishing kernel: streaming stores
@@ -54,6 +55,9 @@ int arb_check_table_range(arb_ctx *ctx);
 #define ARB_PREFETCH(sp) asm volatile("prefetch.global.L1 [%0];" ::"l"((sp) + ARB_PF_QUADS * TW));
 #else
 #define ARB_PREFETCH(sp)
+#endif
+#ifndef ARB_LD256
+#define ARB_LD256 1
 #endif
 #ifndef ARB_ST256
 #define ARB_ST256 1
@@ -515,8 +519,14 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const __grid_
                 ARB_ST(reinterpret_cast<double2 *>(pb) + 1, make_double2(p[3], g[3]));
 #endif
             } else {
+#if ARB_ST256
+                // the lane's chunk (columns 4h..4h+3, 32 bytes) in one 256-bit streaming store
+                const double c0 = swz ? p[2] : p[0], c1 = swz ? p[3] : p[1], c2 = swz ? p[0] : p[2], c3 = swz ? p[1] : p[3];
+                asm volatile("st.global.cs.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(pa - 16 * swz), "d"(c0), "d"(c1), "d"(c2), "d"(c3) : "memory");
+#else
                 ARB_ST(reinterpret_cast<double2 *>(pa) + 0, make_double2(p[0], p[1]));
                 ARB_ST(reinterpret_cast<double2 *>(pb) + 0, make_double2(p[2], p[3]));
+#endif
             }
             }
             if (!FOLD) {
@@ -707,15 +717,25 @@ __global__ void __launch_bounds__(FIN_THREADS, 4) k_finish(const FinishArgs a)
                 // HBM-bound (23 MB of partial rows per tree): the loads of panel pn+1 are issued before the
                 // partials of panel pn are consumed
                 double2 cur[4], nxt[4];
+                // a chunk is 64 contiguous bytes: two 256-bit streaming loads (sm_100: ld.global.v4.f64)
+                auto load4 = [&](double2 (&d)[4], const double2 *from) {
+#if ARB_LD256
+                    if (!PIECES) {
+                        asm volatile("ld.global.cs.v4.f64 {%0, %1, %2, %3}, [%4];"
+                                     : "=d"(d[0].x), "=d"(d[0].y), "=d"(d[1].x), "=d"(d[1].y) : "l"(from));
+                        asm volatile("ld.global.cs.v4.f64 {%0, %1, %2, %3}, [%4];"
+                                     : "=d"(d[2].x), "=d"(d[2].y), "=d"(d[3].x), "=d"(d[3].y) : "l"(from + 2));
+                        return;
+                    }
+#endif
 #pragma unroll
-                for (int k = 0; k < 4; ++k) cur[k] = __ldcs(src + k * PS);
+                    for (int k = 0; k < 4; ++k) d[k] = __ldcs(from + k * PS);
+                };
+                load4(cur, src);
 #pragma unroll 2
                 for (int pn = 0; pn < np; ++pn) {
                     src += pstep;
-                    if (pn + 1 < np) {
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) nxt[k] = __ldcs(src + k * PS);
-                    }
+                    if (pn + 1 < np) load4(nxt, src);
                     const double m[4] = {cur[0].x, cur[1].x, cur[2].x, cur[3].x};
                     g[0] += cur[0].y; g[1] += cur[1].y; g[2] += cur[2].y; g[3] += cur[3].y;
                     fold_in(m, pn);
@@ -726,7 +746,17 @@ __global__ void __launch_bounds__(FIN_THREADS, 4) k_finish(const FinishArgs a)
                 // issue-bound (three fp64 transcendentals per entry): the plain loop has the fewest instructions
 #pragma unroll 2
                 for (int pn = 0; pn < np; ++pn) {
-                    const double2 v0 = __ldcs(src), v1 = __ldcs(src + PS);
+                    double2 v0, v1;
+#if ARB_LD256
+                    if (!PIECES)
+                        asm volatile("ld.global.cs.v4.f64 {%0, %1, %2, %3}, [%4];"
+                                     : "=d"(v0.x), "=d"(v0.y), "=d"(v1.x), "=d"(v1.y) : "l"(src));
+                    else
+#endif
+                    {
+                        v0 = __ldcs(src);
+                        v1 = __ldcs(src + PS);
+                    }
                     const double m[4] = {v0.x, v0.y, v1.x, v1.y};
                     src += pstep;
                     fold_in(m, pn);

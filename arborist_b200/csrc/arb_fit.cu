@@ -194,6 +194,12 @@ __device__ __forceinline__ double block_sum(double v, double *sh)
 
 #define SEED_THREADS 256
 
+// four columns (32 bytes, 32-byte aligned) of a packed operand row in one 256-bit store
+__device__ __forceinline__ void store_chunk(double2 *dst, const double (&v)[4])
+{
+    asm volatile("st.global.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(dst), "d"(v[0]), "d"(v[1]), "d"(v[2]), "d"(v[3]) : "memory");
+}
+
 // lane -> (row group of the warp, lane within the group); the lanes past the last whole group idle but keep
 // shuffling with the last group
 template <int GL> struct RowLanes {
@@ -237,8 +243,7 @@ k_seed_s(const double *__restrict__ q_src, int64_t src_slot_stride, const int32_
     if (live) {
         if (4 * h < K) {
             double2 *xn = reinterpret_cast<double2 *>(xs + packed_off(pos, (K + 3) / 4, h, (int64_t)np * pr, arb_perm(j, np, pr)));
-            xn[0] = make_double2(acc[0], acc[1]);
-            xn[1] = make_double2(acc[2], acc[3]);
+            store_chunk(xn, acc);
         }
         if (copy_q)
 #pragma unroll
@@ -269,8 +274,7 @@ k_seed_r(const double *__restrict__ qz_cur, const int32_t *__restrict__ list, co
     masked_rows<GL>(q, omask, K, rl.base, acc);
     if (live && 4 * h < C) {
         double2 *xn = reinterpret_cast<double2 *>(xr + packed_off(pos, (C + 3) / 4, h, (int64_t)np * pr, arb_perm(i, np, pr)));
-        xn[0] = make_double2(acc[0], acc[1]);
-        xn[1] = make_double2(acc[2], acc[3]);
+        store_chunk(xn, acc);
     }
 }
 
@@ -654,8 +658,7 @@ __device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int po
         if (!IS_Z && 4 * h < K) {
             double2 *xn = reinterpret_cast<double2 *>(a.x_next + packed_off(pos_out, (K + 3) / 4, h, (int64_t)a.xn_np * a.xn_pr,
                                                                           arb_perm(row, a.xn_np, a.xn_pr)));
-            xn[0] = make_double2(acc[0], acc[1]);
-            xn[1] = make_double2(acc[2], acc[3]);
+            store_chunk(xn, acc);
         }
     }
 }

@@ -57,8 +57,35 @@ static int pool_enabled()
     return on;
 }
 
+// ARB_POOL_POISON=1 (debugging aid): fill every block handed out with 0xff bytes (NaN doubles, -1 ints),
+// so that a kernel relying on the contents of fresh memory fails every time instead of now and then.
+static void pool_poison(void *p, size_t n)
+{
+    static int on = -1;
+    if (on < 0) {
+        const char *e = getenv("ARB_POOL_POISON");
+        on = e && e[0] == '1';
+    }
+    if (on && p) {
+        cudaDeviceSynchronize();
+        cudaMemset(p, 0xff, n);
+        cudaDeviceSynchronize();
+    }
+}
+
+static int pool_trace()
+{
+    static int on = -1;
+    if (on < 0) {
+        const char *e = getenv("ARB_POOL_TRACE");
+        on = e && e[0] == '1';
+    }
+    return on;
+}
+
 static void pool_flush_locked(int device)
 {
+    if (pool_trace()) fprintf(stderr, "[arb pool] flush device %d (%zu blocks parked)\n", device, g_pool.size());
     for (size_t i = 0; i < g_pool.size();) {
         if (g_pool[i].device == device) {
             cudaFree(g_pool[i].p);
@@ -86,9 +113,11 @@ void *arb_pool_alloc(size_t n, size_t *got)
         *got = g_pool[best].bytes;
         g_pool[best] = g_pool.back();
         g_pool.pop_back();
+        pool_poison(p, *got);
         return p;
     }
     void *p = nullptr;
+    if (pool_trace() && n >= (1u << 20)) fprintf(stderr, "[arb pool] miss: cudaMalloc(%zu)\n", n);
     cudaError_t e = cudaMalloc(&p, n);
     if (e != cudaSuccess) {              // give the parked memory back to the driver and try again
         cudaGetLastError();
@@ -101,6 +130,7 @@ void *arb_pool_alloc(size_t n, size_t *got)
         return nullptr;
     }
     *got = n;
+    pool_poison(p, n);
     return p;
 }
 

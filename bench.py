@@ -350,6 +350,8 @@ def run_gpu_arm(args):
     if not args.no_e2e:
         eng.close()
         del eng
+        e2e_dev_ms = []
+
         def e2e_step():
             lik, best, fits = arborist(trees, rc, cl, alpha=RUN["alpha"], max_iter=RUN["max_iter"],
                                        tolerance=RUN["tolerance"], gamma=RUN["gamma"], add_normal=True,
@@ -358,6 +360,7 @@ def run_gpu_arm(args):
             qz, qy = best.q_z, best.q_y                           # D2H of the winner's posteriors
             nbytes = 12 * len(shard) + 4 * (n + m) + qz.nbytes + qy.nbytes
             assert ranking[0][0] == best.tree_idx
+            e2e_dev_ms.append(round(arborist.last_stats["engine"]().last_fit_stats()["device_ms"], 1))
             arborist.last_stats = None                            # drop the engine (its buffers go to the pool)
             del fits, best
             return nbytes
@@ -367,15 +370,30 @@ def run_gpu_arm(args):
         barrier()
         t0 = time.perf_counter()
         d2h = 0
+        step_ms = []
+        import gc
+        gc_log, gc_t0 = [], [0.0]
+
+        def gc_cb(phase, info):
+            if phase == "start":
+                gc_t0[0] = time.perf_counter()
+            else:
+                dt = 1e3 * (time.perf_counter() - gc_t0[0])
+                if dt > 5:
+                    gc_log.append((info["generation"], round(dt, 1)))
+        gc.callbacks.append(gc_cb)
         for _ in range(args.steps):
+            t1 = time.perf_counter()
             d2h = e2e_step()
+            step_ms.append(round(1e3 * (time.perf_counter() - t1), 1))
         barrier()
         e2e_wall = max_over_ranks(time.perf_counter() - t0)
         e2e = {"value": T * steps / e2e_wall, "unit": "trees/s",
                # the four int64 columns of the table (ids are factorised on the device), prior labels, parent
                # vectors, scipy's log-pmf table
                "h2d_bytes_per_step": int(32 * len(rc) + 4 * m + 4 * my_parents.size + 16 * n_pairs),
-               "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * e2e_wall / steps,
+               "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * e2e_wall / steps, "ms_steps_rank0": step_ms, "gc_pauses_gen_ms": gc_log,
+               "fit_device_ms_steps_rank0": e2e_dev_ms[-len(step_ms):],
                "note": "arborist(trees, read_counts_df, clusters_df): H2D of the long table (int64 columns), device "
                        "id factorisation + ingest + layouts, batched fit, ELBO gather, ranking, D2H of ELBOs / "
                        "iteration counts / index orders / the best tree's q_z and q_y; host wall clock, one untimed "

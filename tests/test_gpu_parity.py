@@ -443,7 +443,13 @@ def test_clone_counts_against_oracle(eng_mod, n_clones):
     rc, cl = d.read_counts_frame(), d.clusters_frame()
     lik, best, fits = arborist(d.trees, rc, cl, max_iter=6, tolerance=1.0, add_normal=True)
     olik, obest, ofits, _ = orc.arborist_oracle(d.trees, rc, cl, max_iter=6, tolerance=1.0, add_normal=True)
-    assert best.tree_idx == obest
+    # With three clones the five candidates repeat a topology, so their ELBOs tie to the last bit and the
+    # oracle's own argmax depends on the order its OpenMP reduction happened to combine in: the winner has to
+    # be one of the oracle's maximisers, and THE oracle's winner whenever that one is unique.
+    ties = [t for t in olik if abs(olik[t] - olik[obest]) <= 1e-12 * abs(olik[obest])]
+    assert best.tree_idx in ties
+    if len(ties) == 1:
+        assert best.tree_idx == obest
     for t in range(len(d.trees)):
         assert lik[t] == pytest.approx(olik[t], rel=ELBO_RTOL)
         assert arborist.last_stats["iters"][t] == ofits[t][3]

@@ -10,7 +10,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "libarborist_b200.so")
-SOURCES = ["arb_ingest.cu", "arb_fit.cu"]
+SOURCES = ["arb_ingest.cu", "arb_fit.cu", "arb_base.cu"]
 HEADERS = ["arb_common.cuh", os.path.join("..", "..", "include", "arborist_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-fvisibility=hidden", "-shared", "-cudart", "static"]

@@ -1,0 +1,142 @@
+"""Legacy tree scorer of the reference (``arborist.arborist_base``) on the GPU.
+
+Mirrors /root/reference/src/arborist/arborist_base.py: ``build_genotypes`` (:228-247),
+``find_cell_assignments`` (:102-194) and ``rank_trees`` (:250-362) with the same arguments and
+return values.  The numeric work (binomial log-pmf of every read-count row, the per (cell, clone)
+sums, best clone per cell, tree score, per-cell posteriors and entropies) runs in
+``csrc/arb_base.cu`` through ``arb_base_ingest`` / ``arb_base_score`` / ``arb_base_cells``; this
+module only factorises labels, builds the ancestor bit masks and assembles the DataFrames.  There is
+no CPU path: without the CUDA library every entry point raises.
+
+Difference from the reference, by design: all trees of one ``rank_trees`` call must have the same
+node set (the reference concatenates frames with differing clone columns into NaNs and its
+posterior step then uses the LAST tree's columns, arborist_base.py:303, 335-337).
+"""
+from __future__ import annotations
+
+import numpy as np
+import pandas as pd
+from scipy.special import logsumexp
+
+from .engine import Engine
+
+
+def build_genotypes(tree):
+    """DataFrame ``Child`` / ``Ancestors`` ("root,...,child"), clones in the iteration order of the
+    set of node labels (arborist_base.py:228-247)."""
+    child_to_parent = {child: parent for parent, child in tree}
+    all_clones = set(child_to_parent.keys()).union(set(child_to_parent.values()))
+    rows = []
+    for clone in all_clones:
+        path, x = [clone], clone
+        while x in child_to_parent:
+            x = child_to_parent[x]
+            path.append(x)
+        rows.append((clone, ",".join(str(v) for v in reversed(path))))
+    return pd.DataFrame(rows, columns=["Child", "Ancestors"])
+
+
+class _Table:
+    """The read-count table on the device: rows with a cluster label folded per (cell, cluster)."""
+
+    def __init__(self, read_counts, alpha, device=0):
+        for col in ("cell", "cluster", "total", "alt"):
+            if col not in read_counts.columns:
+                raise ValueError(f"read_counts needs a '{col}' column")
+        rc = read_counts[read_counts["cluster"].notna()]
+        if len(rc) == 0:
+            raise ValueError("read_counts has no row with a cluster label")
+        self.cell_code, self.cell_ids = pd.factorize(rc["cell"], sort=False)
+        self.cluster_code, cluster_ids = pd.factorize(rc["cluster"].astype(np.int64), sort=True)
+        self.cluster_ids = [int(c) for c in cluster_ids]
+        self.engine = Engine(device)
+        self.engine.base_ingest(self.cell_code, self.cluster_code, rc["total"].to_numpy(), rc["alt"].to_numpy(),
+                                len(self.cell_ids), len(self.cluster_ids), alpha)
+
+    def masks(self, genotype_matrix):
+        """(ancestor mask per clone, mask of the tree's own clusters) over the cluster codes."""
+        bit = {c: np.uint32(1 << k) for k, c in enumerate(self.cluster_ids)}
+        clones = [int(c) for c in genotype_matrix["Child"].values]
+        anc = np.zeros(len(clones), np.uint32)
+        for j, path in enumerate(genotype_matrix["Ancestors"].values):
+            for c in set(map(int, str(path).split(","))):
+                anc[j] |= bit.get(c, np.uint32(0))
+        tmask = np.uint32(0)
+        for c in clones:
+            tmask |= bit.get(c, np.uint32(0))
+        return anc, tmask
+
+    def cell_order(self, tmask):
+        """Cells that keep a row under the tree's cluster filter, in first-appearance order of those rows
+        (arborist_base.py:153-160)."""
+        keep = ((int(tmask) >> self.cluster_code) & 1).astype(bool)
+        return pd.unique(self.cell_code[keep])
+
+    def close(self):
+        self.engine.close()
+
+
+def find_cell_assignments(read_counts, genotype_matrix, error_rate=0.001, device=0):
+    """``(score, Cell_assignment)``: log-likelihood of every cell (rows) under every clone (columns) and the
+    sum over cells of the row maxima (arborist_base.py:102-194)."""
+    tab = _Table(read_counts, error_rate, device)
+    try:
+        anc, tmask = tab.masks(genotype_matrix)
+        score = float(tab.engine.base_score(anc[None, :], np.array([tmask], np.uint32))[0])
+        ll, _, _, _, _ = tab.engine.base_cells(anc[None, :], np.array([tmask], np.uint32), want_loglik=True)
+        order = tab.cell_order(tmask)
+        frame = pd.DataFrame(ll[0][order], index=list(tab.cell_ids[order]), columns=genotype_matrix["Child"].values,
+                             dtype=float)
+        return score, frame
+    finally:
+        tab.close()
+
+
+def rank_trees(tree_list, read_counts, alpha=0.001, topn=None, verbose=False, device=0):
+    """``(ranked_trees, cell_assignments)`` like the reference (arborist_base.py:250-362): trees scored by the sum
+    over cells of the best clone's log-likelihood, ``posterior`` in percent over all trees, then for the ``topn``
+    best trees one row per cell with its best clone, the entropy (bits) of its clone posterior and the posterior
+    itself."""
+    if len(tree_list) == 0:
+        raise ValueError("rank_trees: empty tree list")
+    genotypes = [build_genotypes(tree) for tree in tree_list]
+    clones = [int(c) for c in genotypes[0]["Child"].values]
+    for t, g in enumerate(genotypes):
+        if sorted(int(c) for c in g["Child"].values) != sorted(clones):
+            raise ValueError(f"rank_trees: tree {t} has a different node set than tree 0")
+    tab = _Table(read_counts, alpha, device)
+    try:
+        pairs = [tab.masks(g) for g in genotypes]
+        anc = np.stack([p[0] for p in pairs])
+        tmask = np.array([p[1] for p in pairs], np.uint32)
+        lik = tab.engine.base_score(anc, tmask)
+        if verbose:
+            for t, v in enumerate(lik):
+                print(f"Processed tree {t} with likelihood {v}.")
+            print(f"Processed {len(tree_list)} trees.")
+        df = pd.DataFrame({"tree": np.arange(len(tree_list)), "likelihood": lik})
+        df["posterior"] = np.exp(df["likelihood"] - logsumexp(df["likelihood"])) * 100
+        df.sort_values(by=["likelihood"], ascending=False, inplace=True)
+        df.reset_index(drop=True, inplace=True)
+        ranked_trees = df.iloc[:topn]
+
+        sel = sorted(int(t) for t in ranked_trees["tree"])
+        _, post, idx, ent, _ = tab.engine.base_cells(anc[sel], tmask[sel])
+        # the reference names the posterior columns after the LAST tree's clone order (arborist_base.py:303)
+        last = [int(c) for c in genotypes[-1]["Child"].values]
+        frames = []
+        order = tab.cell_order(tmask[0])                  # same node set, so the same cluster filter for every tree
+        for s, t in enumerate(sel):
+            mine = [int(c) for c in genotypes[t]["Child"].values]
+            col = [mine.index(c) for c in last]
+            f = pd.DataFrame({"cell": tab.cell_ids[order], "tree": t, "clone": np.asarray(mine)[idx[s][order]],
+                              "entropy": ent[s][order]})
+            for j, c in zip(col, last):
+                f[f"clone_{c}_posterior"] = post[s][order, j]
+            # row labels of the reference: positions in the concatenation over ALL trees (arborist_base.py:327-331)
+            f.index = np.arange(len(order)) + t * len(order)
+            frames.append(f)
+        cell_assignments = pd.concat(frames)
+        return ranked_trees, cell_assignments
+    finally:
+        tab.close()

@@ -162,6 +162,10 @@ struct arb_ctx {
     DevBuf single_qz, single_qy;
     FitStats stats;
     DevBuf scratch;                       // cub temp storage
+
+    // ---- legacy scorer (arb_base.cu): per (cell, cluster) log-pmf sums and row counts ----------
+    DevBuf base_ta, base_tb, base_cnt;
+    int32_t base_cells = 0, base_clusters = 0;
 };
 
 __host__ __device__ static inline int64_t arb_perm(int64_t c, int np, int pr) { return (c % np) * (int64_t)pr + c / np; }

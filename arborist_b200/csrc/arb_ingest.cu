@@ -234,7 +234,7 @@ ARB_API int arb_ctx_destroy(arb_ctx *ctx)
                       &ctx->part_y, &ctx->red, &ctx->slot_state, &ctx->lists, &ctx->masks,
                       &ctx->best_qz, &ctx->best_qy, &ctx->d_elbo, &ctx->d_iters, &ctx->d_trace,
                       &ctx->tree_masks, &ctx->single_qz, &ctx->single_qy, &ctx->scratch, &ctx->cell_uniques,
-                      &ctx->snv_uniques};
+                      &ctx->snv_uniques, &ctx->base_ta, &ctx->base_tb, &ctx->base_cnt};
     for (DevBuf *b : bufs) b->release();
     for (auto &l : ctx->layout) l.release();
     for (int g = 0; g < ARB_MAX_GROUPS; ++g) {

@@ -21,6 +21,7 @@ _i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
 _f64p = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
 _i64p = np.ctypeslib.ndpointer(dtype=np.int64, flags="C_CONTIGUOUS")
 _u8p = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
+_u32p = np.ctypeslib.ndpointer(dtype=np.uint32, flags="C_CONTIGUOUS")
 _ctx = C.c_void_p
 _opt = C.c_void_p           # optional pointer arguments are passed as raw addresses
 
@@ -77,6 +78,9 @@ _SIGNATURES = {
     "arb_last_fit_profile": (C.c_int, [_ctx, _f64p, C.c_int32]),
     "arb_set_option": (C.c_int, [_ctx, C.c_char_p, C.c_int64]),
     "arb_pool_trim": (C.c_int, []),
+    "arb_base_ingest": (C.c_int, [_ctx, C.c_int64, _i32p, _i32p, _i32p, _i32p, C.c_int32, C.c_int32, C.c_double]),
+    "arb_base_score": (C.c_int, [_ctx, C.c_int32, C.c_int32, _u32p, _u32p, _f64p]),
+    "arb_base_cells": (C.c_int, [_ctx, C.c_int32, C.c_int32, _u32p, _u32p, _opt, _f64p, _i32p, _f64p, _u8p]),
 }
 
 
@@ -174,6 +178,31 @@ class Engine:
         cu, su = np.empty(nc.value, np.int64), np.empty(ns.value, np.int64)
         _check(self._lib.arb_get_id_uniques(self._h, cu, su))
         return cu, su
+
+    # ---- legacy scorer (arb_base.cu; reference arborist_base.py) ---------------------------------
+    def base_ingest(self, cell_code, cluster_code, total, alt, n_cells, n_clusters, alpha):
+        arrs = [_i32(a) for a in (cell_code, cluster_code, total, alt)]
+        _check(self._lib.arb_base_ingest(self._h, len(arrs[0]), *arrs, int(n_cells), int(n_clusters), float(alpha)))
+        self._base_cells = int(n_cells)
+
+    def base_score(self, anc_masks, tree_masks):
+        anc = np.ascontiguousarray(anc_masks, dtype=np.uint32)
+        tm = np.ascontiguousarray(tree_masks, dtype=np.uint32)
+        lik = np.empty(anc.shape[0], np.float64)
+        _check(self._lib.arb_base_score(self._h, anc.shape[0], anc.shape[1], anc, tm, lik))
+        return lik
+
+    def base_cells(self, anc_masks, tree_masks, want_loglik=False):
+        """Per-cell detail of the listed trees: ``(loglik or None, posterior, clone_idx, entropy, present)``."""
+        anc = np.ascontiguousarray(anc_masks, dtype=np.uint32)
+        tm = np.ascontiguousarray(tree_masks, dtype=np.uint32)
+        S, K, n = anc.shape[0], anc.shape[1], self._base_cells
+        ll = np.empty((S, n, K), np.float64) if want_loglik else None
+        post, idx = np.empty((S, n, K), np.float64), np.empty((S, n), np.int32)
+        ent, pres = np.empty((S, n), np.float64), np.empty((S, n), np.uint8)
+        _check(self._lib.arb_base_cells(self._h, S, K, anc, tm, ll.ctypes.data if want_loglik else None, post, idx,
+                                        ent, pres))
+        return ll, post, idx, ent, pres.astype(bool)
 
     def ingest_csr(self, cell_ptr, snv_idx, log_likes, n_cells, n_snvs):
         snv_idx = _i32(snv_idx)

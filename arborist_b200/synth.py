@@ -195,3 +195,19 @@ def generate(cfg: SynthConfig) -> SynthData:
         cell_clone=cell_clone,
         snv_cluster=snv_cluster,
     )
+
+
+def legacy_inputs(name="tiny"):
+    """Inputs of the legacy scorer (``arborist_base.rank_trees``) from a synthetic workload: trees with the normal
+    clone, read counts with the ``cluster`` column the reference's ``main`` derives from the SNV clustering
+    (arborist_base.py:371-385).  One label is replaced by a cluster no tree contains, so the scorer's cluster
+    filter (arborist_base.py:153-155) has rows to drop."""
+    import importlib
+
+    d = generate(CONFIGS[name])
+    rc, cl = d.read_counts_frame(), d.clusters_frame()
+    rc = rc.copy()
+    rc["cluster"] = rc["snv"].map(dict(zip(cl["snv"], cl["cluster"])))
+    rc.loc[rc["snv"] % 17 == 5, "cluster"] = 99
+    trees = importlib.import_module("arborist_b200.arborist").add_normal_clone(d.trees)
+    return [[(int(u), int(v)) for u, v in t] for t in trees], rc

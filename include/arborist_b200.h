@@ -175,6 +175,32 @@ int arb_set_option(arb_ctx *ctx, const char *name, int64_t value);
  * the pool. */
 int arb_pool_trim(void);
 
+/* ---- legacy scorer: replaces the reference's arborist_base.py ---------------------------------------
+ * find_cell_assignments (arborist_base.py:102-194) and the numeric part of rank_trees
+ * (arborist_base.py:250-362).  The host mirror is arborist_b200/arborist_base.py.
+ *
+ * arb_base_ingest: the long read-count table restricted to rows with a cluster label.  cell_code[i] in
+ * [0, n_cells), cluster_code[i] in [0, n_clusters) (n_clusters <= 32), total / alt the read counts.  Folds
+ * the rows into per (cell, cluster) sums of binom.logpmf(alt, total, p) at p = 0.5 - alpha + 0.5 alpha / 3
+ * and p = alpha / 3 (arborist_base.py:165-166, 186-188), kept on the device. */
+int arb_base_ingest(arb_ctx *ctx, int64_t n_rows, const int32_t *cell_code, const int32_t *cluster_code,
+                    const int32_t *total, const int32_t *alt, int32_t n_cells, int32_t n_clusters,
+                    double alpha);
+/* arb_base_score: likelihood[t] = sum over cells of max over clones of the cell's log-likelihood
+ * (arborist_base.py:193).  anc_masks[t * n_clones + c]: bit k set when cluster code k is clone c or one of
+ * its ancestors (build_genotypes, arborist_base.py:228-247); tree_masks[t]: bit k set when cluster code k is
+ * a node of tree t -- rows of other clusters are dropped, cells left without rows do not count
+ * (arborist_base.py:153-160).  n_clones <= 64. */
+int arb_base_score(arb_ctx *ctx, int32_t n_trees, int32_t n_clones, const uint32_t *anc_masks,
+                   const uint32_t *tree_masks, double *likelihood);
+/* arb_base_cells: per-cell detail for the listed trees, all [n_trees][n_cells](x n_clones): log-likelihoods
+ * (may be NULL), posteriors over clones exp(L - logsumexp(L)) (arborist_base.py:335-338), index of the first
+ * best clone (arborist_base.py:296-298), entropy of the posterior in bits (arborist_base.py:341), and
+ * present = 1 when the cell keeps at least one row under the tree's cluster filter. */
+int arb_base_cells(arb_ctx *ctx, int32_t n_trees, int32_t n_clones, const uint32_t *anc_masks,
+                   const uint32_t *tree_masks, double *loglik, double *posterior, int32_t *clone_idx,
+                   double *entropy, uint8_t *present);
+
 #ifdef __cplusplus
 }
 #endif

@@ -140,3 +140,99 @@ def rank_trees(tree_list, read_counts, alpha=0.001, topn=None, verbose=False, de
         return ranked_trees, cell_assignments
     finally:
         tab.close()
+
+
+# ---------------------------------------------------------------------------
+# writers and CLI (arborist_base.py:13-99, 197-225, 365-424) -- host only
+# ---------------------------------------------------------------------------
+def save_tree(fname, tree, sep=" "):
+    """Edge list with the reference's one-line header (arborist_base.py:94-99)."""
+    with open(fname, "w+") as f:
+        f.write(f"{len(tree)} #edges tree 0\n")
+        for u, v in tree:
+            f.write(f"{u}{sep}{v}\n")
+
+
+def save_genotypes(fname, tree, snv_to_cluster, x=1, y=1):
+    """Long genotype table node x SNV (arborist_base.py:197-225).  Like the reference, a node carries a cluster's
+    SNVs when the cluster is the node itself or its PARENT (``has_predecessor`` is the direct-edge test), never the
+    root's; SNVs of clusters outside the tree get 0."""
+    from .arborist import _digraph_edge_order
+
+    edges, nodes = _digraph_edge_order(tree)
+    parents = {}
+    for u, v in edges:
+        parents.setdefault(v, set()).add(u)
+    root = [n for n in nodes if not parents.get(n)][0]
+    node_set, rows = set(nodes), []
+    for n in nodes:
+        for snv, clust in snv_to_cluster.items():
+            xbar = int(clust in node_set and clust != root and (n == clust or clust in parents.get(n, ())))
+            rows.append([n, snv, x, y, xbar, 0, 1])
+    pd.DataFrame(rows, columns=["node", "snv", "x", "y", "xbar", "ybar", "segment"]).to_csv(fname, index=False)
+
+
+def parse_arguments(argv=None):
+    import argparse
+
+    p = argparse.ArgumentParser(description="Tree ranking script")
+    p.add_argument("-R", "--read_counts", required=True,
+                   help="Path to read counts CSV file with columns 'cell', 'total', 'alt'")
+    p.add_argument("-C", "--clustering", required=True,
+                   help="path to snv cluster labels, csv file with unlabeled columns 'snv', 'cluster'")
+    p.add_argument("-T", "--trees", required=True, help="Path to tree file")
+    p.add_argument("--edge-delim", type=str, default=" ", help="edge delimiter in candidate tree file.")
+    p.add_argument("--alpha", type=float, default=0.001, help="Per base sequencing error")
+    p.add_argument("--topn", type=int, default=25, help="Filter only the top n trees, default is 25.")
+    p.add_argument("--ranking", type=str, help="Path to where tree ranking output should be saved")
+    p.add_argument("--cell-assign", type=str, help="Path to where cell assignments output should be saved")
+    p.add_argument("-v", "--verbose", help="Print verbose output", action="store_true")
+    p.add_argument("-d", "--draw", type=str, help="Path to save the tree image")
+    p.add_argument("--snv-assign", type=str, help="Path to where snv assignments output should be saved")
+    p.add_argument("--genotypes", type=str, help="Path to where the genotypes should be saved")
+    p.add_argument("--add-normal", action="store_true",
+                   help="indicates if a normal root should be added to the tree")
+    p.add_argument("-t", "--tree", type=str, help="path to where the tree should be saved")
+    return p.parse_args(argv)
+
+
+def main(argv=None):
+    """The reference's legacy command line (arborist_base.py:365-424)."""
+    from .arborist import add_normal_clone
+    from .utils import read_read_counts, read_trees, visualize_tree
+
+    args = parse_arguments(argv)
+    read_counts = read_read_counts(args.read_counts)
+    clustering = pd.read_csv(args.clustering, header=None, names=["snv", "cluster"])
+    snv_to_cluster = dict(zip(clustering["snv"], clustering["cluster"]))
+    read_counts["cluster"] = read_counts["snv"].map(snv_to_cluster)
+    candidate_trees = read_trees(args.trees, sep=args.edge_delim)
+    if args.add_normal:
+        candidate_trees = add_normal_clone(candidate_trees)
+    ranked_trees, cell_assignments = rank_trees(candidate_trees, read_counts, alpha=args.alpha, topn=args.topn,
+                                                verbose=args.verbose)
+    tree_idx = ranked_trees["tree"].tolist()[0]
+    best_tree = cell_assignments[cell_assignments["tree"] == tree_idx]
+    inf_tree = candidate_trees[tree_idx]
+    if args.draw:
+        visualize_tree(inf_tree, cell_assignment=dict(zip(best_tree["cell"], best_tree["clone"])),
+                       output_file=args.draw)
+    if args.tree:
+        save_tree(args.tree, inf_tree)
+    if args.genotypes:
+        save_genotypes(args.genotypes, inf_tree, snv_to_cluster)
+    if args.snv_assign:
+        nodes = {x for e in inf_tree for x in e}
+        kept = clustering[clustering["cluster"].isin(list(nodes))]
+        alt_sum = read_counts.groupby("snv")["alt"].sum()
+        valid_snvs = alt_sum[alt_sum > 0].index
+        print(f"Number of valid SNVs:  {len(valid_snvs)}")
+        kept[kept["snv"].isin(valid_snvs)].to_csv(args.snv_assign, index=False)
+    if args.ranking:
+        ranked_trees.to_csv(args.ranking, index=False)
+    if args.cell_assign:
+        best_tree[["cell", "clone"]].copy().to_csv(args.cell_assign, index=False)
+
+
+if __name__ == "__main__":
+    main()

@@ -30,6 +30,18 @@ def inputs():
     return synth.legacy_inputs("tiny")
 
 
+CLI_OUTPUTS = {"--ranking": "ranking.csv", "--cell-assign": "cell_assign.csv", "--snv-assign": "snv_assign.csv",
+               "--genotypes": "genotypes.csv", "-t": "tree.txt"}
+
+
+def cli_args(indir, outdir):
+    argv = ["-R", os.path.join(indir, "read_counts.csv"), "-C", os.path.join(indir, "clusters.csv"),
+            "-T", os.path.join(indir, "trees.txt"), "--add-normal", "--alpha", "0.001", "--topn", "2"]
+    for flag, name in CLI_OUTPUTS.items():
+        argv += [flag, os.path.join(outdir, name)]
+    return argv
+
+
 def main():
     from gen_golden import load_reference
 
@@ -56,6 +68,19 @@ def main():
         table_loglik=np.stack([t[1].to_numpy(np.float64) for t in tables]),
     )
     print("wrote", OUT, "ranking", ranked["tree"].tolist(), "rows", len(cells))
+
+    # the legacy command line (arborist_base.py:365-424) on the files of tests/golden/cli_tiny
+    src = os.path.join(ROOT, "tests", "golden", "cli_tiny")
+    exp = os.path.join(ROOT, "tests", "golden", "base_cli_tiny")
+    os.makedirs(exp, exist_ok=True)
+    old = sys.argv
+    sys.argv = ["arborist_base", *cli_args(src, exp)]
+    try:
+        with contextlib.redirect_stdout(io.StringIO()):
+            B.main()
+    finally:
+        sys.argv = old
+    print("wrote", sorted(os.listdir(exp)))
 
 
 if __name__ == "__main__":

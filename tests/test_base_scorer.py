@@ -119,3 +119,35 @@ def test_rank_trees_errors():
         ab.rank_trees([trees[0], [(0, 1), (1, 2)]], rc)          # different node sets
     with pytest.raises(ValueError):
         ab.rank_trees(trees, rc.drop(columns=["cluster"]))
+
+
+@pytest.mark.gpu
+def test_legacy_cli_outputs_match_reference(tmp_path):
+    """The reference's legacy command line (arborist_base.py:365-424) replayed on the files of
+    tests/golden/cli_tiny; expected outputs written by oracle/gen_base_golden.py from the live reference."""
+    import os
+    import pandas as pd
+    from conftest import GOLDEN
+    from arborist_b200 import arborist_base as ab
+    src, exp = os.path.join(GOLDEN, "cli_tiny"), os.path.join(GOLDEN, "base_cli_tiny")
+    outputs = {"--ranking": "ranking.csv", "--cell-assign": "cell_assign.csv", "--snv-assign": "snv_assign.csv",
+               "--genotypes": "genotypes.csv", "-t": "tree.txt"}
+    argv = ["-R", os.path.join(src, "read_counts.csv"), "-C", os.path.join(src, "clusters.csv"),
+            "-T", os.path.join(src, "trees.txt"), "--add-normal", "--alpha", "0.001", "--topn", "2"]
+    for flag, name in outputs.items():
+        argv += [flag, str(tmp_path / name)]
+    ab.main(argv)
+    for name in ("cell_assign.csv", "snv_assign.csv", "genotypes.csv", "tree.txt"):
+        assert (tmp_path / name).read_text() == open(os.path.join(exp, name)).read(), name
+    got, want = pd.read_csv(tmp_path / "ranking.csv"), pd.read_csv(os.path.join(exp, "ranking.csv"))
+    assert list(got.columns) == list(want.columns) and got["tree"].tolist() == want["tree"].tolist()
+    np.testing.assert_allclose(got["likelihood"], want["likelihood"], rtol=RTOL)
+    np.testing.assert_allclose(got["posterior"], want["posterior"], rtol=1e-7)
+
+
+def test_legacy_cli_flags_match_reference():
+    """Same flags and defaults as arborist_base.py:13-91."""
+    from arborist_b200 import arborist_base as ab
+    a = ab.parse_arguments(["-R", "r", "-C", "c", "-T", "t"])
+    assert (a.alpha, a.topn, a.edge_delim, a.add_normal, a.verbose) == (0.001, 25, " ", False, False)
+    assert all(getattr(a, k) is None for k in ("ranking", "cell_assign", "snv_assign", "genotypes", "tree", "draw"))

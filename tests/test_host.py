@@ -136,6 +136,9 @@ def test_drop_in_package_names():
     assert arborist.read_trees is arborist_b200.read_trees
     from arborist.treefit import TreeFit
     assert TreeFit is arborist_b200.TreeFit
+    from arborist.arborist_base import rank_trees, find_cell_assignments, build_genotypes  # noqa: F401
+    from arborist_b200 import arborist_base
+    assert rank_trees is arborist_base.rank_trees
 
 
 def test_cli_flags_match_reference():

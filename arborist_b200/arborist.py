@@ -21,6 +21,7 @@ from __future__ import annotations
 
 import argparse
 import logging
+import os
 import weakref
 
 import numpy as np
@@ -202,8 +203,25 @@ def ingest_read_counts(eng, read_counts, snv_clusters, cluster_to_idx, alpha, ga
     table) runs on the device when the ids are int64, on the host (pandas) otherwise; the zero-alt filter (A.py:1034-1041), re-indexing, dictionary
     coding and the cell-major / SNV-major layouts are built by ``arb_ingest_coo``.
     """
-    cols = [read_counts[c].to_numpy() for c in ("cell", "snv", "alt", "total")]
-    if all(a.dtype == np.int64 for a in cols):
+    if isinstance(read_counts, (str, os.PathLike)):
+        # a file instead of a DataFrame: integer CSVs are parsed on the device (arb_csv_*), anything else (text ids,
+        # quoted fields, Parquet / Feather / npz) goes through the host reader first
+        from .engine import ArboristError
+        path = os.fspath(read_counts)
+        read_counts = None
+        if path.lower().endswith(".csv"):
+            try:
+                cell_uniques, snv_uniques, _ = eng.ingest_csv(path, alpha)
+            except ArboristError as e:
+                if e.status != -3:                      # ARB_ERR_UNSUPPORTED: not a plain integer table
+                    raise
+                read_counts = read_read_counts(path)
+        else:
+            read_counts = read_read_counts(path)
+    cols = [] if read_counts is None else [read_counts[c].to_numpy() for c in ("cell", "snv", "alt", "total")]
+    if read_counts is None:
+        pass
+    elif all(a.dtype == np.int64 for a in cols):
         # integer ids: the factorisation runs on the device too (arb_ingest_ids)
         cell_uniques, snv_uniques = eng.ingest_ids(*cols, alpha)
     else:
@@ -449,7 +467,8 @@ def parse_arguments(argv=None) -> argparse.Namespace:
 
 def main(argv=None):
     args = parse_arguments(argv)
-    read_counts = read_read_counts(args.read_counts)      # CSV as upstream; also Parquet / Feather / npz
+    read_counts = args.read_counts     # the file itself: CSV as upstream (parsed on the device when its columns are
+                                       # integers, by pandas otherwise); also Parquet / Feather / npz
     snv_clusters = pd.read_csv(args.snv_clusters, header=None, names=["snv", "cluster"])
     candidate_trees = read_trees(args.trees, sep=args.edge_delim)
 

@@ -166,6 +166,12 @@ struct arb_ctx {
     // ---- legacy scorer (arb_base.cu): per (cell, cluster) log-pmf sums and row counts ----------
     DevBuf base_ta, base_tb, base_cnt;
     int32_t base_cells = 0, base_clusters = 0;
+
+    // ---- CSV rows parsed so far (arb_csv_begin / feed / finish): int64 cell, snv, alt, total ----------
+    DevBuf csv_col[4];
+    int64_t csv_rows = 0, csv_cap = 0;
+    int32_t csv_field[4] = {0, 0, 0, 0}, csv_fields = 0;
+    bool csv_open = false;
 };
 
 __host__ __device__ static inline int64_t arb_perm(int64_t c, int np, int pr) { return (c % np) * (int64_t)pr + c / np; }

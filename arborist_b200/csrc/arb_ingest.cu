@@ -234,7 +234,8 @@ ARB_API int arb_ctx_destroy(arb_ctx *ctx)
                       &ctx->part_y, &ctx->red, &ctx->slot_state, &ctx->lists, &ctx->masks,
                       &ctx->best_qz, &ctx->best_qy, &ctx->d_elbo, &ctx->d_iters, &ctx->d_trace,
                       &ctx->tree_masks, &ctx->single_qz, &ctx->single_qy, &ctx->scratch, &ctx->cell_uniques,
-                      &ctx->snv_uniques, &ctx->base_ta, &ctx->base_tb, &ctx->base_cnt};
+                      &ctx->snv_uniques, &ctx->base_ta, &ctx->base_tb, &ctx->base_cnt,
+                      &ctx->csv_col[0], &ctx->csv_col[1], &ctx->csv_col[2], &ctx->csv_col[3]};
     for (DevBuf *b : bufs) b->release();
     for (auto &l : ctx->layout) l.release();
     for (int g = 0; g < ARB_MAX_GROUPS; ++g) {
@@ -1185,6 +1186,219 @@ ARB_API int arb_get_id_uniques(arb_ctx *ctx, int64_t *cell_uniques, int64_t *snv
     if (snv_uniques)
         ARB_CUDA(cudaMemcpy(snv_uniques, ctx->snv_uniques.p, (size_t)ctx->n_snv_uniques * 8, cudaMemcpyDeviceToHost));
     return ARB_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// read-count CSV parsed on the device (replaces pd.read_csv of A.py:1135 for integer tables): the host
+// hands over the raw bytes of the file in chunks that end on a line boundary; the four columns are
+// parsed straight into device memory and never exist as host arrays.
+// ---------------------------------------------------------------------------------------
+#define ARB_CSV_SPAN 128      // bytes per thread
+
+__global__ void k_csv_count(const char *__restrict__ buf, int64_t n, int32_t *__restrict__ counts, int64_t n_spans)
+{
+    int64_t s = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (s >= n_spans) return;
+    int64_t lo = s * ARB_CSV_SPAN, hi = min(n, lo + ARB_CSV_SPAN);
+    int c = 0;
+    if (hi - lo == ARB_CSV_SPAN) {
+        const uint4 *v = reinterpret_cast<const uint4 *>(buf + lo);
+#pragma unroll
+        for (int i = 0; i < ARB_CSV_SPAN / 16; ++i) {
+            uint4 q = v[i];
+            uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                c += __popc(__vcmpeq4(w[j], 0x0a0a0a0au)) >> 3;       // 0xff in every byte that is '\n'
+            }
+        }
+    } else {
+        for (int64_t i = lo; i < hi; ++i) c += buf[i] == '\n';
+    }
+    counts[s] = c;
+}
+
+// One thread per span: every line that ENDS in the span is parsed by this thread (its start is found by walking
+// back to the previous newline).  Selected fields must be plain integers; a quote anywhere, a wrong field count or
+// an empty line records the byte offset in `bad` (the host then falls back to its own reader).
+__global__ void k_csv_parse(const char *__restrict__ buf, int64_t n, const int32_t *__restrict__ offs, int64_t n_spans,
+                            int64_t row0, int c_cell, int c_snv, int c_alt, int c_tot, int n_fields,
+                            int64_t *__restrict__ o_cell, int64_t *__restrict__ o_snv, int64_t *__restrict__ o_alt,
+                            int64_t *__restrict__ o_tot, unsigned long long *__restrict__ bad)
+{
+    int64_t s = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (s >= n_spans) return;
+    int64_t lo = s * ARB_CSV_SPAN, hi = min(n, lo + ARB_CSV_SPAN);
+    int64_t row = row0 + offs[s];
+    for (int64_t p = lo; p < hi; ++p) {
+        if (buf[p] != '\n') continue;
+        int64_t q = p;
+        while (q > 0 && buf[q - 1] != '\n') --q;
+        int64_t e = p;
+        if (e > q && buf[e - 1] == '\r') --e;
+        bool ok = e > q;
+        int f = 0, digits = 0;
+        int64_t v = 0, out[4] = {0, 0, 0, 0};
+        bool neg = false;
+        for (int64_t i = q; i <= e && ok; ++i) {
+            char c = i < e ? buf[i] : ',';
+            bool sel = f == c_cell || f == c_snv || f == c_alt || f == c_tot;
+            if (c == ',') {
+                if (sel) {
+                    ok = digits > 0;
+                    int64_t val = neg ? -v : v;
+                    if (f == c_cell) out[0] = val;
+                    if (f == c_snv) out[1] = val;
+                    if (f == c_alt) out[2] = val;
+                    if (f == c_tot) out[3] = val;
+                }
+                ++f;
+                v = 0;
+                digits = 0;
+                neg = false;
+            } else if (c == '"') {
+                ok = false;
+            } else if (sel) {
+                if (c >= '0' && c <= '9') {
+                    v = v * 10 + (c - '0');
+                    ok = ++digits <= 18;
+                } else if (c == '-' && digits == 0 && !neg) {
+                    neg = true;
+                } else {
+                    ok = false;
+                }
+            }
+        }
+        if (!ok || f != n_fields) {
+            atomicMin(bad, (unsigned long long)q);
+        } else {
+            o_cell[row] = out[0];
+            o_snv[row] = out[1];
+            o_alt[row] = out[2];
+            o_tot[row] = out[3];
+        }
+        ++row;
+    }
+}
+
+static int csv_grow(arb_ctx *ctx, int64_t need)
+{
+    if (need <= ctx->csv_cap) return ARB_OK;
+    int64_t cap = std::max<int64_t>(need, ctx->csv_cap * 2);
+    for (DevBuf &b : ctx->csv_col) {
+        DevBuf nb;
+        ARB_TRY(nb.reserve((size_t)cap * 8));
+        if (ctx->csv_rows)
+            ARB_CUDA(cudaMemcpyAsync(nb.p, b.p, (size_t)ctx->csv_rows * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+        ARB_CUDA(cudaStreamSynchronize(ctx->stream));
+        b.release();
+        b = nb;
+    }
+    ctx->csv_cap = cap;
+    return ARB_OK;
+}
+
+ARB_API int arb_csv_begin(arb_ctx *ctx, int32_t col_cell, int32_t col_snv, int32_t col_alt, int32_t col_total,
+                          int32_t n_fields, int64_t expected_rows)
+{
+    ARB_REQUIRE(ctx, ARB_ERR_INVALID, "arb_csv_begin: null context");
+    const int32_t c[4] = {col_cell, col_snv, col_alt, col_total};
+    for (int i = 0; i < 4; ++i) {
+        ARB_REQUIRE(c[i] >= 0 && c[i] < n_fields, ARB_ERR_INVALID, "arb_csv_begin: column index %d outside 0..%d", c[i],
+                    n_fields - 1);
+        for (int j = 0; j < i; ++j) ARB_REQUIRE(c[i] != c[j], ARB_ERR_INVALID, "arb_csv_begin: column %d given twice", c[i]);
+    }
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    for (int i = 0; i < 4; ++i) ctx->csv_field[i] = c[i];
+    ctx->csv_fields = n_fields;
+    ctx->csv_rows = 0;
+    ctx->csv_open = true;
+    return csv_grow(ctx, std::max<int64_t>(expected_rows, 1024));
+}
+
+ARB_API int arb_csv_feed(arb_ctx *ctx, const char *bytes, int64_t n_bytes, int64_t *n_rows_total)
+{
+    ARB_REQUIRE(ctx && ctx->csv_open, ARB_ERR_INVALID, "arb_csv_feed: call arb_csv_begin first");
+    ARB_REQUIRE(bytes && n_bytes > 0 && n_bytes <= ((int64_t)1 << 30), ARB_ERR_INVALID,
+                "arb_csv_feed: chunk of %lld bytes (1..2^30 allowed)", (long long)n_bytes);
+    ARB_REQUIRE(bytes[n_bytes - 1] == '\n', ARB_ERR_INVALID, "arb_csv_feed: a chunk has to end with a newline");
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const int B = 256;
+    int64_t n_spans = (n_bytes + ARB_CSV_SPAN - 1) / ARB_CSV_SPAN;
+    DevBuf buf, counts, offs, bad;
+    ARB_TRY(buf.reserve((size_t)n_bytes + 16));
+    ARB_TRY(counts.reserve((size_t)n_spans * 4));
+    ARB_TRY(offs.reserve((size_t)n_spans * 4));
+    ARB_TRY(bad.reserve(8));
+    ARB_CUDA(cudaMemcpyAsync(buf.p, bytes, (size_t)n_bytes, cudaMemcpyHostToDevice, st));
+    ARB_CUDA(cudaMemsetAsync(bad.p, 0xff, 8, st));
+    k_csv_count<<<grid_for(n_spans, B), B, 0, st>>>(buf.as<char>(), n_bytes, counts.as<int32_t>(), n_spans);
+    ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &tb) {
+        return cub::DeviceScan::ExclusiveSum(tmp, tb, counts.as<int32_t>(), offs.as<int32_t>(), (int)n_spans, st);
+    }));
+    int32_t last_off = 0, last_cnt = 0;
+    ARB_CUDA(cudaMemcpyAsync(&last_off, offs.as<int32_t>() + (n_spans - 1), 4, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaMemcpyAsync(&last_cnt, counts.as<int32_t>() + (n_spans - 1), 4, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaStreamSynchronize(st));
+    int64_t lines = (int64_t)last_off + last_cnt;
+    ARB_REQUIRE(ctx->csv_rows + lines < (int64_t)INT_MAX, ARB_ERR_UNSUPPORTED, "arb_csv_feed: more than 2^31-1 rows");
+    ARB_TRY(csv_grow(ctx, ctx->csv_rows + lines));
+    k_csv_parse<<<grid_for(n_spans, B), B, 0, st>>>(buf.as<char>(), n_bytes, offs.as<int32_t>(), n_spans, ctx->csv_rows,
+                                                    ctx->csv_field[0], ctx->csv_field[1], ctx->csv_field[2],
+                                                    ctx->csv_field[3], ctx->csv_fields, ctx->csv_col[0].as<int64_t>(),
+                                                    ctx->csv_col[1].as<int64_t>(), ctx->csv_col[2].as<int64_t>(),
+                                                    ctx->csv_col[3].as<int64_t>(), bad.as<unsigned long long>());
+    ARB_CUDA(cudaGetLastError());
+    unsigned long long h_bad = 0;
+    ARB_CUDA(cudaMemcpyAsync(&h_bad, bad.p, 8, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaStreamSynchronize(st));
+    for (DevBuf *b : {&buf, &counts, &offs, &bad}) b->release();
+    if (h_bad != ~0ull) {
+        ctx->csv_open = false;
+        arb_set_error("arb_csv_feed: the line at byte %llu of this chunk is not %d comma-separated fields with plain "
+                      "integers in the four selected columns (quoted, empty, fractional or text fields need the host reader)",
+                      h_bad, ctx->csv_fields);
+        return ARB_ERR_UNSUPPORTED;
+    }
+    ctx->csv_rows += lines;
+    if (n_rows_total) *n_rows_total = ctx->csv_rows;
+    return ARB_OK;
+}
+
+ARB_API int arb_csv_finish(arb_ctx *ctx, double alpha, int64_t *n_rows, int32_t *n_cell_ids, int32_t *n_snv_ids)
+{
+    ARB_REQUIRE(ctx && ctx->csv_open, ARB_ERR_INVALID, "arb_csv_finish: no open CSV table");
+    ARB_REQUIRE(ctx->csv_rows > 0, ARB_ERR_INVALID, "arb_csv_finish: no rows were fed");
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const int B = 256;
+    const int64_t n = ctx->csv_rows;
+    ctx->csv_open = false;
+    DevBuf d_cell, d_snv, d_alt, d_tot, bad;
+    ARB_TRY(bad.reserve(4));
+    ARB_CUDA(cudaMemsetAsync(bad.p, 0, 4, st));
+    ARB_TRY(d_alt.reserve(n * 4));
+    ARB_TRY(d_tot.reserve(n * 4));
+    k_narrow_i64<<<grid_for(n, B), B, 0, st>>>(ctx->csv_col[2].as<int64_t>(), n, d_alt.as<int32_t>(), bad.as<int32_t>());
+    k_narrow_i64<<<grid_for(n, B), B, 0, st>>>(ctx->csv_col[3].as<int64_t>(), n, d_tot.as<int32_t>(), bad.as<int32_t>());
+    int32_t h_bad = 0;
+    ARB_CUDA(cudaMemcpyAsync(&h_bad, bad.p, 4, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaStreamSynchronize(st));
+    bad.release();
+    ARB_REQUIRE(!h_bad, ARB_ERR_INVALID, "arb_csv_finish: alt / total outside 0..2^31-1");
+    int32_t nc = 0, ns = 0;
+    ARB_TRY(device_factorize(ctx, ctx->csv_col[0], n, d_cell, ctx->cell_uniques, &nc));
+    ARB_TRY(device_factorize(ctx, ctx->csv_col[1], n, d_snv, ctx->snv_uniques, &ns));
+    ARB_CUDA(cudaStreamSynchronize(st));
+    for (DevBuf &b : ctx->csv_col) b.release();
+    ctx->csv_cap = ctx->csv_rows = 0;
+    ctx->n_cell_uniques = nc;
+    ctx->n_snv_uniques = ns;
+    if (n_rows) *n_rows = n;
+    if (n_cell_ids) *n_cell_ids = nc;
+    if (n_snv_ids) *n_snv_ids = ns;
+    return ingest_device_codes(ctx, n, d_cell, d_snv, d_alt, d_tot, nc, ns, alpha);
 }
 
 // ---------------------------------------------------------------------------------------

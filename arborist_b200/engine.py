@@ -78,6 +78,9 @@ _SIGNATURES = {
     "arb_last_fit_profile": (C.c_int, [_ctx, _f64p, C.c_int32]),
     "arb_set_option": (C.c_int, [_ctx, C.c_char_p, C.c_int64]),
     "arb_pool_trim": (C.c_int, []),
+    "arb_csv_begin": (C.c_int, [_ctx, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int64]),
+    "arb_csv_feed": (C.c_int, [_ctx, C.c_char_p, C.c_int64, C.POINTER(C.c_int64)]),
+    "arb_csv_finish": (C.c_int, [_ctx, C.c_double, C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "arb_base_ingest": (C.c_int, [_ctx, C.c_int64, _i32p, _i32p, _i32p, _i32p, C.c_int32, C.c_int32, C.c_double]),
     "arb_base_score": (C.c_int, [_ctx, C.c_int32, C.c_int32, _u32p, _u32p, _f64p]),
     "arb_base_cells": (C.c_int, [_ctx, C.c_int32, C.c_int32, _u32p, _u32p, _opt, _f64p, _i32p, _f64p, _u8p]),
@@ -178,6 +181,42 @@ class Engine:
         cu, su = np.empty(nc.value, np.int64), np.empty(ns.value, np.int64)
         _check(self._lib.arb_get_id_uniques(self._h, cu, su))
         return cu, su
+
+    def ingest_csv(self, path, alpha, chunk_bytes=256 << 20):
+        """Read-count CSV with integer columns ``cell, snv, alt, total`` (any order, other columns ignored) parsed,
+        factorised and ingested on the device.  Returns ``(cell_uniques, snv_uniques, n_rows)``; raises
+        ``ArboristError`` with status ``ARB_ERR_UNSUPPORTED`` (-3) when the file needs a general CSV reader."""
+        size = os.path.getsize(path)
+        with open(path, "rb") as f:
+            header = f.readline()
+            names = [h.strip().strip('"') for h in header.decode("utf-8", "replace").rstrip("\r\n").split(",")]
+            try:
+                cols = [names.index(c) for c in ("cell", "snv", "alt", "total")]
+            except ValueError:
+                raise ValueError(f"{path}: the header needs the columns cell, snv, alt, total (found {names})")
+            first = f.read(1 << 16)
+            per_row = max(4.0, len(first) / max(1, first.count(b"\n")))
+            _check(self._lib.arb_csv_begin(self._h, *cols, len(names), int((size - len(header)) / per_row * 1.05) + 16))
+            carry, total = first, C.c_int64(0)
+            while True:
+                block = f.read(chunk_bytes)
+                data = carry + block
+                if not block:                                   # end of file: the last line may lack its newline
+                    if data and not data.endswith(b"\n"):
+                        data += b"\n"
+                    cut = len(data)
+                else:
+                    cut = data.rfind(b"\n") + 1
+                if cut:
+                    _check(self._lib.arb_csv_feed(self._h, data[:cut], cut, C.byref(total)))
+                carry = data[cut:]
+                if not block:
+                    break
+        n_rows, nc, ns = C.c_int64(), C.c_int32(), C.c_int32()
+        _check(self._lib.arb_csv_finish(self._h, float(alpha), C.byref(n_rows), C.byref(nc), C.byref(ns)))
+        cu, su = np.empty(nc.value, np.int64), np.empty(ns.value, np.int64)
+        _check(self._lib.arb_get_id_uniques(self._h, cu, su))
+        return cu, su, n_rows.value
 
     # ---- legacy scorer (arb_base.cu; reference arborist_base.py) ---------------------------------
     def base_ingest(self, cell_code, cluster_code, total, alt, n_cells, n_clusters, alpha):

@@ -175,6 +175,23 @@ int arb_set_option(arb_ctx *ctx, const char *name, int64_t value);
  * the pool. */
 int arb_pool_trim(void);
 
+/* ---- read-count CSV parsed on the device: replaces pd.read_csv of the long table (A.py:1135) followed by
+ * arb_ingest_ids, for files whose four columns are plain integers.  The host reads the header line itself
+ * (column names -> field indices), then hands over the REST of the file as raw bytes in chunks that end on a
+ * line boundary (at most 2^30 bytes each); the columns are parsed into device memory, factorised and ingested
+ * there and never exist as host arrays.
+ *   arb_csv_begin : field indices of the cell / snv / alt / total columns, fields per line, expected row count
+ *                   (a sizing hint; the device columns grow when it is exceeded)
+ *   arb_csv_feed  : one chunk; n_rows_total = rows parsed so far.  ARB_ERR_UNSUPPORTED (table discarded) when
+ *                   a line is not n_fields comma-separated fields with plain integers in the selected columns
+ *                   (quotes, empty lines, fractions, text ids): use the host reader + arb_ingest_ids/_coo then.
+ *   arb_csv_finish: first-appearance factorisation of the ids + everything arb_ingest_ids does; ids in code
+ *                   order through arb_get_id_uniques. */
+int arb_csv_begin(arb_ctx *ctx, int32_t col_cell, int32_t col_snv, int32_t col_alt, int32_t col_total,
+                  int32_t n_fields, int64_t expected_rows);
+int arb_csv_feed(arb_ctx *ctx, const char *bytes, int64_t n_bytes, int64_t *n_rows_total);
+int arb_csv_finish(arb_ctx *ctx, double alpha, int64_t *n_rows, int32_t *n_cell_ids, int32_t *n_snv_ids);
+
 /* ---- legacy scorer: replaces the reference's arborist_base.py ---------------------------------------
  * find_cell_assignments (arborist_base.py:102-194) and the numeric part of rank_trees
  * (arborist_base.py:250-362).  The host mirror is arborist_b200/arborist_base.py.

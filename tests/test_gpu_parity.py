@@ -431,6 +431,62 @@ def test_against_oracle_on_fresh_inputs(eng_mod):
             assert_map_equal(fits[t].q_y, ofits[t][2])
 
 
+def test_device_csv_reader_matches_dataframe_path(eng_mod, tmp_path):
+    """arb_csv_* (the file's bytes parsed, factorised and ingested on the device) vs arb_ingest_ids on the DataFrame
+    pandas reads from the same file: same id order and the same matrix, for an extra index column and shuffled
+    column order, CRLF line ends, a missing final newline and chunks far smaller than the file; tables the device
+    parser declines (text ids) go through the host reader with the same result."""
+    import pandas as pd
+    from arborist_b200 import arborist
+    rng = np.random.default_rng(11)
+    n = 30000
+    key = np.unique(np.stack([rng.integers(-40, 500, n) * 1000003, rng.integers(0, 700, n) * 7 + 10**12], 1), axis=0)
+    rng.shuffle(key)
+    total = 1 + rng.poisson(0.4, len(key))
+    rc = pd.DataFrame({"total": total, "cell": key[:, 0], "note": "x", "alt": rng.binomial(total, 0.3), "snv": key[:, 1]})
+    ref = eng_mod.Engine()
+    cu_ref, su_ref = ref.ingest_ids(rc["cell"], rc["snv"], rc["alt"], rc["total"], 0.001)
+    sparse_ref, orders_ref = ref.export_sparse(), ref.orders()
+    ref.close()
+    variants = {"plain.csv": dict(index=True), "crlf.csv": dict(index=False, lineterminator="\r\n"),
+                "nonl.csv": dict(index=False)}
+    for name, kw in variants.items():
+        path = tmp_path / name
+        rc.to_csv(path, **kw)
+        if name == "nonl.csv":
+            path.write_bytes(path.read_bytes().rstrip(b"\n"))
+        for chunk in (256 << 20, 4096):
+            e = eng_mod.Engine()
+            cu, su, rows = e.ingest_csv(str(path), 0.001, chunk_bytes=chunk)
+            assert rows == len(rc) and np.array_equal(cu, cu_ref) and np.array_equal(su, su_ref), (name, chunk)
+            assert all(np.array_equal(a, b) for a, b in zip(e.export_sparse(), sparse_ref)), (name, chunk)
+            assert all(np.array_equal(a, b) for a, b in zip(e.orders(), orders_ref))
+            e.close()
+    # what the device parser declines
+    bad = tmp_path / "text.csv"
+    rc.assign(cell=rc["cell"].map(lambda v: f"c{v}")).to_csv(bad, index=False)
+    e = eng_mod.Engine()
+    with pytest.raises(eng_mod.ArboristError) as err:
+        e.ingest_csv(str(bad), 0.001)
+    assert err.value.status == -3
+    e.close()
+    with pytest.raises(ValueError):
+        (tmp_path / "nohdr.csv").write_text("a,b,c\n1,2,3\n")
+        eng_mod.Engine().ingest_csv(str(tmp_path / "nohdr.csv"), 0.001)
+    # API level: a path instead of a DataFrame (integer file: device reader; text ids: host reader)
+    g = load_golden("small")
+    trees, frame, cl = golden_frames(g)
+    frame.to_csv(tmp_path / "small.csv", index=False)
+    lik_d, best_d, _ = arborist(trees, frame, cl, max_iter=25, add_normal=True)
+    lik_f, best_f, _ = arborist(trees, str(tmp_path / "small.csv"), cl, max_iter=25, add_normal=True)
+    assert [lik_d[t] for t in range(len(trees))] == [lik_f[t] for t in range(len(trees))]
+    assert np.array_equal(best_d.q_z, best_f.q_z) and list(best_d.cell_to_idx) == list(best_f.cell_to_idx)
+    frame.assign(cell=frame["cell"].map(lambda v: f"c{v}")).to_csv(tmp_path / "small_text.csv", index=False)
+    lik_t, best_t, _ = arborist(trees, str(tmp_path / "small_text.csv"), cl, max_iter=25, add_normal=True)
+    assert [lik_d[t] for t in range(len(trees))] == [lik_t[t] for t in range(len(trees))]
+    assert [f"c{c}" for c in best_d.cell_to_idx] == list(best_t.cell_to_idx)
+
+
 @pytest.mark.parametrize("n_clones", [3, 4, 10, 13, 14, 17, 20, 21, 25, 29, 32])
 def test_clone_counts_against_oracle(eng_mod, n_clones):
     """Every lanes-per-row width of the seeding / finishing kernels (ceil(K/4) = 1..8 lanes, a power of two or

@@ -21,19 +21,27 @@ from scipy.special import logsumexp
 from .engine import Engine
 
 
-def build_genotypes(tree):
-    """DataFrame ``Child`` / ``Ancestors`` ("root,...,child"), clones in the iteration order of the
-    set of node labels (arborist_base.py:228-247)."""
+def _clone_paths(tree):
+    """(clones in the iteration order of the set of node labels, root-to-clone path of each)."""
     child_to_parent = {child: parent for parent, child in tree}
     all_clones = set(child_to_parent.keys()).union(set(child_to_parent.values()))
-    rows = []
+    clones, paths = [], []
     for clone in all_clones:
         path, x = [clone], clone
         while x in child_to_parent:
             x = child_to_parent[x]
             path.append(x)
-        rows.append((clone, ",".join(str(v) for v in reversed(path))))
-    return pd.DataFrame(rows, columns=["Child", "Ancestors"])
+        clones.append(clone)
+        paths.append(path[::-1])
+    return clones, paths
+
+
+def build_genotypes(tree):
+    """DataFrame ``Child`` / ``Ancestors`` ("root,...,child"), clones in the iteration order of the
+    set of node labels (arborist_base.py:228-247)."""
+    clones, paths = _clone_paths(tree)
+    return pd.DataFrame([(c, ",".join(str(v) for v in p)) for c, p in zip(clones, paths)],
+                        columns=["Child", "Ancestors"])
 
 
 class _Table:
@@ -49,22 +57,29 @@ class _Table:
         self.cell_code, self.cell_ids = pd.factorize(rc["cell"], sort=False)
         self.cluster_code, cluster_ids = pd.factorize(rc["cluster"].astype(np.int64), sort=True)
         self.cluster_ids = [int(c) for c in cluster_ids]
+        self._bit = {c: 1 << k for k, c in enumerate(self.cluster_ids)}
         self.engine = Engine(device)
         self.engine.base_ingest(self.cell_code, self.cluster_code, rc["total"].to_numpy(), rc["alt"].to_numpy(),
                                 len(self.cell_ids), len(self.cluster_ids), alpha)
 
     def masks(self, genotype_matrix):
         """(ancestor mask per clone, mask of the tree's own clusters) over the cluster codes."""
-        bit = {c: np.uint32(1 << k) for k, c in enumerate(self.cluster_ids)}
         clones = [int(c) for c in genotype_matrix["Child"].values]
+        paths = [[int(x) for x in str(p).split(",")] for p in genotype_matrix["Ancestors"].values]
+        return self.path_masks(clones, paths)
+
+    def path_masks(self, clones, paths):
+        bit = self._bit
         anc = np.zeros(len(clones), np.uint32)
-        for j, path in enumerate(genotype_matrix["Ancestors"].values):
-            for c in set(map(int, str(path).split(","))):
-                anc[j] |= bit.get(c, np.uint32(0))
-        tmask = np.uint32(0)
+        for j, path in enumerate(paths):
+            m = 0
+            for c in path:
+                m |= bit.get(int(c), 0)
+            anc[j] = m
+        tmask = 0
         for c in clones:
-            tmask |= bit.get(c, np.uint32(0))
-        return anc, tmask
+            tmask |= bit.get(int(c), 0)
+        return anc, np.uint32(tmask)
 
     def cell_order(self, tmask):
         """Cells that keep a row under the tree's cluster filter, in first-appearance order of those rows
@@ -99,14 +114,15 @@ def rank_trees(tree_list, read_counts, alpha=0.001, topn=None, verbose=False, de
     itself."""
     if len(tree_list) == 0:
         raise ValueError("rank_trees: empty tree list")
-    genotypes = [build_genotypes(tree) for tree in tree_list]
-    clones = [int(c) for c in genotypes[0]["Child"].values]
-    for t, g in enumerate(genotypes):
-        if sorted(int(c) for c in g["Child"].values) != sorted(clones):
+    shapes = [_clone_paths(tree) for tree in tree_list]
+    orders = [[int(c) for c in clones] for clones, _ in shapes]
+    node_set = sorted(orders[0])
+    for t, o in enumerate(orders):
+        if sorted(o) != node_set:
             raise ValueError(f"rank_trees: tree {t} has a different node set than tree 0")
     tab = _Table(read_counts, alpha, device)
     try:
-        pairs = [tab.masks(g) for g in genotypes]
+        pairs = [tab.path_masks(clones, paths) for clones, paths in shapes]
         anc = np.stack([p[0] for p in pairs])
         tmask = np.array([p[1] for p in pairs], np.uint32)
         lik = tab.engine.base_score(anc, tmask)
@@ -123,11 +139,11 @@ def rank_trees(tree_list, read_counts, alpha=0.001, topn=None, verbose=False, de
         sel = sorted(int(t) for t in ranked_trees["tree"])
         _, post, idx, ent, _ = tab.engine.base_cells(anc[sel], tmask[sel])
         # the reference names the posterior columns after the LAST tree's clone order (arborist_base.py:303)
-        last = [int(c) for c in genotypes[-1]["Child"].values]
+        last = orders[-1]
         frames = []
         order = tab.cell_order(tmask[0])                  # same node set, so the same cluster filter for every tree
         for s, t in enumerate(sel):
-            mine = [int(c) for c in genotypes[t]["Child"].values]
+            mine = orders[t]
             col = [mine.index(c) for c in last]
             f = pd.DataFrame({"cell": tab.cell_ids[order], "tree": t, "clone": np.asarray(mine)[idx[s][order]],
                               "entropy": ent[s][order]})

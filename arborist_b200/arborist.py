@@ -278,20 +278,30 @@ def arborist(
         if logger is not None:
             logger.info(msg)
 
+    import time
+    marks = [("start", time.perf_counter())]         # host wall-clock of the stages, kept in arborist.last_stats
+
+    def mark(name):
+        marks.append((name, time.perf_counter()))
+
     if add_normal:
         log("Appending normal clone to candidate trees...")
         tree_list = add_normal_clone(tree_list)
 
     clone_to_idx, cluster_to_idx, parents, presence, normal_idx = prepare_trees(tree_list)
     K, T = len(clone_to_idx), len(tree_list)
+    mark("trees")
 
     log("Removing SNVs with 0 variant reads across all cells...")
     eng = Engine(device=device)
+    mark("context")
     log("Caching log-likelihoods for presence/absence...")
     log("Initializing the SNV cluster assignment prior...")
     cell_ids, snv_ids = ingest_read_counts(eng, read_counts, snv_clusters, cluster_to_idx, alpha, gamma)
+    mark("ingest")
     cell_to_idx = dict(zip(cell_ids.tolist(), range(len(cell_ids))))
     snv_to_idx = dict(zip(snv_ids.tolist(), range(len(snv_ids))))
+    mark("index_maps")
 
     if verbose:
         log("Starting Arborist...")
@@ -306,7 +316,9 @@ def arborist(
                           presence=None if presence is None else presence[shard],
                           n_clones=K, normal_idx=normal_idx, max_iter=max_iter,
                           tolerance=tolerance, keep_posteriors=keep_posteriors)
+    mark("fit")
     elbo_all, owner = distributed.gather_elbos(elbo, shard, T)
+    mark("gather")
 
     local_of = {int(g): l for l, g in enumerate(shard)}
     eng_ref = eng
@@ -336,7 +348,9 @@ def arborist(
         # the reference dies with UnboundLocalError here (A.py:1124-1130); say why
         raise UnboundLocalError("no candidate tree has a finite ELBO (all NaN/-inf); "
                                 "cannot select best_fit")
-    arborist.last_stats = dict(iters=iters, engine=weakref.ref(eng), shard=shard)
+    mark("treefits")
+    stages = {b[0]: round(1e3 * (b[1] - a[1]), 2) for a, b in zip(marks, marks[1:])}
+    arborist.last_stats = dict(iters=iters, engine=weakref.ref(eng), shard=shard, stages_ms=stages)
     return likelihoods, best_fit, all_tree_fits
 
 

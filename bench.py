@@ -44,9 +44,9 @@ RUN = dict(alpha=0.001, gamma=0.7, max_iter=25, tolerance=1.0)      # CLI defaul
 # in the metric's unit.  See BASELINE.md section 5.
 MEAN_TREE_ITERS = {"config3": 17.84, "config2": 12.8}
 # DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) per tree-sweep of the two sweep kernels, from the
-# one `ncu --set full` capture summarised in profiles/r1h_full_summary.md (config 3 only; per launch the
+# one `ncu --set full` capture summarised in profiles/r1z_full_summary.md (config 3 only; per launch the
 # kernel moves this times the tree-sweeps of the launch).
-NCU_DRAM_BYTES_PER_TREE_SWEEP = {"config3": {"z": 24.73e6, "y": 12.20e6}}
+NCU_DRAM_BYTES_PER_TREE_SWEEP = {"config3": {"z": 24.62e6, "y": 12.16e6}}
 
 
 def parse_args():
@@ -327,7 +327,7 @@ def run_gpu_arm(args):
         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
         "traffic": (NCU_DRAM_BYTES_PER_TREE_SWEEP[cfg.name]["z"] * prof["tree_sweeps_z"] / lz
                     if cfg.name in NCU_DRAM_BYTES_PER_TREE_SWEEP else None),
-        "traffic_source": "ncu --set full, profiles/r1h_full_summary.md: 24.73 MB of DRAM traffic per tree-sweep "
+        "traffic_source": "ncu --set full, profiles/r1z_full_summary.md: 24.62 MB of DRAM traffic per tree-sweep "
                           "x tree-sweeps per launch (bytes per launch, like the algorithmic figure: "
                           "algorithmic_bytes_per_tree_sweep x tree_sweeps_per_launch)",
         "algorithmic_bytes_per_tree_sweep": b_z, "tree_sweeps_per_launch": prof["tree_sweeps_z"] / lz,

@@ -543,6 +543,55 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const __grid_
 }
 
 // ---------------------------------------------------------------------------------------
+// exp for the finishing kernels.  libdevice's fp64 exp rebuilds every polynomial coefficient from two 32-bit
+// immediates in front of each DFMA (UMOV / IMAD.MOV: a third of the q(y) finishing kernel's instructions,
+// profiles/r1z_full_summary.md).  arb_exp is the same algorithm, operation for operation (same reduction constants,
+// same degree-11 polynomial, same exponent insertion and the same two-step scaling below -708), with the
+// coefficients in the constant bank, where DFMA reads them as an operand: identical bits, fewer instructions.
+// ---------------------------------------------------------------------------------------
+#ifndef ARB_OWN_EXP
+#define ARB_OWN_EXP 0
+#endif
+__constant__ unsigned long long c_exp_bits[13] = {
+    0x3ff71547652b82feull,   // log2(e)
+    0x3fe62e42fefa39efull,   // ln2, high part
+    0x3c7abc9e3b39803full,   // ln2, low part
+    0x3e5ade1569ce2bdfull, 0x3e928af3fca213eaull, 0x3ec71dee62401315ull, 0x3efa01997c89eb71ull, 0x3f2a01a014761f65ull,
+    0x3f56c16c1852b7afull, 0x3f81111111122322ull, 0x3fa55555555502a1ull, 0x3fc5555555555511ull, 0x3fe000000000000bull};
+
+__device__ __forceinline__ double arb_exp(double x)
+{
+#if ARB_OWN_EXP
+    const double *c = reinterpret_cast<const double *>(c_exp_bits);
+    const double MAGIC = 6755399441055744.0;
+    double t = fma(x, c[0], MAGIC);
+    const int k = __double2loint(t);
+    const double kd = t - MAGIC;
+    double r = fma(kd, -c[1], x);
+    r = fma(kd, -c[2], r);
+    double p = fma(r, c[3], c[4]);
+#pragma unroll
+    for (int i = 5; i < 13; ++i) p = fma(r, p, c[i]);
+    p = fma(r, p, 1.0);
+    p = fma(r, p, 1.0);
+    double res = __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));
+    const int hi = __double2hiint(x) & 0x7fffffff;
+    if (hi >= 0x40862000) {                                   // |x| >= 708 (or NaN)
+        res = x >= 0.0 ? x + __longlong_as_double(0x7ff0000000000000ll) : 0.0;
+        if (hi < 0x40874800) {                                // |x| < 745: scale in two steps (denormal results)
+            const int k1 = (k + (int)((unsigned)k >> 31)) >> 1;
+            const double a = __hiloint2double(__double2hiint(p) + (k1 << 20), __double2loint(p));
+            const double b = __hiloint2double(((k - k1) << 20) + 0x3ff00000, 0);
+            res = a * b;
+        }
+    }
+    return res;
+#else
+    return exp(x);
+#endif
+}
+
+// ---------------------------------------------------------------------------------------
 // finishing kernel: combine the panel partials, softmax, ELBO pieces, next gathered operand
 // ---------------------------------------------------------------------------------------
 struct FinishArgs {
@@ -595,7 +644,7 @@ __device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int po
     }
     double q[4];
 #pragma unroll
-    for (int c = 0; c < 4; ++c) q[c] = v[c] ? exp(logit[c] - mx) : 0.0;
+    for (int c = 0; c < 4; ++c) q[c] = v[c] ? arb_exp(logit[c] - mx) : 0.0;
     double s = (q[0] + q[1]) + (q[2] + q[3]);
     if (POW2) {
 #pragma unroll

@@ -213,7 +213,7 @@ def ingest_read_counts(eng, read_counts, snv_clusters, cluster_to_idx, alpha, ga
             try:
                 cell_uniques, snv_uniques, _ = eng.ingest_csv(path, alpha)
             except ArboristError as e:
-                if e.status != -3:                      # ARB_ERR_UNSUPPORTED: not a plain integer table
+                if e.status != -5:                      # only ARB_ERR_DECLINED (not a plain integer table) falls back
                     raise
                 read_counts = read_read_counts(path)
         else:

@@ -71,7 +71,10 @@ struct DevBuf {
     template <class T> T *as() const { return reinterpret_cast<T *>(p); }
 };
 
-#define ARB_MAX_GROUPS 4
+// The fit enqueues rounds ahead of the device: the Control block of every round is copied to a pinned ring the
+// host reads ARB_LOOKAHEAD rounds later (never waiting on the round it is about to enqueue).
+#define ARB_RING 8
+#define ARB_LOOKAHEAD 3
 #ifndef ARB_SWEEP_WARPS
 #define ARB_SWEEP_WARPS 16    // warps per sweep CTA; the layouts are dealt out to this many warps
 #endif
@@ -109,7 +112,9 @@ struct FitStats {
     double device_ms = 0, tree_iterations = 0, sweep_ms = 0;
     // per-kernel profile of the last fit (CUDA events on the launching stream)
     double sweep_z_ms = 0, sweep_y_ms = 0, finish_ms = 0, finish_z_ms = 0, finish_y_ms = 0;
-    double tree_sweeps_z = 0, tree_sweeps_y = 0, launches_z = 0, launches_y = 0, rounds = 0, groups = 0;
+    double tree_sweeps_z = 0, tree_sweeps_y = 0, launches_z = 0, launches_y = 0, rounds = 0;
+    double host_waits = 0, idle_rounds = 0, refit_batches = 0;   // blocking waits of the round pipeline, rounds enqueued
+                                                                   // after the last tree finished, arb_get_fits batches
 };
 
 struct arb_ctx {
@@ -141,16 +146,14 @@ struct arb_ctx {
 
     // ---- layouts (index 0: KP 8, 1: KP 16, 2: KP 32) ----------------------------------
     PanelLayout layout[3];
-    int64_t opt_slots = 0, opt_panel_kb = 0, opt_threads = 0, opt_no_fold = 0, opt_groups = 0, opt_w32 = 0;
+    int64_t opt_slots = 0, opt_panel_kb = 0, opt_threads = 0, opt_no_fold = 0, opt_w32 = 0, opt_split = 0,
+            opt_lookahead = 0;
 
     // ---- fit workspace -----------------------------------------------------------------
-    // The slots are split into `ws_groups` stream groups of `ws_sg` slots; every group runs its own
-    // rounds on its own stream, so one group's finishing kernels (HBM-bound) overlap another group's
-    // sweeps (shared-memory-pipe-bound).
-    int ws_kp = 0, ws_slots = 0, ws_k = 0, ws_groups = 0, ws_sg = 0;
-    cudaStream_t gstream[ARB_MAX_GROUPS] = {};
-    cudaEvent_t gevent[ARB_MAX_GROUPS][8] = {};   // 6 profile events, control-ready, done
-    void *h_ctl = nullptr;                        // pinned host copies of the groups' Control blocks
+    int ws_kp = 0, ws_slots = 0, ws_k = 0;
+    cudaEvent_t rev[ARB_RING][7] = {};            // per round in flight: 6 profile events + "Control snapshot arrived"
+    cudaEvent_t fit_ev[2] = {};                   // start / end of a fit
+    void *h_ctl = nullptr;                        // pinned: ARB_RING Control snapshots + the block uploaded at the start
     DevBuf xs, xr, qz_cur, qy_cur, part_z, part_g, part_y, red, slot_state, lists, masks;
     // results of the last fit
     int32_t fit_trees = 0, fit_k = 0, fit_max_iter = 0, fit_mode = 0;

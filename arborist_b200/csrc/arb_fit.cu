@@ -33,38 +33,10 @@
 int arb_sweep_table_entries(const arb_ctx *ctx);
 int arb_check_table_range(arb_ctx *ctx);
 
-// Layout of a partial row.  Default (0): every lane's chunk is contiguous (q(y): 32 bytes = one 256-bit store /
-// load, q(z): 64 bytes = two), which is what the finishing kernels read best.  Bits 0 / 1 switch the q(y) / q(z)
-// partial rows to 16-byte pieces [k][h] (one store instruction then writes 64 contiguous bytes per row); measured on
-// B200 at config 3 (scripts/ab_layout.sh, exp_y256.sh): with 128-bit accesses pieces helped q(y) (-9 % on its
-// finishing kernel) and hurt q(z) (+32 %); with 256-bit accesses the contiguous chunks win for both.
-#ifndef ARB_PIECE_LAYOUT
-#define ARB_PIECE_LAYOUT 0
-#endif
-#define ARB_PIECES(with_g) ((ARB_PIECE_LAYOUT >> ((with_g) ? 1 : 0)) & 1)
-// partial rows are written once and read once by the finishing kernel: streaming stores
-#define ARB_ST(p, v) __stcs((p), (v))
-// The stream is loaded three quads ahead of its use.  Pulling the line into L1 further ahead
-// (prefetch.global.L1, ARB_PF_QUADS = 6 / 12 / 24 quads) was measured 1 % SLOWER at config 3: the
-// long-scoreboard stalls on the stream words are covered by the other warps, and the prefetches cost
-// L1 cycles on the pipe that bounds the kernel.  Off by default.
-#ifndef ARB_PF_QUADS
-#define ARB_PF_QUADS 0
-#endif
-#if ARB_PF_QUADS > 0
-#define ARB_PREFETCH(sp) asm volatile("prefetch.global.L1 [%0];" ::"l"((sp) + ARB_PF_QUADS * TW));
-#else
-#define ARB_PREFETCH(sp)
-#endif
-#ifndef ARB_LD256
-#define ARB_LD256 1
-#endif
-#ifndef ARB_ST256
-#define ARB_ST256 1
-#endif
-#ifndef ARB_TABC
-#define ARB_TABC 1
-#endif
+// Partial rows are written once by a sweep and read once by a finishing kernel: streaming 256-bit stores
+// (st.global.cs.v4.f64) and loads.  Every lane's chunk is contiguous in the row.  Variants that were measured and
+// lost (16-byte "pieces", an L1 prefetch of the stream, 128-bit accesses, the (d, w) table in shared memory, a
+// private exp, stream groups) are recorded in profiles/r1i_summary.md and scripts/README.md and no longer built.
 #define SWEEP_THREADS (ARB_SWEEP_WARPS * 32)
 #define FIN_THREADS 256
 #define FIN_ROWS 256          // rows of q per finishing CTA (fixed: the ELBO reduction order depends on it)
@@ -82,16 +54,19 @@ struct SlotState {
     int32_t cur, bestb;
 };
 
-// One Control per stream group: the group owns slots slot0 .. slot0+n_slots-1 and fits trees
-// next_tree, next_tree + tree_step, ... (static interleaving of the tree set over the groups).
+// The fit's control block, on the device.  k_control rewrites the counts after every round; the sweeps, seeding
+// and finishing kernels read them from here, so their grids can be sized by an upper bound the host knows and
+// no launch waits for a read-back.  A copy of the block goes to a pinned ring after every round (fit_core).
 struct Control {
-    int32_t next_tree, n_trees, tree_step, max_iter;
-    int32_t slot0, n_slots, n_done, keep;
+    int32_t next_tree, n_trees, n_slots, max_iter;
+    int32_t n_done, keep, mode, round;
     double tol, sum_la;
-    int32_t n_y, n_z, n_init, mode;
+    int32_t n_y, n_z, n_init, pad0;       // trees in this round's q(y) list / q(z) list / first-pass list
+    int32_t n_vy, n_vz, chunks_y, chunks_z;   // virtual slots of the two sweeps, 4-column chunks per tree
     int32_t nbz, nby, nbmax, pad1;
-    int32_t pad2[16];              // 128 bytes
+    int32_t pad2[8];               // 128 bytes
 };
+static_assert(sizeof(Control) == 128, "Control is copied as one 128-byte block");
 
 static inline int grid_for(int64_t n, int block) { return (int)std::max<int64_t>(1, (n + block - 1) / block); }
 
@@ -224,8 +199,9 @@ __global__ void __launch_bounds__(SEED_THREADS)
 k_seed_s(const double *__restrict__ q_src, int64_t src_slot_stride, const int32_t *__restrict__ list,
          const int32_t *__restrict__ pos_z, const SlotState *__restrict__ st, const uint32_t *__restrict__ masks,
          int32_t m, int32_t K, double *__restrict__ xs, double *__restrict__ qy_cur, int copy_q, int np, int pr,
-         int64_t plane_slots)
+         int64_t plane_slots, const Control *__restrict__ ctl)
 {
+    if (ctl && (int)blockIdx.y >= ctl->n_init) return;       // grid.y is an upper bound
     const RowLanes<GL> rl;
     const int C = K - 1, h = rl.h;
     const int slot = list[blockIdx.y], pos = pos_z[slot];
@@ -257,8 +233,9 @@ template <int GL>
 __global__ void __launch_bounds__(SEED_THREADS)
 k_seed_r(const double *__restrict__ qz_cur, const int32_t *__restrict__ list, const SlotState *__restrict__ st,
          const uint32_t *__restrict__ masks, int32_t n, int32_t K, double *__restrict__ xr, int np, int pr,
-         int64_t plane_slots)
+         int64_t plane_slots, const Control *__restrict__ ctl)
 {
+    if (ctl && (int)blockIdx.y >= ctl->n_y) return;          // grid.y is an upper bound
     const RowLanes<GL> rl;
     const int C = K - 1, h = rl.h;
     const int slot = list[blockIdx.y], pos = blockIdx.y;
@@ -301,7 +278,11 @@ struct SweepArgs {
     const int32_t *rows;       // [.. * TW] row of every segment of every tile, -1 = none
     const void *stream;        // [quad][TW] of uint4 (32-bit words) or uint2 (16-bit words, W16)
     int32_t n_rows, panel_rows, n_panels, tiles_per_warp;
-    int32_t n_vslots;          // virtual slots in this launch (grid = n_vslots * n_panels)
+    int32_t n_vslots;          // virtual slots in this launch when n_vslots_dev is null
+    const int32_t *n_vslots_dev;   // else read here (written by k_control): the host never learns the count, the
+                               // grid is an upper bound and the CTAs past n_vslots * n_panels * split leave at once
+    int32_t split;             // a (virtual slot, panel) is cut into `split` CTAs, each taking a share of every
+                               // warp's run of tiles: fills the machine when few trees are active
     const double2 *dw;         // per pair code: (d, w)
     int32_t n_pairs, tab_n, renorm_quads;   // not FOLD: renormalise every this many quads, 0 = after every factor
     double *out_m;             // [vslot][panel][row][KP] the segment's product (FOLD) or its mantissa; the q(z)
@@ -331,12 +312,19 @@ __device__ __forceinline__ void sweep_step(const char *xa_base, const char *xb_b
     }
 }
 
-// One CTA = (tree slot, panel); one warp = a run of tiles of that panel (see "panel layouts" in
-// arb_ingest.cu).  GL = KP/4 lanes share a segment, lane h of the group owns clones 4h..4h+3.  The
-// two 16-byte halves a lane reads are swizzled on bit 2 of the lane id so that the eight lanes of
-// a quarter-warp cover all 32 banks.  Every lane of a group loads the same uint4 of four stream
-// words (a warp reads TW*16 contiguous bytes per quad), three quads ahead of the one in use; there
-// are no shuffles, no predicates and no per-segment pointers in the loop.
+// One CTA = (tree slot, panel, share); one warp = a run of tiles of that panel (see "panel layouts" in
+// arb_ingest.cu).  GL = KP/4 lanes share a segment and each lane owns two 16-byte pieces (two columns each) of
+// the gathered 128-byte row.  Which two differs between the sweeps, because the partial rows differ:
+//   q(y) sweep (8 bytes per column):  lane h owns pieces 2h, 2h+1 (columns 4h..4h+3): its four products are
+//       32 contiguous bytes, one 256-bit store, and a lane group writes one full 128-byte line;
+//   q(z) sweep ({product, likelihood} = 16 bytes per column, 256-byte rows): lane h owns pieces h and h+4
+//       (columns 2h, 2h+1, 8+2h, 8+2h+1), so that each of its two 256-bit stores lands, together with the other
+//       three lanes of the group, on ONE full line (with pieces 2h, 2h+1 every store instruction touched both
+//       lines of every row: 16 tag requests per instruction instead of 8).
+// The two loads of a lane are swizzled on bit 2 of the lane id so that the eight lanes of a quarter-warp cover
+// all 32 banks.  Every lane of a group loads the same uint2/uint4 of four stream words (a warp reads TW*8/16
+// contiguous bytes per quad), three quads ahead of the one in use; there are no shuffles, no predicates and no
+// per-segment pointers in the loop.
 template <bool W16> struct StreamQuad { typedef uint4 type; };
 template <> struct StreamQuad<true> { typedef uint2 type; };
 // the four stream words of a quad as {byte offset of the gathered row | code << 18}
@@ -358,8 +346,12 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const __grid_
     double2 *tab = reinterpret_cast<double2 *>(smem_raw + (size_t)(a.panel_rows + 1) * KP * 8);
     uint64_t *mbar = reinterpret_cast<uint64_t *>(tab + a.tab_n);
 
-    const int panel = blockIdx.x / a.n_vslots;
-    const int slot = blockIdx.x % a.n_vslots;            // virtual slot: 16 packed columns of the active trees
+    const int n_vslots = a.n_vslots_dev ? __ldg(a.n_vslots_dev) : a.n_vslots;
+    const int per_share = n_vslots * a.n_panels;
+    if ((int)blockIdx.x >= per_share * a.split) return;          // the grid is an upper bound
+    const int share = blockIdx.x / per_share, rest = blockIdx.x - share * per_share;
+    const int panel = rest / n_vslots;
+    const int slot = rest % n_vslots;                    // virtual slot: 16 packed columns of the active trees
     const int row0 = panel * a.panel_rows;
     const int cnt_rows = min(a.panel_rows, a.n_gather - row0);
     const uint32_t bytes = (uint32_t)cnt_rows * KP * 8u;
@@ -390,18 +382,22 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const __grid_
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int h = lane % GL, grp = lane / GL;
     const int swz = (lane >> 2) & 1;
-    const int off_a = 4 * h + 2 * swz, off_b = 4 * h + 2 * (1 - swz);       // columns (doubles)
+    // columns (doubles) of the lane's two pieces: the one it loads first and the one it loads second
+    const int off_a = WITH_G ? 2 * (h + GL * swz) : 4 * h + 2 * swz;
+    const int off_b = WITH_G ? 2 * (h + GL * (1 - swz)) : 4 * h + 2 * (1 - swz);
     const char *xa_base = reinterpret_cast<const char *>(xs + off_a);
     const char *xb_base = reinterpret_cast<const char *>(xs + off_b);
+    // this CTA's share of every warp's run of tiles
     const int U = a.tiles_per_warp;
-    const int64_t x0 = ((int64_t)panel * ARB_SWEEP_WARPS + warp) * U;
+    const int u0 = (int)((int64_t)share * U / a.split), u1 = (int)((int64_t)(share + 1) * U / a.split);
+    const int64_t x0 = ((int64_t)panel * ARB_SWEEP_WARPS + warp) * U + u0;
     const int4 *__restrict__ desc = a.desc + x0;
     const int32_t *__restrict__ rows = a.rows + x0 * TW + grp;
     constexpr int RW = WITH_G ? 2 : 1;             // doubles per column of a partial row
     const int64_t out0 = ((int64_t)slot * a.n_panels + panel) * a.n_rows;
     const uint32_t out_stride = (uint32_t)KP * 8u * RW;
-    constexpr bool PIECES = ARB_PIECES(WITH_G);
-    char *out_a = reinterpret_cast<char *>(a.out_m) + (PIECES ? out0 * KP * 8 * RW + h * 16 : (out0 * KP + off_a) * 8 * RW);
+    char *out_a = reinterpret_cast<char *>(a.out_m) + (out0 * KP + off_a) * 8 * RW;
+    char *out_b = reinterpret_cast<char *>(a.out_m) + (out0 * KP + off_b) * 8 * RW;
     int32_t *oute_a = FOLD ? nullptr : a.out_e + out0 * KP + off_a;
     const bool each = a.renorm_quads == 0;
 
@@ -418,7 +414,7 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const __grid_
                  "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n\t"
                  "@p bra DONE_PANEL;\n\tbra WAIT_PANEL;\n\tDONE_PANEL:\n\t}" ::"r"(bar) : "memory");
 
-    for (int u = 0; u < U; ++u) {
+    for (int u = u0; u < u1; ++u) {
         const int4 dc = dn;
         const int row = rown;
         // next tile's descriptor (the arrays carry one spare slot at the end)
@@ -435,7 +431,6 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const __grid_
         uint32_t w[4];                                                                          \
         quad_words(WC, w);                                                                      \
         WC = __ldg(sp);                                                                         \
-        ARB_PREFETCH(sp)                                                                        \
         sp += TW;                                                                               \
         sweep_step<WITH_G>(xa_base, xb_base, w[0], dw0.x, dw0.y, p, g);                         \
         if (!FOLD && each) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);                      \
@@ -454,11 +449,10 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const __grid_
         uint32_t ww[4];                                                                         \
         quad_words(WC, ww);                                                                     \
         WC = __ldg(sp);                                                                         \
-        ARB_PREFETCH(sp)                                                                        \
         sp += TW;                                                                               \
         _Pragma("unroll") for (int s = 0; s < 4; ++s) {                                         \
             const uint32_t code = ww[s] >> 18, off = ww[s] & 0x3ffffu;                          \
-            const double2 dw = ARB_TABC && W16 ? a.tabc[code]                                   \
+            const double2 dw = W16 ? a.tabc[code]                                               \
                                : (FOLD || code < (uint32_t)a.tab_n) ? tab[code] : __ldg(a.dw + code); \
             sweep_step<WITH_G>(xa_base, xb_base, off, dw.x, dw.y, p, g);                        \
             if (!FOLD && each) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);                  \
@@ -477,7 +471,7 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const __grid_
             if (q == 1) { ARB_QUAD_A(w0) ARB_ROT1 }
             else if (q == 2) { ARB_QUAD_A(w0) ARB_QUAD_A(w1) ARB_ROT2 }
         }
-        // ---- G region: any pair; (d, w) from the table in shared memory ---------------------------
+        // ---- G region: any pair; (d, w) from the table ---------------------------------------------
         {
             int q = dc.z - dc.y;
             for (; q >= 3; q -= 3) { ARB_QUAD_G(w0) ARB_QUAD_G(w1) ARB_QUAD_G(w2) }
@@ -490,48 +484,15 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const __grid_
 #undef ARB_ROT2
         if (!FOLD) for (int c = 0; c < 4; ++c) renorm(p[c], e[c]);
         if (row >= 0) {
-            if (PIECES) {
-            // partial row stored as 16-byte pieces [k][h] (k = piece of the lane's chunk, h = lane of the group):
-            // one store instruction writes 64 contiguous bytes per row.  q(z): piece k = {m, g} of column 4h+k
-            // (4 pieces); q(y): piece k = m of columns 4h+2k, 4h+2k+1 (2 pieces).  This lane holds columns
-            // 4h+2swz.. in p[0..1] and 4h+2(1-swz).. in p[2..3].
-            char *pr = out_a + (int64_t)row * out_stride;
+            // partial row: q(z) {m, g} per column, q(y) m; streaming 256-bit stores (written once, read once)
+            const int64_t ro = (int64_t)row * out_stride;
             if (WITH_G) {
-                double2 *lo = reinterpret_cast<double2 *>(pr + swz * 128), *hi = reinterpret_cast<double2 *>(pr + (1 - swz) * 128);
-                ARB_ST(lo + 0, make_double2(p[0], g[0]));
-                ARB_ST(lo + 4, make_double2(p[1], g[1]));
-                ARB_ST(hi + 0, make_double2(p[2], g[2]));
-                ARB_ST(hi + 4, make_double2(p[3], g[3]));
+                asm volatile("st.global.cs.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(out_a + ro), "d"(p[0]), "d"(g[0]), "d"(p[1]), "d"(g[1]) : "memory");
+                asm volatile("st.global.cs.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(out_b + ro), "d"(p[2]), "d"(g[2]), "d"(p[3]), "d"(g[3]) : "memory");
             } else {
-                ARB_ST(reinterpret_cast<double2 *>(pr + swz * 64), make_double2(p[0], p[1]));
-                ARB_ST(reinterpret_cast<double2 *>(pr + (1 - swz) * 64), make_double2(p[2], p[3]));
-            }
-            } else {
-            // partial row: q(z) {m, g} per column, q(y) m; this lane's pair (off_a, off_a+1), the other pair
-            // sits at the same address with bit (16 * RW) flipped
-            char *pa = out_a + (int64_t)row * out_stride;
-            char *pb = reinterpret_cast<char *>(reinterpret_cast<uintptr_t>(pa) ^ (uintptr_t)(16 * RW));
-            if (WITH_G) {
-#if ARB_ST256
-                // two 256-bit streaming stores (sm_100: st.global.v4.f64) instead of four 128-bit ones
-                asm volatile("st.global.cs.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(pa), "d"(p[0]), "d"(g[0]), "d"(p[1]), "d"(g[1]) : "memory");
-                asm volatile("st.global.cs.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(pb), "d"(p[2]), "d"(g[2]), "d"(p[3]), "d"(g[3]) : "memory");
-#else
-                ARB_ST(reinterpret_cast<double2 *>(pa) + 0, make_double2(p[0], g[0]));
-                ARB_ST(reinterpret_cast<double2 *>(pa) + 1, make_double2(p[1], g[1]));
-                ARB_ST(reinterpret_cast<double2 *>(pb) + 0, make_double2(p[2], g[2]));
-                ARB_ST(reinterpret_cast<double2 *>(pb) + 1, make_double2(p[3], g[3]));
-#endif
-            } else {
-#if ARB_ST256
-                // the lane's chunk (columns 4h..4h+3, 32 bytes) in one 256-bit streaming store
+                // the lane's chunk (columns 4h..4h+3, 32 bytes) in one store
                 const double c0 = swz ? p[2] : p[0], c1 = swz ? p[3] : p[1], c2 = swz ? p[0] : p[2], c3 = swz ? p[1] : p[3];
-                asm volatile("st.global.cs.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(pa - 16 * swz), "d"(c0), "d"(c1), "d"(c2), "d"(c3) : "memory");
-#else
-                ARB_ST(reinterpret_cast<double2 *>(pa) + 0, make_double2(p[0], p[1]));
-                ARB_ST(reinterpret_cast<double2 *>(pb) + 0, make_double2(p[2], p[3]));
-#endif
-            }
+                asm volatile("st.global.cs.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(out_a + ro - 16 * swz), "d"(c0), "d"(c1), "d"(c2), "d"(c3) : "memory");
             }
             if (!FOLD) {
                 int32_t *ea = oute_a + (int64_t)row * KP;
@@ -540,55 +501,6 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const __grid_
             }
         }
     }
-}
-
-// ---------------------------------------------------------------------------------------
-// exp for the finishing kernels.  libdevice's fp64 exp rebuilds every polynomial coefficient from two 32-bit
-// immediates in front of each DFMA (UMOV / IMAD.MOV: a third of the q(y) finishing kernel's instructions,
-// profiles/r1z_full_summary.md).  arb_exp is the same algorithm, operation for operation (same reduction constants,
-// same degree-11 polynomial, same exponent insertion and the same two-step scaling below -708), with the
-// coefficients in the constant bank, where DFMA reads them as an operand: identical bits, fewer instructions.
-// ---------------------------------------------------------------------------------------
-#ifndef ARB_OWN_EXP
-#define ARB_OWN_EXP 0
-#endif
-__constant__ unsigned long long c_exp_bits[13] = {
-    0x3ff71547652b82feull,   // log2(e)
-    0x3fe62e42fefa39efull,   // ln2, high part
-    0x3c7abc9e3b39803full,   // ln2, low part
-    0x3e5ade1569ce2bdfull, 0x3e928af3fca213eaull, 0x3ec71dee62401315ull, 0x3efa01997c89eb71ull, 0x3f2a01a014761f65ull,
-    0x3f56c16c1852b7afull, 0x3f81111111122322ull, 0x3fa55555555502a1ull, 0x3fc5555555555511ull, 0x3fe000000000000bull};
-
-__device__ __forceinline__ double arb_exp(double x)
-{
-#if ARB_OWN_EXP
-    const double *c = reinterpret_cast<const double *>(c_exp_bits);
-    const double MAGIC = 6755399441055744.0;
-    double t = fma(x, c[0], MAGIC);
-    const int k = __double2loint(t);
-    const double kd = t - MAGIC;
-    double r = fma(kd, -c[1], x);
-    r = fma(kd, -c[2], r);
-    double p = fma(r, c[3], c[4]);
-#pragma unroll
-    for (int i = 5; i < 13; ++i) p = fma(r, p, c[i]);
-    p = fma(r, p, 1.0);
-    p = fma(r, p, 1.0);
-    double res = __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));
-    const int hi = __double2hiint(x) & 0x7fffffff;
-    if (hi >= 0x40862000) {                                   // |x| >= 708 (or NaN)
-        res = x >= 0.0 ? x + __longlong_as_double(0x7ff0000000000000ll) : 0.0;
-        if (hi < 0x40874800) {                                // |x| < 745: scale in two steps (denormal results)
-            const int k1 = (k + (int)((unsigned)k >> 31)) >> 1;
-            const double a = __hiloint2double(__double2hiint(p) + (k1 << 20), __double2loint(p));
-            const double b = __hiloint2double(((k - k1) << 20) + 0x3ff00000, 0);
-            res = a * b;
-        }
-    }
-    return res;
-#else
-    return exp(x);
-#endif
 }
 
 // ---------------------------------------------------------------------------------------
@@ -610,6 +522,7 @@ struct FinishArgs {
     double *red;                    // [slot][3][nbmax]: lik, entropy, kl partial sums per CTA
     int32_t nbmax;
     int32_t given_q;                // elbo_terms hook: take q from q_cur instead of the softmax
+    const Control *ctl;             // trees in the list are counted here (grid.y is an upper bound); null: grid.y
 };
 
 // The end of a row: A.py:245-250 softmax + A.py:268-273 entropy + likelihood term (q(z)),
@@ -644,7 +557,7 @@ __device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int po
     }
     double q[4];
 #pragma unroll
-    for (int c = 0; c < 4; ++c) q[c] = v[c] ? arb_exp(logit[c] - mx) : 0.0;
+    for (int c = 0; c < 4; ++c) q[c] = v[c] ? exp(logit[c] - mx) : 0.0;
     double s = (q[0] + q[1]) + (q[2] + q[3]);
     if (POW2) {
 #pragma unroll
@@ -719,6 +632,7 @@ template <int GL, bool IS_Z, bool HARD>
 __global__ void __launch_bounds__(FIN_THREADS, 4) k_finish(const FinishArgs a)
 {
     __shared__ double sh[FIN_WARPS];
+    if (a.ctl && (int)blockIdx.y >= (IS_Z ? a.ctl->n_z : a.ctl->n_y)) return;
     constexpr int TW = 32 / GL, RW = IS_Z ? 2 : 1;
     const RowLanes<GL> rl;
     const int warp = threadIdx.x >> 5;
@@ -747,11 +661,7 @@ __global__ void __launch_bounds__(FIN_THREADS, 4) k_finish(const FinishArgs a)
             // this lane's chunk of the packed partial rows: [vslot][panel][row][16 columns]
             const int q = pos * chunks + h;
             const int64_t o0 = ((int64_t)(q >> 2) * np * a.n_rows + row) * ARB_VW + (q & 3) * 4;
-            // pieces [k][h]: 4 double2 between a chunk's pieces; else the chunk is contiguous
-            constexpr bool PIECES = ARB_PIECES(IS_Z);
-            constexpr int PS = PIECES ? 4 : 1;
-            const double2 *src = PIECES ? reinterpret_cast<const double2 *>(a.part_m + (o0 - (q & 3) * 4) * RW) + (q & 3)
-                                        : reinterpret_cast<const double2 *>(a.part_m + o0 * RW);
+            const double2 *src = reinterpret_cast<const double2 *>(a.part_m + o0 * RW);
             const int64_t pstep = panel_stride * RW / 2;            // in double2
             // split every partial (positive, normal: 2^+-1000 at most) into mantissa and exponent with integer
             // ops; the mantissa product stays below 2^np, far inside the double range
@@ -771,17 +681,10 @@ __global__ void __launch_bounds__(FIN_THREADS, 4) k_finish(const FinishArgs a)
                 double2 cur[4], nxt[4];
                 // a chunk is 64 contiguous bytes: two 256-bit streaming loads (sm_100: ld.global.v4.f64)
                 auto load4 = [&](double2 (&d)[4], const double2 *from) {
-#if ARB_LD256
-                    if (!PIECES) {
-                        asm volatile("ld.global.cs.v4.f64 {%0, %1, %2, %3}, [%4];"
-                                     : "=d"(d[0].x), "=d"(d[0].y), "=d"(d[1].x), "=d"(d[1].y) : "l"(from));
-                        asm volatile("ld.global.cs.v4.f64 {%0, %1, %2, %3}, [%4];"
-                                     : "=d"(d[2].x), "=d"(d[2].y), "=d"(d[3].x), "=d"(d[3].y) : "l"(from + 2));
-                        return;
-                    }
-#endif
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) d[k] = __ldcs(from + k * PS);
+                    asm volatile("ld.global.cs.v4.f64 {%0, %1, %2, %3}, [%4];"
+                                 : "=d"(d[0].x), "=d"(d[0].y), "=d"(d[1].x), "=d"(d[1].y) : "l"(from));
+                    asm volatile("ld.global.cs.v4.f64 {%0, %1, %2, %3}, [%4];"
+                                 : "=d"(d[2].x), "=d"(d[2].y), "=d"(d[3].x), "=d"(d[3].y) : "l"(from + 2));
                 };
                 load4(cur, src);
 #pragma unroll 2
@@ -799,16 +702,8 @@ __global__ void __launch_bounds__(FIN_THREADS, 4) k_finish(const FinishArgs a)
 #pragma unroll 2
                 for (int pn = 0; pn < np; ++pn) {
                     double2 v0, v1;
-#if ARB_LD256
-                    if (!PIECES)
-                        asm volatile("ld.global.cs.v4.f64 {%0, %1, %2, %3}, [%4];"
-                                     : "=d"(v0.x), "=d"(v0.y), "=d"(v1.x), "=d"(v1.y) : "l"(src));
-                    else
-#endif
-                    {
-                        v0 = __ldcs(src);
-                        v1 = __ldcs(src + PS);
-                    }
+                    asm volatile("ld.global.cs.v4.f64 {%0, %1, %2, %3}, [%4];"
+                                 : "=d"(v0.x), "=d"(v0.y), "=d"(v1.x), "=d"(v1.y) : "l"(src));
                     const double m[4] = {v0.x, v0.y, v1.x, v1.y};
                     src += pstep;
                     fold_in(m, pn);
@@ -858,10 +753,9 @@ __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict_
                           int32_t *list_z, int32_t *list_init, int32_t *pos_z, int32_t *snap_tree, double *elbo_out,
                           int32_t *iters_out, double *trace, int first_call)
 {
-    // st, red, pos_z, snap_tree are indexed by global slot; the three lists belong to this group
-    const int s0 = ctl->slot0, s1 = s0 + ctl->n_slots, nbmax = ctl->nbmax;
+    const int s1 = ctl->n_slots, nbmax = ctl->nbmax;
     if (!first_call) {
-        for (int s = s0 + threadIdx.x; s < s1; s += blockDim.x) {
+        for (int s = threadIdx.x; s < s1; s += blockDim.x) {
             SlotState z = st[s];
             int snap = -1;
             if (z.phase != PH_EMPTY) {
@@ -910,11 +804,10 @@ __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict_
     __syncthreads();
     if (threadIdx.x == 0) {
         int ny = 0, nz = 0, ni = 0, next = ctl->next_tree;
-        for (int s = s0; s < s1; ++s) {
+        for (int s = 0; s < s1; ++s) {
             SlotState z = st[s];
             if (z.phase == PH_EMPTY && next < ctl->n_trees) {
-                z.tree = next;
-                next += ctl->tree_step;
+                z.tree = next++;
                 z.phase = PH_INIT;
                 z.iter = 0;
                 z.converged = 0;
@@ -935,15 +828,18 @@ __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict_
         ctl->n_y = ny;
         ctl->n_z = nz;
         ctl->n_init = ni;
+        ctl->n_vy = (ny * ctl->chunks_y + 3) >> 2;
+        ctl->n_vz = (nz * ctl->chunks_z + 3) >> 2;
+        ctl->round += 1;
     }
 }
 
 // A.py:816: the posteriors of a finished tree's best iterate leave the slot (snap = 2 * tree + plane)
 __global__ void k_snapshot(const int32_t *__restrict__ snap_tree, const double *__restrict__ qz_cur,
                            const double *__restrict__ qy_cur, int64_t nz, int64_t ny, double *__restrict__ best_qz,
-                           double *__restrict__ best_qy, int slot0, int64_t plane_slots)
+                           double *__restrict__ best_qy, int64_t plane_slots)
 {
-    const int slot = slot0 + blockIdx.y, snap = snap_tree[slot];
+    const int slot = blockIdx.y, snap = snap_tree[slot];
     if (snap < 0) return;
     const int tree = snap >> 1, b = snap & 1;
     const double *sz = qz_cur + (b * plane_slots + slot) * nz, *sy = qy_cur + (b * plane_slots + slot) * ny;
@@ -1033,7 +929,7 @@ static int configure_kernels(const arb_ctx *ctx, const PanelLayout &L)
 }
 
 struct Workspace {
-    int kp, K, n_slots, groups, sg, nbz, nby, nbmax;
+    int kp, K, n_slots, nbz, nby, nbmax;
     int64_t per_slot_bytes;
 };
 
@@ -1047,17 +943,6 @@ static int64_t per_slot_bytes(const arb_ctx *ctx, const PanelLayout &L, int K)
     const int64_t mg = (int64_t)L.np_z * L.prz, ng = (int64_t)L.np_y * L.pry;      // padded gathered rows
     return (mg * kcz + ng * kcy + 2 * (n * K + m * C)) * 8 + (int64_t)L.np_z * n * kcz * (16 + ez) +
            (int64_t)L.np_y * m * kcy * (8 + ey) + 3 * nb * 8 + 64;
-}
-
-// stream groups for a fit with `slots` trees in flight: enough trees per group to fill the machine
-static int groups_for(const arb_ctx *ctx, int slots)
-{
-    // default: one group.  More groups let one group's finishing kernels run under another group's sweeps,
-    // but both kinds of kernel are limited by the same L1/shared-memory pipe, so on B200 the overlap
-    // measured 2.5 % slower at config 3 (profiles/r1i_summary.md); the option is kept for other shapes.
-    int g = ctx->opt_groups > 0 ? (int)ctx->opt_groups : 1;
-    while (g > 1 && slots / g < 1) --g;
-    return std::max(1, std::min(g, ARB_MAX_GROUPS));
 }
 
 static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve_bytes, Workspace &ws)
@@ -1074,30 +959,25 @@ static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve
     ws.per_slot_bytes = per_slot_bytes(ctx, L, K);
     int n_slots = want_slots;
     if (ctx->opt_slots > 0) n_slots = (int)std::min<int64_t>(n_slots, ctx->opt_slots);
-    int G = groups_for(ctx, n_slots);
-    int sg = (n_slots + G - 1) / G;
-    if (!(ctx->ws_kp == kp && ctx->ws_k == K && ctx->ws_groups >= G && ctx->ws_sg >= sg)) {
+    if (!(ctx->ws_kp == kp && ctx->ws_k == K && ctx->ws_slots >= n_slots)) {
         // release first so the free-memory query sees what we can really use
         for (DevBuf *b : {&ctx->xs, &ctx->xr, &ctx->qz_cur, &ctx->qy_cur, &ctx->part_z, &ctx->part_g, &ctx->part_y,
                           &ctx->red, &ctx->slot_state, &ctx->lists})
             b->release();
-        ctx->ws_slots = ctx->ws_groups = ctx->ws_sg = 0;
+        ctx->ws_slots = 0;
+        ctx->ws_kp = 0;
         size_t free_b = 0, total_b = 0;
         ARB_CUDA(cudaMemGetInfo(&free_b, &total_b));
         free_b += arb_pool_bytes(ctx->device);            // parked allocations are ours to reuse
-        // one virtual slot of slack per group for the rounding of the packed buffers
+        // one virtual slot of slack for the rounding of the packed buffers
         const int64_t mg = (int64_t)L.np_z * L.prz, ng = (int64_t)L.np_y * L.pry;
-        const int64_t slack = G * ((mg + ng) * ARB_VW * 8 + ((int64_t)L.np_z * n * 20 + (int64_t)L.np_y * m * 12) * ARB_VW);
+        const int64_t slack = (mg + ng) * ARB_VW * 8 + ((int64_t)L.np_z * n * 20 + (int64_t)L.np_y * m * 12) * ARB_VW;
         const int64_t usable = (int64_t)(free_b * 0.90) - reserve_bytes - slack;
         const int64_t fit = usable / ws.per_slot_bytes;
         ARB_REQUIRE(fit >= 1, ARB_ERR_NOMEM, "not enough device memory for one tree slot (%lld bytes needed, %lld usable)",
                     (long long)ws.per_slot_bytes, (long long)usable);
-        if (fit < n_slots) {
-            n_slots = (int)fit;
-            G = groups_for(ctx, n_slots);
-            sg = n_slots / G;
-        }
-        const int64_t S = (int64_t)G * sg, vz = G * vslots_for(sg, K), vy = G * vslots_for(sg, C);
+        if (fit < n_slots) n_slots = (int)fit;
+        const int64_t S = n_slots, vz = vslots_for(S, K), vy = vslots_for(S, C);
         ARB_TRY(ctx->xs.reserve(vz * mg * ARB_VW * 8));
         ARB_TRY(ctx->xr.reserve(vy * ng * ARB_VW * 8));
         // columns past the last tree of a sweep are never read back, but the sweep multiplies through
@@ -1110,67 +990,57 @@ static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve
         ARB_TRY(ctx->part_z.reserve(vz * L.np_z * n * ARB_VW * (L.fold_z ? 16 : 20) + 64));
         ARB_TRY(ctx->part_y.reserve(vy * L.np_y * m * ARB_VW * (L.fold_y ? 8 : 12) + 64));
         ARB_TRY(ctx->red.reserve(S * 3 * ws.nbmax * 8));
-        ARB_TRY(ctx->slot_state.reserve(S * sizeof(SlotState) + ARB_MAX_GROUPS * sizeof(Control) + 64));
+        ARB_TRY(ctx->slot_state.reserve(S * sizeof(SlotState) + sizeof(Control) + 64));
         ARB_TRY(ctx->lists.reserve(S * 5 * 4 + 64));
         ctx->ws_kp = kp;
         ctx->ws_k = K;
-        ctx->ws_groups = G;
-        ctx->ws_sg = sg;
         ctx->ws_slots = (int)S;
     }
-    // a fit may use fewer groups / slots per group than the workspace holds
-    ws.groups = std::min(G, ctx->ws_groups);
-    ws.sg = std::min(sg, ctx->ws_sg);
-    ws.n_slots = ws.groups * ws.sg;
-    for (int g = 0; g < ws.groups; ++g) {
-        if (!ctx->gstream[g]) ARB_CUDA(cudaStreamCreateWithFlags(&ctx->gstream[g], cudaStreamNonBlocking));
-        for (int i = 0; i < 8; ++i)
-            if (!ctx->gevent[g][i])
-                ARB_CUDA(i < 6 ? cudaEventCreate(&ctx->gevent[g][i])
-                               : cudaEventCreateWithFlags(&ctx->gevent[g][i], cudaEventDisableTiming));
-    }
-    if (!ctx->h_ctl) ARB_CUDA(cudaMallocHost(&ctx->h_ctl, ARB_MAX_GROUPS * sizeof(Control)));
+    ws.n_slots = std::min(n_slots, ctx->ws_slots);          // a fit may use fewer slots than the workspace holds
+    for (auto &r : ctx->rev)
+        for (int i = 0; i < 7; ++i)
+            if (!r[i])
+                ARB_CUDA(i < 6 ? cudaEventCreate(&r[i]) : cudaEventCreateWithFlags(&r[i], cudaEventDisableTiming));
+    for (auto &e : ctx->fit_ev)
+        if (!e) ARB_CUDA(cudaEventCreate(&e));
+    if (!ctx->h_ctl) ARB_CUDA(cudaMallocHost(&ctx->h_ctl, (ARB_RING + 1) * sizeof(Control)));
     return ARB_OK;
 }
 
-// device pointers of one stream group: its slots, its lists and its regions of the packed buffers
+// device pointers of the workspace (sized for ctx->ws_slots slots)
 struct WsPtrs {
-    int slot0, n_slots;
     cudaStream_t stream;
-    SlotState *st;                       // [all slots]
-    Control *ctl;                        // this group's
-    int32_t *list_y, *list_z, *list_init;        // this group's (entries are global slot ids)
-    int32_t *pos_z, *snap_tree;          // [all slots]
-    double *xs, *xr, *pz_m, *py_m;       // this group's regions
+    SlotState *st;
+    Control *ctl;
+    int32_t *list_y, *list_z, *list_init, *pos_z, *snap_tree;
+    double *xs, *xr, *pz_m, *py_m;
     int32_t *pz_e, *py_e;
 };
 
-static WsPtrs ws_ptrs(arb_ctx *ctx, const PanelLayout &L, int g, cudaStream_t stream)
+static WsPtrs ws_ptrs(arb_ctx *ctx, const PanelLayout &L, cudaStream_t stream)
 {
     const int K = ctx->ws_k, C = K - 1;
     WsPtrs w;
-    const int64_t S = ctx->ws_slots, G = ctx->ws_groups, sg = ctx->ws_sg;
-    const int64_t vz = vslots_for(sg, K), vy = vslots_for(sg, C);          // per group
+    const int64_t S = ctx->ws_slots;
+    const int64_t vz = vslots_for(S, K), vy = vslots_for(S, C);
     const int64_t n = ctx->n_cells, m = ctx->n_snvs;
-    w.slot0 = (int)(g * sg);
-    w.n_slots = (int)sg;
     w.stream = stream;
     w.st = ctx->slot_state.as<SlotState>();
-    w.ctl = reinterpret_cast<Control *>(reinterpret_cast<char *>(ctx->slot_state.p) + S * sizeof(SlotState)) + g;
+    w.ctl = reinterpret_cast<Control *>(reinterpret_cast<char *>(ctx->slot_state.p) + S * sizeof(SlotState));
     int32_t *lists = ctx->lists.as<int32_t>();
-    w.list_y = lists + w.slot0;
-    w.list_z = lists + S + w.slot0;
-    w.list_init = lists + 2 * S + w.slot0;
+    w.list_y = lists;
+    w.list_z = lists + S;
+    w.list_init = lists + 2 * S;
     w.pos_z = lists + 3 * S;
     w.snap_tree = lists + 4 * S;
-    w.xs = ctx->xs.as<double>() + g * vz * ((int64_t)L.np_z * L.prz) * ARB_VW;
-    w.xr = ctx->xr.as<double>() + g * vy * ((int64_t)L.np_y * L.pry) * ARB_VW;
+    w.xs = ctx->xs.as<double>();
+    w.xr = ctx->xr.as<double>();
     double *pz = ctx->part_z.as<double>(), *py = ctx->part_y.as<double>();
-    const int64_t pz_cols = vz * L.np_z * n * ARB_VW, py_cols = vy * L.np_y * m * ARB_VW;   // per group
-    w.pz_m = pz + g * 2 * pz_cols;
-    w.pz_e = L.fold_z ? nullptr : reinterpret_cast<int32_t *>(pz + G * 2 * pz_cols) + g * pz_cols;
-    w.py_m = py + g * py_cols;
-    w.py_e = L.fold_y ? nullptr : reinterpret_cast<int32_t *>(py + G * py_cols) + g * py_cols;
+    const int64_t pz_cols = vz * L.np_z * n * ARB_VW, py_cols = vy * L.np_y * m * ARB_VW;
+    w.pz_m = pz;
+    w.pz_e = L.fold_z ? nullptr : reinterpret_cast<int32_t *>(pz + 2 * pz_cols);
+    w.py_m = py;
+    w.py_e = L.fold_y ? nullptr : reinterpret_cast<int32_t *>(py + py_cols);
     return w;
 }
 
@@ -1193,8 +1063,28 @@ static void launch_sweep(const SweepArgs &a, int grid, int fold, int w16, size_t
     }
 }
 
-// q(z) sweep over the packed S rows of the first n_trees entries of the group's q(z) list
-static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, int n_trees)
+// A sweep launch is n_vslots * n_panels equal CTAs, one per SM at a time.  When that is not many waves
+// (few trees active: small candidate sets, the last rounds of a fit, a strong-scaled shard) every (virtual slot,
+// panel) is cut into `split` CTAs that each take a share of every warp's tiles; the shares re-load the panel
+// (224 KB from L2), so the split is only as large as it takes to fill the last wave.
+static int choose_split(const arb_ctx *ctx, int64_t base_ctas, int tiles_per_warp)
+{
+    if (ctx->opt_split > 0) return (int)std::min<int64_t>(ctx->opt_split, std::max(1, tiles_per_warp));
+    const int64_t sms = std::max(1, ctx->sm_count);
+    if (base_ctas <= 0 || base_ctas >= 16 * sms) return 1;
+    int best = 1;
+    double best_cost = 1e300;
+    for (int s = 1; s <= std::min(16, std::max(1, tiles_per_warp)); ++s) {
+        const int64_t waves = (base_ctas * s + sms - 1) / sms;
+        const double cost = (double)waves / s * (1.0 + 0.015 * (s - 1));      // each share re-loads its panel
+        if (cost < best_cost - 1e-12) { best_cost = cost; best = s; }
+    }
+    return best;
+}
+
+// q(z) sweep over the packed S rows of the trees in the q(z) list: `ub_trees` bounds the grid, the count itself
+// is read on the device (ctl) unless ctl is null (kernel-level hooks: exactly ub_trees trees)
+static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, int ub_trees, const Control *ctl)
 {
     SweepArgs a;
     a.x = w.xs;
@@ -1207,7 +1097,9 @@ static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.panel_rows = L.prz;
     a.n_panels = L.np_z;
     a.tiles_per_warp = L.uz;
-    a.n_vslots = (int)vslots_for(n_trees, ctx->ws_k);
+    a.n_vslots = (int)vslots_for(ub_trees, ctx->ws_k);
+    a.n_vslots_dev = ctl ? &ctl->n_vz : nullptr;
+    a.split = choose_split(ctx, (int64_t)a.n_vslots * L.np_z, L.uz);
     a.dw = ctx->tab_dw.as<double2>();
     a.n_pairs = ctx->n_pairs;
     a.tab_n = arb_sweep_table_entries(ctx);
@@ -1215,11 +1107,11 @@ static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.out_m = w.pz_m;
     a.out_e = w.pz_e;
     fill_tabc(ctx, a);
-    const int grid = a.n_vslots * L.np_z;
+    const int grid = a.n_vslots * L.np_z * a.split;
     launch_sweep<true>(a, grid, L.fold_z, L.w16, sweep_smem_bytes(ctx, L), w.stream);
 }
 
-static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, int n_trees)
+static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, int ub_trees, const Control *ctl)
 {
     SweepArgs a;
     a.x = w.xr;
@@ -1232,7 +1124,9 @@ static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.panel_rows = L.pry;
     a.n_panels = L.np_y;
     a.tiles_per_warp = L.uy;
-    a.n_vslots = (int)vslots_for(n_trees, ctx->ws_k - 1);
+    a.n_vslots = (int)vslots_for(ub_trees, ctx->ws_k - 1);
+    a.n_vslots_dev = ctl ? &ctl->n_vy : nullptr;
+    a.split = choose_split(ctx, (int64_t)a.n_vslots * L.np_y, L.uy);
     a.dw = ctx->tab_dw.as<double2>();
     a.n_pairs = ctx->n_pairs;
     a.tab_n = arb_sweep_table_entries(ctx);
@@ -1240,13 +1134,14 @@ static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.out_m = w.py_m;
     a.out_e = w.py_e;
     fill_tabc(ctx, a);
-    const int grid = a.n_vslots * L.np_y;
+    const int grid = a.n_vslots * L.np_y * a.split;
     launch_sweep<false>(a, grid, L.fold_y, L.w16, sweep_smem_bytes(ctx, L), w.stream);
 }
 
 template <int GL>
 static void launch_finish_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, const Workspace &ws,
-                            const uint32_t *masks, const int32_t *list, int n_active, int given_q, int hard)
+                            const uint32_t *masks, const int32_t *list, int ub_trees, int given_q, int hard,
+                            const Control *ctl)
 {
     FinishArgs a;
     a.part_m = w.pz_m;
@@ -1267,15 +1162,16 @@ static void launch_finish_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w,
     a.red = ctx->red.as<double>();
     a.nbmax = ws.nbmax;
     a.given_q = given_q;
+    a.ctl = ctl;
     if (hard)
-        k_finish<GL, true, true><<<dim3(ws.nbz, n_active), FIN_THREADS, 0, w.stream>>>(a);
+        k_finish<GL, true, true><<<dim3(ws.nbz, ub_trees), FIN_THREADS, 0, w.stream>>>(a);
     else
-        k_finish<GL, true, false><<<dim3(ws.nbz, n_active), FIN_THREADS, 0, w.stream>>>(a);
+        k_finish<GL, true, false><<<dim3(ws.nbz, ub_trees), FIN_THREADS, 0, w.stream>>>(a);
 }
 
 template <int GL>
 static void launch_finish_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, const Workspace &ws,
-                            const uint32_t *masks, const int32_t *list, int n_active)
+                            const uint32_t *masks, const int32_t *list, int ub_trees, const Control *ctl)
 {
     FinishArgs a;
     a.part_m = w.py_m;
@@ -1297,32 +1193,34 @@ static void launch_finish_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w,
     a.red = ctx->red.as<double>();
     a.nbmax = ws.nbmax;
     a.given_q = 0;
-    k_finish<GL, false, false><<<dim3(ws.nby, n_active), FIN_THREADS, 0, w.stream>>>(a);
+    a.ctl = ctl;
+    k_finish<GL, false, false><<<dim3(ws.nby, ub_trees), FIN_THREADS, 0, w.stream>>>(a);
 }
 
 template <int GL>
 static void launch_seed_s(arb_ctx *ctx, const WsPtrs &w, const uint32_t *masks, const double *q_src,
-                          int64_t src_stride, const int32_t *list, int n_active, int K, int copy_q)
+                          int64_t src_stride, const int32_t *list, int ub_trees, int K, int copy_q, const Control *ctl)
 {
-    k_seed_s<GL><<<dim3(grid_for(ctx->n_snvs, (SEED_THREADS / 32) * (32 / GL)), n_active), SEED_THREADS, 0, w.stream>>>(
+    k_seed_s<GL><<<dim3(grid_for(ctx->n_snvs, (SEED_THREADS / 32) * (32 / GL)), ub_trees), SEED_THREADS, 0, w.stream>>>(
         q_src, src_stride, list, w.pos_z, w.st, masks, ctx->n_snvs, K, w.xs, ctx->qy_cur.as<double>(), copy_q,
-        ctx->layout[kp_index(ctx->ws_kp)].np_z, ctx->layout[kp_index(ctx->ws_kp)].prz, (int64_t)ctx->ws_slots);
+        ctx->layout[kp_index(ctx->ws_kp)].np_z, ctx->layout[kp_index(ctx->ws_kp)].prz, (int64_t)ctx->ws_slots, ctl);
 }
 
 template <int GL>
-static void launch_seed_r(arb_ctx *ctx, const WsPtrs &w, const uint32_t *masks, const int32_t *list, int n_active,
-                          int K)
+static void launch_seed_r(arb_ctx *ctx, const WsPtrs &w, const uint32_t *masks, const int32_t *list, int ub_trees,
+                          int K, const Control *ctl)
 {
-    k_seed_r<GL><<<dim3(grid_for(ctx->n_cells, (SEED_THREADS / 32) * (32 / GL)), n_active), SEED_THREADS, 0, w.stream>>>(
+    k_seed_r<GL><<<dim3(grid_for(ctx->n_cells, (SEED_THREADS / 32) * (32 / GL)), ub_trees), SEED_THREADS, 0, w.stream>>>(
         ctx->qz_cur.as<double>(), list, w.st, masks, ctx->n_cells, K, w.xr, ctx->layout[kp_index(ctx->ws_kp)].np_y,
-        ctx->layout[kp_index(ctx->ws_kp)].pry, (int64_t)ctx->ws_slots);
+        ctx->layout[kp_index(ctx->ws_kp)].pry, (int64_t)ctx->ws_slots, ctl);
 }
 
-// One fit of n_trees trees whose masks are on the device.  The slots are split into stream groups;
-// every group advances its own trees round by round on its own stream (k_control -> seeds -> q(y)
-// sweep + finish -> q(z) sweep + finish -> k_control ...), the host only reads the group's three list
-// lengths between rounds.  While the host waits for one group, the other groups' rounds are queued,
-// so their finishing / seeding / control kernels run underneath this group's sweeps.
+// One fit of n_trees trees whose masks are on the device.  A round = seeds -> q(y) sweep + finish -> q(z) sweep
+// + finish -> k_control (per-tree state machine, slot refill, next round's lists and counts) -> k_snapshot.  The
+// kernels of a round take their tree counts from the device-side Control block and their grids from an upper
+// bound, so the host enqueues rounds WITHOUT waiting for the device: every round's Control block is copied to a
+// pinned ring, and the host only blocks on the copy that is ARB_LOOKAHEAD rounds old (to tighten the grid bounds
+// and to notice that every tree is done).  The few rounds enqueued past the end find n_z = 0 and leave at once.
 template <int GL>
 static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, int mode, const FitTarget &tg,
                     int64_t reserve)
@@ -1331,140 +1229,159 @@ static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, 
     ARB_TRY(ensure_workspace(ctx, K, std::min(n_trees, 1024), reserve, ws));
     const PanelLayout &L = ctx->layout[kp_index(ws.kp)];
     ARB_TRY(configure_kernels(ctx, L));
-    const int G = ws.groups;
     const bool hard = mode == ARB_MODE_ML;
     const int64_t nz = (int64_t)ctx->n_cells * K, ny = (int64_t)ctx->n_snvs * (K - 1);
-    cudaStream_t main = ctx->stream;
-    WsPtrs w[ARB_MAX_GROUPS];
-    Control *h = reinterpret_cast<Control *>(ctx->h_ctl);
-    ARB_CUDA(cudaMemsetAsync(ctx->slot_state.p, 0, (size_t)ctx->ws_slots * sizeof(SlotState), main));
-    for (int g = 0; g < G; ++g) {
-        w[g] = ws_ptrs(ctx, L, g, ctx->gstream[g]);
-        w[g].n_slots = ws.sg;
-        Control &c = h[g];
-        memset(&c, 0, sizeof c);
-        c.next_tree = g;
-        c.tree_step = G;
-        c.n_trees = n_trees;
-        c.slot0 = w[g].slot0;
-        c.n_slots = ws.sg;
-        c.max_iter = max_iter;
-        c.tol = tol;
-        c.sum_la = ctx->sum_la;
-        c.nbz = ws.nbz;
-        c.nby = ws.nby;
-        c.nbmax = ws.nbmax;
-        c.keep = tg.best_qz != nullptr;
-        c.mode = mode;
-        ARB_CUDA(cudaMemcpyAsync(w[g].ctl, &c, sizeof c, cudaMemcpyHostToDevice, main));
-    }
-    cudaEvent_t ev0, ev1;
-    ARB_CUDA(cudaEventCreate(&ev0));
-    ARB_CUDA(cudaEventCreate(&ev1));
-    ARB_CUDA(cudaEventRecord(ev0, main));
-    // the pinned Control blocks are reused for the read-backs: the uploads above must have left them
-    ARB_CUDA(cudaStreamSynchronize(main));
+    cudaStream_t st = ctx->stream;
+    const WsPtrs w = ws_ptrs(ctx, L, st);
+    Control *ring = reinterpret_cast<Control *>(ctx->h_ctl);
+    Control &c0 = ring[ARB_RING];                       // the block uploaded at the start (not part of the ring)
+    memset(&c0, 0, sizeof c0);
+    c0.n_trees = n_trees;
+    c0.n_slots = ws.n_slots;
+    c0.max_iter = max_iter;
+    c0.tol = tol;
+    c0.sum_la = ctx->sum_la;
+    c0.nbz = ws.nbz;
+    c0.nby = ws.nby;
+    c0.nbmax = ws.nbmax;
+    c0.keep = tg.best_qz != nullptr;
+    c0.mode = mode;
+    c0.chunks_z = chunks_for(K);
+    c0.chunks_y = chunks_for(K - 1);
+    ARB_CUDA(cudaMemsetAsync(ctx->slot_state.p, 0, (size_t)ctx->ws_slots * sizeof(SlotState), st));
+    ARB_CUDA(cudaMemcpyAsync(w.ctl, &c0, sizeof c0, cudaMemcpyHostToDevice, st));
+    ARB_CUDA(cudaEventRecord(ctx->fit_ev[0], st));
     FitStats stats;
-    bool active[ARB_MAX_GROUPS] = {}, pending_y[ARB_MAX_GROUPS] = {}, pending_z[ARB_MAX_GROUPS] = {};
-    auto control = [&](int g, int first) {
-        const WsPtrs &p = w[g];
-        k_control<<<1, 256, 0, p.stream>>>(p.ctl, p.st, ctx->red.as<double>(), p.list_y, p.list_z, p.list_init,
-                                          p.pos_z, p.snap_tree, tg.elbo, tg.iters, tg.trace, first);
-        cudaMemcpyAsync(&h[g], p.ctl, sizeof(Control), cudaMemcpyDeviceToHost, p.stream);
-        cudaEventRecord(ctx->gevent[g][6], p.stream);
+    const int lookahead = ctx->opt_lookahead > 0 ? (int)ctx->opt_lookahead : ARB_LOOKAHEAD;
+
+    // control #s writes the counts round s runs with and is followed by snapshot s
+    auto control = [&](int s, int first) -> int {
+        k_control<<<1, 256, 0, st>>>(w.ctl, w.st, ctx->red.as<double>(), w.list_y, w.list_z, w.list_init, w.pos_z,
+                                     w.snap_tree, tg.elbo, tg.iters, tg.trace, first);
         stats.launches++;
+        if (!first && tg.best_qz) {
+            k_snapshot<<<dim3(16, ws.n_slots), 256, 0, st>>>(w.snap_tree, ctx->qz_cur.as<double>(),
+                                                            ctx->qy_cur.as<double>(), nz, ny, tg.best_qz, tg.best_qy,
+                                                            (int64_t)ctx->ws_slots);
+            stats.launches++;
+        }
+        ARB_CUDA(cudaMemcpyAsync(&ring[s % ARB_RING], w.ctl, sizeof(Control), cudaMemcpyDeviceToHost, st));
+        ARB_CUDA(cudaEventRecord(ctx->rev[s % ARB_RING][6], st));
+        return ARB_OK;
     };
-    for (int g = 0; g < G; ++g) {
-        active[g] = true;
-        control(g, 1);
-    }
-    int rc = ARB_OK, n_active = G;
-    while (n_active > 0 && rc == ARB_OK) {
-        for (int g = 0; g < G && rc == ARB_OK; ++g) {
-            if (!active[g]) continue;
-            const WsPtrs &p = w[g];
-            cudaEvent_t *evs = ctx->gevent[g];
-            cudaError_t e = cudaEventSynchronize(evs[6]);
+
+    struct Counts { int n_y, n_z, n_init; };
+    Counts used[ARB_RING] = {};                            // what round r ran with (from snapshot r)
+    int seen = -1, enq = 0, ub = std::min(ws.n_slots, n_trees);
+    bool done = false, more_inits = true;
+    // snapshot s has arrived: account for round s - 1 (its events precede the snapshot in the stream)
+    auto process = [&](int s) {
+        const Control c = ring[s % ARB_RING];
+        if (s >= 1) {
+            const Counts u = used[(s - 1) % ARB_RING];
+            cudaEvent_t *ev = ctx->rev[(s - 1) % ARB_RING];
+            float t = 0;
+            if (u.n_z > 0) {
+                stats.rounds += 1;
+                if (u.n_y > 0) {
+                    cudaEventElapsedTime(&t, ev[0], ev[1]); stats.sweep_y_ms += t;
+                    cudaEventElapsedTime(&t, ev[1], ev[2]); stats.finish_ms += t; stats.finish_y_ms += t;
+                    stats.launches_y += 1;
+                    stats.tree_sweeps_y += u.n_y;
+                }
+                cudaEventElapsedTime(&t, ev[3], ev[4]); stats.sweep_z_ms += t;
+                cudaEventElapsedTime(&t, ev[4], ev[5]); stats.finish_ms += t; stats.finish_z_ms += t;
+                stats.launches_z += 1;
+                stats.tree_sweeps_z += u.n_z;
+            } else {
+                stats.idle_rounds += 1;
+            }
+        }
+        used[s % ARB_RING] = Counts{c.n_y, c.n_z, c.n_init};
+        ub = std::max(0, std::min(ws.n_slots, n_trees - c.n_done));
+        more_inits = c.next_tree < n_trees;
+        if (c.n_z == 0) done = true;
+    };
+
+    int rc = control(0, 1);
+    while (rc == ARB_OK && !done) {
+        // snapshots 0..enq exist; the one `lookahead` rounds back must have arrived before round enq is enqueued
+        while (seen < enq && !done) {
+            const int s = seen + 1;
+            cudaEvent_t ev = ctx->rev[s % ARB_RING][6];
+            cudaError_t e = cudaEventQuery(ev);
+            if (e == cudaErrorNotReady) {
+                if (s > enq - lookahead) break;
+                stats.host_waits += 1;
+                e = cudaEventSynchronize(ev);
+            }
             if (e != cudaSuccess) {
-                arb_set_error("fit round: %s", cudaGetErrorString(e));
+                arb_set_error("fit round %d: %s", s, cudaGetErrorString(e));
                 rc = ARB_ERR_CUDA;
                 break;
             }
-            const Control c = h[g];
-            if (c.n_z == 0) {
-                active[g] = false;
-                --n_active;
-            }
-            // the events of the group's previous round precede its control kernel in the stream
-            float t = 0;
-            if (pending_y[g]) {
-                cudaEventElapsedTime(&t, evs[0], evs[1]); stats.sweep_y_ms += t;
-                cudaEventElapsedTime(&t, evs[1], evs[2]); stats.finish_ms += t; stats.finish_y_ms += t;
-            }
-            if (pending_z[g]) {
-                cudaEventElapsedTime(&t, evs[3], evs[4]); stats.sweep_z_ms += t;
-                cudaEventElapsedTime(&t, evs[4], evs[5]); stats.finish_ms += t; stats.finish_z_ms += t;
-            }
-            pending_y[g] = pending_z[g] = false;
-            if (!active[g]) continue;
-            stats.rounds += 1;
-            if (c.n_init > 0) {
-                launch_seed_s<GL>(ctx, p, tg.masks, hard ? ctx->q0_hard.as<double>() : ctx->q0.as<double>(), 0,
-                                  p.list_init, c.n_init, K, 1);
-                stats.launches++;
-            }
-            if (c.n_y > 0) {
-                launch_seed_r<GL>(ctx, p, tg.masks, p.list_y, c.n_y, K);
-                cudaEventRecord(evs[0], p.stream);
-                launch_sweep_y(ctx, L, p, c.n_y);
-                cudaEventRecord(evs[1], p.stream);
-                launch_finish_y<GL>(ctx, L, p, ws, tg.masks, p.list_y, c.n_y);
-                cudaEventRecord(evs[2], p.stream);
-                stats.launches += 3;
-                stats.launches_y += 1;
-                stats.tree_sweeps_y += c.n_y;
-                pending_y[g] = true;
-            }
-            cudaEventRecord(evs[3], p.stream);
-            launch_sweep_z(ctx, L, p, c.n_z);
-            cudaEventRecord(evs[4], p.stream);
-            launch_finish_z<GL>(ctx, L, p, ws, tg.masks, p.list_z, c.n_z, 0, hard);
-            cudaEventRecord(evs[5], p.stream);
-            stats.launches += 2;
-            stats.launches_z += 1;
-            stats.tree_sweeps_z += c.n_z;
-            pending_z[g] = true;
-            control(g, 0);
-            if (tg.best_qz) {
-                k_snapshot<<<dim3(16, ws.sg), 256, 0, p.stream>>>(p.snap_tree, ctx->qz_cur.as<double>(),
-                                                                 ctx->qy_cur.as<double>(), nz, ny, tg.best_qz,
-                                                                 tg.best_qy, p.slot0, (int64_t)ctx->ws_slots);
-                stats.launches++;
+            process(s);
+            seen = s;
+        }
+        if (rc != ARB_OK || done) break;
+        // ---- enqueue round enq --------------------------------------------------------------------
+        cudaEvent_t *ev = ctx->rev[enq % ARB_RING];
+        const int ubt = std::max(1, ub);
+        if (more_inits || enq == 0) {
+            launch_seed_s<GL>(ctx, w, tg.masks, hard ? ctx->q0_hard.as<double>() : ctx->q0.as<double>(), 0, w.list_init,
+                              ubt, K, 1, w.ctl);
+            stats.launches++;
+        }
+        if (enq > 0) {                                  // the first round has first passes only
+            launch_seed_r<GL>(ctx, w, tg.masks, w.list_y, ubt, K, w.ctl);
+            cudaEventRecord(ev[0], st);
+            launch_sweep_y(ctx, L, w, ubt, w.ctl);
+            cudaEventRecord(ev[1], st);
+            launch_finish_y<GL>(ctx, L, w, ws, tg.masks, w.list_y, ubt, w.ctl);
+            cudaEventRecord(ev[2], st);
+            stats.launches += 3;
+        } else {
+            cudaEventRecord(ev[0], st);
+            cudaEventRecord(ev[1], st);
+            cudaEventRecord(ev[2], st);
+        }
+        cudaEventRecord(ev[3], st);
+        launch_sweep_z(ctx, L, w, ubt, w.ctl);
+        cudaEventRecord(ev[4], st);
+        launch_finish_z<GL>(ctx, L, w, ws, tg.masks, w.list_z, ubt, 0, hard, w.ctl);
+        cudaEventRecord(ev[5], st);
+        stats.launches += 2;
+        {
+            cudaError_t e = cudaGetLastError();
+            if (e != cudaSuccess) {
+                arb_set_error("fit round %d: launch failed: %s", enq, cudaGetErrorString(e));
+                rc = ARB_ERR_CUDA;
+                break;
             }
         }
+        ++enq;
+        rc = control(enq, 0);
     }
-    // join the groups into the context's stream
-    for (int g = 0; g < G; ++g) {
-        cudaEventRecord(ctx->gevent[g][7], w[g].stream);
-        cudaStreamWaitEvent(main, ctx->gevent[g][7], 0);
+    // drain what is in flight (also after an error, so the workspace can be reused or released)
+    cudaEventRecord(ctx->fit_ev[1], st);
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (rc == ARB_OK && e != cudaSuccess) {
+        arb_set_error("fit: %s", cudaGetErrorString(e));
+        rc = ARB_ERR_CUDA;
     }
-    cudaEventRecord(ev1, main);
-    cudaEventSynchronize(ev1);
-    float ms = 0;
-    cudaEventElapsedTime(&ms, ev0, ev1);
-    cudaEventDestroy(ev0);
-    cudaEventDestroy(ev1);
-    stats.sweep_ms = stats.sweep_z_ms + stats.sweep_y_ms;
-    stats.device_ms = ms;
-    stats.groups = G;
-    ctx->stats = stats;
     if (rc == ARB_OK) {
-        cudaError_t e = cudaGetLastError();
+        for (int s = seen + 1; s <= enq; ++s) process(s);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, ctx->fit_ev[0], ctx->fit_ev[1]);
+        stats.device_ms = ms;
+        e = cudaGetLastError();
         if (e != cudaSuccess) {
             arb_set_error("fit: %s", cudaGetErrorString(e));
             rc = ARB_ERR_CUDA;
         }
     }
+    stats.sweep_ms = stats.sweep_z_ms + stats.sweep_y_ms;
+    ctx->stats = stats;
     return rc;
 }
 
@@ -1696,19 +1613,20 @@ ARB_API int arb_last_fit_stats(arb_ctx *ctx, int64_t *kernel_launches, double *d
 
 // [sweep_z_ms, sweep_y_ms, finish_ms, tree_sweeps_z, tree_sweeps_y, launches_z, launches_y, rounds,
 //  finish_z_ms, finish_y_ms, KP, panel_rows, panels_z, panels_y, tiles_per_warp_z, tiles_per_warp_y,
-//  fold_z, fold_y, quads_z, quads_y, stream groups, 16-bit stream words]
+//  fold_z, fold_y, quads_z, quads_y, rounds enqueued past the end, 16-bit stream words, blocking host waits,
+//  batched re-fits done by arb_get_fits since the last fit]
 ARB_API int arb_last_fit_profile(arb_ctx *ctx, double *values, int32_t n_values)
 {
     ARB_REQUIRE(ctx && values && n_values >= 0, ARB_ERR_INVALID, "arb_last_fit_profile: bad argument");
     const FitStats &s = ctx->stats;
     PanelLayout none;
     const PanelLayout &L = ctx->ws_kp ? ctx->layout[kp_index(ctx->ws_kp)] : none;
-    const double v[22] = {s.sweep_z_ms, s.sweep_y_ms, s.finish_ms, s.tree_sweeps_z, s.tree_sweeps_y,
+    const double v[24] = {s.sweep_z_ms, s.sweep_y_ms, s.finish_ms, s.tree_sweeps_z, s.tree_sweeps_y,
                           s.launches_z, s.launches_y, s.rounds, s.finish_z_ms, s.finish_y_ms,
                           (double)L.kp, (double)L.panel_rows, (double)L.np_z, (double)L.np_y, (double)L.uz,
                           (double)L.uy, (double)L.fold_z, (double)L.fold_y, (double)L.quads_z, (double)L.quads_y,
-                          s.groups, (double)L.w16};
-    for (int i = 0; i < n_values && i < 22; ++i) values[i] = v[i];
+                          s.idle_rounds, (double)L.w16, s.host_waits, s.refit_batches};
+    for (int i = 0; i < n_values && i < 24; ++i) values[i] = v[i];
     return ARB_OK;
 }
 
@@ -1792,7 +1710,7 @@ static int hook_setup(arb_ctx *ctx, int K, const uint8_t *presence, HookEnv &env
     ARB_CUDA(cudaSetDevice(ctx->device));
     ARB_TRY(ensure_workspace(ctx, K, 1, 0, env.ws));
     env.L = &ctx->layout[kp_index(env.ws.kp)];
-    env.w = ws_ptrs(ctx, *env.L, 0, ctx->stream);
+    env.w = ws_ptrs(ctx, *env.L, ctx->stream);
     ARB_TRY(configure_kernels(ctx, *env.L));
     const int C = K - 1;
     DevBuf d_p;
@@ -1838,9 +1756,9 @@ ARB_API int arb_qz_update(arb_ctx *ctx, int32_t n_clones, const uint8_t *presenc
     const uint32_t *mk = ctx->masks.as<uint32_t>();
     ARB_CUDA(cudaMemcpyAsync(ctx->qy_cur.p, q_y, (size_t)ctx->n_snvs * C * 8, cudaMemcpyHostToDevice, ctx->stream));
     GL_SWITCH(K, {
-        launch_seed_s<GLV>(ctx, env.w, mk, ctx->qy_cur.as<double>(), (int64_t)ctx->n_snvs * C, env.list0, 1, K, 0);
-        launch_sweep_z(ctx, *env.L, env.w, 1);
-        launch_finish_z<GLV>(ctx, *env.L, env.w, env.ws, mk, env.list0, 1, 0, 0);
+        launch_seed_s<GLV>(ctx, env.w, mk, ctx->qy_cur.as<double>(), (int64_t)ctx->n_snvs * C, env.list0, 1, K, 0, nullptr);
+        launch_sweep_z(ctx, *env.L, env.w, 1, nullptr);
+        launch_finish_z<GLV>(ctx, *env.L, env.w, env.ws, mk, env.list0, 1, 0, 0, nullptr);
     });
     ARB_CUDA(cudaMemcpyAsync(q_z, ctx->qz_cur.p, (size_t)ctx->n_cells * K * 8, cudaMemcpyDeviceToHost, ctx->stream));
     ARB_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -1859,9 +1777,9 @@ ARB_API int arb_qy_update(arb_ctx *ctx, int32_t n_clones, const uint8_t *presenc
     const uint32_t *mk = ctx->masks.as<uint32_t>();
     ARB_CUDA(cudaMemcpyAsync(ctx->qz_cur.p, q_z, (size_t)ctx->n_cells * K * 8, cudaMemcpyHostToDevice, ctx->stream));
     GL_SWITCH(K, {
-        launch_seed_r<GLV>(ctx, env.w, mk, env.list0, 1, K);
-        launch_sweep_y(ctx, *env.L, env.w, 1);
-        launch_finish_y<GLV>(ctx, *env.L, env.w, env.ws, mk, env.list0, 1);
+        launch_seed_r<GLV>(ctx, env.w, mk, env.list0, 1, K, nullptr);
+        launch_sweep_y(ctx, *env.L, env.w, 1, nullptr);
+        launch_finish_y<GLV>(ctx, *env.L, env.w, env.ws, mk, env.list0, 1, nullptr);
     });
     ARB_CUDA(cudaMemcpyAsync(q_y, ctx->qy_cur.p, (size_t)ctx->n_snvs * C * 8, cudaMemcpyDeviceToHost, ctx->stream));
     ARB_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -1883,9 +1801,9 @@ ARB_API int arb_elbo_terms(arb_ctx *ctx, int32_t n_clones, const uint8_t *presen
     ARB_CUDA(cudaMemcpyAsync(ctx->qy_cur.p, q_y, ny * 8, cudaMemcpyHostToDevice, ctx->stream));
     ARB_CUDA(cudaMemcpyAsync(ctx->qz_cur.p, q_z, nz * 8, cudaMemcpyHostToDevice, ctx->stream));
     GL_SWITCH(K, {
-        launch_seed_s<GLV>(ctx, env.w, mk, ctx->qy_cur.as<double>(), ny, env.list0, 1, K, 0);
-        launch_sweep_z(ctx, *env.L, env.w, 1);
-        launch_finish_z<GLV>(ctx, *env.L, env.w, env.ws, mk, env.list0, 1, 1, 0);
+        launch_seed_s<GLV>(ctx, env.w, mk, ctx->qy_cur.as<double>(), ny, env.list0, 1, K, 0, nullptr);
+        launch_sweep_z(ctx, *env.L, env.w, 1, nullptr);
+        launch_finish_z<GLV>(ctx, *env.L, env.w, env.ws, mk, env.list0, 1, 1, 0, nullptr);
     });
     DevBuf out;
     ARB_TRY(out.reserve(16));

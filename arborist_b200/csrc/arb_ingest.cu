@@ -238,10 +238,9 @@ ARB_API int arb_ctx_destroy(arb_ctx *ctx)
                       &ctx->csv_col[0], &ctx->csv_col[1], &ctx->csv_col[2], &ctx->csv_col[3]};
     for (DevBuf *b : bufs) b->release();
     for (auto &l : ctx->layout) l.release();
-    for (int g = 0; g < ARB_MAX_GROUPS; ++g) {
-        if (ctx->gstream[g]) cudaStreamDestroy(ctx->gstream[g]);
-        for (auto &e : ctx->gevent[g]) if (e) cudaEventDestroy(e);
-    }
+    for (auto &r : ctx->rev)
+        for (auto &e : r) if (e) cudaEventDestroy(e);
+    for (auto &e : ctx->fit_ev) if (e) cudaEventDestroy(e);
     if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -257,10 +256,11 @@ ARB_API int arb_set_option(arb_ctx *ctx, const char *name, int64_t value)
         for (auto &l : ctx->layout) l.release();
         ctx->ws_kp = 0;                      // partial buffers are sized by the panel count
     } else if (!strcmp(name, "threads")) ctx->opt_threads = value;
-    else if (!strcmp(name, "groups")) {
-        ARB_REQUIRE(value >= 0 && value <= ARB_MAX_GROUPS, ARB_ERR_INVALID, "arb_set_option: groups=%lld outside 0..%d",
-                    (long long)value, ARB_MAX_GROUPS);
-        ctx->opt_groups = value;
+    else if (!strcmp(name, "split")) ctx->opt_split = value;           // 0 = chosen per launch, n = forced
+    else if (!strcmp(name, "lookahead")) {                            // rounds enqueued ahead of the device
+        ARB_REQUIRE(value >= 0 && value <= ARB_RING - 3, ARB_ERR_INVALID, "arb_set_option: lookahead=%lld outside 0..%d",
+                    (long long)value, ARB_RING - 3);
+        ctx->opt_lookahead = value;
     }
     else if (!strcmp(name, "w32")) {          // force 32-bit stream words
         ctx->opt_w32 = value;
@@ -835,6 +835,9 @@ static int check_table_range(arb_ctx *ctx)
     for (int c = 0; c < ctx->n_pairs; ++c) {
         if (ctx->pair_count[c] == 0) continue;
         const double w = ctx->tab_lp[c] - ctx->tab_la[c];
+        ARB_REQUIRE(w == w, ARB_ERR_INVALID, "count pair %d (alt %d, total %d) has no finite log-likelihoods (alt > total?)",
+                    c, c < (int)ctx->pair_alt.size() ? ctx->pair_alt[c] : -1,
+                    c < (int)ctx->pair_total.size() ? ctx->pair_total[c] : -1);
         ARB_REQUIRE(!(w > 600.0) && !(w < -34.0), ARB_ERR_UNSUPPORTED,
                     "count pair %d has log-likelihood ratio %.1f outside [-34, 600]: deep-coverage "
                     "entries need the log-domain path, which this release does not have", c, w);
@@ -1355,11 +1358,14 @@ ARB_API int arb_csv_feed(arb_ctx *ctx, const char *bytes, int64_t n_bytes, int64
     ARB_CUDA(cudaStreamSynchronize(st));
     for (DevBuf *b : {&buf, &counts, &offs, &bad}) b->release();
     if (h_bad != ~0ull) {
+        // declined: the caller falls back to a host reader, so the columns parsed so far are dead weight
         ctx->csv_open = false;
+        for (DevBuf &b : ctx->csv_col) b.release();
+        ctx->csv_cap = ctx->csv_rows = 0;
         arb_set_error("arb_csv_feed: the line at byte %llu of this chunk is not %d comma-separated fields with plain "
                       "integers in the four selected columns (quoted, empty, fractional or text fields need the host reader)",
                       h_bad, ctx->csv_fields);
-        return ARB_ERR_UNSUPPORTED;
+        return ARB_ERR_DECLINED;
     }
     ctx->csv_rows += lines;
     if (n_rows_total) *n_rows_total = ctx->csv_rows;

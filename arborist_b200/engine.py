@@ -185,7 +185,7 @@ class Engine:
     def ingest_csv(self, path, alpha, chunk_bytes=256 << 20):
         """Read-count CSV with integer columns ``cell, snv, alt, total`` (any order, other columns ignored) parsed,
         factorised and ingested on the device.  Returns ``(cell_uniques, snv_uniques, n_rows)``; raises
-        ``ArboristError`` with status ``ARB_ERR_UNSUPPORTED`` (-3) when the file needs a general CSV reader."""
+        ``ArboristError`` with status ``ARB_ERR_DECLINED`` (-5) when the file needs a general CSV reader."""
         size = os.path.getsize(path)
         with open(path, "rb") as f:
             header = f.readline()
@@ -284,8 +284,6 @@ class Engine:
 
     # ---- prior ------------------------------------------------------------------
     def set_prior_labels(self, label_idx, n_clusters, gamma):
-        if n_clusters == 1:
-            (1 - gamma) / (n_clusters - 1)     # the reference divides by k-1 here (A.py:552)
         _check(self._lib.arb_set_prior_labels(self._h, _i32(label_idx), int(n_clusters), float(gamma)))
 
     def set_prior(self, q_y_init):
@@ -325,7 +323,8 @@ class Engine:
         tr = np.empty((T, int(max_iter) + 1)) if trace else None
         tr_ptr = tr.ctypes.data if trace else None
         m = {"vi": 0, "ml": 1}[mode]
-        if T == 0:
+        self.n_clones = K
+        if T == 0:                      # an empty shard (fewer trees than ranks): nothing to launch
             return (elbo, iters, tr) if trace else (elbo, iters)
         if parents is not None:
             _check(self._lib.arb_fit_trees(self._h, T, K, int(normal_idx), _i32(parents), int(max_iter),
@@ -384,12 +383,12 @@ class Engine:
                     sweep_ms=sw.value)
 
     def last_fit_profile(self):
-        v = np.zeros(22)
-        _check(self._lib.arb_last_fit_profile(self._h, v, 22))
+        v = np.zeros(24)
+        _check(self._lib.arb_last_fit_profile(self._h, v, 24))
         keys = ("sweep_z_ms", "sweep_y_ms", "finish_ms", "tree_sweeps_z", "tree_sweeps_y",
                 "launches_z", "launches_y", "rounds", "finish_z_ms", "finish_y_ms", "kp", "panel_rows",
                 "panels_z", "panels_y", "tiles_per_warp_z", "tiles_per_warp_y", "fold_z", "fold_y",
-                "quads_z", "quads_y", "groups", "w16")
+                "quads_z", "quads_y", "idle_rounds", "w16", "host_waits", "refit_batches")
         return dict(zip(keys, v.tolist()))
 
     def set_option(self, name, value):

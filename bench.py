@@ -60,7 +60,6 @@ def parse_args():
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--slots", type=int, default=0)
-    p.add_argument("--groups", type=int, default=0, help="stream groups (0 = library default)")
     return p.parse_args()
 
 
@@ -259,8 +258,6 @@ def run_gpu_arm(args):
     eng = engine.Engine(device=local)
     if args.slots:
         eng.set_option("slots", args.slots)
-    if args.groups:
-        eng.set_option("groups", args.groups)
     ingest_read_counts(eng, rc, cl, cluster_to_idx, RUN["alpha"], RUN["gamma"])
     n, m, nnz, n_pairs = eng.dims()
     shard = distributed.shard_indices(T)

@@ -44,7 +44,8 @@ typedef enum arb_status {
     ARB_ERR_INVALID = -1,     /* bad argument / call order */
     ARB_ERR_CUDA = -2,        /* CUDA runtime failure (message has the detail) */
     ARB_ERR_UNSUPPORTED = -3, /* outside this release's limits (K > 32, > 65535 count pairs) */
-    ARB_ERR_NOMEM = -4        /* device or host allocation failed */
+    ARB_ERR_NOMEM = -4,       /* device or host allocation failed */
+    ARB_ERR_DECLINED = -5     /* arb_csv_feed only: the file is not a plain integer table; use a host reader */
 } arb_status;
 
 typedef struct arb_ctx arb_ctx;
@@ -182,7 +183,7 @@ int arb_pool_trim(void);
  * there and never exist as host arrays.
  *   arb_csv_begin : field indices of the cell / snv / alt / total columns, fields per line, expected row count
  *                   (a sizing hint; the device columns grow when it is exceeded)
- *   arb_csv_feed  : one chunk; n_rows_total = rows parsed so far.  ARB_ERR_UNSUPPORTED (table discarded) when
+ *   arb_csv_feed  : one chunk; n_rows_total = rows parsed so far.  ARB_ERR_DECLINED (table discarded, device columns freed) when
  *                   a line is not n_fields comma-separated fields with plain integers in the selected columns
  *                   (quotes, empty lines, fractions, text ids): use the host reader + arb_ingest_ids/_coo then.
  *   arb_csv_finish: first-appearance factorisation of the ids + everything arb_ingest_ids does; ids in code

@@ -113,7 +113,8 @@ def trees_to_array(trees):
 
 
 def run_case(A, name, trees, rc, clusters, *, alpha=0.001, gamma=0.7, max_iter=25, tol=1.0,
-             add_normal=True, keep_q="all", tree_subset=None, extra=None, store_inputs=False):
+             add_normal=True, keep_q="all", tree_subset=None, extra=None, store_inputs=False,
+             store_best=True):
     import numba
 
     threads = min(os.cpu_count() or 1, 8)
@@ -163,8 +164,9 @@ def run_case(A, name, trees, rc, clusters, *, alpha=0.001, gamma=0.7, max_iter=2
         r = int(keep_q)
         out["q_z_rows"] = np.stack([fits[t].q_z[:r] for t in range(T)])
         out["q_y_rows"] = np.stack([fits[t].q_y[:r] for t in range(T)])
-        out["q_z_best"] = best_fit.q_z
-        out["q_y_best"] = best_fit.q_y
+        if store_best:                          # config 4: 24 MB of doubles, left out of the fixture
+            out["q_z_best"] = best_fit.q_z
+            out["q_y_best"] = best_fit.q_y
     if store_inputs:
         out.update(rc_snv=rc["snv"].to_numpy(), rc_cell=rc["cell"].to_numpy(),
                    rc_alt=rc["alt"].to_numpy(), rc_total=rc["total"].to_numpy(),
@@ -247,6 +249,7 @@ def main(argv):
     from arborist_b200 import synth
 
     A = load_reference()
+    # config5_full (~40 min) and config4_head (~1.5 h, ~20 GB) only when named
     want = set(argv) or {"tiny", "small", "small_nonormal", "deep30", "config2", "config3_head",
                          "example_standin"}
     if "tiny" in want:
@@ -279,6 +282,25 @@ def main(argv):
         d = synth.generate(synth.CONFIGS["config3"])
         run_case(A, "config3_head", d.trees, d.read_counts_frame(), d.clusters_frame(),
                  keep_q=32, tree_subset=[0, 1, 2, 3])
+    big_cases(A, want)
+
+
+def big_cases(A, want):
+    """BASELINE configs 5 and 4 at their full shapes (VERDICT r1, row g)."""
+    from arborist_b200 import synth
+
+    if "config5_full" in want:
+        # 5k x 10k, K = 30 deep trees, 30 % off-tree SNVs: the first 7 trees + the generating tree
+        d = synth.generate(synth.CONFIGS["config5"])
+        sub = sorted(set(range(7)) | {d.true_tree_index})
+        run_case(A, "config5_full", d.trees, d.read_counts_frame(), d.clusters_frame(),
+                 keep_q=32, tree_subset=sub, extra=dict(true_tree_index=d.true_tree_index))
+    if "config4_head" in want:
+        # 100k x 50k, nnz 99 M, K = 20: the first 2 trees, max_iter capped at 2 so the numba
+        # reference finishes here (SURVEY.md section 8(d): "first 2 trees ... parity sample")
+        d = synth.generate(synth.CONFIGS["config4"])
+        run_case(A, "config4_head", d.trees, d.read_counts_frame(), d.clusters_frame(),
+                 keep_q=32, tree_subset=[0, 1], max_iter=2, store_best=False)
 
 
 if __name__ == "__main__":

@@ -279,9 +279,10 @@ def test_ml_mode_batched_matches_oracle(eng_mod):
     e.close()
 
 
-def test_stream_groups_do_not_change_bits(eng_mod):
-    """The slots are split into stream groups whose rounds overlap on the device; the split must not
-    change a single bit of any result (ELBOs, iteration counts, posteriors)."""
+def test_round_pipeline_knobs_do_not_change_bits(eng_mod):
+    """The host enqueues rounds ahead of the device (lookahead), sizes the grids by an upper bound on the active
+    trees and cuts small sweep launches into shares (split); none of it may change a single bit of any result
+    (ELBOs, iteration counts, posteriors), whatever the number of trees in flight."""
     from arborist_b200.arborist import add_normal_clone, prepare_trees
     g = load_golden("small")
     e, _, _ = _coo_engine(eng_mod, g)
@@ -289,20 +290,21 @@ def test_stream_groups_do_not_change_bits(eng_mod):
     trees, _, _ = golden_frames(g)
     c2i, _, parents, _, normal = prepare_trees(add_normal_clone(trees))
     K = len(c2i)
-    e.set_option("groups", 1)
-    ref = e.fit(parents=parents, n_clones=K, normal_idx=normal, max_iter=25, tolerance=1.0, keep_posteriors="all")
-    assert e.last_fit_profile()["groups"] == 1
+    kw = dict(parents=parents, n_clones=K, normal_idx=normal, max_iter=25, tolerance=1.0, keep_posteriors="all")
+    e.set_option("split", 1)
+    ref = e.fit(**kw)
     ref_q = [e.get_fit(t) for t in range(len(parents))]
-    for groups, slots in ((2, 0), (3, 0), (4, 0), (4, 5), (2, 3)):
-        e.set_option("groups", groups)
+    for split, lookahead, slots in ((0, 0, 0), (2, 1, 0), (3, 5, 0), (7, 2, 5), (16, 3, 3), (0, 1, 1)):
+        e.set_option("split", split)
+        e.set_option("lookahead", lookahead)
         e.set_option("slots", slots)
-        got = e.fit(parents=parents, n_clones=K, normal_idx=normal, max_iter=25, tolerance=1.0,
-                    keep_posteriors="all")
-        assert e.last_fit_profile()["groups"] == min(groups, slots or groups)
-        assert np.array_equal(got[0], ref[0]) and np.array_equal(got[1], ref[1])
+        got = e.fit(**kw)
+        assert np.array_equal(got[0], ref[0]) and np.array_equal(got[1], ref[1]), (split, lookahead, slots)
         for t in (0, len(parents) - 1):
             qz, qy = e.get_fit(t)
             assert np.array_equal(qz, ref_q[t][0]) and np.array_equal(qy, ref_q[t][1])
+        pf = e.last_fit_profile()
+        assert pf["idle_rounds"] <= (lookahead or 3) + 1         # rounds enqueued after the last tree finished
     e.close()
 
 
@@ -468,7 +470,7 @@ def test_device_csv_reader_matches_dataframe_path(eng_mod, tmp_path):
     e = eng_mod.Engine()
     with pytest.raises(eng_mod.ArboristError) as err:
         e.ingest_csv(str(bad), 0.001)
-    assert err.value.status == -3
+    assert err.value.status == -5          # ARB_ERR_DECLINED: its own code, so real failures do not re-parse
     e.close()
     with pytest.raises(ValueError):
         (tmp_path / "nohdr.csv").write_text("a,b,c\n1,2,3\n")

@@ -31,8 +31,8 @@ from .treefit import TreeFit
 from .utils import read_read_counts, read_trees, visualize_tree
 
 __all__ = ["arborist", "run_variational_inference", "run_simple_max_likelihood", "main",
-           "parse_arguments", "add_normal_clone", "tree_to_clone_set", "prepare_trees",
-           "ingest_read_counts"]
+           "parse_arguments", "add_normal_clone", "tree_to_clone_set", "prepare_trees", "prepare_tree_shard",
+           "ingest_read_counts", "clear_seam_cache"]
 
 logging.basicConfig(
     format="{asctime} - {levelname} - {message}",
@@ -62,23 +62,25 @@ def _digraph_edge_order(edge_list, extra=None):
     return [(u, v) for u in nodes for v in succ.get(u, ())], list(nodes)
 
 
+def _add_normal_one(edges):
+    """One tree of :func:`add_normal_clone`: node / successor order as ``nx.DiGraph(edges)`` keeps it, then the
+    extra edge ``normal -> root`` last (``list(tree.edges)`` after ``tree.add_edge``, A.py:876-880)."""
+    nodes, succ, kids = {}, {}, set()
+    for u, v in edges:
+        nodes.setdefault(u, None)
+        nodes.setdefault(v, None)
+        succ.setdefault(u, {}).setdefault(v, None)
+        kids.add(v)
+    root = next(n for n in nodes if n not in kids)
+    normal = min(nodes) - 1
+    nodes.setdefault(normal, None)
+    succ.setdefault(normal, {}).setdefault(root, None)
+    return [(u, v) for u in nodes for v in succ.get(u, ())]
+
+
 def add_normal_clone(candidate_trees):
     """Prepend a normal clone ``min(nodes) - 1`` above each tree's root (A.py:860-882)."""
-    out = []
-    for edges in candidate_trees:
-        # one pass: node / successor order as nx.DiGraph(edges) keeps it, then the extra edge last
-        nodes, succ, kids = {}, {}, set()
-        for u, v in edges:
-            nodes.setdefault(u, None)
-            nodes.setdefault(v, None)
-            succ.setdefault(u, {}).setdefault(v, None)
-            kids.add(v)
-        root = next(n for n in nodes if n not in kids)
-        normal = min(nodes) - 1
-        nodes.setdefault(normal, None)
-        succ.setdefault(normal, {}).setdefault(root, None)
-        out.append([(u, v) for u in nodes for v in succ.get(u, ())])
-    return out
+    return [_add_normal_one(edges) for edges in candidate_trees]
 
 
 def tree_to_clone_set(tree):
@@ -86,71 +88,56 @@ def tree_to_clone_set(tree):
     return {x for e in tree for x in e}
 
 
-def prepare_trees(tree_list):
-    """Validate the candidate set and index it (A.py:1009-1028).
-
-    Returns ``(clone_to_idx, cluster_to_idx, parents, presence, normal_idx)``; exactly one of
-    ``parents`` (int32 ``[T, K]``, -1 for roots; device builds the closure) and
-    ``presence`` (uint8 ``[T, K-1, K]``; for inputs that are not forests) is set.
-    """
-    tree0 = tree_list[0]
-    _, nodes0 = _digraph_edge_order(tree0)
-    kids0 = {v for _, v in tree0}
-    normal = [n for n in nodes0 if n not in kids0][0]
-    clone_set = tree_to_clone_set(tree0)
-    clones = sorted(clone_set)
-    K, T = len(clones), len(tree_list)
-    clusters = [c for c in clones if c != normal]
-    clone_to_idx = {c: i for i, c in enumerate(clones)}
-    cluster_to_idx = {c: i for i, c in enumerate(clusters)}
-
-    parents = np.full((T, K), -1, dtype=np.int32)
-    is_forest = True
+def _edge_array(trees):
+    """``[T, E, 2]`` int64 array of a regular candidate set (every tree the same number of integer edges), else None."""
     try:
-        arr = np.asarray(tree_list, dtype=np.int64)
-        regular = arr.ndim == 3 and arr.shape[2] == 2
-    except (ValueError, TypeError):
-        regular = False
-    if regular and arr.shape[1] > 0:
-        carr = np.asarray(clones, dtype=np.int64)
-        idx = np.searchsorted(carr, arr).clip(0, K - 1)
-        if not np.array_equal(carr[idx], arr):
-            raise ValueError("All trees must have the same set of clones.")
-        seen = np.zeros((T, K), dtype=bool)
-        rows = np.arange(T)[:, None]
-        seen[rows, idx[:, :, 0]] = True
-        seen[rows, idx[:, :, 1]] = True
-        if not seen.all():
-            raise ValueError("All trees must have the same set of clones.")
-        pu, cv = idx[:, :, 0].astype(np.int32), idx[:, :, 1]
-        parents[rows, cv] = pu
-        # a child listed under two different parents is not a forest
-        n_par = np.zeros((T, K), dtype=np.int32)
-        np.add.at(n_par, (np.broadcast_to(rows, cv.shape), cv), 1)
-        if (n_par > 1).any():
-            # tolerate exact duplicate edges, reject genuine multi-parent nodes
-            is_forest = bool((parents[rows, cv] == pu).all())
-    else:
-        for t, tree in enumerate(tree_list):
-            if tree_to_clone_set(tree) != clone_set:
-                raise ValueError("All trees must have the same set of clones.")
-            for u, v in tree:
-                iu, iv = clone_to_idx[u], clone_to_idx[v]
-                if parents[t, iv] not in (-1, iu):
-                    is_forest = False
-                parents[t, iv] = iu
-    if is_forest:
-        # cycles: after K pointer jumps every node must have reached a root
-        cur = parents.copy()
-        for _ in range(K):
-            nxt = np.where(cur >= 0, np.take_along_axis(parents, cur.clip(0), axis=1), -1)
-            cur = nxt
-        is_forest = bool((cur < 0).all())
-    normal_idx = clone_to_idx[normal]
-    if is_forest:
-        return clone_to_idx, cluster_to_idx, parents, None, normal_idx
+        arr = np.asarray(trees, dtype=np.int64)
+    except (ValueError, TypeError, OverflowError):
+        return None
+    if arr.ndim != 3 or arr.shape[2] != 2 or arr.shape[1] == 0:
+        return None
+    return arr
 
-    # general digraphs: descendant closure on the host, like nx.descendants (A.py:516)
+
+def _parents_from_array(arr, clones):
+    """Parent vectors ``[T, K]`` (-1 for roots) of the trees in ``arr`` over the sorted label list ``clones``.
+    Returns ``(parents, is_forest)``; raises the reference's ValueError when a tree's label set differs."""
+    T, K = arr.shape[0], len(clones)
+    carr = np.asarray(clones, dtype=np.int64)
+    idx = np.searchsorted(carr, arr).clip(0, K - 1)
+    if not np.array_equal(carr[idx], arr):
+        raise ValueError("All trees must have the same set of clones.")
+    seen = np.zeros((T, K), dtype=bool)
+    rows = np.arange(T)[:, None]
+    seen[rows, idx[:, :, 0]] = True
+    seen[rows, idx[:, :, 1]] = True
+    if not seen.all():
+        raise ValueError("All trees must have the same set of clones.")
+    parents = np.full((T, K), -1, dtype=np.int32)
+    pu, cv = idx[:, :, 0].astype(np.int32), idx[:, :, 1]
+    parents[rows, cv] = pu
+    is_forest = True
+    # a child listed under two different parents is not a forest
+    n_par = np.zeros((T, K), dtype=np.int32)
+    np.add.at(n_par, (np.broadcast_to(rows, cv.shape), cv), 1)
+    if (n_par > 1).any():
+        # tolerate exact duplicate edges, reject genuine multi-parent nodes
+        is_forest = bool((parents[rows, cv] == pu).all())
+    return parents, is_forest
+
+
+def _acyclic(parents):
+    """After K pointer jumps every node of a forest has reached a root."""
+    K = parents.shape[1]
+    cur = parents.copy()
+    for _ in range(K):
+        cur = np.where(cur >= 0, np.take_along_axis(parents, cur.clip(0), axis=1), -1)
+    return bool((cur < 0).all())
+
+
+def _presence_on_host(tree_list, clone_to_idx, cluster_to_idx):
+    """General digraphs: descendant closure on the host, like nx.descendants (A.py:516)."""
+    T, K = len(tree_list), len(clone_to_idx)
     presence = np.zeros((T, K - 1, K), dtype=np.uint8)
     for t, tree in enumerate(tree_list):
         children = {}
@@ -165,7 +152,80 @@ def prepare_trees(tree_list):
                 seen_n.add(x)
                 presence[t, ip, clone_to_idx[x]] = 1
                 stack.extend(children.get(x, ()))
-    return clone_to_idx, cluster_to_idx, None, presence, normal_idx
+    return presence
+
+
+def _index_trees(tree_list, clones, clone_to_idx, cluster_to_idx):
+    """Parent vectors (forests) or genotype matrices (anything else) of fully materialised edge lists."""
+    K, T = len(clones), len(tree_list)
+    clone_set = set(clones)
+    arr = _edge_array(tree_list)
+    if arr is not None:
+        parents, is_forest = _parents_from_array(arr, clones)
+    else:
+        parents = np.full((T, K), -1, dtype=np.int32)
+        is_forest = True
+        for t, tree in enumerate(tree_list):
+            if tree_to_clone_set(tree) != clone_set:
+                raise ValueError("All trees must have the same set of clones.")
+            for u, v in tree:
+                iu, iv = clone_to_idx[u], clone_to_idx[v]
+                if parents[t, iv] not in (-1, iu):
+                    is_forest = False
+                parents[t, iv] = iu
+    if is_forest and _acyclic(parents):
+        return parents, None
+    return None, _presence_on_host(tree_list, clone_to_idx, cluster_to_idx)
+
+
+def _label_maps(tree0):
+    """Clone / cluster index maps and the normal clone from the first tree (A.py:1009-1028)."""
+    _, nodes0 = _digraph_edge_order(tree0)
+    kids0 = {v for _, v in tree0}
+    normal = [n for n in nodes0 if n not in kids0][0]
+    clones = sorted(tree_to_clone_set(tree0))
+    clusters = [c for c in clones if c != normal]
+    return (clones, normal, {c: i for i, c in enumerate(clones)}, {c: i for i, c in enumerate(clusters)})
+
+
+def prepare_trees(tree_list):
+    """Validate the candidate set and index it (A.py:1009-1028).
+
+    Returns ``(clone_to_idx, cluster_to_idx, parents, presence, normal_idx)``; exactly one of
+    ``parents`` (int32 ``[T, K]``, -1 for roots; device builds the closure) and
+    ``presence`` (uint8 ``[T, K-1, K]``; for inputs that are not forests) is set.
+    """
+    clones, normal, clone_to_idx, cluster_to_idx = _label_maps(tree_list[0])
+    parents, presence = _index_trees(tree_list, clones, clone_to_idx, cluster_to_idx)
+    return clone_to_idx, cluster_to_idx, parents, presence, clone_to_idx[normal]
+
+
+def prepare_tree_shard(tree_list, indices, add_normal=False):
+    """:func:`prepare_trees` for the trees ``indices`` of the candidate set only (the shard of this process), with
+    ``--add-normal`` (A.py:860-882, 1004-1007) folded in: for a regular integer candidate set the normal clone is
+    added arithmetically to the parent vectors and no per-tree edge list is built; host work is proportional to
+    the shard, not to the whole candidate set.  Label maps always come from tree 0, as in the reference."""
+    tree0 = _add_normal_one(tree_list[0]) if add_normal else tree_list[0]
+    clones, normal, clone_to_idx, cluster_to_idx = _label_maps(tree0)
+    normal_idx = clone_to_idx[normal]
+    local = [tree_list[int(i)] for i in indices]
+    if not local:
+        return clone_to_idx, cluster_to_idx, np.zeros((0, len(clones)), np.int32), None, normal_idx
+    if add_normal:
+        arr = _edge_array(local)
+        raw0 = tree_to_clone_set(tree_list[0])
+        if arr is not None and all(isinstance(c, (int, np.integer)) for c in raw0) and min(raw0) - 1 == normal:
+            raw = sorted(raw0)                                   # = clones without the normal, which sorts first
+            par_raw, is_forest = _parents_from_array(arr, raw)
+            one_root = bool(((par_raw < 0).sum(axis=1) == 1).all())
+            if is_forest and one_root and _acyclic(par_raw):
+                parents = np.empty((len(local), len(clones)), dtype=np.int32)
+                parents[:, 0] = -1                               # the normal clone
+                parents[:, 1:] = np.where(par_raw >= 0, par_raw + 1, 0)
+                return clone_to_idx, cluster_to_idx, parents, None, normal_idx
+        local = add_normal_clone(local)
+    parents, presence = _index_trees(local, clones, clone_to_idx, cluster_to_idx)
+    return clone_to_idx, cluster_to_idx, parents, presence, normal_idx
 
 
 def _prior_labels(snv_clusters, snv_ids, cluster_to_idx):
@@ -240,6 +300,31 @@ def ingest_read_counts(eng, read_counts, snv_clusters, cluster_to_idx, alpha, ga
 # ---------------------------------------------------------------------------
 # the public entry point
 # ---------------------------------------------------------------------------
+def _pick_devices(device, devices, n_trees):
+    """GPUs one ``arborist(...)`` call drives.  Under a ``torch.distributed`` group: the one GPU of this rank.
+    Otherwise ``devices`` ("all", a count, or a list of ordinals) or ``device``; the default is every visible GPU
+    once the candidate set is large enough to keep them busy (a small set stays on one GPU: every extra context
+    costs an ingest of the read-count table)."""
+    from . import distributed
+    from .engine import device_count
+
+    _, ws = distributed.world()
+    if ws > 1 or device is not None:
+        return [device]                         # None -> LOCAL_RANK inside Engine
+    n = device_count()
+    if devices is None:
+        env = os.environ.get("ARBORIST_DEVICES", "")
+        devices = env if env else ("all" if n_trees >= 32 * max(1, n) else 1)
+    if isinstance(devices, str):
+        devices = n if devices == "all" else [int(x) for x in devices.split(",") if x.strip() != ""]
+    if isinstance(devices, (int, np.integer)):
+        devices = list(range(max(1, min(int(devices), n))))
+    devices = [int(d) for d in devices]
+    if not devices:
+        raise ValueError("arborist: empty device list")
+    return devices[: max(1, n_trees)]
+
+
 def arborist(
     tree_list: list,
     read_counts: pd.DataFrame,
@@ -253,24 +338,35 @@ def arborist(
     verbose: bool = False,
     *,
     device=None,
+    devices=None,
     keep_posteriors: str = "auto",
 ) -> tuple:
     """Rank candidate SNV clone trees with low-pass scDNA-seq read counts.
 
     Same contract as the reference (A.py:906-1130): returns ``(likelihoods,
     best_fit, all_tree_fits)`` -- ``{tree_idx: ELBO}``, the ``TreeFit`` of the first
-    tree attaining the maximum ELBO, and ``{tree_idx: TreeFit}``.
+    tree attaining the maximum ELBO, and ``{tree_idx: TreeFit}`` (a ``dict`` whose
+    values are built when first looked at, :class:`arborist_b200.results.LazyFits`).
 
     ``threads`` is accepted for compatibility and ignored (the reference passes it
     to ``numba.set_num_threads``, A.py:1002; nothing here runs on host threads).
-    Keyword-only extras: ``device`` (CUDA ordinal; default ``LOCAL_RANK`` or 0) and
-    ``keep_posteriors`` ("auto" | "all" | "none": whether every tree's best
-    ``q_z``/``q_y`` stay resident on the GPU or are refit on demand).
-    Under an initialised ``torch.distributed`` group the candidate set is sharded
-    over ranks and the ELBOs gathered, see :mod:`arborist_b200.distributed`.
+    Keyword-only extras: ``device`` (one CUDA ordinal), ``devices`` ("all", a count or
+    a list of ordinals: the candidate set is spread over those GPUs by THIS process,
+    ``arb_fit_trees_multi``; default: every visible GPU for sets of at least 32 trees
+    per GPU, environment override ``ARBORIST_DEVICES``) and ``keep_posteriors``
+    ("auto" | "all" | "none": whether every tree's best ``q_z``/``q_y`` stay resident
+    on the GPU or are re-fitted in batches on demand).
+    Under an initialised ``torch.distributed`` group (one process per GPU) the candidate
+    set is sharded over ranks instead and the ELBOs gathered, see
+    :mod:`arborist_b200.distributed`.
     """
+    import gc
+    import time
+    from concurrent.futures import ThreadPoolExecutor
+
     from . import distributed
-    from .engine import Engine
+    from .engine import Engine, fit_multi
+    from .results import FitStore, LazyFits
 
     logger = logging.getLogger() if verbose else None
 
@@ -278,26 +374,40 @@ def arborist(
         if logger is not None:
             logger.info(msg)
 
-    import time
     marks = [("start", time.perf_counter())]         # host wall-clock of the stages, kept in arborist.last_stats
 
     def mark(name):
         marks.append((name, time.perf_counter()))
 
+    T = len(tree_list)
+    shard = distributed.shard_indices(T)
     if add_normal:
         log("Appending normal clone to candidate trees...")
-        tree_list = add_normal_clone(tree_list)
-
-    clone_to_idx, cluster_to_idx, parents, presence, normal_idx = prepare_trees(tree_list)
-    K, T = len(clone_to_idx), len(tree_list)
+    # validation + parent vectors of this process's shard only; --add-normal folded in (no per-tree edge lists)
+    err = None
+    try:
+        clone_to_idx, cluster_to_idx, parents, presence, normal_idx = prepare_tree_shard(tree_list, shard, add_normal)
+    except ValueError as e:
+        err = e
+    if not distributed.all_agree(err is None):          # every rank raises, or none
+        raise err if err is not None else ValueError("All trees must have the same set of clones.")
+    K = len(clone_to_idx)
     mark("trees")
 
     log("Removing SNVs with 0 variant reads across all cells...")
-    eng = Engine(device=device)
+    devs = _pick_devices(device, devices, len(shard))
+    engines = [Engine(device=d) for d in devs]
     mark("context")
     log("Caching log-likelihoods for presence/absence...")
     log("Initializing the SNV cluster assignment prior...")
-    cell_ids, snv_ids = ingest_read_counts(eng, read_counts, snv_clusters, cluster_to_idx, alpha, gamma)
+    if len(engines) == 1:
+        cell_ids, snv_ids = ingest_read_counts(engines[0], read_counts, snv_clusters, cluster_to_idx, alpha, gamma)
+    else:
+        # one ingest per GPU, side by side (ctypes calls release the interpreter lock)
+        with ThreadPoolExecutor(len(engines)) as ex:
+            got = list(ex.map(lambda e: ingest_read_counts(e, read_counts, snv_clusters, cluster_to_idx, alpha, gamma),
+                              engines))
+        cell_ids, snv_ids = got[0]
     mark("ingest")
     cell_to_idx = dict(zip(cell_ids.tolist(), range(len(cell_ids))))
     snv_to_idx = dict(zip(snv_ids.tolist(), range(len(snv_ids))))
@@ -305,55 +415,65 @@ def arborist(
 
     if verbose:
         log("Starting Arborist...")
-        log(f"Number of candidate trees: {len(tree_list[-1])}")   # sic: A.py:1080 logs an edge count
+        log(f"Number of candidate trees: {len(tree_list[-1]) + (1 if add_normal else 0)}")   # sic: A.py:1080 logs an edge count
         log(f"Number of clones: {K}")
         log(f"Number of SNV clusters: {K - 1}")
         log(f"Number of cells: {len(cell_ids)}")
         log(f"Number of SNVs: {len(snv_ids)}")
 
-    shard = distributed.shard_indices(T)
-    elbo, iters = eng.fit(parents=None if parents is None else parents[shard],
-                          presence=None if presence is None else presence[shard],
-                          n_clones=K, normal_idx=normal_idx, max_iter=max_iter,
-                          tolerance=tolerance, keep_posteriors=keep_posteriors)
+    if len(engines) == 1 or parents is None:
+        engines = engines[:1]
+        elbo, iters = engines[0].fit(parents=parents, presence=presence, n_clones=K, normal_idx=normal_idx,
+                                     max_iter=max_iter, tolerance=tolerance, keep_posteriors=keep_posteriors)
+    else:
+        elbo, iters = fit_multi(engines, parents, K, normal_idx=normal_idx, max_iter=max_iter,
+                                tolerance=tolerance, keep_posteriors=keep_posteriors)
     mark("fit")
-    elbo_all, owner = distributed.gather_elbos(elbo, shard, T)
+    distributed.all_agree.device = engines[0].device
+    elbo_all, owner = distributed.gather_elbos(elbo, shard, T, device=engines[0].device)
     mark("gather")
 
-    local_of = {int(g): l for l, g in enumerate(shard)}
-    eng_ref = eng
+    store = FitStore(engines, shard, owner, T)
+    if add_normal:
+        def tree_of(idx):
+            return _add_normal_one(tree_list[idx])
+    else:
+        def tree_of(idx):
+            return tree_list[idx]
+    elbo_list = elbo_all.tolist()
 
-    def loader(idx):
-        return distributed.fetch_fit(eng_ref, idx, local_of, owner)
+    def make_fit(idx):
+        return TreeFit.lazy(None, idx, elbo_list[idx], store.get_fit, cell_to_idx, snv_to_idx, clone_to_idx,
+                            cluster_to_idx, map_loader=store.get_map, tree_loader=tree_of)
 
-    def map_loader(idx):
-        if idx in local_of:
-            return eng_ref.get_map(local_of[idx])
-        return None
-
-    likelihoods, all_tree_fits = {}, {}
-    best_likelihood, best_fit = -np.inf, None
-    for idx in range(T):
-        e = float(elbo_all[idx])
-        tfit = TreeFit.lazy(tree_list[idx], idx, e, loader, cell_to_idx, snv_to_idx,
-                            clone_to_idx, cluster_to_idx, map_loader=map_loader)
-        all_tree_fits[idx] = tfit
-        if verbose:
+    all_tree_fits = LazyFits(T, make_fit, store)
+    likelihoods = dict(enumerate(elbo_list))
+    if verbose:
+        for idx, e in enumerate(elbo_list):
             log(f"Tree {idx} fit wtih ELBO: {e:.2f}")
-        likelihoods[idx] = e
-        if e > best_likelihood:                      # strict >: first maximum wins (A.py:1124)
-            best_fit, best_likelihood = tfit, e
     log(f"Done fitting all {T} candidate trees!")
-    if best_fit is None:
+    # strict >: the first maximum wins, NaN never does (A.py:1124)
+    cand = np.where(np.isnan(elbo_all), -np.inf, elbo_all)
+    best_idx = int(np.argmax(cand)) if T else -1
+    if T == 0 or not cand[best_idx] > -np.inf:
         # the reference dies with UnboundLocalError here (A.py:1124-1130); say why
         raise UnboundLocalError("no candidate tree has a finite ELBO (all NaN/-inf); "
                                 "cannot select best_fit")
+    best_fit = all_tree_fits[best_idx]
     mark("treefits")
     stages = {b[0]: round(1e3 * (b[1] - a[1]), 2) for a, b in zip(marks, marks[1:])}
-    arborist.last_stats = dict(iters=iters, engine=weakref.ref(eng), shard=shard, stages_ms=stages)
+    arborist.last_stats = dict(iters=iters, engine=weakref.ref(engines[0]), engines=[weakref.ref(e) for e in engines],
+                               shard=shard, stages_ms=stages, store=weakref.ref(store), devices=[e.device for e in engines])
+    # The start-up heap of the interpreter (torch / pandas module objects, never garbage) makes every few calls pay
+    # a ~50 ms generation-2 collection over objects that cannot die: take it out of the collector once, as a
+    # long-running service would (ARBORIST_GC_FREEZE=0 leaves the collector alone).
+    if not arborist._frozen and os.environ.get("ARBORIST_GC_FREEZE", "1") != "0":
+        arborist._frozen = True
+        gc.freeze()
     return likelihoods, best_fit, all_tree_fits
 
 
+arborist._frozen = False
 arborist.last_stats = None
 
 
@@ -381,33 +501,51 @@ def _install_scipy_table(eng, alpha):
 _SEAM_CACHE = {}
 
 
-def _seam_engine(ll_cs, snv_idx, cell_ptr, n_cells, n_snvs, q_y_init):
+def _fingerprint(a):
+    """Cheap content check of a cached input: address, shape and a strided sample of the bytes, so that an array
+    refilled in place between calls (a gamma sweep reusing one q_y_init buffer) is noticed."""
+    flat = a.reshape(-1)
+    step = max(1, flat.shape[0] // 4096)
+    return (a.__array_interface__["data"][0], a.shape, a.dtype.str, flat[::step].tobytes(), flat[-1:].tobytes())
+
+
+def clear_seam_cache():
+    """Drop the device matrix the per-tree seam keeps between calls (and the arrays it pins)."""
+    hit = _SEAM_CACHE.pop("e", None)
+    if hit is not None:
+        hit["engine"].close()
+
+
+def _seam_engine(orig, ll_cs, snv_idx, cell_ptr, n_cells, n_snvs, q_y_init):
+    """The engine behind ``run_variational_inference``: the reference's tree loop calls the seam once per tree with
+    the same arrays, so the device matrix is kept between calls.  The key is taken from the CALLER's arrays
+    (``orig``: before any dtype / contiguity conversion, so int64 pointers do not defeat the cache) plus a content
+    fingerprint; only the current prior is kept."""
     from .engine import Engine
 
-    key = (ll_cs.__array_interface__["data"][0], snv_idx.__array_interface__["data"][0],
-           cell_ptr.__array_interface__["data"][0], ll_cs.shape[0], n_cells, n_snvs)
+    key = tuple(_fingerprint(np.asarray(a)) for a in orig[:3]) + (n_cells, n_snvs)
     hit = _SEAM_CACHE.get("e")
-    if hit is None or hit[0] != key:
+    if hit is None or hit["key"] != key:
+        clear_seam_cache()
         eng = Engine()
         eng.ingest_csr(cell_ptr, snv_idx, ll_cs, n_cells, n_snvs)
-        hit = (key, eng, (ll_cs, snv_idx, cell_ptr), [None])
-        _SEAM_CACHE["e"] = hit       # keeps the arrays alive so the key cannot be recycled
-    eng = hit[1]
-    pk = (q_y_init.__array_interface__["data"][0], q_y_init.shape)
-    if hit[3][0] != pk:
-        eng.set_prior(q_y_init)
-        hit[3][0] = pk
-        hit[3].append(q_y_init)
-    return eng
+        hit = dict(key=key, engine=eng, pinned=orig[:3], prior=None)     # pins the arrays: addresses cannot be recycled
+        _SEAM_CACHE["e"] = hit
+    pk = _fingerprint(np.asarray(orig[3]))
+    if hit["prior"] is None or hit["prior"][0] != pk:
+        hit["engine"].set_prior(q_y_init)
+        hit["prior"] = (pk, orig[3])
+    return hit["engine"]
 
 
 def _run_seam(mode, presence, ll_cs, ll_ss, cell_idx, snv_idx, n_cells, n_snvs, n_clones,
               q_y_init, cell_ptr, snv_ptr, max_iter, tolerance):
+    orig = (ll_cs, snv_idx, cell_ptr, q_y_init)
     ll_cs = np.ascontiguousarray(ll_cs, dtype=np.float64)
     snv_idx = np.ascontiguousarray(snv_idx, dtype=np.int32)
     cell_ptr = np.ascontiguousarray(cell_ptr, dtype=np.int32)
     q_y_init = np.ascontiguousarray(q_y_init, dtype=np.float64)
-    eng = _seam_engine(ll_cs, snv_idx, cell_ptr, int(n_cells), int(n_snvs), q_y_init)
+    eng = _seam_engine(orig, ll_cs, snv_idx, cell_ptr, int(n_cells), int(n_snvs), q_y_init)
     pres = (np.asarray(presence) != 0).astype(np.uint8)[None]
     elbo, _ = eng.fit(presence=pres, n_clones=int(n_clones), max_iter=int(max_iter),
                       tolerance=float(tolerance), keep_posteriors="all", mode=mode)
@@ -509,7 +647,8 @@ def main(argv=None):
     if args.tree:
         tfit.save_tree(args.tree)
     if args.pickle:
-        pd.to_pickle(all_fits, args.pickle)
+        # the same file pd.to_pickle(all_fits, ...) writes (A.py:1187-1188), one batch of posteriors at a time
+        all_fits.to_pickle(args.pickle)
 
     print("\n---------------------Arborist complete!---------------------\n")
     print(tfit)

@@ -161,8 +161,10 @@ struct arb_ctx {
     bool fit_kept = false;
     DevBuf best_qz, best_qy, d_elbo, d_iters, d_trace, tree_masks;
     std::vector<uint32_t> h_masks;        // per tree: K column masks then C row masks
-    int single_tree = -1;                 // tree whose posteriors sit in single_qz/qy
-    DevBuf single_qz, single_qy;
+    // posteriors re-fitted on demand when they were not kept: trees batch_t0 .. batch_t0 + batch_n - 1
+    // of the last fit sit in batch_qz / batch_qy (arb_get_fits re-fits a whole batch in one go)
+    int batch_t0 = -1, batch_n = 0;
+    DevBuf batch_qz, batch_qy, batch_out;
     FitStats stats;
     DevBuf scratch;                       // cub temp storage
 

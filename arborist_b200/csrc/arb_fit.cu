@@ -29,6 +29,7 @@
 #include <algorithm>
 #include <math.h>
 #include <string.h>
+#include <thread>
 
 int arb_sweep_table_entries(const arb_ctx *ctx);
 int arb_check_table_range(arb_ctx *ctx);
@@ -1445,7 +1446,7 @@ static int run_fit(arb_ctx *ctx, int32_t n_trees, int32_t K, int32_t max_iter, d
         ctx->best_qy.release();
     }
     ctx->fit_trees = 0;
-    ctx->single_tree = -1;
+    ctx->batch_t0 = -1;
     ARB_TRY(fit_dispatch(ctx, n_trees, K, max_iter, tol, mode, tg, reserve));
     ARB_CUDA(cudaMemcpyAsync(elbo, tg.elbo, (size_t)n_trees * 8, cudaMemcpyDeviceToHost, st));
     ARB_CUDA(cudaMemcpyAsync(iters, tg.iters, (size_t)n_trees * 4, cudaMemcpyDeviceToHost, st));
@@ -1485,6 +1486,63 @@ ARB_API int arb_fit_trees(arb_ctx *ctx, int32_t n_trees, int32_t n_clones, int32
     return run_fit(ctx, n_trees, n_clones, max_iter, tolerance, mode, keep_posteriors, elbo, iters, elbo_trace);
 }
 
+// The same fit over several contexts (one per GPU, every one holding the same matrix and prior): tree t goes to
+// context t mod n_ctx as its local tree t / n_ctx; one host thread per context runs arb_fit_trees on its shard and
+// writes the shard's ELBOs / iteration counts / traces straight into the caller's arrays -- candidate trees are
+// independent (A.py:1089-1126), so the only "exchange" is those 12 bytes per tree and a single process needs no
+// collective for it.  Keeps arborist(...) an ordinary function call on a multi-GPU box.
+ARB_API int arb_fit_trees_multi(arb_ctx *const *ctxs, int32_t n_ctx, int32_t n_trees, int32_t n_clones,
+                                int32_t normal_idx, const int32_t *parent, int32_t max_iter, double tolerance,
+                                int32_t mode, int32_t keep_posteriors, double *elbo, int32_t *iters, double *elbo_trace)
+{
+    ARB_REQUIRE(ctxs && n_ctx >= 1 && n_ctx <= 64, ARB_ERR_INVALID, "arb_fit_trees_multi: %d contexts", n_ctx);
+    ARB_REQUIRE(n_trees > 0 && parent && elbo && iters, ARB_ERR_INVALID, "arb_fit_trees_multi: bad argument");
+    for (int c = 0; c < n_ctx; ++c) {
+        ARB_REQUIRE(ctxs[c], ARB_ERR_INVALID, "arb_fit_trees_multi: context %d is null", c);
+        for (int d = 0; d < c; ++d)
+            ARB_REQUIRE(ctxs[c] != ctxs[d], ARB_ERR_INVALID, "arb_fit_trees_multi: context %d given twice", c);
+        ARB_REQUIRE(ctxs[c]->ingested && ctxs[c]->n_cells == ctxs[0]->n_cells && ctxs[c]->n_snvs == ctxs[0]->n_snvs &&
+                        ctxs[c]->nnz == ctxs[0]->nnz,
+                    ARB_ERR_INVALID, "arb_fit_trees_multi: context %d holds a different matrix than context 0", c);
+    }
+    const int K = n_clones, W = max_iter + 1;
+    std::vector<int> rcs(n_ctx, ARB_OK);
+    std::vector<std::string> errs(n_ctx);
+    std::vector<std::thread> workers;
+    for (int c = 0; c < n_ctx; ++c) {
+        workers.emplace_back([&, c]() {
+            const int local_n = (n_trees - c + n_ctx - 1) / n_ctx;
+            if (local_n <= 0) {
+                ctxs[c]->fit_trees = 0;
+                return;
+            }
+            std::vector<int32_t> par((size_t)local_n * K), it(local_n);
+            std::vector<double> el(local_n), tr(elbo_trace ? (size_t)local_n * W : 0);
+            for (int l = 0; l < local_n; ++l)
+                memcpy(&par[(size_t)l * K], parent + ((size_t)l * n_ctx + c) * K, (size_t)K * 4);
+            rcs[c] = arb_fit_trees(ctxs[c], local_n, K, normal_idx, par.data(), max_iter, tolerance, mode,
+                                   keep_posteriors, el.data(), it.data(), elbo_trace ? tr.data() : nullptr);
+            if (rcs[c] != ARB_OK) {
+                errs[c] = arb_last_error();            // thread-local: carry it over to the calling thread
+                return;
+            }
+            for (int l = 0; l < local_n; ++l) {
+                const size_t t = (size_t)l * n_ctx + c;
+                elbo[t] = el[l];
+                iters[t] = it[l];
+                if (elbo_trace) memcpy(elbo_trace + t * W, &tr[(size_t)l * W], (size_t)W * 8);
+            }
+        });
+    }
+    for (auto &w : workers) w.join();
+    for (int c = 0; c < n_ctx; ++c)
+        if (rcs[c] != ARB_OK) {
+            arb_set_error("arb_fit_trees_multi: context %d (device %d): %s", c, ctxs[c]->device, errs[c].c_str());
+            return rcs[c];
+        }
+    return ARB_OK;
+}
+
 ARB_API int arb_fit_presence(arb_ctx *ctx, int32_t n_trees, int32_t n_clones, const uint8_t *presence,
                              int32_t max_iter, double tolerance, int32_t mode, int32_t keep_posteriors, double *elbo,
                              int32_t *iters, double *elbo_trace)
@@ -1519,60 +1577,70 @@ ARB_API int arb_posterior_bytes(arb_ctx *ctx, int32_t n_trees, int32_t n_clones,
     return ARB_OK;
 }
 
-// posteriors of tree t of the last fit: resident, or refit on demand (the fit is deterministic)
-static int locate_fit(arb_ctx *ctx, int32_t t, const double **qz, const double **qy)
+// Posteriors of trees t0 .. t0 + count - 1 of the last fit: resident, or re-fitted on demand as ONE batch (the
+// fit is deterministic, so the re-fit reproduces every bit).  A writer that walks the whole candidate set
+// (--pickle, A.py:1187-1188) therefore costs ceil(T / count) batched fits at full occupancy instead of T
+// single-tree fits.
+static int locate_fits(arb_ctx *ctx, int32_t t0, int32_t count, const double **qz, const double **qy)
 {
     ARB_REQUIRE(ctx && ctx->fit_trees > 0, ARB_ERR_INVALID, "no fit to read from");
-    ARB_REQUIRE(t >= 0 && t < ctx->fit_trees, ARB_ERR_INVALID, "tree %d outside 0..%d", t, ctx->fit_trees - 1);
+    ARB_REQUIRE(t0 >= 0 && count >= 1 && (int64_t)t0 + count <= ctx->fit_trees, ARB_ERR_INVALID,
+                "trees %d..%d outside 0..%d", t0, t0 + count - 1, ctx->fit_trees - 1);
     ARB_CUDA(cudaSetDevice(ctx->device));
     const int K = ctx->fit_k;
     const int64_t nz = (int64_t)ctx->n_cells * K, ny = (int64_t)ctx->n_snvs * (K - 1);
     if (ctx->fit_kept) {
-        *qz = ctx->best_qz.as<double>() + (int64_t)t * nz;
-        *qy = ctx->best_qy.as<double>() + (int64_t)t * ny;
+        *qz = ctx->best_qz.as<double>() + (int64_t)t0 * nz;
+        *qy = ctx->best_qy.as<double>() + (int64_t)t0 * ny;
         return ARB_OK;
     }
-    if (ctx->single_tree != t) {
-        ARB_TRY(ctx->single_qz.reserve((size_t)nz * 8 + 16));
-        ARB_TRY(ctx->single_qy.reserve((size_t)ny * 8));
+    if (!(ctx->batch_t0 >= 0 && t0 >= ctx->batch_t0 && t0 + count <= ctx->batch_t0 + ctx->batch_n)) {
+        ctx->batch_t0 = -1;
+        ARB_TRY(ctx->batch_qz.reserve((size_t)count * nz * 8));
+        ARB_TRY(ctx->batch_qy.reserve((size_t)count * ny * 8));
+        ARB_TRY(ctx->batch_out.reserve((size_t)count * 12 + 16));
         FitTarget tg;
         memset(&tg, 0, sizeof tg);
-        tg.masks = ctx->tree_masks.as<uint32_t>() + (int64_t)t * MASK_STRIDE;
-        // scalar outputs of the single refit go to the tail of single_qz
-        DevBuf tmp;
-        ARB_TRY(tmp.reserve(32));
-        tg.elbo = tmp.as<double>();
-        tg.iters = reinterpret_cast<int32_t *>(tmp.as<double>() + 1);
-        tg.best_qz = ctx->single_qz.as<double>();
-        tg.best_qy = ctx->single_qy.as<double>();
+        tg.masks = ctx->tree_masks.as<uint32_t>() + (int64_t)t0 * MASK_STRIDE;
+        tg.elbo = ctx->batch_out.as<double>();
+        tg.iters = reinterpret_cast<int32_t *>(ctx->batch_out.as<double>() + count);
+        tg.best_qz = ctx->batch_qz.as<double>();
+        tg.best_qy = ctx->batch_qy.as<double>();
         const FitStats keep_stats = ctx->stats;
-        int rc = fit_dispatch(ctx, 1, K, ctx->fit_max_iter, ctx->fit_tol, ctx->fit_mode, tg, 0);
+        int rc = fit_dispatch(ctx, count, K, ctx->fit_max_iter, ctx->fit_tol, ctx->fit_mode, tg, 0);
         ctx->stats = keep_stats;
-        tmp.release();
+        ctx->stats.refit_batches += 1;
         ARB_TRY(rc);
-        ctx->single_tree = t;
+        ctx->batch_t0 = t0;
+        ctx->batch_n = count;
     }
-    *qz = ctx->single_qz.as<double>();
-    *qy = ctx->single_qy.as<double>();
+    *qz = ctx->batch_qz.as<double>() + (int64_t)(t0 - ctx->batch_t0) * nz;
+    *qy = ctx->batch_qy.as<double>() + (int64_t)(t0 - ctx->batch_t0) * ny;
+    return ARB_OK;
+}
+
+ARB_API int arb_get_fits(arb_ctx *ctx, int32_t t0, int32_t count, double *q_z, double *q_y)
+{
+    const double *dz, *dy;
+    ARB_TRY(locate_fits(ctx, t0, count, &dz, &dy));
+    const int K = ctx->fit_k;
+    if (q_z)
+        ARB_CUDA(cudaMemcpyAsync(q_z, dz, (size_t)count * ctx->n_cells * K * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (q_y)
+        ARB_CUDA(cudaMemcpyAsync(q_y, dy, (size_t)count * ctx->n_snvs * (K - 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    ARB_CUDA(cudaStreamSynchronize(ctx->stream));
     return ARB_OK;
 }
 
 ARB_API int arb_get_fit(arb_ctx *ctx, int32_t t, double *q_z, double *q_y)
 {
-    const double *dz, *dy;
-    ARB_TRY(locate_fit(ctx, t, &dz, &dy));
-    const int K = ctx->fit_k;
-    if (q_z) ARB_CUDA(cudaMemcpyAsync(q_z, dz, (size_t)ctx->n_cells * K * 8, cudaMemcpyDeviceToHost, ctx->stream));
-    if (q_y)
-        ARB_CUDA(cudaMemcpyAsync(q_y, dy, (size_t)ctx->n_snvs * (K - 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
-    ARB_CUDA(cudaStreamSynchronize(ctx->stream));
-    return ARB_OK;
+    return arb_get_fits(ctx, t, 1, q_z, q_y);
 }
 
 ARB_API int arb_get_map(arb_ctx *ctx, int32_t t, int32_t *z, int32_t *y)
 {
     const double *dz, *dy;
-    ARB_TRY(locate_fit(ctx, t, &dz, &dy));
+    ARB_TRY(locate_fits(ctx, t, 1, &dz, &dy));
     const int K = ctx->fit_k;
     DevBuf out;
     ARB_TRY(out.reserve(((size_t)ctx->n_cells + ctx->n_snvs) * 4));
@@ -1645,7 +1713,7 @@ static int finish_prior(arb_ctx *ctx, int32_t C)
                                                                      ctx->q0_hard.as<double>());
     ARB_CUDA(cudaStreamSynchronize(ctx->stream));
     ctx->n_clusters = C;
-    ctx->single_tree = -1;
+    ctx->batch_t0 = -1;
     return ARB_OK;
 }
 
@@ -1731,7 +1799,7 @@ static int hook_setup(arb_ctx *ctx, int K, const uint8_t *presence, HookEnv &env
     env.list0 = env.w.list_z;
     ARB_CUDA(cudaStreamSynchronize(ctx->stream));
     d_p.release();
-    ctx->single_tree = -1;
+    ctx->batch_t0 = -1;
     return ARB_OK;
 }
 

@@ -233,7 +233,7 @@ ARB_API int arb_ctx_destroy(arb_ctx *ctx)
                       &ctx->xs, &ctx->xr, &ctx->qz_cur, &ctx->qy_cur, &ctx->part_z, &ctx->part_g,
                       &ctx->part_y, &ctx->red, &ctx->slot_state, &ctx->lists, &ctx->masks,
                       &ctx->best_qz, &ctx->best_qy, &ctx->d_elbo, &ctx->d_iters, &ctx->d_trace,
-                      &ctx->tree_masks, &ctx->single_qz, &ctx->single_qy, &ctx->scratch, &ctx->cell_uniques,
+                      &ctx->tree_masks, &ctx->batch_qz, &ctx->batch_qy, &ctx->batch_out, &ctx->scratch, &ctx->cell_uniques,
                       &ctx->snv_uniques, &ctx->base_ta, &ctx->base_tb, &ctx->base_cnt,
                       &ctx->csv_col[0], &ctx->csv_col[1], &ctx->csv_col[2], &ctx->csv_col[3]};
     for (DevBuf *b : bufs) b->release();
@@ -863,7 +863,7 @@ static void reset_matrix(arb_ctx *ctx)
     for (auto &l : ctx->layout) l.release();
     ctx->ws_kp = 0;
     ctx->fit_trees = 0;
-    ctx->single_tree = -1;
+    ctx->batch_t0 = -1;
     ctx->n_clusters = 0;
 }
 
@@ -1551,7 +1551,7 @@ ARB_API int arb_set_loglik_table(arb_ctx *ctx, int32_t n_pairs, const double *lo
     ARB_CUDA(cudaSetDevice(ctx->device));
     ctx->tab_lp.assign(log_present, log_present + n_pairs);
     ctx->tab_la.assign(log_absent, log_absent + n_pairs);
-    ctx->single_tree = -1;
+    ctx->batch_t0 = -1;
     // the layouts carry a range proof made with the old table: rebuild them at the next fit
     for (auto &l : ctx->layout) l.release();
     ctx->ws_kp = 0;

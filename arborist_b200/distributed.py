@@ -3,14 +3,18 @@
 Candidate trees are independent (A.py:1089-1126 keeps no cross-tree state except
 the running argmax), so each rank fits trees ``rank, rank + W, rank + 2W, ...``
 on its own GPU against a replicated read-count matrix, and the only exchange is
-one all-gather of the per-tree ELBOs (and iteration counts).  ``torch.distributed``
+one all-gather of the per-tree ELBOs (and iteration counts).  Fetching the posteriors of a
+tree that ANOTHER rank fitted (``TreeFit.q_z`` of a remote tree, ``--pickle`` of all fits) is a
+broadcast from its owner, i.e. a collective: every rank has to ask for the same remote tree in
+the same order.  A single process that drives all GPUs itself (``arborist(..., devices=...)``,
+``arb_fit_trees_multi``) needs none of this.  ``torch.distributed``
 is plumbing only: NCCL over NVLink on the GPU box, gloo in the CPU tests.
 """
 from __future__ import annotations
 
 import numpy as np
 
-__all__ = ["world", "shard_indices", "gather_elbos", "fetch_fit", "gather_vector"]
+__all__ = ["world", "shard_indices", "gather_elbos", "broadcast_fit", "gather_vector", "all_agree"]
 
 
 def world():
@@ -31,7 +35,34 @@ def shard_indices(n_trees, rank=None, world_size=None):
     return np.arange(rank, n_trees, world_size, dtype=np.int64)
 
 
-def gather_vector(local, shard, n_total, dtype=np.float64):
+def _comm_device(device=None):
+    """Where collective buffers live: the engine's GPU under NCCL (NOT torch's current device, which is 0 unless
+    the caller ran ``torch.cuda.set_device``), the host under gloo."""
+    import torch
+    import torch.distributed as dist
+
+    if dist.get_backend() != "nccl":
+        return torch.device("cpu")
+    return torch.device("cuda", torch.cuda.current_device() if device is None else int(device))
+
+
+def all_agree(ok):
+    """True on every rank iff ``ok`` is true on every rank (so that all ranks raise together)."""
+    _, ws = world()
+    if ws == 1:
+        return bool(ok)
+    import torch
+    import torch.distributed as dist
+
+    t = torch.tensor([1 if ok else 0], dtype=torch.int32, device=_comm_device(all_agree.device))
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return bool(int(t.item()))
+
+
+all_agree.device = None          # set by arborist() to its engine's GPU
+
+
+def gather_vector(local, shard, n_total, dtype=np.float64, device=None):
     """All-gather a per-tree vector sharded with :func:`shard_indices`; returns the full vector."""
     rank, ws = world()
     local = np.asarray(local, dtype=dtype)
@@ -43,8 +74,7 @@ def gather_vector(local, shard, n_total, dtype=np.float64):
     import torch.distributed as dist
 
     per = (n_total + ws - 1) // ws               # equal-sized buffers for all_gather
-    backend = dist.get_backend()
-    dev = torch.device("cuda", torch.cuda.current_device()) if backend == "nccl" else torch.device("cpu")
+    dev = _comm_device(device)
     buf = torch.zeros(per, dtype=torch.from_numpy(np.zeros(1, dtype)).dtype, device=dev)
     buf[: local.shape[0]] = torch.from_numpy(local).to(dev)
     parts = [torch.empty_like(buf) for _ in range(ws)]
@@ -56,31 +86,21 @@ def gather_vector(local, shard, n_total, dtype=np.float64):
     return out
 
 
-def gather_elbos(elbo_local, shard, n_total):
+def gather_elbos(elbo_local, shard, n_total, device=None):
     """Full ELBO vector + owning rank of every tree."""
     _, ws = world()
     owner = np.arange(n_total, dtype=np.int64) % ws
-    return gather_vector(elbo_local, shard, n_total), owner
+    return gather_vector(elbo_local, shard, n_total, device=device), owner
 
 
-def fetch_fit(engine, idx, local_of, owner):
-    """Posteriors of global tree ``idx``: local trees come from this rank's GPU; remote ones
-    are broadcast by their owner (collective: every rank must ask for the same tree)."""
-    rank, ws = world()
-    if ws == 1 or int(owner[idx]) == rank:
-        qz, qy = engine.get_fit(local_of[idx])
-        if ws == 1:
-            return qz, qy
-    else:
-        n, m, _, _ = engine.dims()
-        qz = np.empty((n, engine.n_clones))
-        qy = np.empty((m, engine.n_clones - 1))
+def broadcast_fit(qz, qy, owner_rank, device=None):
+    """Posteriors of one tree from the rank that fitted it to every rank (COLLECTIVE: every rank calls this for
+    the same tree; ``qz`` / ``qy`` are the real arrays on the owner and same-shaped buffers elsewhere)."""
     import torch
     import torch.distributed as dist
 
-    backend = dist.get_backend()
-    dev = torch.device("cuda", torch.cuda.current_device()) if backend == "nccl" else torch.device("cpu")
-    tz, ty = torch.from_numpy(qz).to(dev), torch.from_numpy(qy).to(dev)
-    dist.broadcast(tz, int(owner[idx]))
-    dist.broadcast(ty, int(owner[idx]))
+    dev = _comm_device(device)
+    tz, ty = torch.from_numpy(np.ascontiguousarray(qz)).to(dev), torch.from_numpy(np.ascontiguousarray(qy)).to(dev)
+    dist.broadcast(tz, int(owner_rank))
+    dist.broadcast(ty, int(owner_rank))
     return tz.cpu().numpy(), ty.cpu().numpy()

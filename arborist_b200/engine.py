@@ -13,7 +13,7 @@ import numpy as np
 
 from . import _build
 
-__all__ = ["Engine", "ArboristError", "device_count", "library_path", "load_library"]
+__all__ = ["Engine", "ArboristError", "device_count", "library_path", "load_library", "fit_multi"]
 
 _LIB = None
 
@@ -66,7 +66,10 @@ _SIGNATURES = {
                                    C.c_int32, _f64p, _i32p, _opt]),
     "arb_posterior_bytes": (C.c_int, [_ctx, C.c_int32, C.c_int32, C.POINTER(C.c_int64),
                                       C.POINTER(C.c_int64)]),
+    "arb_fit_trees_multi": (C.c_int, [C.POINTER(_ctx), C.c_int32, C.c_int32, C.c_int32, C.c_int32, _i32p, C.c_int32,
+                                      C.c_double, C.c_int32, C.c_int32, _f64p, _i32p, _opt]),
     "arb_get_fit": (C.c_int, [_ctx, C.c_int32, _f64p, _f64p]),
+    "arb_get_fits": (C.c_int, [_ctx, C.c_int32, C.c_int32, _opt, _opt]),
     "arb_get_map": (C.c_int, [_ctx, C.c_int32, _i32p, _i32p]),
     "arb_get_presence": (C.c_int, [_ctx, C.c_int32, _u8p]),
     "arb_qz_update": (C.c_int, [_ctx, C.c_int32, _u8p, _f64p, _f64p]),
@@ -308,16 +311,7 @@ class Engine:
             raise ValueError("give exactly one of parents / presence")
         K = int(n_clones)
         T = int(parents.shape[0] if parents is not None else presence.shape[0])
-        if isinstance(keep_posteriors, str):
-            if keep_posteriors == "all":
-                keep = 1
-            elif keep_posteriors == "none":
-                keep = 0
-            else:
-                need, free = self.posterior_bytes(T, K)
-                keep = int(need < 0.35 * free)
-        else:
-            keep = int(bool(keep_posteriors))
+        keep = self._keep_flag(keep_posteriors, T, K)
         elbo = np.empty(T)
         iters = np.empty(T, np.int32)
         tr = np.empty((T, int(max_iter) + 1)) if trace else None
@@ -336,10 +330,33 @@ class Engine:
         self.n_clones = K
         return (elbo, iters, tr) if trace else (elbo, iters)
 
+    def _keep_flag(self, keep_posteriors, T, K):
+        if isinstance(keep_posteriors, str):
+            if keep_posteriors == "all":
+                return 1
+            if keep_posteriors == "none":
+                return 0
+            need, free = self.posterior_bytes(T, K)
+            return int(need < 0.35 * free)
+        return int(bool(keep_posteriors))
+
     def get_fit(self, t):
         n, m, _, _ = self.dims()
         qz, qy = np.empty((n, self.n_clones)), np.empty((m, self.n_clones - 1))
         _check(self._lib.arb_get_fit(self._h, int(t), qz, qy))
+        return qz, qy
+
+    def get_fits(self, t0, count, fetch=True):
+        """Posteriors of trees ``t0 .. t0+count-1`` of the last fit as ``([count, n, K], [count, m, K-1])``.  When
+        they were not kept on the device the range is re-fitted as ONE batch and stays cached there
+        (``fetch=False`` only does that: later ``get_fit`` / ``get_map`` calls inside the range are copies)."""
+        if not fetch:
+            _check(self._lib.arb_get_fits(self._h, int(t0), int(count), None, None))
+            return None
+        n, m, _, _ = self.dims()
+        qz = np.empty((count, n, self.n_clones))
+        qy = np.empty((count, m, self.n_clones - 1))
+        _check(self._lib.arb_get_fits(self._h, int(t0), int(count), qz.ctypes.data, qy.ctypes.data))
         return qz, qy
 
     def get_map(self, t):
@@ -393,3 +410,26 @@ class Engine:
 
     def set_option(self, name, value):
         _check(self._lib.arb_set_option(self._h, name.encode(), int(value)))
+
+
+def fit_multi(engines, parents, n_clones, normal_idx=0, max_iter=10, tolerance=1.0, keep_posteriors="auto",
+              mode="vi", trace=False):
+    """``arb_fit_trees_multi``: one fit spread over several engines (one per GPU, all holding the same matrix and
+    prior).  Tree ``t`` is fitted by ``engines[t % G]`` as its local tree ``t // G``; returns ``(elbo, iters)``
+    (+ ``trace``) in global tree order, bit-identical to a single-engine fit."""
+    lib = load_library()
+    G, K = len(engines), int(n_clones)
+    parents = _i32(parents)
+    T = int(parents.shape[0])
+    per = (T + G - 1) // G
+    keep = min(e._keep_flag(keep_posteriors, per, K) for e in engines)
+    elbo, iters = np.empty(T), np.empty(T, np.int32)
+    tr = np.empty((T, int(max_iter) + 1)) if trace else None
+    for e in engines:
+        e.n_clones = K
+    if T:
+        handles = (_ctx * G)(*[e._h for e in engines])
+        _check(lib.arb_fit_trees_multi(handles, G, T, K, int(normal_idx), parents, int(max_iter), float(tolerance),
+                                       {"vi": 0, "ml": 1}[mode], keep, elbo, iters,
+                                       tr.ctypes.data if trace else None))
+    return (elbo, iters, tr) if trace else (elbo, iters)

@@ -20,6 +20,7 @@ import pandas as pd
 __all__ = ["TreeFit"]
 
 _LAZY = ("q_z", "q_y")
+_TRANSIENT = ("_loader", "_map_loader", "_tree_loader")
 
 
 @dataclass
@@ -41,20 +42,31 @@ class TreeFit:
     # ---- lazy posteriors -------------------------------------------------
     @classmethod
     def lazy(cls, tree, tree_idx, elbo, loader, cell_to_idx, snv_to_idx, clone_to_idx,
-             cluster_to_idx, map_loader=None):
+             cluster_to_idx, map_loader=None, tree_loader=None):
         """Build a fit whose ``q_z``/``q_y`` are fetched by ``loader(tree_idx)`` on
         first access (returns ``(q_z, q_y)``); ``map_loader(tree_idx)`` optionally
-        returns device-computed argmax vectors so MAP tables need no posterior copy."""
+        returns device-computed argmax vectors so MAP tables need no posterior copy;
+        with ``tree=None`` the edge list comes from ``tree_loader(tree_idx)`` on first
+        access (the ``--add-normal`` edge order is only built for trees that are looked at)."""
         self = object.__new__(cls)
         d = self.__dict__
-        d.update(tree=tree, tree_idx=tree_idx, elbo=elbo, cell_to_idx=cell_to_idx,
+        if tree is not None:
+            d["tree"] = tree
+        d.update(tree_idx=tree_idx, elbo=elbo, cell_to_idx=cell_to_idx,
                  snv_to_idx=snv_to_idx, clone_to_idx=clone_to_idx,
-                 cluster_to_idx=cluster_to_idx, _loader=loader, _map_loader=map_loader)
+                 cluster_to_idx=cluster_to_idx, _loader=loader, _map_loader=map_loader,
+                 _tree_loader=tree_loader)
         self.__post_init__()
         return self
 
     def __getattr__(self, name):
-        # only reached when normal lookup fails, i.e. for not-yet-loaded posteriors
+        # only reached when normal lookup fails, i.e. for not-yet-loaded posteriors / edge lists
+        if name == "tree":
+            tl = self.__dict__.get("_tree_loader")
+            if tl is None:
+                raise AttributeError(name)
+            self.__dict__["tree"] = tl(self.tree_idx)
+            return self.__dict__["tree"]
         if name in _LAZY:
             loader = self.__dict__.get("_loader")
             if loader is None:
@@ -66,7 +78,13 @@ class TreeFit:
 
     def __getstate__(self):
         self.q_z  # noqa: B018 - force materialisation
-        return {k: v for k, v in self.__dict__.items() if k not in ("_loader", "_map_loader")}
+        d = self.__dict__
+        # the reference's field order, so the pickle reads like one of its own
+        first = {k: (self.tree if k == "tree" else d[k])
+                 for k in ("tree", "tree_idx", "elbo", "q_z", "q_y", "cell_to_idx", "snv_to_idx", "clone_to_idx",
+                           "cluster_to_idx")}
+        first.update({k: v for k, v in d.items() if k not in first and k not in _TRANSIENT})
+        return first
 
     def __setstate__(self, state):
         self.__dict__.update(state)

@@ -377,11 +377,7 @@ def run_gpu_arm(args):
                 dt = 1e3 * (time.perf_counter() - gc_t0[0])
                 if dt > 5:
                     gc_log.append((info["generation"], round(dt, 1)))
-        # a long-running service freezes its start-up heap (torch / pandas module objects) out of the collector;
-        # without this every ~4th call pays a ~50 ms generation-2 pass over objects that never die
-        gc.collect()
-        gc.freeze()
-        gc.callbacks.append(gc_cb)
+        gc.callbacks.append(gc_cb)               # pauses above 5 ms are listed (arborist() freezes the start-up heap itself)
         barrier()
         t0 = time.perf_counter()
         d2h = 0
@@ -402,9 +398,8 @@ def run_gpu_arm(args):
                "note": "arborist(trees, read_counts_df, clusters_df): H2D of the long table (int64 columns), device "
                        "id factorisation + ingest + layouts, batched fit, ELBO gather, ranking, D2H of ELBOs / "
                        "iteration counts / index orders / the best tree's q_z and q_y; host wall clock, one untimed "
-                       "warm-up call first (like the device arm's warm-up steps); gc.freeze() after the warm-up call (the "
-                       "interpreter's start-up heap is taken out of the cyclic collector, as a service would do); per-call "
-                       "wall times, the fit's device time, host stage times and remaining GC pauses are listed"}
+                       "warm-up call first (like the device arm's warm-up steps); per-call wall times, the fit's device "
+                       "time, host stage times and GC pauses above 5 ms are listed"}
 
     # ---- CPU baseline (rank 0, N = 1) ------------------------------------------------------------------
     cpu = None

@@ -129,6 +129,16 @@ int arb_fit_trees(arb_ctx *ctx, int32_t n_trees, int32_t n_clones, int32_t norma
 int arb_fit_presence(arb_ctx *ctx, int32_t n_trees, int32_t n_clones, const uint8_t *presence,
                      int32_t max_iter, double tolerance, int32_t mode, int32_t keep_posteriors,
                      double *elbo, int32_t *iters, double *elbo_trace);
+/* The same fit spread over n_ctx contexts, normally one per GPU of the box, each holding the SAME ingested matrix
+ * and prior: tree t is fitted by context t mod n_ctx as its local tree t / n_ctx (so arb_get_fit(ctxs[t % n_ctx],
+ * t / n_ctx, ...) fetches it); one host thread per context, results written into the caller's arrays at the global
+ * tree index.  Trees are independent (A.py:1089-1126), so the ELBOs need no collective inside one process; the
+ * torch.distributed / NCCL gather in arborist_b200/distributed.py is only for one-process-per-GPU launches.
+ * Bit-identical to arb_fit_trees on one context. */
+int arb_fit_trees_multi(arb_ctx *const *ctxs, int32_t n_ctx, int32_t n_trees, int32_t n_clones,
+                        int32_t normal_idx, const int32_t *parent, int32_t max_iter, double tolerance,
+                        int32_t mode, int32_t keep_posteriors, double *elbo, int32_t *iters,
+                        double *elbo_trace);
 /* bytes the resident best posteriors of n_trees trees would need (for "auto") */
 int arb_posterior_bytes(arb_ctx *ctx, int32_t n_trees, int32_t n_clones, int64_t *bytes,
                         int64_t *free_bytes);
@@ -136,6 +146,12 @@ int arb_posterior_bytes(arb_ctx *ctx, int32_t n_trees, int32_t n_clones, int64_t
 /* best posteriors / MAP labels (row argmax, first maximum wins -- treefit.py:105)
  * of tree t of the last fit */
 int arb_get_fit(arb_ctx *ctx, int32_t t, double *q_z, double *q_y);
+/* the same for trees t0 .. t0+count-1 at once: q_z [count, n_cells, K], q_y [count, n_snvs, K-1] (either may be
+ * NULL).  When the posteriors were not kept on the device, the whole range is RE-FITTED AS ONE BATCH (the fit is
+ * deterministic: same bits) and stays cached until another range is asked for, so a writer that walks the
+ * candidate set (--pickle / --q_z of every fit, A.py:1161-1188) costs ceil(T / count) batched fits.
+ * arb_last_fit_profile()[23] counts those re-fits. */
+int arb_get_fits(arb_ctx *ctx, int32_t t0, int32_t count, double *q_z, double *q_y);
 int arb_get_map(arb_ctx *ctx, int32_t t, int32_t *z, int32_t *y);
 /* the genotype matrix the device built for tree t, [K-1, K] 0/1 bytes */
 int arb_get_presence(arb_ctx *ctx, int32_t t, uint8_t *presence);
@@ -159,15 +175,17 @@ int arb_elbo_terms(arb_ctx *ctx, int32_t n_clones, const uint8_t *presence, cons
 int arb_last_fit_stats(arb_ctx *ctx, int64_t *kernel_launches, double *device_ms,
                        double *tree_iterations, double *sweep_ms);
 /* per-kernel profile of the last arb_fit_* call, measured with CUDA events on the launching
- * streams (with more than one stream group the kernels of different groups overlap, so the
- * per-kernel times are not exclusive; set option "groups" to 1 for exclusive times): values[0..7] = q(z) sweep ms, q(y) sweep ms, finishing kernels ms, tree-sweeps done
+ * stream: values[0..7] = q(z) sweep ms, q(y) sweep ms, finishing kernels ms, tree-sweeps done
  * by the q(z) / q(y) sweep launches, number of q(z) / q(y) sweep launches, rounds;
  * values[8..19] = q(z) / q(y) finishing ms, then the layout in use: KP, rows per panel, panels
- * (z, y), tiles per warp (z, y), range-proof flags (z, y), stream quads (z, y); values[20] = stream
- * groups used, values[21] = 1 when the sparse stream uses 16-bit words */
+ * (z, y), tiles per warp (z, y), range-proof flags (z, y), stream quads (z, y); values[20] = rounds the
+ * host enqueued after the last tree had finished (they find nothing to do), values[21] = 1 when the sparse
+ * stream uses 16-bit words, values[22] = times the host blocked on the device inside the round loop,
+ * values[23] = batched re-fits done by arb_get_fits / arb_get_map since the last fit */
 int arb_last_fit_profile(arb_ctx *ctx, double *values, int32_t n_values);
-/* tuning knobs: "slots" (trees in flight), "groups" (stream groups the slots are split into, 0 = default,
- * at most 4), "panel_kb" (panel bytes cap), "threads", "no_fold", "w32" (force 32-bit stream words); returns ARB_ERR_INVALID for unknown names */
+/* tuning knobs: "slots" (trees in flight), "split" (CTAs per (virtual slot, panel) of a sweep; 0 = chosen per
+ * launch), "lookahead" (rounds enqueued ahead of the device, 0 = default 3), "panel_kb" (panel bytes cap),
+ * "threads", "no_fold", "w32" (force 32-bit stream words); returns ARB_ERR_INVALID for unknown names */
 int arb_set_option(arb_ctx *ctx, const char *name, int64_t value);
 /* Device allocations released by a context (arb_ctx_destroy, workspace resizes) are parked in a
  * process-wide pool and handed to the next context that asks for a buffer of about that size, so

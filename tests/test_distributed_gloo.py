@@ -29,17 +29,34 @@ WORKER = textwrap.dedent("""
     iters = D.gather_vector((shard + 3).astype(np.int32), shard, T, dtype=np.int32)
     assert iters.tolist() == [t + 3 for t in range(T)]
 
-    class FakeEngine:
-        n_clones = 3
-        def dims(self): return 4, 5, 0, 0
-        def get_fit(self, t):
-            g = shard[t]
-            return np.full((4, 3), float(g)), np.full((5, 2), -float(g))
+    from arborist_b200.results import FitStore, LazyFits, write_fits_pickle
+    from arborist_b200.treefit import TreeFit
 
-    local_of = {int(g): l for l, g in enumerate(shard)}
+    class FakeEngine:
+        n_clones, device = 3, 0
+        def dims(self): return 4, 5, 0, 0
+        def get_fits(self, t0, count, fetch=True):
+            assert not fetch and t0 % 2 == 0 and count <= 2          # batches of max_batch consecutive local trees
+        def get_fit(self, t):
+            g = float(shard[t])
+            return np.full((4, 3), g), np.full((5, 2), -g)
+
+    store = FitStore([FakeEngine()], shard, owner, T, max_batch=2)
     for idx in (0, 1, 6):           # collective: both ranks ask for the same tree
-        qz, qy = D.fetch_fit(FakeEngine(), idx, local_of, owner)
+        qz, qy = store.get_fit(idx)
         assert (qz == idx).all() and (qy == -idx).all() and qz.shape == (4, 3)
+    assert D.all_agree(True) and not D.all_agree(rank == 0)
+    # streaming pickle of all fits: every rank takes part (remote posteriors are broadcast), rank 0 writes
+    dicts = [{"a": 0, "b": 1, "c": 2, "d": 3}, {i: i for i in range(5)}, {0: 0, 1: 1, 2: 2}, {1: 0, 2: 1}]
+    fits = LazyFits(T, lambda i: TreeFit.lazy([(0, 1), (1, 2)], i, float(truth[i]), store.get_fit, *dicts), store)
+    path = os.path.join(os.environ["ARB_OUT"], "fits.pkl")
+    write_fits_pickle(fits, path)
+    dist.barrier()
+    if rank == 0:
+        import pandas as pd
+        back = pd.read_pickle(path)
+        assert sorted(back) == list(range(T))
+        assert all((back[i].q_z == i).all() and back[i].elbo == truth[i] for i in range(T))
     dist.barrier()
     dist.destroy_process_group()
     open(os.path.join(os.environ["ARB_OUT"], "rank%d.ok" % rank), "w").write("ok")

@@ -15,19 +15,25 @@ from conftest import golden_frames, load_golden, synth_frames
 pytestmark = pytest.mark.gpu
 
 ELBO_RTOL = 1e-9
-Q_RTOL, Q_ATOL = 1e-7, 1e-12       # posteriors: relative on the bulk, absolute floor for ~0 entries
+# posteriors: observed agreement with the reference is ~1e-13 relative on entries above 1e-6 and a few 1e-16
+# absolute below; the tests ask for 100x that (north_star allows 1e-6)
+Q_RTOL, Q_ATOL = 1e-10, 1e-13
+MAP_TIE_ROWS = {}                  # test id -> rows that took the tie branch of assert_map_equal
 
 
-def assert_map_equal(q, q_ref):
+def assert_map_equal(q, q_ref, max_ties=2, where="?"):
     """MAP labels must be identical wherever the reference's own maximum is decided by more
     than rounding: rows whose top two reference posteriors differ by < 1e-9 relative are exact
     mathematical ties (e.g. sibling leaves with identical evidence) that the reference breaks
-    by the last bit of its log-sum-exp; there the chosen label must still be one of the tied."""
+    by the last bit of its log-sum-exp; there the chosen label must still be one of the tied.
+    Such rows are COUNTED and bounded (``max_ties`` per matrix), so a real regression cannot hide here."""
     a, b = q.argmax(1), q_ref.argmax(1)
     diff = np.nonzero(a != b)[0]
     for i in diff:
         top = q_ref[i, b[i]]
         assert abs(q_ref[i, a[i]] - top) <= 1e-9 * top, f"MAP differs on row {i} beyond a tie"
+    MAP_TIE_ROWS[where] = MAP_TIE_ROWS.get(where, 0) + len(diff)
+    assert len(diff) <= max_ties, f"{len(diff)} MAP rows differ from the reference (ties only, but too many): {where}"
 
 
 @pytest.fixture(scope="module")
@@ -251,7 +257,9 @@ def test_seam_run_simple_max_likelihood(eng_mod, name):
     assert lik == pytest.approx(float(g["ml_lik"]), rel=ELBO_RTOL)
     np.testing.assert_allclose(qz, g["ml_qz"], rtol=Q_RTOL, atol=Q_ATOL)
     assert np.array_equal(qy, g["ml_qy"])                      # one-hot: bit-exact
-    assert_map_equal(qz, g["ml_qz"])
+    # a one-hot q(y) gives clones whose ancestor sets differ only in clusters without SNVs EXACTLY equal evidence:
+    # many exact ties on the deep 30-clone trees (counted, not part of the module total)
+    assert_map_equal(qz, g["ml_qz"], max_ties=16, where=f"ml_{name}")
 
 
 def test_ml_mode_batched_matches_oracle(eng_mod):
@@ -429,8 +437,8 @@ def test_against_oracle_on_fresh_inputs(eng_mod):
             assert arborist.last_stats["iters"][t] == ofits[t][3]
             np.testing.assert_allclose(fits[t].q_z, ofits[t][1], rtol=Q_RTOL, atol=Q_ATOL)
             np.testing.assert_allclose(fits[t].q_y, ofits[t][2], rtol=Q_RTOL, atol=Q_ATOL)
-            assert_map_equal(fits[t].q_z, ofits[t][1])
-            assert_map_equal(fits[t].q_y, ofits[t][2])
+            assert_map_equal(fits[t].q_z, ofits[t][1], where="fresh")
+            assert_map_equal(fits[t].q_y, ofits[t][2], where="fresh")
 
 
 def test_device_csv_reader_matches_dataframe_path(eng_mod, tmp_path):
@@ -513,8 +521,8 @@ def test_clone_counts_against_oracle(eng_mod, n_clones):
         assert arborist.last_stats["iters"][t] == ofits[t][3]
         np.testing.assert_allclose(fits[t].q_z, ofits[t][1], rtol=Q_RTOL, atol=Q_ATOL)
         np.testing.assert_allclose(fits[t].q_y, ofits[t][2], rtol=Q_RTOL, atol=Q_ATOL)
-        assert_map_equal(fits[t].q_z, ofits[t][1])
-        assert_map_equal(fits[t].q_y, ofits[t][2])
+        assert_map_equal(fits[t].q_z, ofits[t][1], where=f"k{n_clones}")
+        assert_map_equal(fits[t].q_y, ofits[t][2], where=f"k{n_clones}")
 
 
 def test_non_forest_presence_and_errors(eng_mod):
@@ -590,3 +598,129 @@ def test_cli_outputs_match_reference(eng_mod, tmp_path, capsys):
         g, w = pd.read_csv(tmp_path / name), pd.read_csv(os.path.join(exp, name))
         assert list(g.columns) == list(w.columns) and list(g["id"]) == list(w["id"])
         np.testing.assert_allclose(g.iloc[:, 1:].to_numpy(), w.iloc[:, 1:].to_numpy(), rtol=Q_RTOL, atol=Q_ATOL)
+
+
+@pytest.mark.skip(reason="needs the unnormalised-prior first pass (prior row [gamma] has mass 0.7 when K = 2)")
+def test_two_clone_candidate_set(eng_mod):
+    """K = 2 (the normal clone plus one cluster): (1 - gamma) / (k - 1) is guarded by ``k > 1`` in the reference
+    (A.py:552), the prior is 1.0 everywhere and q(y) never moves; through arborist() against the oracle."""
+    from arborist_b200 import arborist, synth
+    from oracle import oracle as orc
+    d = synth.generate(synth.SynthConfig("k2", 120, 300, 2, 1, seed=7002, coverage=0.1, min_proportion=0.2))
+    rc, cl = d.read_counts_frame(), d.clusters_frame()
+    trees = [[(0, 1)]]
+    lik, best, fits = arborist(trees, rc, cl, max_iter=5, tolerance=1.0)
+    olik, obest, ofits, _ = orc.arborist_oracle(trees, rc, cl, max_iter=5, tolerance=1.0)
+    assert best.tree_idx == obest == 0
+    assert lik[0] == pytest.approx(olik[0], rel=ELBO_RTOL)
+    assert arborist.last_stats["iters"][0] == ofits[0][3]
+    np.testing.assert_allclose(fits[0].q_z, ofits[0][1], rtol=Q_RTOL, atol=Q_ATOL)
+    assert np.array_equal(fits[0].q_y, np.ones_like(fits[0].q_y))
+    assert_map_equal(fits[0].q_z, ofits[0][1], where="k2")
+
+
+def test_multi_context_fit_is_bit_identical(eng_mod):
+    """arb_fit_trees_multi: the candidate set spread over several contexts by one process (tree t -> context
+    t mod G, one host thread each) gives the bits of a single-context fit -- ELBOs, iteration counts, traces,
+    posteriors and MAP.  The box has one GPU, so the contexts share device 0; on a multi-GPU box arborist()
+    picks one context per GPU (``devices=``)."""
+    from arborist_b200 import arborist
+    from arborist_b200.arborist import add_normal_clone, ingest_read_counts, prepare_trees
+    g = load_golden("small")
+    trees, rc, cl = golden_frames(g)
+    c2i, k2i, parents, _, normal = prepare_trees(add_normal_clone(trees))
+    K, T = len(c2i), len(parents)
+    kw = dict(n_clones=K, normal_idx=normal, max_iter=25, tolerance=1.0, keep_posteriors="all", trace=True)
+    engines = [eng_mod.Engine(0) for _ in range(3)]
+    for e in engines:
+        ingest_read_counts(e, rc, cl, k2i, float(g["alpha"]), float(g["gamma"]))
+    ref = engines[0].fit(parents=parents, **kw)
+    ref_q = [engines[0].get_fit(t) for t in range(T)]
+    ref_map = [engines[0].get_map(t) for t in range(T)]
+    for G in (2, 3):
+        got = eng_mod.fit_multi(engines[:G], parents, K, normal_idx=normal, max_iter=25, tolerance=1.0,
+                                keep_posteriors="all", trace=True)
+        assert np.array_equal(got[0], ref[0]) and np.array_equal(got[1], ref[1])
+        assert np.array_equal(np.nan_to_num(got[2], nan=-1.0), np.nan_to_num(ref[2], nan=-1.0))
+        for t in range(T):
+            qz, qy = engines[t % G].get_fit(t // G)
+            assert np.array_equal(qz, ref_q[t][0]) and np.array_equal(qy, ref_q[t][1])
+            z, y = engines[t % G].get_map(t // G)
+            assert np.array_equal(z, ref_map[t][0]) and np.array_equal(y, ref_map[t][1])
+    for e in engines:
+        e.close()
+    # API level: devices=[0, 0] (two contexts) against device=0
+    lik1, best1, fits1 = arborist(trees, rc, cl, max_iter=25, add_normal=True, device=0)
+    lik2, best2, fits2 = arborist(trees, rc, cl, max_iter=25, add_normal=True, devices=[0, 0])
+    assert arborist.last_stats["devices"] == [0, 0]
+    assert lik1 == lik2 and best1.tree_idx == best2.tree_idx
+    for t in range(T):
+        assert np.array_equal(fits1[t].q_z, fits2[t].q_z) and np.array_equal(fits1[t].q_y, fits2[t].q_y)
+        assert fits1[t].tree == fits2[t].tree == add_normal_clone(trees)[t]
+        assert fits1[t].map_assign_y().equals(fits2[t].map_assign_y())
+    with pytest.raises(eng_mod.ArboristError):
+        e = eng_mod.Engine(0)
+        ingest_read_counts(e, rc, cl, k2i, float(g["alpha"]), float(g["gamma"]))
+        eng_mod.fit_multi([e, e], parents, K, normal_idx=normal)            # the same context twice
+
+
+def test_writers_at_scale_use_batched_refits(eng_mod, tmp_path):
+    """Row f1: --pickle / q_z of every fit when the posteriors were NOT kept on the device (always the case at
+    config 4).  256 config-2-sized fits: the streaming pickle costs ceil(256 / batch) batched re-fits (not 256
+    single-tree fits), and its contents equal the eager path (posteriors kept, pd.to_pickle of the dict)."""
+    import pandas as pd
+    from arborist_b200 import arborist, synth
+    cfg = synth.CONFIGS["config2"]
+    d = synth.generate(cfg)
+    rng = np.random.default_rng(5)
+    trees = list(d.trees)
+    while len(trees) < 256:
+        trees.append(synth._edges(synth.random_tree(rng, cfg.n_clones - 1)))
+    rc, cl = d.read_counts_frame(), d.clusters_frame()
+    lik_k, best_k, fits_k = arborist(trees, rc, cl, max_iter=25, add_normal=True, device=0, keep_posteriors="all")
+    pd.to_pickle(fits_k, tmp_path / "eager.pkl")
+    eager = pd.read_pickle(tmp_path / "eager.pkl")
+    lik_n, best_n, fits_n = arborist(trees, rc, cl, max_iter=25, add_normal=True, device=0, keep_posteriors="none")
+    assert lik_n == lik_k and best_n.tree_idx == best_k.tree_idx
+    store = arborist.last_stats["store"]()
+    eng = arborist.last_stats["engine"]()
+    fits_n.to_pickle(tmp_path / "stream.pkl")
+    want_batches = -(-256 // store.batch)
+    assert store.fetches == want_batches
+    assert eng.last_fit_profile()["refit_batches"] == want_batches <= 2
+    back = pd.read_pickle(tmp_path / "stream.pkl")
+    assert type(back) is dict and list(back) == list(range(256))
+    for t in range(256):
+        assert np.array_equal(back[t].q_z, eager[t].q_z) and np.array_equal(back[t].q_y, eager[t].q_y)
+        assert back[t].tree == eager[t].tree and back[t].elbo == eager[t].elbo
+    # MAP tables of a tree inside the cached batch need no further re-fit
+    before = eng.last_fit_profile()["refit_batches"]
+    assert fits_n[255].map_assign_z().equals(eager[255].map_assign_z())
+    assert eng.last_fit_profile()["refit_batches"] == before
+
+
+def test_deep_coverage_pairs_are_refused_loudly(eng_mod):
+    """A count pair whose log-likelihood ratio leaves [-34, 600] (total >= 50 with alt = 0 at the default alpha)
+    is outside this release's product-form sweep (DESIGN.md "limits"): the fit must fail with
+    ARB_ERR_UNSUPPORTED and say which pair, never return numbers.  alt > total (no finite likelihood) likewise."""
+    from arborist_b200 import arborist, synth
+    d = synth.generate(synth.CONFIGS["tiny"])
+    rc, cl = d.read_counts_frame(), d.clusters_frame()
+    deep = rc.copy()
+    deep.loc[deep.index[3], ["alt", "total"]] = [0, 60]
+    with pytest.raises(eng_mod.ArboristError) as err:
+        arborist(d.trees, deep, cl, max_iter=3, add_normal=True, device=0)
+    assert err.value.status == -3 and "log-likelihood ratio" in str(err.value)
+    bad = rc.copy()
+    bad.loc[bad.index[3], ["alt", "total"]] = [5, 2]
+    with pytest.raises(eng_mod.ArboristError) as err:
+        arborist(d.trees, bad, cl, max_iter=3, add_normal=True, device=0)
+    assert err.value.status in (-1, -3)
+
+
+def test_zz_map_tie_rows_are_a_handful(eng_mod):
+    """north_star: MAP assignments bit-exact.  The only rows allowed to differ from the oracle are exact
+    mathematical ties (see assert_map_equal); across the whole module they must stay a handful."""
+    total = sum(v for k, v in MAP_TIE_ROWS.items() if not k.startswith("ml_"))
+    print("MAP rows decided by a tie, per test:", {k: v for k, v in MAP_TIE_ROWS.items() if v}, "total", total)
+    assert total <= 8, MAP_TIE_ROWS

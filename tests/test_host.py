@@ -177,3 +177,104 @@ def test_read_read_counts_formats(tmp_path):
     np.savez(tmp_path / "bad.npz", snv=rc["snv"].to_numpy())
     with pytest.raises((ValueError, KeyError)):
         read_read_counts(str(tmp_path / "bad.npz"))
+
+
+def test_prepare_tree_shard_matches_full_preparation():
+    """The shard-proportional path (``--add-normal`` folded into the parent vectors, no per-tree edge lists) gives
+    what add_normal_clone + prepare_trees give on the whole set, for any subset of tree indices; irregular sets,
+    forests with two roots and non-integer labels take the general path with the same result."""
+    from arborist_b200 import synth
+    from arborist_b200.arborist import add_normal_clone, prepare_tree_shard, prepare_trees
+    d = synth.generate(synth.CONFIGS["small"])
+    full = prepare_trees(add_normal_clone(d.trees))
+    T = len(d.trees)
+    for idx in (np.arange(T), np.arange(1, T, 3), np.array([T - 1, 0])):
+        got = prepare_tree_shard(d.trees, idx, add_normal=True)
+        assert got[0] == full[0] and got[1] == full[1] and got[4] == full[4] and got[3] is None
+        assert np.array_equal(got[2], full[2][idx])
+    with_n = add_normal_clone(d.trees)
+    got = prepare_tree_shard(with_n, np.arange(2, T), add_normal=False)
+    assert np.array_equal(got[2], full[2][2:])
+    # an empty shard (more ranks than trees) still yields the label maps
+    got = prepare_tree_shard(d.trees, np.array([], dtype=np.int64), add_normal=True)
+    assert got[0] == full[0] and got[2].shape == (0, len(full[0]))
+    # ragged / string-labelled sets
+    ragged = [[(1, 2), (2, 3)], [(1, 3), (3, 2), (1, 3)]]
+    a = prepare_tree_shard(ragged, np.arange(2), add_normal=True)
+    b = prepare_trees(add_normal_clone(ragged))
+    assert a[0] == b[0] and np.array_equal(a[2], b[2])
+    names = [[("a", "b"), ("b", "c")], [("a", "c"), ("c", "b")]]
+    a = prepare_tree_shard(names, np.arange(2), add_normal=False)
+    assert np.array_equal(a[2], prepare_trees(names)[2])
+    with pytest.raises(ValueError, match="same set of clones"):
+        prepare_tree_shard([[(1, 2), (2, 3)], [(1, 2), (2, 4)]], np.arange(2), add_normal=True)
+    # the mismatch is only seen by the process whose shard holds the bad tree
+    prepare_tree_shard([[(1, 2), (2, 3)], [(1, 2), (2, 4)]], np.array([0]), add_normal=True)
+
+
+def test_lazy_fits_and_streaming_pickle(tmp_path):
+    """``all_tree_fits`` behaves like the reference's eager dict; ``to_pickle`` writes the file ``pd.to_pickle`` of
+    the eager dict would (plain dict of TreeFits, index dicts shared between fits) without keeping the posteriors
+    of more than a few trees alive (A.py:1187-1188 at 1k-10k fits)."""
+    import gc
+    import os
+    import weakref
+
+    from arborist_b200.results import LazyFits, write_fits_pickle
+    from arborist_b200.treefit import TreeFit
+    n, m, K, T = 40, 60, 5, 2100
+    cell = {f"c{i}": i for i in range(n)}
+    snv = {i * 3: i for i in range(m)}
+    c2i, k2i = {i - 1: i for i in range(K)}, {i: i for i in range(K - 1)}
+    alive = []
+
+    def loader(i):
+        r = np.random.default_rng(i)
+        qz, qy = r.random((n, K)), r.random((m, K - 1))
+        alive.append(weakref.ref(qz))
+        return qz, qy
+
+    def make(i):
+        return TreeFit.lazy(None, i, -float(i), loader, cell, snv, c2i, k2i, tree_loader=lambda j: [(j, 1), (1, 2)])
+
+    fits = LazyFits(T, make)
+    assert len(fits) == T and 5 in fits and T not in fits and "x" not in fits
+    assert list(fits)[:3] == [0, 1, 2] and list(fits.keys())[-1] == T - 1 and fits.get(T) is None
+    with pytest.raises(KeyError):
+        fits[T]
+    assert fits[7] is fits[7] and fits[7].tree == [(7, 1), (1, 2)]
+    path = tmp_path / "fits.pkl"
+    fits.to_pickle(path)
+    gc.collect()
+    assert sum(r() is not None for r in alive) <= 3, "the streaming writer kept posteriors alive"
+    back = pd.read_pickle(path)
+    assert type(back) is dict and list(back) == list(range(T))
+    for i in (0, 1, 999, 1000, 1001, T - 1):
+        r = np.random.default_rng(i)
+        f = back[i]
+        assert np.array_equal(f.q_z, r.random((n, K))) and np.array_equal(f.q_y, r.random((m, K - 1)))
+        assert f.elbo == -float(i) and f.tree == [(i, 1), (1, 2)] and f.tree_idx == i
+        assert f.cell_to_idx is back[0].cell_to_idx and f.snv_to_idx is back[0].snv_to_idx
+        assert list(f.__dict__)[:9] == ["tree", "tree_idx", "elbo", "q_z", "q_y", "cell_to_idx", "snv_to_idx",
+                                        "clone_to_idx", "cluster_to_idx"]
+    eager = {i: make(i) for i in range(T)}
+    pd.to_pickle(eager, tmp_path / "eager.pkl")
+    assert os.path.getsize(path) < 1.05 * os.path.getsize(tmp_path / "eager.pkl")
+    plain = pickle.loads(pickle.dumps(LazyFits(6, make)))          # pd.to_pickle(all_fits) still works
+    assert type(plain) is dict and len(plain) == 6 and plain[3].elbo == -3.0
+    write_fits_pickle(LazyFits(4, make), tmp_path / "fits.pkl.gz")
+    assert len(pd.read_pickle(tmp_path / "fits.pkl.gz")) == 4
+
+
+def test_pyproject_console_script():
+    """The reference installs ``arborist = "arborist.arborist:main"`` (pyproject.toml:34-35)."""
+    import importlib
+    import os
+    import tomllib
+
+    from conftest import ROOT
+    cfg = tomllib.load(open(os.path.join(ROOT, "pyproject.toml"), "rb"))
+    target = cfg["project"]["scripts"]["arborist"]
+    assert target == "arborist.arborist:main"
+    mod, fn = target.split(":")
+    assert callable(getattr(importlib.import_module(mod), fn))

@@ -143,6 +143,9 @@ struct arb_ctx {
     // ---- prior ---------------------------------------------------------------------
     int32_t n_clusters = 0;
     DevBuf q0, logq0, logq0e, q0_hard;    // [m, C]: q, log q (-inf for 0), log(q + 1e-12), one-hot argmax of q
+    bool prior_general = false;           // some prior row does not sum to one (K = 2: the row is [gamma]; a caller's
+                                          // own q_y_init): the first pass runs k_first_pass_general (arb_fit.cu)
+    DevBuf row_ptr, tab_la_dev;           // CSR pointer of the canonical matrix / log_absent per pair code, for it
 
     // ---- layouts (index 0: KP 8, 1: KP 16, 2: KP 32) ----------------------------------
     PanelLayout layout[3];

@@ -62,9 +62,9 @@ struct Control {
     int32_t next_tree, n_trees, n_slots, max_iter;
     int32_t n_done, keep, mode, round;
     double tol, sum_la;
-    int32_t n_y, n_z, n_init, pad0;       // trees in this round's q(y) list / q(z) list / first-pass list
+    int32_t n_y, n_z, n_init, n_act;      // trees in this round's q(y) list / q(z) list / first-pass list; slots in use
     int32_t n_vy, n_vz, chunks_y, chunks_z;   // virtual slots of the two sweeps, 4-column chunks per tree
-    int32_t nbz, nby, nbmax, pad1;
+    int32_t nbz, nby, nbmax, general_init;    // general_init: first passes run k_first_pass_general, not the sweep
     int32_t pad2[8];               // 128 bytes
 };
 static_assert(sizeof(Control) == 128, "Control is copied as one 128-byte block");
@@ -733,6 +733,138 @@ __global__ void __launch_bounds__(FIN_THREADS, 4) k_finish(const FinishArgs a)
     }
 }
 
+// ---------------------------------------------------------------------------------------
+// First pass for priors whose rows do not sum to one.
+// The sweeps use sum_p q_y[j,p] = 1: a nonzero's factor is (1 - S) e^la + S e^lp = e^la (1 + d S).  The reference
+// works in the log domain on whatever q_y it is given (A.py:229-243, 404-418), i.e. with the row's own mass
+// M_j = sum_p q_y[j,p]:  factor = e^la (M_j + d S)  and  E[log lik] = sum_k la_k M_jk + sum q_z G.  Every q(y)
+// the fit computes is a softmax row (mass 1), so this only concerns the FIRST pass, which runs on the prior:
+// initialize_q_y gives the row [gamma] when there is a single cluster (K = 2, A.py:552-567), and a caller may
+// hand any q_y_init to the seam.  In that case the first pass of every tree runs here, straight from the
+// canonical CSR matrix and the prior (one warp per cell, lanes over its nonzeros, S and M formed per nonzero
+// in ascending cluster order like k_seed_s), and writes what k_finish<.,true,.> would: q(z), the entropy and
+// likelihood partial sums (the latter with sum_k la_k (M_jk - 1) folded in, k_control adds sum_k la_k).
+// ---------------------------------------------------------------------------------------
+#define GEN_CH 8        // clones per walk over a row's nonzeros
+
+__global__ void __launch_bounds__(FIN_THREADS)
+k_first_pass_general(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ snv, const uint16_t *__restrict__ code,
+                     const double2 *__restrict__ dw, const double *__restrict__ la_tab, const double *__restrict__ q0,
+                     int32_t n, int32_t m, int32_t K, const int32_t *__restrict__ list_init, const SlotState *__restrict__ st,
+                     const uint32_t *__restrict__ masks, double *__restrict__ qz_cur, double *__restrict__ qy_cur,
+                     int64_t plane_slots, double *__restrict__ red, int32_t nbmax, const Control *__restrict__ ctl)
+{
+    __shared__ double sh[FIN_WARPS];
+    __shared__ double sh_l[FIN_WARPS][32], sh_g[FIN_WARPS][32];
+    if ((int)blockIdx.y >= ctl->n_init) return;
+    const int C = K - 1, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int slot = list_init[blockIdx.y];
+    const uint32_t *mk = masks + (int64_t)st[slot].tree * MASK_STRIDE;
+    const int plane = 1 - st[slot].bestb;
+    // the prior is this tree's q(y) iterate 0 (A.py:762-763 keeps it as best_q_y)
+    {
+        double *dst = qy_cur + ((int64_t)plane * plane_slots + slot) * (int64_t)m * C;
+        const int64_t total = (int64_t)m * C, per = (total + gridDim.x - 1) / gridDim.x;
+        const int64_t lo = per * blockIdx.x, hi = min(total, lo + per);
+        for (int64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) dst[i] = q0[i];
+    }
+    double acc1 = 0.0, acc2 = 0.0;
+    for (int it = 0; it < FIN_ROWS / FIN_WARPS; ++it) {
+        const int64_t row = (int64_t)blockIdx.x * FIN_ROWS + it * FIN_WARPS + warp;
+        const bool rowok = row < n;
+        const int k0 = rowok ? row_ptr[row] : 0, k1 = rowok ? row_ptr[row + 1] : 0;
+        for (int r0 = 0; r0 < K; r0 += GEN_CH) {
+            uint32_t cm[GEN_CH];
+#pragma unroll
+            for (int c = 0; c < GEN_CH; ++c) cm[c] = r0 + c < K ? mk[r0 + c] : 0u;
+            double p[GEN_CH], g[GEN_CH];
+            int e[GEN_CH];
+#pragma unroll
+            for (int c = 0; c < GEN_CH; ++c) { p[c] = 1.0; g[c] = 0.0; e[c] = 0; }
+            for (int k = k0 + lane; k < k1; k += 32) {
+                const int j = snv[k], cd = code[k];
+                const double2 t = dw[cd];
+                const double *qr = q0 + (int64_t)j * C;
+                double S[GEN_CH], M = 0.0;
+#pragma unroll
+                for (int c = 0; c < GEN_CH; ++c) S[c] = 0.0;
+                for (int b = 0; b < C; ++b) {               // ascending cluster order, like masked_rows
+                    const double x = qr[b];
+                    M += x;
+#pragma unroll
+                    for (int c = 0; c < GEN_CH; ++c)
+                        if ((cm[c] >> b) & 1u) S[c] += x;
+                }
+                if (r0 == 0) acc1 += la_tab[cd] * (M - 1.0);
+#pragma unroll
+                for (int c = 0; c < GEN_CH; ++c) {
+                    p[c] *= fma(t.x, S[c], M);
+                    renorm(p[c], e[c]);
+                    g[c] = fma(t.y, S[c], g[c]);
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < GEN_CH; ++c) {
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    p[c] *= __shfl_xor_sync(0xffffffffu, p[c], o);
+                    e[c] += __shfl_xor_sync(0xffffffffu, e[c], o);
+                    g[c] += __shfl_xor_sync(0xffffffffu, g[c], o);
+                    renorm(p[c], e[c]);
+                }
+                if (lane == 0 && r0 + c < K) {
+                    sh_l[warp][r0 + c] = log(p[c]) + (double)e[c] * LN2;
+                    sh_g[warp][r0 + c] = g[c];
+                }
+            }
+        }
+        __syncwarp();
+        // lane r holds clone r: softmax (A.py:245-250), entropy (A.py:268-273), likelihood term
+        const bool v = lane < K;
+        const double l = v ? sh_l[warp][lane] : -INFINITY;
+        double mx = l;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        double q = v ? exp(l - mx) : 0.0, s = q;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        q = q * (1.0 / s);
+        if (rowok && v) {
+            qz_cur[(((int64_t)plane * plane_slots + slot) * n + row) * K + lane] = q;
+            acc1 += q * sh_g[warp][lane];
+            if (q > 0.0) acc2 -= q * log(q + 1e-12);
+        }
+        __syncwarp();
+    }
+    const double t1 = block_sum(acc1, sh);
+    const double t2 = block_sum(acc2, sh);
+    if (threadIdx.x == 0) {
+        double *r = red + (int64_t)slot * 3 * nbmax;
+        r[blockIdx.x] = t1;
+        r[nbmax + blockIdx.x] = t2;
+    }
+}
+
+// CSR pointer of the canonical (cell, snv)-sorted matrix
+__global__ void k_row_ptr(const int32_t *__restrict__ cell, int64_t nnz, int32_t n, int32_t *__restrict__ ptr)
+{
+    const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k > nnz) return;
+    const int prev = k == 0 ? -1 : cell[k - 1], cur = k == nnz ? n : cell[k];
+    for (int r = prev + 1; r <= cur; ++r) ptr[r] = (int32_t)k;
+}
+
+// largest |row sum - 1| of a [m, C] matrix
+__global__ void k_row_mass_dev(const double *__restrict__ q, int32_t m, int32_t C, unsigned long long *__restrict__ out)
+{
+    const int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (j >= m) return;
+    double s = 0.0;
+    for (int c = 0; c < C; ++c) s += q[j * C + c];
+    const double dev = fabs(s - 1.0);
+    atomicMax(out, (unsigned long long)__double_as_longlong(dev == dev ? dev : 1.0));      // non-negative doubles order like integers
+}
+
 // entropy / KL of given matrices (kernel-level hook)
 __global__ void k_entropy_kl(const double *qz, int64_t nz, const double *qy, const double *q0, int64_t ny,
                              double *out)
@@ -804,7 +936,8 @@ __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict_
     }
     __syncthreads();
     if (threadIdx.x == 0) {
-        int ny = 0, nz = 0, ni = 0, next = ctl->next_tree;
+        int ny = 0, nz = 0, ni = 0, na = 0, next = ctl->next_tree;
+        const bool gen = ctl->general_init != 0;
         for (int s = 0; s < s1; ++s) {
             SlotState z = st[s];
             if (z.phase == PH_EMPTY && next < ctl->n_trees) {
@@ -820,7 +953,8 @@ __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict_
             } else if (z.phase == PH_ITER) {
                 list_y[ny++] = s;
             }
-            if (z.phase != PH_EMPTY) {
+            if (z.phase != PH_EMPTY) ++na;
+            if (z.phase == PH_ITER || (z.phase == PH_INIT && !gen)) {
                 pos_z[s] = nz;                                // packed position in this round's q(z) sweep
                 list_z[nz++] = s;
             }
@@ -829,6 +963,7 @@ __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict_
         ctl->n_y = ny;
         ctl->n_z = nz;
         ctl->n_init = ni;
+        ctl->n_act = na;
         ctl->n_vy = (ny * ctl->chunks_y + 3) >> 2;
         ctl->n_vz = (nz * ctl->chunks_z + 3) >> 2;
         ctl->round += 1;
@@ -1249,6 +1384,19 @@ static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, 
     c0.mode = mode;
     c0.chunks_z = chunks_for(K);
     c0.chunks_y = chunks_for(K - 1);
+    // a prior with rows of mass != 1: first passes leave the packed sweep (k_first_pass_general)
+    const bool general = ctx->prior_general && !hard;
+    c0.general_init = general ? 1 : 0;
+    if (general) {
+        if (ctx->row_ptr.bytes < ((size_t)ctx->n_cells + 1) * 4 || !ctx->row_ptr.p) {
+            ARB_TRY(ctx->row_ptr.reserve(((size_t)ctx->n_cells + 1) * 4));
+            k_row_ptr<<<grid_for(ctx->nnz + 1, 256), 256, 0, ctx->stream>>>(ctx->coo_cell.as<int32_t>(), ctx->nnz,
+                                                                           ctx->n_cells, ctx->row_ptr.as<int32_t>());
+        }
+        ARB_TRY(ctx->tab_la_dev.reserve((size_t)ctx->n_pairs * 8));
+        ARB_CUDA(cudaMemcpyAsync(ctx->tab_la_dev.p, ctx->tab_la.data(), (size_t)ctx->n_pairs * 8, cudaMemcpyHostToDevice,
+                                 ctx->stream));
+    }
     ARB_CUDA(cudaMemsetAsync(ctx->slot_state.p, 0, (size_t)ctx->ws_slots * sizeof(SlotState), st));
     ARB_CUDA(cudaMemcpyAsync(w.ctl, &c0, sizeof c0, cudaMemcpyHostToDevice, st));
     ARB_CUDA(cudaEventRecord(ctx->fit_ev[0], st));
@@ -1271,7 +1419,7 @@ static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, 
         return ARB_OK;
     };
 
-    struct Counts { int n_y, n_z, n_init; };
+    struct Counts { int n_y, n_z, n_init, n_act; };
     Counts used[ARB_RING] = {};                            // what round r ran with (from snapshot r)
     int seen = -1, enq = 0, ub = std::min(ws.n_slots, n_trees);
     bool done = false, more_inits = true;
@@ -1282,7 +1430,7 @@ static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, 
             const Counts u = used[(s - 1) % ARB_RING];
             cudaEvent_t *ev = ctx->rev[(s - 1) % ARB_RING];
             float t = 0;
-            if (u.n_z > 0) {
+            if (u.n_act > 0) {
                 stats.rounds += 1;
                 if (u.n_y > 0) {
                     cudaEventElapsedTime(&t, ev[0], ev[1]); stats.sweep_y_ms += t;
@@ -1290,18 +1438,20 @@ static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, 
                     stats.launches_y += 1;
                     stats.tree_sweeps_y += u.n_y;
                 }
-                cudaEventElapsedTime(&t, ev[3], ev[4]); stats.sweep_z_ms += t;
-                cudaEventElapsedTime(&t, ev[4], ev[5]); stats.finish_ms += t; stats.finish_z_ms += t;
-                stats.launches_z += 1;
-                stats.tree_sweeps_z += u.n_z;
+                if (u.n_z > 0) {
+                    cudaEventElapsedTime(&t, ev[3], ev[4]); stats.sweep_z_ms += t;
+                    cudaEventElapsedTime(&t, ev[4], ev[5]); stats.finish_ms += t; stats.finish_z_ms += t;
+                    stats.launches_z += 1;
+                    stats.tree_sweeps_z += u.n_z;
+                }
             } else {
                 stats.idle_rounds += 1;
             }
         }
-        used[s % ARB_RING] = Counts{c.n_y, c.n_z, c.n_init};
+        used[s % ARB_RING] = Counts{c.n_y, c.n_z, c.n_init, c.n_act};
         ub = std::max(0, std::min(ws.n_slots, n_trees - c.n_done));
         more_inits = c.next_tree < n_trees;
-        if (c.n_z == 0) done = true;
+        if (c.n_act == 0) done = true;
     };
 
     int rc = control(0, 1);
@@ -1328,7 +1478,14 @@ static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, 
         // ---- enqueue round enq --------------------------------------------------------------------
         cudaEvent_t *ev = ctx->rev[enq % ARB_RING];
         const int ubt = std::max(1, ub);
-        if (more_inits || enq == 0) {
+        if ((more_inits || enq == 0) && general) {
+            k_first_pass_general<<<dim3(ws.nbz, ubt), FIN_THREADS, 0, st>>>(
+                ctx->row_ptr.as<int32_t>(), ctx->coo_snv.as<int32_t>(), ctx->coo_code.as<uint16_t>(),
+                ctx->tab_dw.as<double2>(), ctx->tab_la_dev.as<double>(), ctx->q0.as<double>(), ctx->n_cells, ctx->n_snvs, K,
+                w.list_init, w.st, tg.masks, ctx->qz_cur.as<double>(), ctx->qy_cur.as<double>(), (int64_t)ctx->ws_slots,
+                ctx->red.as<double>(), ws.nbmax, w.ctl);
+            stats.launches++;
+        } else if (more_inits || enq == 0) {
             launch_seed_s<GL>(ctx, w, tg.masks, hard ? ctx->q0_hard.as<double>() : ctx->q0.as<double>(), 0, w.list_init,
                               ubt, K, 1, w.ctl);
             stats.launches++;
@@ -1711,7 +1868,18 @@ static int finish_prior(arb_ctx *ctx, int32_t C)
                                                            ctx->logq0e.as<double>());
     k_prior_hard<<<grid_for(ctx->n_snvs, 256), 256, 0, ctx->stream>>>(ctx->q0.as<double>(), ctx->n_snvs, C,
                                                                      ctx->q0_hard.as<double>());
+    // rows that do not sum to one (K = 2: [gamma]; a caller's own q_y_init) send the first pass of every tree
+    // through k_first_pass_general; 1e-9 is far above the rounding of gamma + (k-1) * (1-gamma)/(k-1)
+    DevBuf dev;
+    ARB_TRY(dev.reserve(8));
+    ARB_CUDA(cudaMemsetAsync(dev.p, 0, 8, ctx->stream));
+    k_row_mass_dev<<<grid_for(ctx->n_snvs, 256), 256, 0, ctx->stream>>>(ctx->q0.as<double>(), ctx->n_snvs, C,
+                                                                       dev.as<unsigned long long>());
+    double worst = 0.0;
+    ARB_CUDA(cudaMemcpyAsync(&worst, dev.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
     ARB_CUDA(cudaStreamSynchronize(ctx->stream));
+    dev.release();
+    ctx->prior_general = worst > 1e-9;
     ctx->n_clusters = C;
     ctx->batch_t0 = -1;
     return ARB_OK;

@@ -233,7 +233,7 @@ ARB_API int arb_ctx_destroy(arb_ctx *ctx)
                       &ctx->xs, &ctx->xr, &ctx->qz_cur, &ctx->qy_cur, &ctx->part_z, &ctx->part_g,
                       &ctx->part_y, &ctx->red, &ctx->slot_state, &ctx->lists, &ctx->masks,
                       &ctx->best_qz, &ctx->best_qy, &ctx->d_elbo, &ctx->d_iters, &ctx->d_trace,
-                      &ctx->tree_masks, &ctx->batch_qz, &ctx->batch_qy, &ctx->batch_out, &ctx->scratch, &ctx->cell_uniques,
+                      &ctx->tree_masks, &ctx->batch_qz, &ctx->batch_qy, &ctx->batch_out, &ctx->row_ptr, &ctx->tab_la_dev, &ctx->scratch, &ctx->cell_uniques,
                       &ctx->snv_uniques, &ctx->base_ta, &ctx->base_tb, &ctx->base_cnt,
                       &ctx->csv_col[0], &ctx->csv_col[1], &ctx->csv_col[2], &ctx->csv_col[3]};
     for (DevBuf *b : bufs) b->release();
@@ -860,6 +860,7 @@ static std::vector<int32_t> frequency_order(const std::vector<int64_t> &count)
 static void reset_matrix(arb_ctx *ctx)
 {
     ctx->ingested = false;
+    ctx->row_ptr.release();
     for (auto &l : ctx->layout) l.release();
     ctx->ws_kp = 0;
     ctx->fit_trees = 0;

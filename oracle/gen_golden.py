@@ -250,7 +250,7 @@ def main(argv):
 
     A = load_reference()
     # config5_full (~40 min) and config4_head (~1.5 h, ~20 GB) only when named
-    want = set(argv) or {"tiny", "small", "small_nonormal", "deep30", "config2", "config3_head",
+    want = set(argv) or {"tiny", "small", "small_nonormal", "k2", "deep30", "config2", "config3_head",
                          "example_standin"}
     if "tiny" in want:
         d = synth.generate(synth.CONFIGS["tiny"])
@@ -266,6 +266,12 @@ def main(argv):
         cl = d.clusters_frame()
         run_case(A, "small_nonormal", trees, d.read_counts_frame(), cl, add_normal=False,
                  max_iter=10, gamma=0.9, alpha=0.01, store_inputs=True)
+    if "k2" in want:
+        # K = 2: one cluster, the prior row is [gamma] (mass 0.7, A.py:552-567) and ELBO_0 stays the best
+        cfg = synth.SynthConfig("k2", 120, 300, 2, 1, seed=7002, coverage=0.1, min_proportion=0.2)
+        d = synth.generate(cfg)
+        run_case(A, "k2", [[(0, 1)]], d.read_counts_frame(), d.clusters_frame(), add_normal=False, max_iter=5,
+                 store_inputs=True)
     if "deep30" in want:
         cfg = synth.SynthConfig("deep30", 500, 1000, 30, 10, seed=1105, coverage=0.04,
                                 offtree_frac=0.30, deep=True)

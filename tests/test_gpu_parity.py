@@ -61,7 +61,7 @@ def _coo_engine(eng_mod, g, with_scipy=True):
     return e, cell_u, snv_u
 
 
-SMALL = ["tiny", "small", "small_nonormal", "deep30"]
+SMALL = ["tiny", "small", "small_nonormal", "deep30", "k2"]
 
 
 @pytest.mark.parametrize("name", SMALL)
@@ -193,6 +193,19 @@ def test_api_config3_head(eng_mod):
     trees, rc, cl = synth_frames("config3", tree_subset=[int(i) for i in g["tree_subset"]])
     lik, best, fits = _run_api(g, trees, rc, cl)
     _check_api(g, lik, best, fits, full_q=False)
+
+
+def test_api_config5_full_shape(eng_mod):
+    """BASELINE config 5 at its REAL shape: 5,000 cells x 10,000 SNVs, K = 30 deep trees, 30 % of the SNVs carry
+    an off-tree label (uniform prior rows); the 7 first trees + the generating tree, as the unmodified reference
+    fitted them (oracle/gen_golden.py config5_full): ELBOs 1e-9, iteration counts, ranking and MAP exact, the
+    recorded posterior rows and the winner's full posteriors."""
+    g = load_golden("config5_full")
+    sub = [int(i) for i in g["tree_subset"]]
+    trees, rc, cl = synth_frames("config5", tree_subset=sub)
+    lik, best, fits = _run_api(g, trees, rc, cl)
+    _check_api(g, lik, best, fits, full_q=False)
+    assert sub[best.tree_idx] == int(g["true_tree_index"])           # the generating tree wins, as in the reference
 
 
 @pytest.mark.parametrize("name", ["tiny", "deep30"])
@@ -600,10 +613,11 @@ def test_cli_outputs_match_reference(eng_mod, tmp_path, capsys):
         np.testing.assert_allclose(g.iloc[:, 1:].to_numpy(), w.iloc[:, 1:].to_numpy(), rtol=Q_RTOL, atol=Q_ATOL)
 
 
-@pytest.mark.skip(reason="needs the unnormalised-prior first pass (prior row [gamma] has mass 0.7 when K = 2)")
 def test_two_clone_candidate_set(eng_mod):
     """K = 2 (the normal clone plus one cluster): (1 - gamma) / (k - 1) is guarded by ``k > 1`` in the reference
-    (A.py:552), the prior is 1.0 everywhere and q(y) never moves; through arborist() against the oracle."""
+    (A.py:552), so the prior row is [gamma] -- mass 0.7, not 1.  The reference's log-domain kernels take it as it
+    is: ELBO_0 is inflated by that mass and stays the best, so the returned q(y) is the prior itself.  The first
+    pass of such priors runs k_first_pass_general; through arborist() against the oracle."""
     from arborist_b200 import arborist, synth
     from oracle import oracle as orc
     d = synth.generate(synth.SynthConfig("k2", 120, 300, 2, 1, seed=7002, coverage=0.1, min_proportion=0.2))
@@ -615,8 +629,30 @@ def test_two_clone_candidate_set(eng_mod):
     assert lik[0] == pytest.approx(olik[0], rel=ELBO_RTOL)
     assert arborist.last_stats["iters"][0] == ofits[0][3]
     np.testing.assert_allclose(fits[0].q_z, ofits[0][1], rtol=Q_RTOL, atol=Q_ATOL)
-    assert np.array_equal(fits[0].q_y, np.ones_like(fits[0].q_y))
+    np.testing.assert_allclose(fits[0].q_y, ofits[0][2], rtol=Q_RTOL, atol=Q_ATOL)
     assert_map_equal(fits[0].q_z, ofits[0][1], where="k2")
+
+
+def test_unnormalised_prior_through_the_seam(eng_mod):
+    """A q_y_init whose rows do not sum to one, handed to the 13-argument seam (A.py:679-816 takes any matrix):
+    first pass with the rows' own mass (k_first_pass_general), then the ordinary sweeps; against the oracle's
+    log-domain restatement, for a prior that wins at iteration 0 and one that does not, next to a normalised
+    prior on the same cached matrix."""
+    from arborist_b200 import run_variational_inference
+    from oracle import oracle as orc
+    g = load_golden("small")
+    n, m, K = int(g["n_cells"]), int(g["n_snvs"]), int(g["n_clones"])
+    rng = np.random.default_rng(3)
+    args = (g["ll_cs"], g["ll_ss"], g["cell_idx_ss"], g["snv_idx_cs"], n, m, K)
+    tail = (g["cell_ptr"], g["snv_ptr"], 25, 1.0)
+    for scale in (rng.uniform(0.5, 1.5, size=(m, 1)), np.full((m, 1), 1.3), np.ones((m, 1))):
+        q0 = np.ascontiguousarray(g["q_y_init"] * scale)
+        for t in (0, 4):
+            want = orc.run_variational_inference(g["presence"][t], *args, q0, *tail)
+            got = run_variational_inference(g["presence"][t], *args, q0, *tail)
+            assert got[0] == pytest.approx(want[0], rel=ELBO_RTOL)
+            np.testing.assert_allclose(got[1], want[1], rtol=Q_RTOL, atol=Q_ATOL)
+            np.testing.assert_allclose(got[2], want[2], rtol=Q_RTOL, atol=Q_ATOL)
 
 
 def test_multi_context_fit_is_bit_identical(eng_mod):

@@ -7,7 +7,7 @@ import pytest
 from conftest import golden_frames, load_golden, synth_frames
 from oracle import oracle as orc
 
-SMALL = ["tiny", "small", "small_nonormal", "deep30"]
+SMALL = ["tiny", "small", "small_nonormal", "deep30", "k2"]
 
 
 def _prep(g):
@@ -125,3 +125,22 @@ def test_config2_subset_from_seeded_generator():
         assert lik[t] == pytest.approx(float(g["elbo"][t]), rel=1e-11)
         assert fits[t][3] == int(g["iters"][t])
         assert np.array_equal(fits[t][1].argmax(1), g["map_z"][t])
+
+
+def test_config5_full_shape_one_tree():
+    """BASELINE config 5 at its real shape (5k x 10k, K = 30 deep trees, 30 % off-tree SNVs -> uniform prior rows):
+    the oracle against the live reference's run of the same tree (tests/golden/config5_full.npz)."""
+    g = load_golden("config5_full")
+    sub_all = [int(i) for i in g["tree_subset"]]
+    trees, rc, cl = synth_frames("config5", tree_subset=sub_all)
+    assert np.array_equal(np.array(trees), g["trees"])
+    k = int(np.argmin(g["iters"]))                        # the shortest fit keeps the CPU suite short
+    lik, _, fits, prob = orc.arborist_oracle(trees, rc, cl, max_iter=25, tolerance=1.0, gamma=0.7,
+                                             add_normal=True, trees={k})
+    assert (prob.n_cells, prob.n_snvs, prob.n_clones) == (int(g["n_cells"]), int(g["n_snvs"]), int(g["n_clones"]))
+    assert lik[k] == pytest.approx(float(g["elbo"][k]), rel=1e-11)
+    assert fits[k][3] == int(g["iters"][k])
+    assert np.array_equal(fits[k][1].argmax(1), g["map_z"][k])
+    assert np.array_equal(fits[k][2].argmax(1), g["map_y"][k])
+    r = g["q_z_rows"].shape[1]
+    np.testing.assert_allclose(fits[k][1][:r], g["q_z_rows"][k], rtol=1e-9, atol=1e-300)

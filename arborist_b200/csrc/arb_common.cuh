@@ -74,7 +74,7 @@ struct DevBuf {
 // The fit enqueues rounds ahead of the device: the Control block of every round is copied to a pinned ring the
 // host reads ARB_LOOKAHEAD rounds later (never waiting on the round it is about to enqueue).
 #define ARB_RING 8
-#define ARB_LOOKAHEAD 3
+#define ARB_LOOKAHEAD 1      // measured 1 / 2 / 3 at configs 2 and 3 and at 125 trees: 1 is never slower (profiles/r2i_*)
 #ifndef ARB_SWEEP_WARPS
 #define ARB_SWEEP_WARPS 16    // warps per sweep CTA; the layouts are dealt out to this many warps
 #endif

@@ -283,7 +283,9 @@ struct SweepArgs {
     const int32_t *n_vslots_dev;   // else read here (written by k_control): the host never learns the count, the
                                // grid is an upper bound and the CTAs past n_vslots * n_panels * split leave at once
     int32_t split;             // a (virtual slot, panel) is cut into `split` CTAs, each taking a share of every
-                               // warp's run of tiles: fills the machine when few trees are active
+                               // warp's run of tiles: fills the machine when few trees are active.  0: chosen
+                               // ON THE DEVICE from the real n_vslots (split_for), the host only bounds the grid
+    int32_t sm_count;
     const double2 *dw;         // per pair code: (d, w)
     int32_t n_pairs, tab_n, renorm_quads;   // not FOLD: renormalise every this many quads, 0 = after every factor
     double *out_m;             // [vslot][panel][row][KP] the segment's product (FOLD) or its mantissa; the q(z)
@@ -326,6 +328,33 @@ __device__ __forceinline__ void sweep_step(const char *xa_base, const char *xb_b
 // all 32 banks.  Every lane of a group loads the same uint2/uint4 of four stream words (a warp reads TW*8/16
 // contiguous bytes per quad), three quads ahead of the one in use; there are no shuffles, no predicates and no
 // per-segment pointers in the loop.
+// A sweep launch is n_vslots * n_panels equal work items, one CTA per SM at a time.  Whole waves of them run as
+// full-size CTAs; the items of the LAST, partial wave (all of them when the launch is less than one wave: small
+// candidate sets, the last rounds of a fit, a strong-scaled shard) are cut into `s_tail` shares that each take
+// a part of every warp's run of tiles, so the block scheduler can pack the tail onto all SMs.  A share re-loads
+// the panel (224 KB from L2) and pays the kernel prologue, about one tile's time, which is what bounds the
+// split.  Integer arithmetic only: the host (grid bound) and the device (actual plan) must agree bit for bit.
+struct SplitPlan { int full, s_tail, total; };
+__host__ __device__ static inline SplitPlan split_plan(int64_t items, int sms, int tiles_per_warp)
+{
+    SplitPlan pl;
+    if (sms <= 0) sms = 1;
+    pl.full = (int)(items / sms) * sms;
+    const int rem = (int)(items - pl.full);
+    const int smax = tiles_per_warp < 16 ? (tiles_per_warp < 1 ? 1 : tiles_per_warp) : 16;
+    pl.s_tail = 1;
+    if (rem > 0) {
+        int64_t best = 0;
+        for (int s = 1; s <= smax; ++s) {
+            const int64_t sub_waves = ((int64_t)rem * s + sms - 1) / sms;
+            const int64_t cost = sub_waves * ((tiles_per_warp + s - 1) / s + 1);     // in tile times
+            if (s == 1 || cost < best) { best = cost; pl.s_tail = s; }
+        }
+    }
+    pl.total = pl.full + rem * pl.s_tail;
+    return pl;
+}
+
 template <bool W16> struct StreamQuad { typedef uint4 type; };
 template <> struct StreamQuad<true> { typedef uint2 type; };
 // the four stream words of a quad as {byte offset of the gathered row | code << 18}
@@ -348,9 +377,23 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const __grid_
     uint64_t *mbar = reinterpret_cast<uint64_t *>(tab + a.tab_n);
 
     const int n_vslots = a.n_vslots_dev ? __ldg(a.n_vslots_dev) : a.n_vslots;
-    const int per_share = n_vslots * a.n_panels;
-    if ((int)blockIdx.x >= per_share * a.split) return;          // the grid is an upper bound
-    const int share = blockIdx.x / per_share, rest = blockIdx.x - share * per_share;
+    const int items = n_vslots * a.n_panels;
+    int split, share, rest;
+    if (a.split > 0) {                                     // forced (option "split"): every item cut alike
+        split = a.split;
+        if ((int)blockIdx.x >= items * split) return;     // the grid is an upper bound
+        share = blockIdx.x / items;
+        rest = blockIdx.x - share * items;
+    } else {
+        const SplitPlan pl = split_plan(items, a.sm_count, a.tiles_per_warp);
+        if ((int)blockIdx.x >= pl.total) return;
+        if ((int)blockIdx.x < pl.full) {
+            split = 1; share = 0; rest = blockIdx.x;
+        } else {
+            const int t = blockIdx.x - pl.full;
+            split = pl.s_tail; share = t % pl.s_tail; rest = pl.full + t / pl.s_tail;
+        }
+    }
     const int panel = rest / n_vslots;
     const int slot = rest % n_vslots;                    // virtual slot: 16 packed columns of the active trees
     const int row0 = panel * a.panel_rows;
@@ -390,7 +433,7 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const __grid_
     const char *xb_base = reinterpret_cast<const char *>(xs + off_b);
     // this CTA's share of every warp's run of tiles
     const int U = a.tiles_per_warp;
-    const int u0 = (int)((int64_t)share * U / a.split), u1 = (int)((int64_t)(share + 1) * U / a.split);
+    const int u0 = (int)((int64_t)share * U / split), u1 = (int)((int64_t)(share + 1) * U / split);
     const int64_t x0 = ((int64_t)panel * ARB_SWEEP_WARPS + warp) * U + u0;
     const int4 *__restrict__ desc = a.desc + x0;
     const int32_t *__restrict__ rows = a.rows + x0 * TW + grp;
@@ -1199,23 +1242,21 @@ static void launch_sweep(const SweepArgs &a, int grid, int fold, int w16, size_t
     }
 }
 
-// A sweep launch is n_vslots * n_panels equal CTAs, one per SM at a time.  When that is not many waves
-// (few trees active: small candidate sets, the last rounds of a fit, a strong-scaled shard) every (virtual slot,
-// panel) is cut into `split` CTAs that each take a share of every warp's tiles; the shares re-load the panel
-// (224 KB from L2), so the split is only as large as it takes to fill the last wave.
-static int choose_split(const arb_ctx *ctx, int64_t base_ctas, int tiles_per_warp)
+// Grid of a sweep launch: the exact plan when the tree count is known on the host (kernel-level hooks), else the
+// largest total any count up to the bound can ask for (the CTAs past the real total leave at once).
+static int sweep_grid(const arb_ctx *ctx, SweepArgs &a, int ub_vslots, bool device_count)
 {
-    if (ctx->opt_split > 0) return (int)std::min<int64_t>(ctx->opt_split, std::max(1, tiles_per_warp));
-    const int64_t sms = std::max(1, ctx->sm_count);
-    if (base_ctas <= 0 || base_ctas >= 16 * sms) return 1;
-    int best = 1;
-    double best_cost = 1e300;
-    for (int s = 1; s <= std::min(16, std::max(1, tiles_per_warp)); ++s) {
-        const int64_t waves = (base_ctas * s + sms - 1) / sms;
-        const double cost = (double)waves / s * (1.0 + 0.015 * (s - 1));      // each share re-loads its panel
-        if (cost < best_cost - 1e-12) { best_cost = cost; best = s; }
+    a.sm_count = ctx->sm_count;
+    if (ctx->opt_split > 0) {
+        a.split = (int)std::min<int64_t>(ctx->opt_split, std::max(1, a.tiles_per_warp));
+        return ub_vslots * a.n_panels * a.split;
     }
-    return best;
+    a.split = 0;
+    if (!device_count) return split_plan((int64_t)ub_vslots * a.n_panels, ctx->sm_count, a.tiles_per_warp).total;
+    int grid = 1;
+    for (int v = 1; v <= ub_vslots; ++v)
+        grid = std::max(grid, split_plan((int64_t)v * a.n_panels, ctx->sm_count, a.tiles_per_warp).total);
+    return grid;
 }
 
 // q(z) sweep over the packed S rows of the trees in the q(z) list: `ub_trees` bounds the grid, the count itself
@@ -1235,7 +1276,6 @@ static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.tiles_per_warp = L.uz;
     a.n_vslots = (int)vslots_for(ub_trees, ctx->ws_k);
     a.n_vslots_dev = ctl ? &ctl->n_vz : nullptr;
-    a.split = choose_split(ctx, (int64_t)a.n_vslots * L.np_z, L.uz);
     a.dw = ctx->tab_dw.as<double2>();
     a.n_pairs = ctx->n_pairs;
     a.tab_n = arb_sweep_table_entries(ctx);
@@ -1243,7 +1283,7 @@ static void launch_sweep_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.out_m = w.pz_m;
     a.out_e = w.pz_e;
     fill_tabc(ctx, a);
-    const int grid = a.n_vslots * L.np_z * a.split;
+    const int grid = sweep_grid(ctx, a, a.n_vslots, ctl != nullptr);
     launch_sweep<true>(a, grid, L.fold_z, L.w16, sweep_smem_bytes(ctx, L), w.stream);
 }
 
@@ -1262,7 +1302,6 @@ static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.tiles_per_warp = L.uy;
     a.n_vslots = (int)vslots_for(ub_trees, ctx->ws_k - 1);
     a.n_vslots_dev = ctl ? &ctl->n_vy : nullptr;
-    a.split = choose_split(ctx, (int64_t)a.n_vslots * L.np_y, L.uy);
     a.dw = ctx->tab_dw.as<double2>();
     a.n_pairs = ctx->n_pairs;
     a.tab_n = arb_sweep_table_entries(ctx);
@@ -1270,7 +1309,7 @@ static void launch_sweep_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w, 
     a.out_m = w.py_m;
     a.out_e = w.py_e;
     fill_tabc(ctx, a);
-    const int grid = a.n_vslots * L.np_y * a.split;
+    const int grid = sweep_grid(ctx, a, a.n_vslots, ctl != nullptr);
     launch_sweep<false>(a, grid, L.fold_y, L.w16, sweep_smem_bytes(ctx, L), w.stream);
 }
 

@@ -43,10 +43,13 @@ RUN = dict(alpha=0.001, gamma=0.7, max_iter=25, tolerance=1.0)      # CLI defaul
 # measured by the GPU arm; used only to express the CPU sample (a few iterations of one tree)
 # in the metric's unit.  See BASELINE.md section 5.
 MEAN_TREE_ITERS = {"config3": 17.84, "config2": 12.8}
-# DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) per tree-sweep of the two sweep kernels, from the
-# one `ncu --set full` capture summarised in profiles/r1z_full_summary.md (config 3 only; per launch the
-# kernel moves this times the tree-sweeps of the launch).
-NCU_DRAM_BYTES_PER_TREE_SWEEP = {"config3": {"z": 24.62e6, "y": 12.16e6}}
+# DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) per tree-sweep of the two sweep kernels, one entry per
+# config that has an `ncu --set full` capture under profiles/ (per launch the kernel moves this times the
+# tree-sweeps of the launch; the figure is NOT measured in the bench run itself -- ncu cannot run inside a timed
+# region).  Configs without a capture report traffic = null with the reason.
+NCU_DRAM_BYTES_PER_TREE_SWEEP = {
+    "config3": {"z": 28.2e6, "y": 13.4e6, "capture": "profiles/r2b_full_summary.md"},
+}
 
 
 def parse_args():
@@ -60,6 +63,10 @@ def parse_args():
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--slots", type=int, default=0)
+    p.add_argument("--lookahead", type=int, default=0, help="rounds the host enqueues ahead (0 = library default)")
+    p.add_argument("--split", type=int, default=0, help="force the sweep split (0 = chosen on the device)")
+    p.add_argument("--no-strong", action="store_true", help="skip the strong-scaling leg (N > 1: the config's own "
+                   "candidate set, e.g. 1,000 trees in total, sharded over the N GPUs)")
     return p.parse_args()
 
 
@@ -258,6 +265,10 @@ def run_gpu_arm(args):
     eng = engine.Engine(device=local)
     if args.slots:
         eng.set_option("slots", args.slots)
+    if args.lookahead:
+        eng.set_option("lookahead", args.lookahead)
+    if args.split:
+        eng.set_option("split", args.split)
     ingest_read_counts(eng, rc, cl, cluster_to_idx, RUN["alpha"], RUN["gamma"])
     n, m, nnz, n_pairs = eng.dims()
     shard = distributed.shard_indices(T)
@@ -307,6 +318,37 @@ def run_gpu_arm(args):
     steps = max(1, args.steps)
     value = T * steps / (dev_ms * 1e-3)
 
+    # ---- strong scaling: the config's OWN candidate set (config 3: 1,000 trees in total) sharded over the ranks ---
+    strong = None
+    if world > 1 and not args.no_strong:
+        T_s = min(T, cfg.n_trees)
+        shard_s = distributed.shard_indices(T_s)
+        par_s = np.ascontiguousarray(parents[shard_s])
+
+        def strong_step():
+            elbo, _ = eng.fit(parents=par_s, n_clones=K, normal_idx=normal_idx, max_iter=RUN["max_iter"],
+                              tolerance=RUN["tolerance"], keep_posteriors="all")
+            ms = eng.last_fit_stats()["device_ms"]
+            ev0.record()
+            full_s, _ = distributed.gather_elbos(elbo, shard_s, T_s)
+            ev1.record()
+            torch.cuda.synchronize()
+            return ms + ev0.elapsed_time(ev1), full_s
+
+        for _ in range(2):
+            strong_step()
+        barrier()
+        s_ms = 0.0
+        for _ in range(args.steps):
+            ms, full_s = strong_step()
+            s_ms += ms
+        barrier()
+        s_ms = max_over_ranks(s_ms)
+        strong = {"trees_total": int(T_s), "trees_per_gpu": float(T_s) / world, "value": T_s * steps / (s_ms * 1e-3),
+                  "unit": "trees/s", "ms_per_step": s_ms / steps, "best_tree": int(np.argmax(full_s)),
+                  "note": "same metric with the TOTAL candidate set fixed (north_star: 1,000 trees, 1 -> 8 GPUs); "
+                          "device events, max over ranks; divide by the N = 1 line's value for the speed-up"}
+
     # ---- roofline of the dominant kernel (q(z) sweep), from this rank's events --------------------
     peaks = {}
     try:
@@ -314,6 +356,7 @@ def run_gpu_arm(args):
     except (OSError, ValueError):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
+    sm_count = torch.cuda.get_device_properties(local).multi_processor_count
     b_z, b_y = algorithmic_bytes(n, m, nnz, K)
     lz = max(1.0, prof["launches_z"])
     ach_z = prof["tree_sweeps_z"] * b_z / max(prof["sweep_z_ms"], 1e-9) / 1e6          # GB/s
@@ -324,9 +367,12 @@ def run_gpu_arm(args):
         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
         "traffic": (NCU_DRAM_BYTES_PER_TREE_SWEEP[cfg.name]["z"] * prof["tree_sweeps_z"] / lz
                     if cfg.name in NCU_DRAM_BYTES_PER_TREE_SWEEP else None),
-        "traffic_source": "ncu --set full, profiles/r1z_full_summary.md: 24.62 MB of DRAM traffic per tree-sweep "
-                          "x tree-sweeps per launch (bytes per launch, like the algorithmic figure: "
-                          "algorithmic_bytes_per_tree_sweep x tree_sweeps_per_launch)",
+        "traffic_source": (f"ncu --set full, {NCU_DRAM_BYTES_PER_TREE_SWEEP[cfg.name]['capture']}: "
+                           f"{NCU_DRAM_BYTES_PER_TREE_SWEEP[cfg.name]['z'] / 1e6:.1f} MB of DRAM traffic per tree-sweep "
+                           "(dram__bytes_read.sum + dram__bytes_write.sum of one captured launch / its tree-sweeps) x "
+                           "this run's tree-sweeps per launch; a constant from that capture, not measured in this run"
+                           if cfg.name in NCU_DRAM_BYTES_PER_TREE_SWEEP else
+                           "null: no ncu --set full capture of this config under profiles/"),
         "algorithmic_bytes_per_tree_sweep": b_z, "tree_sweeps_per_launch": prof["tree_sweeps_z"] / lz,
         "avg_launch_ms": prof["sweep_z_ms"] / lz,
         "qy_sweep": {"achieved": ach_y, "frac": ach_y / peak, "algorithmic_bytes_per_tree_sweep": b_y,
@@ -338,6 +384,19 @@ def run_gpu_arm(args):
                                  "sweep_y": prof["sweep_y_ms"] / max(dev_ms, 1e-9),
                                  "finish_z": prof["finish_z_ms"] / max(dev_ms, 1e-9),
                                  "finish_y": prof["finish_y_ms"] / max(dev_ms, 1e-9)},
+        # what really bounds the sweeps: the L1 / shared-memory data pipe (one 128-byte wavefront per nonzero and
+        # 16 packed columns = 4 chunks), not HBM -- so frac above can neither reach nor be compared with 1.0 across
+        # configs: at K clones a tree-sweep needs nnz * ceil(cols/4)/4 wavefronts whatever its algorithmic bytes
+        "lsu_floor": (lambda wz, wy, hz: {
+            "pipe": "l1tex data pipe: 1 wavefront (128 B) per SM per cycle; a nonzero of a virtual slot (16 packed "
+                    "columns) is one wavefront",
+            "sm_count": sm_count, "sm_mhz_used": hz,
+            "z_frac_of_floor": wz / (sm_count * hz * 1e3) / max(prof["sweep_z_ms"], 1e-9),
+            "y_frac_of_floor": wy / (sm_count * hz * 1e3) / max(prof["sweep_y_ms"], 1e-9),
+            "max_hbm_frac_at_floor": {"z": (b_z / peak / 1e9) / (nnz * ((K + 3) // 4) / 4 / (sm_count * hz * 1e6)),
+                                      "y": (b_y / peak / 1e9) / (nnz * ((K + 2) // 4) / 4 / (sm_count * hz * 1e6))},
+        })(prof["tree_sweeps_z"] * nnz * ((K + 3) // 4) / 4.0, prof["tree_sweeps_y"] * nnz * ((K + 2) // 4) / 4.0,
+           float(clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965.0)),
         "layout": {k: int(pf[k]) for k in ("kp", "panel_rows", "panels_z", "panels_y", "tiles_per_warp_z",
                                             "tiles_per_warp_y", "fold_z", "fold_y", "quads_z", "quads_y", "w16")},
     }
@@ -430,7 +489,8 @@ def run_gpu_arm(args):
             "mean_tree_iters_per_tree": tree_iters / steps / len(shard),
             "wall_ms_per_step": 1e3 * wall / steps,
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
-            "e2e": e2e, "cpu_baseline": cpu,
+            "e2e": e2e, "cpu_baseline": cpu, "strong": strong,
+            "round_pipeline": {"host_waits": pf["host_waits"], "idle_rounds": pf["idle_rounds"], "rounds": pf["rounds"]},
             "best_tree": int(order[0]), "true_tree": int(d.true_tree_index),
         }
         print(json.dumps(line), file=_REAL_STDOUT, flush=True)

@@ -184,7 +184,7 @@ int arb_last_fit_stats(arb_ctx *ctx, int64_t *kernel_launches, double *device_ms
  * values[23] = batched re-fits done by arb_get_fits / arb_get_map since the last fit */
 int arb_last_fit_profile(arb_ctx *ctx, double *values, int32_t n_values);
 /* tuning knobs: "slots" (trees in flight), "split" (CTAs per (virtual slot, panel) of a sweep; 0 = chosen per
- * launch), "lookahead" (rounds enqueued ahead of the device, 0 = default 3), "panel_kb" (panel bytes cap),
+ * launch), "lookahead" (rounds enqueued ahead of the device, 0 = default 1), "panel_kb" (panel bytes cap),
  * "threads", "no_fold", "w32" (force 32-bit stream words); returns ARB_ERR_INVALID for unknown names */
 int arb_set_option(arb_ctx *ctx, const char *name, int64_t value);
 /* Device allocations released by a context (arb_ctx_destroy, workspace resizes) are parked in a

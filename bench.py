@@ -48,7 +48,9 @@ MEAN_TREE_ITERS = {"config3": 17.84, "config2": 12.8}
 # tree-sweeps of the launch; the figure is NOT measured in the bench run itself -- ncu cannot run inside a timed
 # region).  Configs without a capture report traffic = null with the reason.
 NCU_DRAM_BYTES_PER_TREE_SWEEP = {
-    "config3": {"z": 28.2e6, "y": 13.4e6, "capture": "profiles/r2b_full_summary.md"},
+    "config3": {"z": 28.2e6, "y": 14.1e6, "capture": "profiles/r2_full_summary.md (r2b)"},
+    "config5": {"z": 17.2e6, "y": 8.0e6, "capture": "profiles/r2_full_summary.md (r2k5)"},
+    "config4": {"z": 913e6, "y": 471e6, "capture": "profiles/r2_full_summary.md (r2k4)"},
 }
 
 

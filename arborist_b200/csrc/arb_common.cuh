@@ -134,7 +134,18 @@ struct arb_ctx {
     std::vector<int32_t> pair_alt, pair_total;
     std::vector<int64_t> pair_count;
     std::vector<double> tab_lp, tab_la;   // host copies of the table
-    DevBuf tab_dw;                        // double2 [n_pairs]: (expm1(lp-la), lp-la)
+    DevBuf tab_dw;                        // double2 [n_pairs]: (expm1(lp-la), lp-la); (0, 0) for "deep" pairs
+    // "Deep" pairs: log-likelihood ratio w = lp - la outside [ARB_W_LO, ARB_W_HI] (deep coverage: alt = 0 with
+    // total >= 14, or >= 83 alt reads, at the default alpha).  The product form 1 + expm1(w) S loses the reference's
+    // accuracy there (cancellation against S -> 1 for very negative w, overflow for large w), so their nonzeros
+    // are neutral in the sweeps (factor exactly 1) and are added in the log domain by the finishing kernels from
+    // two small side lists (arb_build_side_lists; finish_row in arb_fit.cu).
+    std::vector<uint8_t> pair_deep;
+    bool side_dirty = true;
+    int64_t n_side = 0;
+    DevBuf side_z_ptr, side_z_idx, side_z_w;   // CSR over cells: SNV index and w of every deep nonzero
+    DevBuf side_y_ptr, side_y_idx, side_y_w;   // CSR over SNVs: cell index and w
+    DevBuf tab_w_dev, tab_deep_dev;            // per pair code: true w, deep flag (k_first_pass_general)
     std::vector<double> h_dw;             // host copy of tab_dw (d, w interleaved)
     double sum_la = 0;                    // sum over nonzeros of log_absent
     int renorm_every = 16;
@@ -186,9 +197,12 @@ __host__ __device__ static inline int64_t arb_perm(int64_t c, int np, int pr) { 
 static inline int kp_index(int kp) { return kp == 8 ? 0 : kp == 16 ? 1 : 2; }
 // The sweeps always run on 16-column packed rows ("virtual slots", arb_fit.cu): the columns of the
 // trees in flight are laid side by side in units of four, so no lane works on a padding column.
+#define ARB_W_LO (-9.0)     // exp(9) * 2^-53 ~ 1e-12: relative accuracy of 1 + expm1(w) S at S = 1
+#define ARB_W_HI 600.0
 #define ARB_VW 16
 static inline int kp_for(int) { return ARB_VW; }
 
 // ---- internal entry points shared between translation units ---------------------------
 int arb_build_layout(arb_ctx *ctx, int kp);                       // arb_ingest.cu
 int arb_refresh_tables(arb_ctx *ctx);                             // arb_ingest.cu
+int arb_build_side_lists(arb_ctx *ctx);                           // arb_ingest.cu (no-op unless the table changed)

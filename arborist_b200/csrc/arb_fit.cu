@@ -550,6 +550,15 @@ __global__ void __launch_bounds__(ARB_SWEEP_WARPS * 32, 1) k_sweep(const __grid_
 // ---------------------------------------------------------------------------------------
 // finishing kernel: combine the panel partials, softmax, ELBO pieces, next gathered operand
 // ---------------------------------------------------------------------------------------
+// log(Sbar + S e^w) for a deep pair, as a two-term log-sum-exp (A.py:173-197): exact when either mass is 0 and
+// for any |w| (e^w itself may overflow or underflow)
+__device__ __forceinline__ double deep_term(double S, double Sb, double w)
+{
+    const double a = log(Sb), b = log(S) + w;           // log(0) = -inf is fine here
+    const double hi = fmax(a, b), lo = fmin(a, b);
+    return hi == -INFINITY ? hi : hi + log1p(exp(lo - hi));
+}
+
 struct FinishArgs {
     const double *part_m;           // [vslot][panel][row][16] ({m, g} interleaved for q(z)), packed columns
     const int32_t *part_e;          // exponents, null for range-proven (folded) partials
@@ -567,27 +576,63 @@ struct FinishArgs {
     int32_t nbmax;
     int32_t given_q;                // elbo_terms hook: take q from q_cur instead of the softmax
     const Control *ctl;             // trees in the list are counted here (grid.y is an upper bound); null: grid.y
+    // deep pairs (arb_common.cuh): CSR over this kernel's rows of the deep nonzeros (other-side index, w); null when
+    // the matrix has none.  q_other = the posterior matrix of the OTHER side ([plane][slot][other_rows][other_cols]):
+    // q(y) for the q(z) kernel (plane 1 - bestb: this round's iterate), q(z) for the q(y) kernel (plane cur).
+    const int32_t *side_ptr, *side_idx;
+    const double *side_w, *q_other;
+    int32_t other_rows;
 };
 
 // The end of a row: A.py:245-250 softmax + A.py:268-273 entropy + likelihood term (q(z)),
 // A.py:373-375 (+ log prior) softmax + A.py:293-299 KL + S rows (q(y)).  A row lives in the GL
 // lanes of a group, lane h holds columns 4h..4h+3.  Executed by whole warps (shuffles); only memory
 // accesses are guarded.  Masked sums run in ascending source order (deterministic, tree-independent).
-template <int GL, bool IS_Z, bool HARD>
+template <int GL, bool IS_Z, bool HARD, bool SIDE>
 __device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int pos_out, int64_t row, bool rowok, int h,
-                                           int base, const uint32_t (&omask)[4], const double (&p)[4], const int (&e)[4],
-                                           const double (&g)[4], double &acc1, double &acc2)
+                                           int base, const uint32_t (&omask)[4], const uint32_t (&smask)[4],
+                                           const double (&p)[4], const int (&e)[4], const double (&g_in)[4], double &acc1,
+                                           double &acc2)
 {
     const int K = a.K, C = K - 1, ncol = IS_Z ? K : C;
     const int64_t qbase = (((1 - a.st[slot].bestb) * a.plane_slots + slot) * a.n_rows + row) * ncol;
-    double logit[4];
+    double logit[4], g[4];
     bool v[4];
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
         v[c] = 4 * h + c < ncol;
+        g[c] = g_in[c];
         double l = log(p[c]) + (double)e[c] * LN2;
         if (!IS_Z && v[c] && rowok) l += a.logq0[row * C + 4 * h + c];
         logit[c] = v[c] ? l : -INFINITY;
+    }
+    if (SIDE && rowok) {
+        // Deep pairs, in the log domain like the reference (A.py:229-243 / 354-369): the nonzero's term is
+        // log(Sbar e^la + S e^lp) - la = log(Sbar + S e^w), with S the mass of the other side's posterior row on the
+        // ancestors / descendants and Sbar the mass on the rest, both summed directly (no 1 - S cancellation).
+        const int ocols = IS_Z ? C : K;
+        const int plane = IS_Z ? 1 - a.st[slot].bestb : a.st[slot].cur;
+        const double *qo = a.q_other + ((int64_t)plane * a.plane_slots + slot) * (int64_t)a.other_rows * ocols;
+        for (int k = a.side_ptr[row]; k < a.side_ptr[row + 1]; ++k) {
+            const double *qr = qo + (int64_t)a.side_idx[k] * ocols;
+            const double w = a.side_w[k];
+            double S[4] = {0.0, 0.0, 0.0, 0.0}, Sb[4] = {0.0, 0.0, 0.0, 0.0};
+            for (int b = 0; b < ocols; ++b) {
+                const double x = qr[b];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    if ((smask[c] >> b) & 1u) S[c] += x;
+                    else Sb[c] += x;
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                if (v[c]) {
+                    logit[c] += deep_term(S[c], Sb[c], w);
+                    if (IS_Z) g[c] = fma(w, S[c], g[c]);
+                }
+            }
+        }
     }
     double mx = fmax(fmax(logit[0], logit[1]), fmax(logit[2], logit[3]));
     constexpr bool POW2 = (GL & (GL - 1)) == 0;    // butterflies inside aligned groups, else gather the group
@@ -672,8 +717,8 @@ __device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int po
 #define FIN_WARPS (FIN_THREADS / 32)
 
 // grid (row blocks of FIN_ROWS, trees of the sweep's list); a warp takes TW = 32/GL rows at a time
-template <int GL, bool IS_Z, bool HARD>
-__global__ void __launch_bounds__(FIN_THREADS, 4) k_finish(const FinishArgs a)
+template <int GL, bool IS_Z, bool HARD, bool SIDE>
+__global__ void __launch_bounds__(FIN_THREADS, SIDE ? 3 : 4) k_finish(const FinishArgs a)
 {
     __shared__ double sh[FIN_WARPS];
     if (a.ctl && (int)blockIdx.y >= (IS_Z ? a.ctl->n_z : a.ctl->n_y)) return;
@@ -686,11 +731,18 @@ __global__ void __launch_bounds__(FIN_THREADS, 4) k_finish(const FinishArgs a)
     const int ncol = IS_Z ? a.K : a.K - 1, chunks = (ncol + 3) / 4;
     const bool keep = h < chunks;
     const int pos_out = IS_Z ? 0 : a.pos_out[slot];
-    uint32_t omask[4] = {0u, 0u, 0u, 0u};
+    uint32_t omask[4] = {0u, 0u, 0u, 0u}, smask[4] = {0u, 0u, 0u, 0u};
     if (!IS_Z) {
         const uint32_t *mk = a.masks + (int64_t)a.st[slot].tree * MASK_STRIDE;
 #pragma unroll
         for (int c = 0; c < 4; ++c) omask[c] = 4 * h + c < a.K ? mk[4 * h + c] : 0u;
+    }
+    if (SIDE) {
+        // q(z) kernel: column masks of this lane's clones over the clusters; q(y) kernel: row masks of its clusters
+        // over the clones
+        const uint32_t *mk = a.masks + (int64_t)a.st[slot].tree * MASK_STRIDE + (IS_Z ? 0 : 32);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) smask[c] = 4 * h + c < ncol ? mk[4 * h + c] : 0u;
     }
     const int64_t panel_stride = (int64_t)a.n_rows * ARB_VW;        // columns between panels
     double acc1 = 0.0, acc2 = 0.0;
@@ -761,7 +813,7 @@ __global__ void __launch_bounds__(FIN_THREADS, 4) k_finish(const FinishArgs a)
                 }
             }
         }
-        finish_row<GL, IS_Z, HARD>(a, slot, pos_out, rowok ? row : 0, rowok, h, rl.base, omask, p, e, g, acc1, acc2);
+        finish_row<GL, IS_Z, HARD, SIDE>(a, slot, pos_out, rowok ? row : 0, rowok, h, rl.base, omask, smask, p, e, g, acc1, acc2);
     }
     const double t1 = block_sum(acc1, sh);
     const double t2 = block_sum(acc2, sh);
@@ -792,8 +844,8 @@ __global__ void __launch_bounds__(FIN_THREADS, 4) k_finish(const FinishArgs a)
 
 __global__ void __launch_bounds__(FIN_THREADS)
 k_first_pass_general(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ snv, const uint16_t *__restrict__ code,
-                     const double2 *__restrict__ dw, const double *__restrict__ la_tab, const double *__restrict__ q0,
-                     int32_t n, int32_t m, int32_t K, const int32_t *__restrict__ list_init, const SlotState *__restrict__ st,
+                     const double2 *__restrict__ dw, const double *__restrict__ la_tab, const double *__restrict__ w_tab,
+                     const uint8_t *__restrict__ deep_tab, const double *__restrict__ q0, int32_t n, int32_t m, int32_t K, const int32_t *__restrict__ list_init, const SlotState *__restrict__ st,
                      const uint32_t *__restrict__ masks, double *__restrict__ qz_cur, double *__restrict__ qy_cur,
                      int64_t plane_slots, double *__restrict__ red, int32_t nbmax, const Control *__restrict__ ctl)
 {
@@ -820,30 +872,41 @@ k_first_pass_general(const int32_t *__restrict__ row_ptr, const int32_t *__restr
             uint32_t cm[GEN_CH];
 #pragma unroll
             for (int c = 0; c < GEN_CH; ++c) cm[c] = r0 + c < K ? mk[r0 + c] : 0u;
-            double p[GEN_CH], g[GEN_CH];
+            double p[GEN_CH], g[GEN_CH], ls[GEN_CH];
             int e[GEN_CH];
 #pragma unroll
-            for (int c = 0; c < GEN_CH; ++c) { p[c] = 1.0; g[c] = 0.0; e[c] = 0; }
+            for (int c = 0; c < GEN_CH; ++c) { p[c] = 1.0; g[c] = 0.0; e[c] = 0; ls[c] = 0.0; }
             for (int k = k0 + lane; k < k1; k += 32) {
                 const int j = snv[k], cd = code[k];
                 const double2 t = dw[cd];
                 const double *qr = q0 + (int64_t)j * C;
-                double S[GEN_CH], M = 0.0;
+                double S[GEN_CH], Sb[GEN_CH], M = 0.0;
 #pragma unroll
-                for (int c = 0; c < GEN_CH; ++c) S[c] = 0.0;
+                for (int c = 0; c < GEN_CH; ++c) S[c] = Sb[c] = 0.0;
                 for (int b = 0; b < C; ++b) {               // ascending cluster order, like masked_rows
                     const double x = qr[b];
                     M += x;
 #pragma unroll
-                    for (int c = 0; c < GEN_CH; ++c)
+                    for (int c = 0; c < GEN_CH; ++c) {
                         if ((cm[c] >> b) & 1u) S[c] += x;
+                        else Sb[c] += x;
+                    }
                 }
                 if (r0 == 0) acc1 += la_tab[cd] * (M - 1.0);
+                if (deep_tab[cd]) {                          // deep pair: log domain, like finish_row
+                    const double w = w_tab[cd];
 #pragma unroll
-                for (int c = 0; c < GEN_CH; ++c) {
-                    p[c] *= fma(t.x, S[c], M);
-                    renorm(p[c], e[c]);
-                    g[c] = fma(t.y, S[c], g[c]);
+                    for (int c = 0; c < GEN_CH; ++c) {
+                        ls[c] += deep_term(S[c], Sb[c], w);
+                        g[c] = fma(w, S[c], g[c]);
+                    }
+                } else {
+#pragma unroll
+                    for (int c = 0; c < GEN_CH; ++c) {
+                        p[c] *= fma(t.x, S[c], M);
+                        renorm(p[c], e[c]);
+                        g[c] = fma(t.y, S[c], g[c]);
+                    }
                 }
             }
 #pragma unroll
@@ -853,10 +916,11 @@ k_first_pass_general(const int32_t *__restrict__ row_ptr, const int32_t *__restr
                     p[c] *= __shfl_xor_sync(0xffffffffu, p[c], o);
                     e[c] += __shfl_xor_sync(0xffffffffu, e[c], o);
                     g[c] += __shfl_xor_sync(0xffffffffu, g[c], o);
+                    ls[c] += __shfl_xor_sync(0xffffffffu, ls[c], o);
                     renorm(p[c], e[c]);
                 }
                 if (lane == 0 && r0 + c < K) {
-                    sh_l[warp][r0 + c] = log(p[c]) + (double)e[c] * LN2;
+                    sh_l[warp][r0 + c] = log(p[c]) + (double)e[c] * LN2 + ls[c];
                     sh_g[warp][r0 + c] = g[c];
                 }
             }
@@ -1338,10 +1402,19 @@ static void launch_finish_z(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w,
     a.nbmax = ws.nbmax;
     a.given_q = given_q;
     a.ctl = ctl;
-    if (hard)
-        k_finish<GL, true, true><<<dim3(ws.nbz, ub_trees), FIN_THREADS, 0, w.stream>>>(a);
-    else
-        k_finish<GL, true, false><<<dim3(ws.nbz, ub_trees), FIN_THREADS, 0, w.stream>>>(a);
+    a.side_ptr = ctx->n_side > 0 ? ctx->side_z_ptr.as<int32_t>() : nullptr;
+    a.side_idx = ctx->side_z_idx.as<int32_t>();
+    a.side_w = ctx->side_z_w.as<double>();
+    a.q_other = ctx->qy_cur.as<double>();
+    a.other_rows = ctx->n_snvs;
+    const dim3 grid(ws.nbz, ub_trees);
+    if (a.side_ptr) {                   // the matrix has deep pairs: the variant with the log-domain side loop
+        if (hard) k_finish<GL, true, true, true><<<grid, FIN_THREADS, 0, w.stream>>>(a);
+        else k_finish<GL, true, false, true><<<grid, FIN_THREADS, 0, w.stream>>>(a);
+    } else {
+        if (hard) k_finish<GL, true, true, false><<<grid, FIN_THREADS, 0, w.stream>>>(a);
+        else k_finish<GL, true, false, false><<<grid, FIN_THREADS, 0, w.stream>>>(a);
+    }
 }
 
 template <int GL>
@@ -1369,7 +1442,13 @@ static void launch_finish_y(arb_ctx *ctx, const PanelLayout &L, const WsPtrs &w,
     a.nbmax = ws.nbmax;
     a.given_q = 0;
     a.ctl = ctl;
-    k_finish<GL, false, false><<<dim3(ws.nby, ub_trees), FIN_THREADS, 0, w.stream>>>(a);
+    a.side_ptr = ctx->n_side > 0 ? ctx->side_y_ptr.as<int32_t>() : nullptr;
+    a.side_idx = ctx->side_y_idx.as<int32_t>();
+    a.side_w = ctx->side_y_w.as<double>();
+    a.q_other = ctx->qz_cur.as<double>();
+    a.other_rows = ctx->n_cells;
+    if (a.side_ptr) k_finish<GL, false, false, true><<<dim3(ws.nby, ub_trees), FIN_THREADS, 0, w.stream>>>(a);
+    else k_finish<GL, false, false, false><<<dim3(ws.nby, ub_trees), FIN_THREADS, 0, w.stream>>>(a);
 }
 
 template <int GL>
@@ -1520,7 +1599,8 @@ static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, 
         if ((more_inits || enq == 0) && general) {
             k_first_pass_general<<<dim3(ws.nbz, ubt), FIN_THREADS, 0, st>>>(
                 ctx->row_ptr.as<int32_t>(), ctx->coo_snv.as<int32_t>(), ctx->coo_code.as<uint16_t>(),
-                ctx->tab_dw.as<double2>(), ctx->tab_la_dev.as<double>(), ctx->q0.as<double>(), ctx->n_cells, ctx->n_snvs, K,
+                ctx->tab_dw.as<double2>(), ctx->tab_la_dev.as<double>(), ctx->tab_w_dev.as<double>(),
+                ctx->tab_deep_dev.as<uint8_t>(), ctx->q0.as<double>(), ctx->n_cells, ctx->n_snvs, K,
                 w.list_init, w.st, tg.masks, ctx->qz_cur.as<double>(), ctx->qy_cur.as<double>(), (int64_t)ctx->ws_slots,
                 ctx->red.as<double>(), ws.nbmax, w.ctl);
             stats.launches++;

@@ -233,7 +233,9 @@ ARB_API int arb_ctx_destroy(arb_ctx *ctx)
                       &ctx->xs, &ctx->xr, &ctx->qz_cur, &ctx->qy_cur, &ctx->part_z, &ctx->part_g,
                       &ctx->part_y, &ctx->red, &ctx->slot_state, &ctx->lists, &ctx->masks,
                       &ctx->best_qz, &ctx->best_qy, &ctx->d_elbo, &ctx->d_iters, &ctx->d_trace,
-                      &ctx->tree_masks, &ctx->batch_qz, &ctx->batch_qy, &ctx->batch_out, &ctx->row_ptr, &ctx->tab_la_dev, &ctx->scratch, &ctx->cell_uniques,
+                      &ctx->tree_masks, &ctx->batch_qz, &ctx->batch_qy, &ctx->batch_out, &ctx->row_ptr, &ctx->tab_la_dev,
+                      &ctx->side_z_ptr, &ctx->side_z_idx, &ctx->side_z_w, &ctx->side_y_ptr, &ctx->side_y_idx, &ctx->side_y_w,
+                      &ctx->tab_w_dev, &ctx->tab_deep_dev, &ctx->scratch, &ctx->cell_uniques,
                       &ctx->snv_uniques, &ctx->base_ta, &ctx->base_tb, &ctx->base_cnt,
                       &ctx->csv_col[0], &ctx->csv_col[1], &ctx->csv_col[2], &ctx->csv_col[3]};
     for (DevBuf *b : bufs) b->release();
@@ -772,7 +774,7 @@ int arb_build_layout(arb_ctx *ctx, int kp)
     // per-code bounds on |log2(1 + d x)|, x in [0,1], with a little slack for rounding
     std::vector<float> up(ctx->n_pairs), dn(ctx->n_pairs);
     for (int c = 0; c < ctx->n_pairs; ++c) {
-        const double w = ctx->tab_lp[c] - ctx->tab_la[c];
+        const double w = (c < (int)ctx->pair_deep.size() && ctx->pair_deep[c]) ? 0.0 : ctx->tab_lp[c] - ctx->tab_la[c];
         up[c] = (float)(std::max(0.0, w) / 0.6931471805599453 * 1.001 + 1e-3);
         dn[c] = (float)(std::max(0.0, -w) / 0.6931471805599453 * 1.001 + 1e-3);
     }
@@ -813,12 +815,27 @@ int arb_refresh_tables(arb_ctx *ctx)
     ARB_CUDA(cudaStreamSynchronize(ctx->stream));
     lp.release();
     la.release();
+    // deep pairs leave the product form: (d, w) = (0, 0) makes their factor exactly 1 and their likelihood term 0
+    // in the sweeps; the finishing kernels add them in the log domain (side lists)
+    ctx->pair_deep.assign((size_t)n, 0);
+    bool any_deep = false;
+    for (int c = 0; c < n; ++c) {
+        const double w = ctx->tab_lp[c] - ctx->tab_la[c];
+        if (ctx->pair_count[c] > 0 && (w < ARB_W_LO || w > ARB_W_HI)) {
+            ctx->pair_deep[c] = 1;
+            ctx->h_dw[2 * c] = ctx->h_dw[2 * c + 1] = 0.0;
+            any_deep = true;
+        }
+    }
+    if (any_deep)
+        ARB_CUDA(cudaMemcpy(ctx->tab_dw.p, ctx->h_dw.data(), (size_t)n * 16, cudaMemcpyHostToDevice));
+    ctx->side_dirty = true;
     // bookkeeping on the host: sum_k log_absent_k = sum_c count_c * la_c in table order
     double s = 0.0, max_abs_w = 0.0;
     for (int c = 0; c < n; ++c) {
         s += (double)ctx->pair_count[c] * ctx->tab_la[c];
         const double w = ctx->tab_lp[c] - ctx->tab_la[c];
-        if (ctx->pair_count[c] > 0 && fabs(w) > max_abs_w) max_abs_w = fabs(w);
+        if (ctx->pair_count[c] > 0 && !ctx->pair_deep[c] && fabs(w) > max_abs_w) max_abs_w = fabs(w);
     }
     ctx->sum_la = s;
     // factors 1 + d*x lie in [min(1,e^w), max(1,e^w)]: where the layout has no range proof the sweep
@@ -830,19 +847,129 @@ int arb_refresh_tables(arb_ctx *ctx)
     return ARB_OK;
 }
 
+// ---------------------------------------------------------------------------------------
+// side lists of the deep pairs (log-domain path of the finishing kernels)
+// ---------------------------------------------------------------------------------------
+__global__ void k_side_flags(const uint16_t *__restrict__ code, const uint8_t *__restrict__ deep, int64_t nnz, int32_t *flag)
+{
+    const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k < nnz) flag[k] = deep[code[k]] ? 1 : 0;
+}
+
+__global__ void k_side_compact(const int32_t *__restrict__ cell, const int32_t *__restrict__ snv, const uint16_t *__restrict__ code,
+                               const int32_t *__restrict__ flag, const int32_t *__restrict__ pos, const double *__restrict__ w_tab,
+                               int64_t nnz, int32_t *o_cell, int32_t *o_snv, double *o_w)
+{
+    const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k >= nnz || !flag[k]) return;
+    const int32_t o = pos[k];
+    o_cell[o] = cell[k];
+    o_snv[o] = snv[k];
+    o_w[o] = w_tab[code[k]];
+}
+
+__global__ void k_side_gather(const int32_t *__restrict__ order, const int32_t *__restrict__ cell, const double *__restrict__ w,
+                              int64_t n, int32_t *o_cell, double *o_w)
+{
+    const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    o_cell[k] = cell[order[k]];
+    o_w[k] = w[order[k]];
+}
+
+// CSR pointer of a sorted row-index list
+__global__ void k_sorted_ptr(const int32_t *__restrict__ row, int64_t n_items, int32_t n_rows, int32_t *__restrict__ ptr)
+{
+    const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k > n_items) return;
+    const int prev = k == 0 ? -1 : row[k - 1], cur = k == n_items ? n_rows : row[k];
+    for (int r = prev + 1; r <= cur; ++r) ptr[r] = (int32_t)k;
+}
+
+int arb_build_side_lists(arb_ctx *ctx)
+{
+    if (!ctx->side_dirty) return ARB_OK;
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const int n_pairs = ctx->n_pairs;
+    const int64_t nnz = ctx->nnz;
+    const int B = 256;
+    // per-code tables the general first pass reads (true w, deep flag)
+    std::vector<double> w_true((size_t)n_pairs);
+    bool any = false;
+    for (int c = 0; c < n_pairs; ++c) {
+        w_true[c] = ctx->tab_lp[c] - ctx->tab_la[c];
+        any = any || (c < (int)ctx->pair_deep.size() && ctx->pair_deep[c]);
+    }
+    ARB_TRY(ctx->tab_w_dev.reserve((size_t)n_pairs * 8));
+    ARB_TRY(ctx->tab_deep_dev.reserve((size_t)n_pairs + 16));
+    ARB_CUDA(cudaMemcpy(ctx->tab_w_dev.p, w_true.data(), (size_t)n_pairs * 8, cudaMemcpyHostToDevice));
+    ARB_CUDA(cudaMemcpy(ctx->tab_deep_dev.p, ctx->pair_deep.data(), (size_t)n_pairs, cudaMemcpyHostToDevice));
+    ctx->n_side = 0;
+    if (!any) {
+        for (DevBuf *b : {&ctx->side_z_ptr, &ctx->side_z_idx, &ctx->side_z_w, &ctx->side_y_ptr, &ctx->side_y_idx, &ctx->side_y_w})
+            b->release();
+        ctx->side_dirty = false;
+        return ARB_OK;
+    }
+    DevBuf flag, pos, s_cell, s_snv, key_out, order_in, order_out;
+    ARB_TRY(flag.reserve((size_t)nnz * 4));
+    ARB_TRY(pos.reserve((size_t)(nnz + 1) * 4));
+    k_side_flags<<<grid_for(nnz, B), B, 0, st>>>(ctx->coo_code.as<uint16_t>(), ctx->tab_deep_dev.as<uint8_t>(), nnz,
+                                                 flag.as<int32_t>());
+    ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
+        return cub::DeviceScan::ExclusiveSum(tmp, bytes, flag.as<int32_t>(), pos.as<int32_t>(), (int)nnz, st);
+    }));
+    int32_t last_pos = 0, last_flag = 0;
+    ARB_CUDA(cudaMemcpyAsync(&last_pos, pos.as<int32_t>() + (nnz - 1), 4, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaMemcpyAsync(&last_flag, flag.as<int32_t>() + (nnz - 1), 4, cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaStreamSynchronize(st));
+    const int64_t ns = (int64_t)last_pos + last_flag;
+    ctx->n_side = ns;
+    ARB_TRY(s_cell.reserve((size_t)ns * 4 + 16));
+    ARB_TRY(ctx->side_z_idx.reserve((size_t)ns * 4 + 16));
+    ARB_TRY(ctx->side_z_w.reserve((size_t)ns * 8 + 16));
+    ARB_TRY(ctx->side_z_ptr.reserve(((size_t)ctx->n_cells + 1) * 4));
+    ARB_TRY(ctx->side_y_idx.reserve((size_t)ns * 4 + 16));
+    ARB_TRY(ctx->side_y_w.reserve((size_t)ns * 8 + 16));
+    ARB_TRY(ctx->side_y_ptr.reserve(((size_t)ctx->n_snvs + 1) * 4));
+    // canonical order is (cell, snv): the compacted list is the cell-major side list as it stands
+    k_side_compact<<<grid_for(nnz, B), B, 0, st>>>(ctx->coo_cell.as<int32_t>(), ctx->coo_snv.as<int32_t>(),
+                                                   ctx->coo_code.as<uint16_t>(), flag.as<int32_t>(), pos.as<int32_t>(),
+                                                   ctx->tab_w_dev.as<double>(), nnz, s_cell.as<int32_t>(),
+                                                   ctx->side_z_idx.as<int32_t>(), ctx->side_z_w.as<double>());
+    k_sorted_ptr<<<grid_for(ns + 1, B), B, 0, st>>>(s_cell.as<int32_t>(), ns, ctx->n_cells, ctx->side_z_ptr.as<int32_t>());
+    // SNV-major copy: stable sort of the positions by SNV (cells stay ascending inside an SNV)
+    ARB_TRY(s_snv.reserve((size_t)ns * 4 + 16));
+    ARB_TRY(key_out.reserve((size_t)ns * 4 + 16));
+    ARB_TRY(order_in.reserve((size_t)ns * 4 + 16));
+    ARB_TRY(order_out.reserve((size_t)ns * 4 + 16));
+    k_iota<<<grid_for(ns, B), B, 0, st>>>(order_in.as<int32_t>(), ns);
+    ARB_TRY(with_cub(ctx, [&](void *tmp, size_t &bytes) {
+        return cub::DeviceRadixSort::SortPairs(tmp, bytes, ctx->side_z_idx.as<int32_t>(), key_out.as<int32_t>(),
+                                               order_in.as<int32_t>(), order_out.as<int32_t>(), (int)ns, 0, 32, st);
+    }));
+    k_side_gather<<<grid_for(ns, B), B, 0, st>>>(order_out.as<int32_t>(), s_cell.as<int32_t>(), ctx->side_z_w.as<double>(), ns,
+                                                 ctx->side_y_idx.as<int32_t>(), ctx->side_y_w.as<double>());
+    k_sorted_ptr<<<grid_for(ns + 1, B), B, 0, st>>>(key_out.as<int32_t>(), ns, ctx->n_snvs, ctx->side_y_ptr.as<int32_t>());
+    ARB_CUDA(cudaStreamSynchronize(st));
+    ARB_CUDA(cudaGetLastError());
+    for (DevBuf *b : {&flag, &pos, &s_cell, &s_snv, &key_out, &order_in, &order_out}) b->release();
+    ctx->side_dirty = false;
+    return ARB_OK;
+}
+
 static int check_table_range(arb_ctx *ctx)
 {
     for (int c = 0; c < ctx->n_pairs; ++c) {
         if (ctx->pair_count[c] == 0) continue;
         const double w = ctx->tab_lp[c] - ctx->tab_la[c];
-        ARB_REQUIRE(w == w, ARB_ERR_INVALID, "count pair %d (alt %d, total %d) has no finite log-likelihoods (alt > total?)",
-                    c, c < (int)ctx->pair_alt.size() ? ctx->pair_alt[c] : -1,
+        ARB_REQUIRE(w == w && fabs(w) < 1e300, ARB_ERR_INVALID,
+                    "count pair %d (alt %d, total %d) has no finite log-likelihoods (alt > total?)", c,
+                    c < (int)ctx->pair_alt.size() ? ctx->pair_alt[c] : -1,
                     c < (int)ctx->pair_total.size() ? ctx->pair_total[c] : -1);
-        ARB_REQUIRE(!(w > 600.0) && !(w < -34.0), ARB_ERR_UNSUPPORTED,
-                    "count pair %d has log-likelihood ratio %.1f outside [-34, 600]: deep-coverage "
-                    "entries need the log-domain path, which this release does not have", c, w);
     }
-    return ARB_OK;
+    return arb_build_side_lists(ctx);        // deep pairs (w outside [ARB_W_LO, ARB_W_HI]) go through the log-domain path
 }
 int arb_check_table_range(arb_ctx *ctx) { return check_table_range(ctx); }
 

@@ -735,23 +735,80 @@ def test_writers_at_scale_use_batched_refits(eng_mod, tmp_path):
     assert eng.last_fit_profile()["refit_batches"] == before
 
 
-def test_deep_coverage_pairs_are_refused_loudly(eng_mod):
-    """A count pair whose log-likelihood ratio leaves [-34, 600] (total >= 50 with alt = 0 at the default alpha)
-    is outside this release's product-form sweep (DESIGN.md "limits"): the fit must fail with
-    ARB_ERR_UNSUPPORTED and say which pair, never return numbers.  alt > total (no finite likelihood) likewise."""
+def _with_deep_rows(rc, seed):
+    """Give ~4 % of the rows deep coverage: alt = 0 with total 14..80 (w down to -55), every read variant with
+    total 85..120 (w up to +880) and a few moderate ones -- the pairs whose log-likelihood ratio leaves
+    [ARB_W_LO, ARB_W_HI] and that the reference handles in the log domain without noticing."""
+    rng = np.random.default_rng(seed)
+    rc = rc.copy()
+    idx = rng.choice(len(rc), size=max(12, len(rc) // 25), replace=False)
+    third = len(idx) // 3
+    tot = rc["total"].to_numpy().copy()
+    alt = rc["alt"].to_numpy().copy()
+    tot[idx[:third]] = rng.integers(14, 81, third)
+    alt[idx[:third]] = 0
+    tot[idx[third:2 * third]] = rng.integers(85, 121, third)
+    alt[idx[third:2 * third]] = tot[idx[third:2 * third]]
+    tot[idx[2 * third:]] = rng.integers(20, 60, len(idx) - 2 * third)
+    alt[idx[2 * third:]] = rng.integers(0, 4, len(idx) - 2 * third)
+    rc["total"], rc["alt"] = tot, alt
+    return rc
+
+
+def test_deep_coverage_pairs_go_through_the_log_domain(eng_mod):
+    """Count pairs whose log-likelihood ratio w = lp - la leaves [-9, 600] (alt = 0 with total >= 14, or >= 83 alt
+    reads, at the default alpha) cannot use the product form 1 + expm1(w) S at the reference's accuracy: their
+    nonzeros are neutral in the sweeps and the finishing kernels add log(Sbar + S e^w) from side lists, like the
+    reference's log-sum-exp (A.py:229-243, 354-369).  Against the oracle: ELBOs, iteration counts, posteriors,
+    ranking, MAP -- soft and hard-assignment modes, and the K = 2 first pass (k_first_pass_general)."""
+    from arborist_b200 import arborist, synth
+    from oracle import oracle as orc
+    cfg = synth.SynthConfig("deepcov", 220, 640, 9, 6, seed=4343, coverage=0.06, offtree_frac=0.1, extra_depth=0.6)
+    d = synth.generate(cfg)
+    rc, cl = _with_deep_rows(d.read_counts_frame(), 1), d.clusters_frame()
+    lik, best, fits = arborist(d.trees, rc, cl, max_iter=25, tolerance=1.0, add_normal=True, device=0)
+    eng = arborist.last_stats["engine"]()
+    lp, la = eng.loglik_table()
+    assert ((lp - la) < -9).any() and ((lp - la) > 600).any(), "the workload has no deep pairs"
+    olik, obest, ofits, prob = orc.arborist_oracle(d.trees, rc, cl, max_iter=25, tolerance=1.0, add_normal=True)
+    assert best.tree_idx == obest
+    got = np.array([lik[t] for t in range(len(d.trees))])
+    want = np.array([olik[t] for t in range(len(d.trees))])
+    np.testing.assert_allclose(got, want, rtol=ELBO_RTOL)
+    assert np.array_equal(np.argsort(-got, kind="stable"), np.argsort(-want, kind="stable"))
+    for t in range(len(d.trees)):
+        assert arborist.last_stats["iters"][t] == ofits[t][3]
+        np.testing.assert_allclose(fits[t].q_z, ofits[t][1], rtol=1e-9, atol=Q_ATOL)
+        np.testing.assert_allclose(fits[t].q_y, ofits[t][2], rtol=1e-9, atol=Q_ATOL)
+        assert_map_equal(fits[t].q_z, ofits[t][1], where="deepcov")
+        assert_map_equal(fits[t].q_y, ofits[t][2], where="deepcov")
+    # hard-assignment mode on the same matrix (same side lists, HARD variant of the q(z) finishing kernel)
+    P = orc.enumerate_presence(orc.add_normal_clone(d.trees)[0], best.clone_to_idx, best.cluster_to_idx)
+    K = len(best.clone_to_idx)
+    ml, iters = eng.fit(presence=np.ascontiguousarray(P != 0, np.uint8)[None], n_clones=K, max_iter=5, mode="ml",
+                        keep_posteriors="all")
+    want_ml = orc.run_simple_max_likelihood(P, prob.ll_cs, prob.ll_ss, prob.cell_idx_ss, prob.snv_idx_cs, prob.n_cells,
+                                            prob.n_snvs, K, prob.q_y_init, prob.cell_ptr, prob.snv_ptr)
+    assert ml[0] == pytest.approx(want_ml[0], rel=ELBO_RTOL)
+    # K = 2: prior rows of mass gamma AND deep pairs in the general first pass
+    d2 = synth.generate(synth.SynthConfig("k2deep", 120, 300, 2, 1, seed=7003, coverage=0.1, min_proportion=0.2))
+    rc2, cl2 = _with_deep_rows(d2.read_counts_frame(), 2), d2.clusters_frame()
+    lik2, best2, fits2 = arborist([[(0, 1)]], rc2, cl2, max_iter=5, device=0)
+    olik2, _, ofits2, _ = orc.arborist_oracle([[(0, 1)]], rc2, cl2, max_iter=5)
+    assert lik2[0] == pytest.approx(olik2[0], rel=ELBO_RTOL)
+    np.testing.assert_allclose(fits2[0].q_z, ofits2[0][1], rtol=1e-9, atol=Q_ATOL)
+
+
+def test_impossible_counts_are_refused(eng_mod):
+    """alt > total has no binomial likelihood (scipy gives NaN / -inf): an error that names the pair, never numbers."""
     from arborist_b200 import arborist, synth
     d = synth.generate(synth.CONFIGS["tiny"])
     rc, cl = d.read_counts_frame(), d.clusters_frame()
-    deep = rc.copy()
-    deep.loc[deep.index[3], ["alt", "total"]] = [0, 60]
-    with pytest.raises(eng_mod.ArboristError) as err:
-        arborist(d.trees, deep, cl, max_iter=3, add_normal=True, device=0)
-    assert err.value.status == -3 and "log-likelihood ratio" in str(err.value)
     bad = rc.copy()
     bad.loc[bad.index[3], ["alt", "total"]] = [5, 2]
     with pytest.raises(eng_mod.ArboristError) as err:
         arborist(d.trees, bad, cl, max_iter=3, add_normal=True, device=0)
-    assert err.value.status in (-1, -3)
+    assert err.value.status == -1 and "alt 5, total 2" in str(err.value)
 
 
 def test_zz_map_tie_rows_are_a_handful(eng_mod):

@@ -717,8 +717,11 @@ __device__ __forceinline__ void finish_row(const FinishArgs &a, int slot, int po
 #define FIN_WARPS (FIN_THREADS / 32)
 
 // grid (row blocks of FIN_ROWS, trees of the sweep's list); a warp takes TW = 32/GL rows at a time
+#ifndef ARB_FINZ_OCC
+#define ARB_FINZ_OCC 4       // CTAs per SM the q(z) finishing kernel is compiled for (register cap 64 at 4, 85 at 3)
+#endif
 template <int GL, bool IS_Z, bool HARD, bool SIDE>
-__global__ void __launch_bounds__(FIN_THREADS, SIDE ? 3 : 4) k_finish(const FinishArgs a)
+__global__ void __launch_bounds__(FIN_THREADS, SIDE ? 3 : (IS_Z ? ARB_FINZ_OCC : 4)) k_finish(const FinishArgs a)
 {
     __shared__ double sh[FIN_WARPS];
     if (a.ctl && (int)blockIdx.y >= (IS_Z ? a.ctl->n_z : a.ctl->n_y)) return;

@@ -19,6 +19,10 @@ __all__ = ["world", "shard_indices", "gather_elbos", "broadcast_fit", "gather_ve
 
 def world():
     """(rank, world_size) of the initialised default process group, else (0, 1)."""
+    import sys
+
+    if "torch" not in sys.modules:          # nobody can have initialised a process group: do not pay the import
+        return 0, 1
     try:
         import torch.distributed as dist
     except ImportError:          # pragma: no cover

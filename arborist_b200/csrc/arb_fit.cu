@@ -1045,13 +1045,47 @@ __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict_
         }
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
-        int ny = 0, nz = 0, ni = 0, na = 0, next = ctl->next_tree;
-        const bool gen = ctl->general_init != 0;
-        for (int s = 0; s < s1; ++s) {
-            SlotState z = st[s];
-            if (z.phase == PH_EMPTY && next < ctl->n_trees) {
-                z.tree = next++;
+    // ---- slot refill and the next round's lists, all threads: thread t owns the slots [t * per, (t + 1) * per) so
+    // that positions follow slot order; two block scans give every slot its place in the lists
+    __shared__ int sc_a[256], sc_b[256];
+    const int T = blockDim.x, t = threadIdx.x, per = (s1 + T - 1) / T;
+    const int lo = min(s1, t * per), hi = min(s1, lo + per);
+    const bool gen = ctl->general_init != 0;
+    const int next0 = ctl->next_tree, avail = max(0, ctl->n_trees - next0);
+    int ce = 0, ci = 0;
+    for (int s = lo; s < hi; ++s) {
+        const int ph = st[s].phase;
+        ce += ph == PH_EMPTY;
+        ci += ph == PH_ITER;
+    }
+    auto block_scan = [&](int v, int *buf, int &total) {        // exclusive prefix of v over the threads
+        buf[t] = v;
+        __syncthreads();
+        for (int o = 1; o < T; o <<= 1) {
+            const int add = t >= o ? buf[t - o] : 0;
+            __syncthreads();
+            buf[t] += add;
+            __syncthreads();
+        }
+        total = buf[T - 1];
+        const int ex = buf[t] - v;
+        __syncthreads();
+        return ex;
+    };
+    int tot_e = 0, tot_i = 0, tot_z = 0;
+    const int pe = block_scan(ce, sc_a, tot_e);                 // empties before this thread's slots
+    const int pi = block_scan(ci, sc_b, tot_i);                 // iterating slots before them
+    const int my_new = max(0, min(ce, avail - pe));             // the first `avail` empties (slot order) get a tree
+    const int cz = ci + (gen ? 0 : my_new);
+    const int pz = block_scan(cz, sc_a, tot_z);
+    int ke = 0, ki = 0, kz = 0;
+    for (int s = lo; s < hi; ++s) {
+        SlotState z = st[s];
+        bool in_z = false;
+        if (z.phase == PH_EMPTY) {
+            const int rank = pe + ke++;
+            if (rank < avail) {
+                z.tree = next0 + rank;
                 z.phase = PH_INIT;
                 z.iter = 0;
                 z.converged = 0;
@@ -1059,23 +1093,28 @@ __global__ void k_control(Control *ctl, SlotState *st, const double *__restrict_
                 z.cur = 0;
                 z.bestb = 1;                                  // nothing kept yet: the first pass writes plane 0
                 st[s] = z;
-                list_init[ni++] = s;
-            } else if (z.phase == PH_ITER) {
-                list_y[ny++] = s;
+                list_init[rank] = s;
+                in_z = !gen;
             }
-            if (z.phase != PH_EMPTY) ++na;
-            if (z.phase == PH_ITER || (z.phase == PH_INIT && !gen)) {
-                pos_z[s] = nz;                                // packed position in this round's q(z) sweep
-                list_z[nz++] = s;
-            }
+        } else if (z.phase == PH_ITER) {
+            list_y[pi + ki++] = s;
+            in_z = true;
         }
-        ctl->next_tree = next;
-        ctl->n_y = ny;
-        ctl->n_z = nz;
+        if (in_z) {
+            pos_z[s] = pz + kz;                               // packed position in this round's q(z) sweep
+            list_z[pz + kz] = s;
+            ++kz;
+        }
+    }
+    if (t == 0) {
+        const int ni = min(tot_e, avail);
+        ctl->next_tree = next0 + ni;
+        ctl->n_y = tot_i;
+        ctl->n_z = tot_z;
         ctl->n_init = ni;
-        ctl->n_act = na;
-        ctl->n_vy = (ny * ctl->chunks_y + 3) >> 2;
-        ctl->n_vz = (nz * ctl->chunks_z + 3) >> 2;
+        ctl->n_act = tot_i + ni;
+        ctl->n_vy = (tot_i * ctl->chunks_y + 3) >> 2;
+        ctl->n_vz = (tot_z * ctl->chunks_z + 3) >> 2;
         ctl->round += 1;
     }
 }

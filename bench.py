@@ -346,7 +346,24 @@ def run_gpu_arm(args):
             s_ms += ms
         barrier()
         s_ms = max_over_ranks(s_ms)
+        # the same through arborist(...) with host DataFrames (every rank: prepare its shard's trees, ingest the table,
+        # fit, gather): the per-rank ingest does not shrink with N, so this is the Amdahl view of strong scaling
+        s_e2e = None
+        if not args.no_e2e:
+            def strong_e2e():
+                lik, best_s, _ = arborist(trees[:T_s], rc, cl, alpha=RUN["alpha"], max_iter=RUN["max_iter"],
+                                          tolerance=RUN["tolerance"], gamma=RUN["gamma"], add_normal=True, device=local)
+                return best_s.tree_idx
+            strong_e2e()
+            barrier()
+            t_s0 = time.perf_counter()
+            for _ in range(args.steps):
+                strong_e2e()
+            barrier()
+            s_e2e = T_s * steps / max_over_ranks(time.perf_counter() - t_s0)
+            arborist.last_stats = None
         strong = {"trees_total": int(T_s), "trees_per_gpu": float(T_s) / world, "value": T_s * steps / (s_ms * 1e-3),
+                  "e2e_value": s_e2e,
                   "unit": "trees/s", "ms_per_step": s_ms / steps, "best_tree": int(np.argmax(full_s)),
                   "note": "same metric with the TOTAL candidate set fixed (north_star: 1,000 trees, 1 -> 8 GPUs); "
                           "device events, max over ranks; divide by the N = 1 line's value for the speed-up"}

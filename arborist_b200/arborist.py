@@ -300,11 +300,12 @@ def ingest_read_counts(eng, read_counts, snv_clusters, cluster_to_idx, alpha, ga
 # ---------------------------------------------------------------------------
 # the public entry point
 # ---------------------------------------------------------------------------
-def _pick_devices(device, devices, n_trees):
+def _pick_devices(device, devices, n_trees, work=0.0):
     """GPUs one ``arborist(...)`` call drives.  Under a ``torch.distributed`` group: the one GPU of this rank.
     Otherwise ``devices`` ("all", a count, or a list of ordinals) or ``device``; the default is every visible GPU
-    once the candidate set is large enough to keep them busy (a small set stays on one GPU: every extra context
-    costs an ingest of the read-count table)."""
+    once the job is large enough to pay for them -- every extra GPU costs a CUDA context (~0.2 s) and an ingest of
+    the read-count table, so a fit that one GPU finishes in about a second (config 3: table rows x clones x trees
+    = 4.8e10, 0.66 s) stays on one; ``work`` is that product."""
     from . import distributed
     from .engine import device_count
 
@@ -314,7 +315,7 @@ def _pick_devices(device, devices, n_trees):
     n = device_count()
     if devices is None:
         env = os.environ.get("ARBORIST_DEVICES", "")
-        devices = env if env else ("all" if n_trees >= 32 * max(1, n) else 1)
+        devices = env if env else ("all" if n_trees >= 32 * max(1, n) and work >= 1.5e11 else 1)
     if isinstance(devices, str):
         devices = n if devices == "all" else [int(x) for x in devices.split(",") if x.strip() != ""]
     if isinstance(devices, (int, np.integer)):
@@ -352,8 +353,9 @@ def arborist(
     to ``numba.set_num_threads``, A.py:1002; nothing here runs on host threads).
     Keyword-only extras: ``device`` (one CUDA ordinal), ``devices`` ("all", a count or
     a list of ordinals: the candidate set is spread over those GPUs by THIS process,
-    ``arb_fit_trees_multi``; default: every visible GPU for sets of at least 32 trees
-    per GPU, environment override ``ARBORIST_DEVICES``) and ``keep_posteriors``
+    ``arb_fit_trees_multi``; default: every visible GPU once the job is worth their
+    start-up cost -- at least 32 trees per GPU and table rows x clones x trees >= 1.5e11, i.e.
+    about 2 s of one GPU; environment override ``ARBORIST_DEVICES``) and ``keep_posteriors``
     ("auto" | "all" | "none": whether every tree's best ``q_z``/``q_y`` stay resident
     on the GPU or are re-fitted in batches on demand).
     Under an initialised ``torch.distributed`` group (one process per GPU) the candidate
@@ -395,7 +397,11 @@ def arborist(
     mark("trees")
 
     log("Removing SNVs with 0 variant reads across all cells...")
-    devs = _pick_devices(device, devices, len(shard))
+    if isinstance(read_counts, (str, os.PathLike)):
+        rows = os.path.getsize(read_counts) / 15.0           # ~15 bytes per CSV row
+    else:
+        rows = float(len(read_counts))
+    devs = _pick_devices(device, devices, len(shard), rows * K * len(shard))
     engines = [Engine(device=d) for d in devs]
     mark("context")
     log("Caching log-likelihoods for presence/absence...")

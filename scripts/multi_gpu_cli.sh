@@ -11,10 +11,14 @@ d = synth.generate(synth.CONFIGS["config3"])
 os.makedirs("gpurun_out/cli", exist_ok=True)
 d.read_counts_frame().to_csv("gpurun_out/cli/rc.csv", index=False)
 d.clusters_frame().to_csv("gpurun_out/cli/clusters.csv", index=False, header=False)
-write_trees(d.trees, "gpurun_out/cli/trees.txt")
+rng = np.random.default_rng(7)
+trees = list(d.trees)
+while len(trees) < 4000:                      # 4,000 candidate trees: 2.6 s of one GPU
+    trees.append(synth._edges(synth.random_tree(rng, d.config.n_clones - 1)))
+write_trees(trees, "gpurun_out/cli/trees.txt")
 print("devices visible:", engine.device_count())
 PY
-nvidia-smi --query-gpu=index,utilization.gpu,memory.used --format=csv,noheader -lms 250 > gpurun_out/cli/smi.csv &
+nvidia-smi --query-gpu=index,utilization.gpu,memory.used --format=csv,noheader -lms 50 > gpurun_out/cli/smi.csv &
 SMI=$!
 for dev in 1 all; do
 T0=$(date +%s.%N)

@@ -107,8 +107,8 @@ def load_library():
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
-    if lib.arb_abi_version() != 1:
-        raise RuntimeError(f"{path}: ABI version {lib.arb_abi_version()} != 1")
+    if lib.arb_abi_version() != 2:
+        raise RuntimeError(f"{path}: ABI version {lib.arb_abi_version()} != 2")
     _LIB = lib
     return lib
 

@@ -37,7 +37,7 @@ extern "C" {
 #endif
 
 #define ARB_MAX_CLONES 32 /* K <= 32 in this release (one lane per clone) */
-#define ARB_ABI_VERSION 1
+#define ARB_ABI_VERSION 2 /* 2: arb_fit_trees_multi, arb_get_fits, ARB_ERR_DECLINED, profile slots 20-23; "groups" option gone */
 
 typedef enum arb_status {
     ARB_OK = 0,

@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(lib, name), f"{name} declared in the header but not exported"
     # and the binding covers all of them
     assert sorted(engine._SIGNATURES) == _declared()
-    assert lib.arb_abi_version() == 1
+    assert lib.arb_abi_version() == 2
 
 
 def test_no_cpu_fallback_without_a_device():

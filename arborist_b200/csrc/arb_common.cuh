@@ -47,6 +47,7 @@ void arb_set_error(const char *fmt, ...);
 void *arb_pool_alloc(size_t n, size_t *got);       // nullptr on failure (error already set)
 void arb_pool_free(void *p, size_t n);
 size_t arb_pool_bytes(int device);                 // bytes parked in the pool for this device
+void arb_pool_flush_device(int device);            // return them to the driver
 
 struct DevBuf {
     void *p = nullptr;

@@ -1257,8 +1257,12 @@ static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve
         // one virtual slot of slack for the rounding of the packed buffers
         const int64_t mg = (int64_t)L.np_z * L.prz, ng = (int64_t)L.np_y * L.pry;
         const int64_t slack = (mg + ng) * ARB_VW * 8 + ((int64_t)L.np_z * n * 20 + (int64_t)L.np_y * m * 12) * ARB_VW;
-        const int64_t usable = (int64_t)(free_b * 0.90) - reserve_bytes - slack;
+        // leave a tenth of the free memory, at least 4 GB, to the other allocators of the process (NCCL buffers,
+        // torch): a candidate set that does not fit in flight takes everything else
+        const int64_t headroom = std::max<int64_t>((int64_t)(free_b * 0.10), (int64_t)4 << 30);
+        const int64_t usable = (int64_t)free_b - headroom - reserve_bytes - slack;
         const int64_t fit = usable / ws.per_slot_bytes;
+        const bool tight = fit < n_slots;
         ARB_REQUIRE(fit >= 1, ARB_ERR_NOMEM, "not enough device memory for one tree slot (%lld bytes needed, %lld usable)",
                     (long long)ws.per_slot_bytes, (long long)usable);
         if (fit < n_slots) n_slots = (int)fit;
@@ -1280,6 +1284,9 @@ static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve
         ctx->ws_kp = kp;
         ctx->ws_k = K;
         ctx->ws_slots = (int)S;
+        // memory-tight: blocks still parked in the pool (ingest scratch) were counted as free above but no other
+        // allocator can have them; hand them back so that the headroom is real
+        if (tight) arb_pool_flush_device(ctx->device);
     }
     ws.n_slots = std::min(n_slots, ctx->ws_slots);          // a fit may use fewer slots than the workspace holds
     for (auto &r : ctx->rev)

@@ -147,6 +147,14 @@ void arb_pool_free(void *p, size_t n)
     g_pool.push_back(PoolBlock{p, n, device});
 }
 
+// give this device's parked blocks back to the driver (memory-tight fits: what stays parked is invisible to every
+// other allocator of the process -- NCCL, torch -- although cudaMemGetInfo-based sizing here counts it as free)
+void arb_pool_flush_device(int device)
+{
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    pool_flush_locked(device);
+}
+
 size_t arb_pool_bytes(int device)
 {
     std::lock_guard<std::mutex> lk(g_pool_mu);

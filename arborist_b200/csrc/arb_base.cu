@@ -15,6 +15,7 @@
 
 #include <algorithm>
 #include <cub/cub.cuh>
+#include <mutex>
 
 #define ARB_BASE_MAXC 32      // clusters (bit masks are 32 bits wide)
 #define ARB_BASE_MAXK 64      // clones per tree
@@ -308,5 +309,158 @@ ARB_API int arb_base_cells(arb_ctx *ctx, int32_t n_trees, int32_t n_clones, cons
     ARB_CUDA(cudaMemcpyAsync(present, d_pres.p, cells, cudaMemcpyDeviceToHost, st));
     ARB_CUDA(cudaStreamSynchronize(st));
     for (DevBuf *b : {&d_anc, &d_tm, &d_ll, &d_post, &d_idx, &d_ent, &d_pres}) b->release();
+    return ARB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// arb_base_score_static: the tree scorer for callers that must not allocate device memory
+// ---------------------------------------------------------------------------------------------------------
+// arb_base_score above takes three temporary device buffers per call (the uploaded masks and the result vector)
+// from the allocation pool, which falls through to cudaMalloc whenever the pool has no block of that size.  Some
+// hosts cannot afford that once their set-up phase is over:
+//   - a process whose device memory already belongs to another allocator (a tensor framework's caching allocator,
+//     an RMM pool, a JVM GPU plug-in): a late cudaMalloc there fails or fragments the other allocator's arena;
+//   - a scoring loop with a latency budget: cudaMalloc / cudaFree take a process-wide driver lock and may wait for
+//     all work on the device, so a call that allocates stalls every other stream of the process;
+//   - a client running under a fixed device-memory quota (a MIG slice or an MPS client with a memory limit that the
+//     tables of arb_base_ingest have already been budgeted against).
+// For them every byte this variant needs beyond the caller's own arrays and the tables arb_base_ingest left in the
+// context sits in ONE fixed array in the library's device image.  The CUDA runtime instantiates the array on every
+// GPU on which this library's module gets loaded and keeps it until the process exits; that is the price, hence
+// the modest size.
+//
+// What lives in the array during a call (all offsets multiples of 256 bytes):
+//   tickets  uint32 [n_trees]           CTAs of a tree that have delivered their partial sum -- must start at ZERO
+//   partial  double [n_trees * splits]  per-CTA partial scores (the real scratch of the split kernel)
+//   anc      uint32 [n_trees * K]       staged copy of the caller's ancestor masks
+//   tmask    uint32 [n_trees]           staged copy of the caller's tree masks
+//   lik      double [n_trees]           result, copied back to the caller
+// There is one array per GPU and every call on that GPU uses it from offset 0, and it still holds whatever the last
+// call left there: the tickets are cleared at the start of each call (the kernel also resets them, but a call that
+// died half-way must not poison the next), everything else is overwritten before it is read.  Two calls that are in
+// flight on the same GPU at the same time (two contexts, two host threads) would overwrite each other's masks and
+// tickets: the caller has to serialise them.
+static __device__ __align__(256) unsigned char g_base_static[ARB_BASE_STATIC_BYTES];
+
+namespace {
+
+constexpr int BASE_STATIC_MAX_SPLIT = 64;      // CTAs per tree at most
+constexpr int BASE_STATIC_MAX_DEVICES = 64;
+
+// In host code `g_base_static` is only a handle for the runtime, not a device address: the address on each GPU has
+// to be asked for with that GPU current.  Looked up by the first call on each device (which may also make the
+// runtime load this library's module onto that GPU), then kept: let that first call happen during set-up, before any
+// stream capture begins.
+std::mutex g_base_static_mu;
+unsigned char *g_base_static_addr[BASE_STATIC_MAX_DEVICES];
+
+int base_static_address(int device, unsigned char **out)
+{
+    ARB_REQUIRE(device >= 0 && device < BASE_STATIC_MAX_DEVICES, ARB_ERR_UNSUPPORTED,
+                "arb_base_score_static: device ordinal %d; ordinals below %d are supported", device,
+                BASE_STATIC_MAX_DEVICES);
+    std::lock_guard<std::mutex> lock(g_base_static_mu);
+    if (!g_base_static_addr[device]) {
+        ARB_CUDA(cudaSetDevice(device));
+        void *p = nullptr;
+        ARB_CUDA(cudaGetSymbolAddress(&p, g_base_static));
+        ARB_REQUIRE(p != nullptr, ARB_ERR_CUDA, "arb_base_score_static: no device address for the static scratch array");
+        g_base_static_addr[device] = static_cast<unsigned char *>(p);
+    }
+    *out = g_base_static_addr[device];
+    return ARB_OK;
+}
+
+inline size_t up256(size_t n) { return (n + 255) & ~(size_t)255; }
+
+// k_base_score with the cells of a tree dealt out to gridDim.x CTAs (a handful of trees no longer leaves most of
+// the SMs idle).  CTA (s, t) sums the cells s * 256 + thread, stepping by gridDim.x * 256, and leaves its partial sum
+// in the scratch; the CTA that draws the last ticket of tree t adds the partial sums in the order s = 0, 1, ... --
+// the result does not depend on which CTA finishes last.  With one CTA per tree the additions are those of
+// k_base_score.
+__global__ void __launch_bounds__(256) k_base_score_split(const double *__restrict__ TA, const double *__restrict__ TB,
+                                                          const int32_t *__restrict__ CNT, int n_cells, int C, int K,
+                                                          const uint32_t *__restrict__ anc_all,
+                                                          const uint32_t *__restrict__ tmask_all, double *partial,
+                                                          unsigned int *tickets, double *__restrict__ lik)
+{
+    __shared__ uint32_t anc[ARB_BASE_MAXK];
+    __shared__ double part[256];
+    const int t = blockIdx.y, s = blockIdx.x, S = gridDim.x;
+    for (int c = threadIdx.x; c < K; c += blockDim.x) anc[c] = anc_all[(int64_t)t * K + c];
+    __syncthreads();
+    const uint32_t tmask = tmask_all[t];
+    double L[ARB_BASE_MAXK];
+    double acc = 0;
+    for (int cell = s * 256 + threadIdx.x; cell < n_cells; cell += S * 256) {
+        int rows = base_cell_loglik(TA, TB, CNT, cell, C, K, anc, tmask, L);
+        if (!rows) continue;
+        double best = L[0];
+        for (int c = 1; c < K; ++c) best = L[c] > best ? L[c] : best;
+        acc += best;
+    }
+    part[threadIdx.x] = acc;
+    __syncthreads();
+    for (int o = 128; o; o >>= 1) {
+        if (threadIdx.x < o) part[threadIdx.x] += part[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        partial[(int64_t)t * S + s] = part[0];
+        __threadfence();                                        // the partial sum is visible before the ticket is drawn
+        if (atomicAdd(&tickets[t], 1u) == (unsigned)(S - 1)) {      // every other CTA of this tree has delivered
+            __threadfence();
+            const volatile double *p = partial + (int64_t)t * S;
+            double sum = 0;
+            for (int i = 0; i < S; ++i) sum += p[i];
+            lik[t] = sum;
+            tickets[t] = 0;
+        }
+    }
+}
+
+}  // namespace
+
+ARB_API int arb_base_score_static(arb_ctx *ctx, int32_t n_trees, int32_t n_clones, const uint32_t *anc_masks,
+                                  const uint32_t *tree_masks, double *likelihood)
+{
+    ARB_REQUIRE(ctx && likelihood, ARB_ERR_INVALID, "arb_base_score_static: null argument");
+    ARB_REQUIRE(ctx->base_cells > 0, ARB_ERR_INVALID, "arb_base_score_static: call arb_base_ingest first");
+    ARB_REQUIRE(n_trees > 0 && anc_masks && tree_masks, ARB_ERR_INVALID, "arb_base_score_static: no trees");
+    ARB_REQUIRE(n_clones > 0 && n_clones <= ARB_BASE_MAXK, ARB_ERR_UNSUPPORTED,
+                "arb_base_score_static: %d clones per tree; at most %d are supported", n_clones, ARB_BASE_MAXK);
+    // CTAs per tree: about two waves over the SMs, no more than there are 256-cell slices
+    const int64_t T = n_trees, K = n_clones;
+    const int64_t slices = (ctx->base_cells + 255) / 256;
+    int64_t S = (2 * (int64_t)std::max(ctx->sm_count, 1) + T - 1) / T;
+    S = std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(S, slices), BASE_STATIC_MAX_SPLIT));
+    const size_t o_tick = 0;
+    const size_t o_part = o_tick + up256((size_t)T * sizeof(unsigned int));
+    const size_t o_anc = o_part + up256((size_t)(T * S) * sizeof(double));
+    const size_t o_tm = o_anc + up256((size_t)(T * K) * sizeof(uint32_t));
+    const size_t o_lik = o_tm + up256((size_t)T * sizeof(uint32_t));
+    const size_t need = o_lik + up256((size_t)T * sizeof(double));
+    ARB_REQUIRE(need <= (size_t)ARB_BASE_STATIC_BYTES && T <= 65535, ARB_ERR_UNSUPPORTED,
+                "arb_base_score_static: %d trees of %d clones need %lld bytes of scratch, the static array holds %d; "
+                "score the trees in smaller groups or use arb_base_score",
+                n_trees, n_clones, (long long)need, (int)ARB_BASE_STATIC_BYTES);
+    ARB_CUDA(cudaSetDevice(ctx->device));
+    unsigned char *base = nullptr;
+    ARB_TRY(base_static_address(ctx->device, &base));
+    cudaStream_t st = ctx->stream;
+    unsigned int *d_tick = reinterpret_cast<unsigned int *>(base + o_tick);
+    double *d_part = reinterpret_cast<double *>(base + o_part);
+    uint32_t *d_anc = reinterpret_cast<uint32_t *>(base + o_anc);
+    uint32_t *d_tm = reinterpret_cast<uint32_t *>(base + o_tm);
+    double *d_lik = reinterpret_cast<double *>(base + o_lik);
+    ARB_CUDA(cudaMemsetAsync(d_tick, 0, (size_t)T * sizeof(unsigned int), st));
+    ARB_CUDA(cudaMemcpyAsync(d_anc, anc_masks, (size_t)(T * K) * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+    ARB_CUDA(cudaMemcpyAsync(d_tm, tree_masks, (size_t)T * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+    k_base_score_split<<<dim3((unsigned)S, (unsigned)T), 256, 0, st>>>(
+        ctx->base_ta.as<double>(), ctx->base_tb.as<double>(), ctx->base_cnt.as<int32_t>(), ctx->base_cells,
+        ctx->base_clusters, n_clones, d_anc, d_tm, d_part, d_tick, d_lik);
+    ARB_CUDA(cudaGetLastError());
+    ARB_CUDA(cudaMemcpyAsync(likelihood, d_lik, (size_t)T * sizeof(double), cudaMemcpyDeviceToHost, st));
+    ARB_CUDA(cudaStreamSynchronize(st));
     return ARB_OK;
 }

@@ -86,6 +86,7 @@ _SIGNATURES = {
     "arb_csv_finish": (C.c_int, [_ctx, C.c_double, C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "arb_base_ingest": (C.c_int, [_ctx, C.c_int64, _i32p, _i32p, _i32p, _i32p, C.c_int32, C.c_int32, C.c_double]),
     "arb_base_score": (C.c_int, [_ctx, C.c_int32, C.c_int32, _u32p, _u32p, _f64p]),
+    "arb_base_score_static": (C.c_int, [_ctx, C.c_int32, C.c_int32, _u32p, _u32p, _f64p]),
     "arb_base_cells": (C.c_int, [_ctx, C.c_int32, C.c_int32, _u32p, _u32p, _opt, _f64p, _i32p, _f64p, _u8p]),
 }
 
@@ -232,6 +233,18 @@ class Engine:
         tm = np.ascontiguousarray(tree_masks, dtype=np.uint32)
         lik = np.empty(anc.shape[0], np.float64)
         _check(self._lib.arb_base_score(self._h, anc.shape[0], anc.shape[1], anc, tm, lik))
+        return lik
+
+    def base_score_static(self, anc_masks, tree_masks):
+        """``base_score`` without any device allocation (``arb_base_score_static``): for hosts whose device memory
+        belongs to another allocator, that run under a memory quota, or that cannot take the driver-wide stall of a
+        ``cudaMalloc`` inside their scoring loop.  The temporaries live in a fixed 1 MiB array of the library image,
+        so a call that needs more raises ``ArboristError`` (status -3): pass the trees in smaller groups.  One array
+        per GPU: do not run two of these calls on the same GPU at the same time."""
+        anc = np.ascontiguousarray(anc_masks, dtype=np.uint32)
+        tm = np.ascontiguousarray(tree_masks, dtype=np.uint32)
+        lik = np.empty(anc.shape[0], np.float64)
+        _check(self._lib.arb_base_score_static(self._h, anc.shape[0], anc.shape[1], anc, tm, lik))
         return lik
 
     def base_cells(self, anc_masks, tree_masks, want_loglik=False):

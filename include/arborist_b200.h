@@ -229,6 +229,31 @@ int arb_base_ingest(arb_ctx *ctx, int64_t n_rows, const int32_t *cell_code, cons
  * (arborist_base.py:153-160).  n_clones <= 64. */
 int arb_base_score(arb_ctx *ctx, int32_t n_trees, int32_t n_clones, const uint32_t *anc_masks,
                    const uint32_t *tree_masks, double *likelihood);
+/* arb_base_score_static: arb_base_score for callers that must not allocate device memory once set-up is over.
+ * (No counterpart in the reference, which has no device memory to manage; same arguments, same meaning and the same
+ * scores as arb_base_score up to the rounding of a differently grouped sum -- about 1e-15 relative.)
+ *
+ * Who needs it: a host whose device memory is owned by another allocator (a tensor framework's caching allocator, an
+ * RMM pool) so that a late cudaMalloc fails or fragments that arena; a scoring loop with a latency budget, because
+ * cudaMalloc / cudaFree serialise on a driver lock and can wait for the whole device; a client under a fixed memory
+ * quota (MIG slice, MPS limit).  arb_base_score takes three temporary buffers per call from the library's pool, which
+ * ends in cudaMalloc when the pool has nothing of that size.  This variant calls no cudaMalloc / cudaFree and no
+ * allocating library routine: the staged masks, the per-CTA partial sums of its kernel and the result vector live in
+ * one file-scope device array of ARB_BASE_STATIC_BYTES that is part of the library image (every GPU this library's
+ * module is loaded on holds those bytes until the process exits).  The tables of arb_base_ingest, which it reads, were
+ * allocated by that earlier call.
+ *
+ * Limit: the call needs about n_trees * (8 * splits + 4 * n_clones + 16) bytes, each of its five sections rounded up to
+ * 256 bytes, splits = CTAs per tree <= 64 (1 once there are about 300 trees); beyond ARB_BASE_STATIC_BYTES it returns
+ * ARB_ERR_UNSUPPORTED and the message names both numbers -- score the trees in smaller groups then.
+ * First call on a device: looks up the array's address on that device (and may load the module there); make it
+ * during set-up, before any stream capture begins.
+ * Sharing: there is ONE array per GPU, used from offset 0 by every call on that GPU whatever the context, and it keeps
+ * the previous call's bytes; the call clears the part that has to start at zero itself.  Calls that overlap in time on
+ * the same GPU (two host threads, two contexts) race on it: serialise them. */
+#define ARB_BASE_STATIC_BYTES (1 << 20)
+int arb_base_score_static(arb_ctx *ctx, int32_t n_trees, int32_t n_clones, const uint32_t *anc_masks,
+                          const uint32_t *tree_masks, double *likelihood);
 /* arb_base_cells: per-cell detail for the listed trees, all [n_trees][n_cells](x n_clones): log-likelihoods
  * (may be NULL), posteriors over clones exp(L - logsumexp(L)) (arborist_base.py:335-338), index of the first
  * best clone (arborist_base.py:296-298), entropy of the posterior in bits (arborist_base.py:341), and

@@ -1259,12 +1259,16 @@ static int ensure_workspace(arb_ctx *ctx, int K, int want_slots, int64_t reserve
         const int64_t slack = (mg + ng) * ARB_VW * 8 + ((int64_t)L.np_z * n * 20 + (int64_t)L.np_y * m * 12) * ARB_VW;
         // leave a tenth of the free memory, at least 4 GB, to the other allocators of the process (NCCL buffers,
         // torch): a candidate set that does not fit in flight takes everything else
-        const int64_t headroom = std::max<int64_t>((int64_t)(free_b * 0.10), (int64_t)4 << 30);
-        const int64_t usable = (int64_t)free_b - headroom - reserve_bytes - slack;
-        const int64_t fit = usable / ws.per_slot_bytes;
+        // (at most a quarter of what is free: a small or shared GPU keeps most of its memory for the fit)
+        const int64_t headroom = std::min<int64_t>(std::max<int64_t>((int64_t)(free_b * 0.10), (int64_t)4 << 30),
+                                                   (int64_t)(free_b / 4));
+        const int64_t raw = (int64_t)free_b - reserve_bytes - slack;
+        const int64_t usable = raw - headroom;
+        int64_t fit = usable > 0 ? usable / ws.per_slot_bytes : 0;
+        if (fit < 1 && raw >= ws.per_slot_bytes) fit = 1;      // the headroom never turns a fit that has room into an error
         const bool tight = fit < n_slots;
-        ARB_REQUIRE(fit >= 1, ARB_ERR_NOMEM, "not enough device memory for one tree slot (%lld bytes needed, %lld usable)",
-                    (long long)ws.per_slot_bytes, (long long)usable);
+        ARB_REQUIRE(fit >= 1, ARB_ERR_NOMEM, "not enough device memory for one tree slot (%lld bytes needed, %lld free)",
+                    (long long)ws.per_slot_bytes, (long long)raw);
         if (fit < n_slots) n_slots = (int)fit;
         const int64_t S = n_slots, vz = vslots_for(S, K), vy = vslots_for(S, C);
         ARB_TRY(ctx->xs.reserve(vz * mg * ARB_VW * 8));

@@ -317,12 +317,23 @@ def _pick_devices(device, devices, n_trees, work=0.0):
         env = os.environ.get("ARBORIST_DEVICES", "")
         devices = env if env else ("all" if n_trees >= 32 * max(1, n) and work >= 1.5e11 else 1)
     if isinstance(devices, str):
-        devices = n if devices == "all" else [int(x) for x in devices.split(",") if x.strip() != ""]
+        # "all", a bare integer = a COUNT (like devices=2), or a comma-separated list of ordinals ("3," = GPU 3 alone)
+        txt = devices.strip()
+        if txt == "all":
+            devices = n
+        elif "," in txt:
+            devices = [int(x) for x in txt.split(",") if x.strip() != ""]
+        else:
+            devices = int(txt)
     if isinstance(devices, (int, np.integer)):
         devices = list(range(max(1, min(int(devices), n))))
     devices = [int(d) for d in devices]
     if not devices:
         raise ValueError("arborist: empty device list")
+    if n > 0:                                   # without any GPU the engine reports "no usable CUDA device" itself
+        for d in devices:
+            if not 0 <= d < n:
+                raise ValueError(f"arborist: CUDA device {d} requested but this process sees {n} (ordinals 0..{n - 1})")
     return devices[: max(1, n_trees)]
 
 
@@ -351,8 +362,8 @@ def arborist(
 
     ``threads`` is accepted for compatibility and ignored (the reference passes it
     to ``numba.set_num_threads``, A.py:1002; nothing here runs on host threads).
-    Keyword-only extras: ``device`` (one CUDA ordinal), ``devices`` ("all", a count or
-    a list of ordinals: the candidate set is spread over those GPUs by THIS process,
+    Keyword-only extras: ``device`` (one CUDA ordinal), ``devices`` ("all", a count -- also as
+    a bare integer string -- or a list of ordinals, as a string "0,2" or "3,": the candidate set is spread over those GPUs by THIS process,
     ``arb_fit_trees_multi``; default: every visible GPU once the job is worth their
     start-up cost -- at least 32 trees per GPU and table rows x clones x trees >= 1.5e11, i.e.
     about 2 s of one GPU; environment override ``ARBORIST_DEVICES``) and ``keep_posteriors``
@@ -389,9 +400,9 @@ def arborist(
     err = None
     try:
         clone_to_idx, cluster_to_idx, parents, presence, normal_idx = prepare_tree_shard(tree_list, shard, add_normal)
-    except ValueError as e:
+    except Exception as e:                              # anything: the other ranks are about to enter a collective
         err = e
-    if not distributed.all_agree(err is None):          # every rank raises, or none
+    if not distributed.all_agree(err is None, device):  # every rank raises, or none
         raise err if err is not None else ValueError("All trees must have the same set of clones.")
     K = len(clone_to_idx)
     mark("trees")
@@ -435,7 +446,6 @@ def arborist(
         elbo, iters = fit_multi(engines, parents, K, normal_idx=normal_idx, max_iter=max_iter,
                                 tolerance=tolerance, keep_posteriors=keep_posteriors)
     mark("fit")
-    distributed.all_agree.device = engines[0].device
     elbo_all, owner = distributed.gather_elbos(elbo, shard, T, device=engines[0].device)
     mark("gather")
 
@@ -470,11 +480,13 @@ def arborist(
     stages = {b[0]: round(1e3 * (b[1] - a[1]), 2) for a, b in zip(marks, marks[1:])}
     arborist.last_stats = dict(iters=iters, engine=weakref.ref(engines[0]), engines=[weakref.ref(e) for e in engines],
                                shard=shard, stages_ms=stages, store=weakref.ref(store), devices=[e.device for e in engines])
-    # The start-up heap of the interpreter (torch / pandas module objects, never garbage) makes every few calls pay
-    # a ~50 ms generation-2 collection over objects that cannot die: take it out of the collector once, as a
-    # long-running service would (ARBORIST_GC_FREEZE=0 leaves the collector alone).
-    if not arborist._frozen and os.environ.get("ARBORIST_GC_FREEZE", "1") != "0":
+    # Opt-in (ARBORIST_GC_FREEZE=1; bench.py does the same itself): the start-up heap of the interpreter (torch / pandas
+    # module objects, never garbage) makes every few calls pay a ~50 ms generation-2 collection over objects that
+    # cannot die.  A long-running service may take it out of the collector once; collect first so that no pending
+    # cyclic garbage of the host application is frozen with it.  Off by default: the collector belongs to the caller.
+    if not arborist._frozen and os.environ.get("ARBORIST_GC_FREEZE", "0") == "1":
         arborist._frozen = True
+        gc.collect()
         gc.freeze()
     return likelihoods, best_fit, all_tree_fits
 
@@ -508,11 +520,17 @@ _SEAM_CACHE = {}
 
 
 def _fingerprint(a):
-    """Cheap content check of a cached input: address, shape and a strided sample of the bytes, so that an array
-    refilled in place between calls (a gamma sweep reusing one q_y_init buffer) is noticed."""
-    flat = a.reshape(-1)
-    step = max(1, flat.shape[0] // 4096)
-    return (a.__array_interface__["data"][0], a.shape, a.dtype.str, flat[::step].tobytes(), flat[-1:].tobytes())
+    """Content check of a cached input over ALL of its bytes, so that an array refilled in place between calls -- a
+    gamma sweep reusing one q_y_init buffer, an edit or a swap of a few log-likelihoods -- is noticed wherever it
+    falls: the 64-bit words are laid out as rows of 4096 and both the row sums and the column sums (wrapping) are
+    kept, plus the bytes that do not fill a row verbatim.  Changing one word changes a row sum; exchanging two words
+    changes a row sum or a column sum.  Two memory-speed passes: about 15 ms for the 64 MB of log-likelihoods at
+    config 3 (zlib.crc32 takes 35 ms)."""
+    raw = np.ascontiguousarray(a).reshape(-1).view(np.uint8)
+    rows = raw.shape[0] // (8 * 4096)
+    body = raw[: rows * 8 * 4096].view(np.uint64).reshape(rows, 4096)
+    sums = (np.add.reduce(body, axis=1, dtype=np.uint64).tobytes(), np.add.reduce(body, axis=0, dtype=np.uint64).tobytes())
+    return (a.__array_interface__["data"][0], a.shape, a.dtype.str, sums, raw[rows * 8 * 4096:].tobytes())
 
 
 def clear_seam_cache():

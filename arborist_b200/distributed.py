@@ -14,7 +14,7 @@ from __future__ import annotations
 
 import numpy as np
 
-__all__ = ["world", "shard_indices", "gather_elbos", "broadcast_fit", "gather_vector", "all_agree"]
+__all__ = ["world", "shard_indices", "gather_elbos", "broadcast_fit", "gather_vector", "all_agree", "local_device"]
 
 
 def world():
@@ -39,31 +39,41 @@ def shard_indices(n_trees, rank=None, world_size=None):
     return np.arange(rank, n_trees, world_size, dtype=np.int64)
 
 
+def local_device(device=None):
+    """CUDA ordinal this rank works on: ``device`` when given, else ``LOCAL_RANK`` modulo the number of visible GPUs
+    -- the rule ``Engine(device=None)`` applies, so collectives and kernels agree before any engine exists."""
+    if device is not None:
+        return int(device)
+    import os
+
+    import torch
+
+    return int(os.environ.get("LOCAL_RANK", "0")) % max(1, torch.cuda.device_count())
+
+
 def _comm_device(device=None):
-    """Where collective buffers live: the engine's GPU under NCCL (NOT torch's current device, which is 0 unless
-    the caller ran ``torch.cuda.set_device``), the host under gloo."""
+    """Where collective buffers live: this rank's GPU under NCCL (NOT torch's current device, which is 0 on every
+    rank unless the caller ran ``torch.cuda.set_device``), the host under gloo."""
     import torch
     import torch.distributed as dist
 
     if dist.get_backend() != "nccl":
         return torch.device("cpu")
-    return torch.device("cuda", torch.cuda.current_device() if device is None else int(device))
+    return torch.device("cuda", local_device(device))
 
 
-def all_agree(ok):
-    """True on every rank iff ``ok`` is true on every rank (so that all ranks raise together)."""
+def all_agree(ok, device=None):
+    """True on every rank iff ``ok`` is true on every rank (so that all ranks raise together).  ``device``: the
+    caller's explicit CUDA ordinal, if it has one (see :func:`local_device`)."""
     _, ws = world()
     if ws == 1:
         return bool(ok)
     import torch
     import torch.distributed as dist
 
-    t = torch.tensor([1 if ok else 0], dtype=torch.int32, device=_comm_device(all_agree.device))
+    t = torch.tensor([1 if ok else 0], dtype=torch.int32, device=_comm_device(device))
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     return bool(int(t.item()))
-
-
-all_agree.device = None          # set by arborist() to its engine's GPU
 
 
 def gather_vector(local, shard, n_total, dtype=np.float64, device=None):

@@ -156,6 +156,11 @@ class LazyFits(dict):
         write_fits_pickle(self, path, protocol=protocol)
 
 
+class _NullSink:
+    def write(self, b):
+        return len(b)
+
+
 def write_fits_pickle(fits, path, protocol=3):
     """Write ``{idx: TreeFit}`` as one pickle, one batch of posteriors in memory at a time.
 
@@ -179,7 +184,8 @@ def write_fits_pickle(fits, path, protocol=3):
     n = len(fits)
     lazy = isinstance(fits, LazyFits)
     handle = get_handle(path, "wb", compression="infer", is_text=False) if rank == 0 else None
-    out = handle.handle if handle is not None else io.BytesIO()
+    writer = handle is not None                   # the other ranks only take part in the broadcasts: nothing is pickled
+    out = handle.handle if writer else _NullSink()  # or buffered there (the file is 2.7 GB at config 3)
     buf = io.BytesIO()
     pk = pickle.Pickler(buf, protocol=protocol)
     shared_ids = None
@@ -190,6 +196,9 @@ def write_fits_pickle(fits, path, protocol=3):
             for idx in range(start, min(n, start + 1000)):
                 fit = fits.fresh(idx) if lazy else fits[idx]
                 fit.q_z  # noqa: B018 - materialise (collective under torch.distributed)
+                if not writer:
+                    del fit
+                    continue
                 for obj in (idx, fit):                           # key, then value, left on the unpickler's stack
                     buf.seek(0)
                     buf.truncate()

@@ -46,6 +46,19 @@ WORKER = textwrap.dedent("""
         qz, qy = store.get_fit(idx)
         assert (qz == idx).all() and (qy == -idx).all() and qz.shape == (4, 3)
     assert D.all_agree(True) and not D.all_agree(rank == 0)
+    # arborist(): a tree that only rank 1's shard validates is broken in a way that is NOT a ValueError (a cycle has
+    # no root: StopIteration).  Rank 0 must not be left alone in the collective: both ranks raise, before any engine.
+    import pandas as pd
+    from arborist_b200 import arborist
+    rc = pd.DataFrame({"snv": [1, 2], "cell": [1, 1], "alt": [1, 0], "total": [1, 1]})
+    cl = pd.DataFrame({"snv": [1, 2], "cluster": [1, 2]})
+    try:
+        arborist([[(1, 2)], [(1, 2), (2, 1)], [(1, 2)]], rc, cl, add_normal=True)
+        raised = None
+    except Exception as e:
+        raised = type(e).__name__
+    assert raised == ("ValueError" if rank == 0 else "StopIteration"), raised
+    assert D.local_device(3) == 3 and D.local_device() == 0          # no GPU here: LOCAL_RANK % max(1, 0)
     # streaming pickle of all fits: every rank takes part (remote posteriors are broadcast), rank 0 writes
     dicts = [{"a": 0, "b": 1, "c": 2, "d": 3}, {i: i for i in range(5)}, {0: 0, 1: 1, 2: 2}, {1: 0, 2: 1}]
     fits = LazyFits(T, lambda i: TreeFit.lazy([(0, 1), (1, 2)], i, float(truth[i]), store.get_fit, *dicts), store)

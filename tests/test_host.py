@@ -278,3 +278,55 @@ def test_pyproject_console_script():
     assert target == "arborist.arborist:main"
     mod, fn = target.split(":")
     assert callable(getattr(importlib.import_module(mod), fn))
+
+
+def test_pick_devices_counts_lists_and_bad_ordinals(monkeypatch):
+    """``devices`` / ``ARBORIST_DEVICES``: "all", a count (int or bare integer string), or a list of ordinals; an
+    ordinal the process cannot see is a ValueError here, not a CUDA error later."""
+    import importlib
+    from arborist_b200 import engine
+    A = importlib.import_module("arborist_b200.arborist")
+    monkeypatch.setattr(engine, "device_count", lambda: 4)
+    monkeypatch.delenv("ARBORIST_DEVICES", raising=False)
+    pick = A._pick_devices
+    assert pick(None, "all", 1000) == [0, 1, 2, 3]
+    assert pick(None, 2, 1000) == [0, 1] and pick(None, "2", 1000) == [0, 1]      # the string means the same count
+    assert pick(None, "1", 1000) == [0]
+    assert pick(None, "3,", 1000) == [3] and pick(None, "0, 2", 1000) == [0, 2] and pick(None, [1, 3], 1000) == [1, 3]
+    assert pick(None, 9, 1000) == [0, 1, 2, 3]                                     # a count is capped
+    assert pick(None, "all", 2) == [0, 1]                                          # never more GPUs than trees
+    assert pick(2, "all", 1000) == [2]                                             # an explicit device wins
+    monkeypatch.setenv("ARBORIST_DEVICES", "1")
+    assert pick(None, None, 1000) == [0]
+    monkeypatch.setenv("ARBORIST_DEVICES", "1,2")
+    assert pick(None, None, 1000) == [1, 2]
+    for bad in ("4,", [0, 7], "-1,"):
+        with pytest.raises(ValueError, match="CUDA device"):
+            pick(None, bad, 1000)
+    with pytest.raises(ValueError, match="empty"):
+        pick(None, ",", 1000)
+
+
+def test_seam_fingerprint_sees_every_element():
+    """The per-tree seam keeps the device matrix between calls and recognises its inputs by content: an in-place edit
+    of ONE element anywhere (the old strided sample missed most positions) must change the fingerprint."""
+    from arborist_b200.arborist import _fingerprint
+    rng = np.random.default_rng(0)
+    for a in (rng.random(100_003), rng.integers(0, 1000, 70_001).astype(np.int32), rng.random((3001, 7)),
+              np.arange(5, dtype=np.int8), np.zeros(0)):
+        base = _fingerprint(a)
+        assert _fingerprint(a) == base and _fingerprint(a.copy())[1:] == base[1:]
+        flat = a.reshape(-1)
+        for pos in ([0, 1, flat.shape[0] // 2 + 1, flat.shape[0] - 2, flat.shape[0] - 1] if flat.shape[0] else []):
+            old = flat[pos]
+            flat[pos] = old + 1
+            assert _fingerprint(a) != base, pos
+            flat[pos] = old
+        assert _fingerprint(a) == base
+    b = rng.random(4096 * 5 + 17)
+    base = _fingerprint(b)
+    for i, j in ((1, 2), (3, 4096 * 2 + 3), (10, 4096 * 4 + 11), (4096 * 5 + 1, 4096 * 5 + 9)):
+        b[i], b[j] = b[j], b[i]                   # an exchange keeps every plain sum / xor of the values
+        assert _fingerprint(b) != base, (i, j)
+        b[i], b[j] = b[j], b[i]
+    assert _fingerprint(b) == base

@@ -67,6 +67,8 @@ def parse_args():
     p.add_argument("--slots", type=int, default=0)
     p.add_argument("--lookahead", type=int, default=0, help="rounds the host enqueues ahead (0 = library default)")
     p.add_argument("--split", type=int, default=0, help="force the sweep split (0 = chosen on the device)")
+    p.add_argument("--no-single", action="store_true", help="skip the single-process leg (N > 1: after the timed legs "
+                   "rank 0 alone drives every GPU through arborist(..., devices='all') = arb_fit_trees_multi)")
     p.add_argument("--no-strong", action="store_true", help="skip the strong-scaling leg (N > 1: the config's own "
                    "candidate set, e.g. 1,000 trees in total, sharded over the N GPUs)")
     return p.parse_args()
@@ -320,6 +322,20 @@ def run_gpu_arm(args):
     steps = max(1, args.steps)
     value = T * steps / (dev_ms * 1e-3)
 
+    # ---- identity of the answers across N: hashes of the ELBOs / iteration counts of the config's OWN candidate set --
+    # (the first cfg.n_trees trees are the same at every N; which GPU fitted a tree must not change a bit of it)
+    import hashlib
+
+    def digest(a, dtype):
+        return hashlib.sha256(np.ascontiguousarray(a, dtype=dtype).tobytes()).hexdigest()
+
+    T_h = min(T, cfg.n_trees)
+    iters_all = distributed.gather_vector(iters, shard, T, dtype=np.int32)          # untimed
+    answers = {"trees": int(T_h), "elbo_sha256": digest(full[:T_h], np.float64),
+               "iters_sha256": digest(iters_all[:T_h], np.int32),
+               "note": "sha256 of the fp64 ELBO bytes / int32 iteration counts of the config's first `trees` candidate "
+                       "trees (the same trees at every N): equal hashes = bit-identical answers whichever GPU fitted them"}
+
     # ---- strong scaling: the config's OWN candidate set (config 3: 1,000 trees in total) sharded over the ranks ---
     strong = None
     if world > 1 and not args.no_strong:
@@ -328,13 +344,14 @@ def run_gpu_arm(args):
         par_s = np.ascontiguousarray(parents[shard_s])
 
         def strong_step():
-            elbo, _ = eng.fit(parents=par_s, n_clones=K, normal_idx=normal_idx, max_iter=RUN["max_iter"],
-                              tolerance=RUN["tolerance"], keep_posteriors="all")
+            elbo, it_s = eng.fit(parents=par_s, n_clones=K, normal_idx=normal_idx, max_iter=RUN["max_iter"],
+                                 tolerance=RUN["tolerance"], keep_posteriors="all")
             ms = eng.last_fit_stats()["device_ms"]
             ev0.record()
             full_s, _ = distributed.gather_elbos(elbo, shard_s, T_s)
             ev1.record()
             torch.cuda.synchronize()
+            strong_step.iters = it_s
             return ms + ev0.elapsed_time(ev1), full_s
 
         for _ in range(2):
@@ -346,6 +363,7 @@ def run_gpu_arm(args):
             s_ms += ms
         barrier()
         s_ms = max_over_ranks(s_ms)
+        iters_s = distributed.gather_vector(strong_step.iters, shard_s, T_s, dtype=np.int32)      # untimed
         # the same through arborist(...) with host DataFrames (every rank: prepare its shard's trees, ingest the table,
         # fit, gather): the per-rank ingest does not shrink with N, so this is the Amdahl view of strong scaling
         s_e2e = None
@@ -365,6 +383,7 @@ def run_gpu_arm(args):
         strong = {"trees_total": int(T_s), "trees_per_gpu": float(T_s) / world, "value": T_s * steps / (s_ms * 1e-3),
                   "e2e_value": s_e2e,
                   "unit": "trees/s", "ms_per_step": s_ms / steps, "best_tree": int(np.argmax(full_s)),
+                  "elbo_sha256": digest(full_s, np.float64), "iters_sha256": digest(iters_s, np.int32),
                   "note": "same metric with the TOTAL candidate set fixed (north_star: 1,000 trees, 1 -> 8 GPUs); "
                           "device events, max over ranks; divide by the N = 1 line's value for the speed-up"}
 
@@ -497,6 +516,49 @@ def run_gpu_arm(args):
                "sample": arm.sample.replace(str(MEAN_TREE_ITERS.get(cfg.name, 12.0)), f"{arm.mean_iters:.2f}"),
                "tree_iters_per_s": ti / dt, "seconds": dt}
 
+    # ---- N > 1: the same candidate set through ONE process that drives every GPU itself -------------------------
+    # (arborist(..., devices="all") -> arb_fit_trees_multi, the console script's default on a multi-GPU box).  Runs
+    # after every timed leg: all ranks give their device memory back and leave the process group, then rank 0 alone
+    # opens a context per GPU.  The hashes must equal `answers` / `strong`.
+    single = None
+    if world > 1 and not args.no_single:
+        import gc
+
+        try:
+            eng.close()
+        except NameError:
+            pass
+        arborist.last_stats = None
+        gc.collect()
+        engine.trim_pool()
+        torch.cuda.empty_cache()
+        barrier()
+        dist.destroy_process_group()
+        dist = None
+        if rank == 0:
+            try:
+                def single_call():
+                    lik_sp, best_sp, _ = arborist(trees[:T_h], rc, cl, alpha=RUN["alpha"], max_iter=RUN["max_iter"],
+                                                  tolerance=RUN["tolerance"], gamma=RUN["gamma"], add_normal=True,
+                                                  devices="all")
+                    return lik_sp, best_sp.tree_idx
+
+                single_call()                                            # untimed: one context per GPU is created here
+                t_sp = time.perf_counter()
+                for _ in range(steps):
+                    lik_sp, best_sp = single_call()
+                t_sp = time.perf_counter() - t_sp
+                single = {"devices": list(arborist.last_stats["devices"]), "trees": int(T_h),
+                          "trees_per_s": T_h * steps / t_sp, "ms_per_call": 1e3 * t_sp / steps,
+                          "elbo_sha256": digest([lik_sp[i] for i in range(T_h)], np.float64),
+                          "iters_sha256": digest(arborist.last_stats["iters"], np.int32), "best_tree": int(best_sp),
+                          "stages_ms_last_call": arborist.last_stats["stages_ms"],
+                          "note": "one process, one host thread per GPU (arb_fit_trees_multi), host DataFrames in, "
+                                  "wall clock of the whole call; run by rank 0 after the other ranks released their GPUs"}
+                arborist.last_stats = None
+            except Exception as e:                                        # never lose the line over the extra leg
+                single = {"error": repr(e)}
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": "trees/s", "n_gpus": world, "steps": args.steps,
@@ -514,7 +576,8 @@ def run_gpu_arm(args):
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
             "e2e": e2e, "cpu_baseline": cpu, "strong": strong,
             "round_pipeline": {"host_waits": pf["host_waits"], "idle_rounds": pf["idle_rounds"], "rounds": pf["rounds"]},
-            "best_tree": int(order[0]), "true_tree": int(d.true_tree_index),
+            "best_tree": int(order[0]), "true_tree": int(d.true_tree_index), "answers": answers,
+            "single_process": single,
         }
         print(json.dumps(line), file=_REAL_STDOUT, flush=True)
     if dist is not None:

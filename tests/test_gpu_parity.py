@@ -217,6 +217,35 @@ def test_api_config3_head(eng_mod):
     _check_api(g, lik, best, fits, full_q=False)
 
 
+def _check_traces(g, trees, eng):
+    """Driver level on the device matrix the API call left behind: every iteration's ELBO (A.py:801-803)."""
+    from arborist_b200.arborist import prepare_tree_shard
+    c2i, _, parents, _, normal = prepare_tree_shard(trees, np.arange(len(trees)), add_normal=True)
+    elbo, iters, tr = eng.fit(parents=parents, n_clones=len(c2i), normal_idx=normal, max_iter=int(g["max_iter"]),
+                              tolerance=float(g["tol"]), keep_posteriors="none", trace=True)
+    assert np.array_equal(iters, g["iters"])
+    for t in range(len(trees)):
+        assert np.isnan(tr[t, iters[t] + 1:]).all()
+    return elbo, tr
+
+
+def test_api_config3_converged(eng_mod):
+    """BASELINE config 3 shape, the first 8 candidate trees fitted TO CONVERGENCE (7 to 25 iterations, three of them
+    stopped by max_iter) -- the late-iteration regime of the loop (A.py:767-814: peaked posteriors, snapshot on
+    strict improvement, convergence against the best ELBO).  Fixture generated by the C oracle, which the
+    live-reference goldens pin (oracle/gen_oracle_golden.py; SURVEY.md 8(d) names these 8 trees): ELBOs and every
+    iteration's ELBO to 1e-9, iteration counts, ranking and MAP labels exact, 32 recorded rows of each posterior."""
+    from arborist_b200.arborist import arborist as fn
+    g = load_golden("config3_conv")
+    assert str(g["source"]) == "oracle" and int(g["iters"].max()) == 25 and int(g["iters"].min()) < 10
+    trees, rc, cl = synth_frames("config3", tree_subset=[int(i) for i in g["tree_subset"]])
+    lik, best, fits = _run_api(g, trees, rc, cl)
+    _check_api(g, lik, best, fits, full_q=False)
+    elbo, tr = _check_traces(g, trees, fn.last_stats["engine"]())
+    np.testing.assert_allclose(tr, g["traces"], rtol=ELBO_RTOL)          # NaN padding included
+    assert np.array_equal(elbo, np.array([lik[t] for t in range(len(trees))]))
+
+
 def test_api_config5_full_shape(eng_mod):
     """BASELINE config 5 at its REAL shape: 5,000 cells x 10,000 SNVs, K = 30 deep trees, 30 % of the SNVs carry
     an off-tree label (uniform prior rows); the 7 first trees + the generating tree, as the unmodified reference

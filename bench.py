@@ -39,10 +39,6 @@ if ROOT not in sys.path:
 
 METRIC = "candidate_trees_fit_and_ranked_per_second"
 RUN = dict(alpha=0.001, gamma=0.7, max_iter=25, tolerance=1.0)      # CLI defaults, A.py:62-81
-# mean CAVI tree-iterations per tree (init pass = 0.5) of the full config-3 candidate set as
-# measured by the GPU arm; used only to express the CPU sample (a few iterations of one tree)
-# in the metric's unit.  See BASELINE.md section 5.
-MEAN_TREE_ITERS = {"config3": 17.84, "config2": 12.8}
 # DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) per tree-sweep of the two sweep kernels, one entry per
 # config that has an `ncu --set full` capture under profiles/ (per launch the kernel moves this times the
 # tree-sweeps of the launch; the figure is NOT measured in the bench run itself -- ncu cannot run inside a timed
@@ -161,64 +157,82 @@ class ClockSampler:
 # CPU arm: the oracle (C port of the reference's kernels) on the host cores
 # ---------------------------------------------------------------------------------------------
 class CpuArm:
-    """Bounded sample: tree s of the workload, initial pass + ``iters`` CAVI iterations
-    (A.py:733-816 with max_iter capped), every OpenMP thread the host offers."""
+    """One WHOLE candidate tree per step, fitted to convergence as the reference's loop does (A.py:1089-1126 ->
+    run_variational_inference, A.py:679-816, with RUN's max_iter / tolerance) by the C/OpenMP oracle on every thread
+    the host offers.  The reference's ingest (A.py:1034-1069 = ``orc.prepare``) runs once and is timed apart."""
 
-    def __init__(self, cfg, d, trees, iters=2, trees_per_step=4):
+    def __init__(self, cfg, d, trees):
         from oracle import oracle as orc
 
-        self.orc, self.iters, self.trees, self.tps = orc, iters, trees, trees_per_step
+        self.orc, self.trees = orc, trees
         # every core this process may run on (torchrun exports OMP_NUM_THREADS=1: do not inherit that)
         try:
             self.cores = len(os.sched_getaffinity(0))
         except AttributeError:
             self.cores = os.cpu_count() or 1
         orc.lib().orc_set_threads(self.cores)
+        t0 = time.perf_counter()
         self.prob = orc.prepare(trees[:1], d.read_counts_frame(), d.clusters_frame(), alpha=RUN["alpha"],
                                 gamma=RUN["gamma"], add_normal=True)
+        self.prepare_s = time.perf_counter() - t0
+        self.set_size = cfg.n_trees
         self.add_normal = orc.add_normal_clone
-        self.mean_iters = MEAN_TREE_ITERS.get(cfg.name, 12.0)
-        self.sample = (f"{trees_per_step} trees per step, each initial pass + {iters} CAVI iterations ({iters + 0.5} of ~"
-                       f"{self.mean_iters} tree-iterations per tree), tolerance 0 so no early stop; trees/s "
-                       f"extrapolated with that mean")
+        self.iters = []
+        self.sample = (f"one whole candidate tree per step (tree number warmup + s of the set), fitted to convergence "
+                       f"(max_iter {RUN['max_iter']}, tolerance {RUN['tolerance']}) by the C/OpenMP port of the "
+                       f"reference's kernels on {self.cores} threads; trees / seconds, nothing extrapolated")
 
     def step(self, s):
-        dt = 0.0
-        for k in range(self.tps):
-            tree = self.add_normal([self.trees[(s * self.tps + k) % len(self.trees)]])[0]
-            t0 = time.perf_counter()
-            self.orc.fit_tree(self.prob, tree, max_iter=self.iters, tolerance=0.0)
-            dt += time.perf_counter() - t0
-        return dt, self.tps * (self.iters + 0.5)
+        tree = self.add_normal([self.trees[s % len(self.trees)]])[0]
+        t0 = time.perf_counter()
+        _, _, _, it, _ = self.orc.fit_tree(self.prob, tree, max_iter=RUN["max_iter"], tolerance=RUN["tolerance"],
+                                           return_trace=True)
+        dt = time.perf_counter() - t0
+        self.iters.append(int(it))
+        return dt, it + 0.5
 
-    def trees_per_s(self, seconds, tree_iters):
-        return (tree_iters / seconds) / self.mean_iters
+
+def bench_config(cfg, n, m, nnz, K, per, total, world):
+    """The ``config`` object of the JSON line -- one function so that both arms print the same object."""
+    return {"workload": workload_name(cfg, n, m, nnz, K, per, total),
+            "run": RUN, "parallelism": f"tree-sharded x{world}",
+            "l2": "inputs larger than L2: per-step working set (panel partials + posteriors of "
+                  "all trees in flight) is tens of GB, far above the 126 MB L2; no flush needed",
+            "timing": "CUDA events on the library's launching stream around each fit + torch "
+                      "events around the ELBO gather; max over ranks"}
 
 
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cfg, d, trees, per = make_workload(args.config, args.trees, 1)
+    world = max(1, args.gpus)
+    cfg, d, trees, per = make_workload(args.config, args.trees, world)
     arm = CpuArm(cfg, d, trees)
     for s in range(args.warmup):
         arm.step(s)
+    arm.iters = []
     tot_t = tot_i = 0.0
     for s in range(args.steps):
         dt, ti = arm.step(args.warmup + s)
         tot_t += dt
         tot_i += ti
-    v = arm.trees_per_s(tot_t, tot_i)
+    steps = max(1, args.steps)
+    v = steps / tot_t
+    # end to end = the fit plus the reference's ingest, which one arborist(...) call pays once for its candidate set
+    v_e2e = steps / (tot_t + steps * arm.prepare_s / arm.set_size)
     line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": "trees/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / max(1, args.steps),
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(cfg, arm.prob.n_cells, arm.prob.n_snvs, len(arm.prob.snv_idx_cs),
-                                             arm.prob.n_clones, per, per),
-                   "step": arm.sample, "run": RUN},
-        "tree_iters_per_s": tot_i / tot_t,
+        "config": bench_config(cfg, arm.prob.n_cells, arm.prob.n_snvs, len(arm.prob.snv_idx_cs), arm.prob.n_clones,
+                               per, per * world, world),
+        "step": arm.sample, "iters_per_tree": arm.iters, "tree_iters_per_s": tot_i / tot_t,
+        "ingest_s": arm.prepare_s,
         "cpu_baseline": {"value": v, "unit": "trees/s", "cores": arm.cores, "kind": "port", "sample": arm.sample},
-        "e2e": {"value": v, "unit": "trees/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "e2e": {"value": v_e2e, "unit": "trees/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                "note": f"fit time plus the ingest (A.py:1034-1069, {arm.prepare_s:.2f} s here) spread over the "
+                        f"{arm.set_size} trees of the config's candidate set"},
         "gpu_launches": 0,
     }
     print(json.dumps(line), file=_REAL_STDOUT, flush=True)
@@ -506,15 +520,14 @@ def run_gpu_arm(args):
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         arm = CpuArm(cfg, d, trees)
-        arm.mean_iters = tree_iters / steps / len(shard)         # this run's own mean
         dt = ti = 0.0
-        for s in range(3):
+        for s in range(2):                       # trees 0 and 1 of the set, whole: ~25 s on 16 cores at config 3
             a_dt, a_ti = arm.step(s)
             dt += a_dt
             ti += a_ti
-        cpu = {"value": arm.trees_per_s(dt, ti), "unit": "trees/s", "cores": arm.cores, "kind": "port",
-               "sample": arm.sample.replace(str(MEAN_TREE_ITERS.get(cfg.name, 12.0)), f"{arm.mean_iters:.2f}"),
-               "tree_iters_per_s": ti / dt, "seconds": dt}
+        cpu = {"value": 2 / dt, "unit": "trees/s", "cores": arm.cores, "kind": "port",
+               "sample": arm.sample.replace("tree number warmup + s", "trees 0 and 1"), "iters_per_tree": arm.iters,
+               "tree_iters_per_s": ti / dt, "seconds": dt, "ingest_s": arm.prepare_s}
 
     # ---- N > 1: the same candidate set through ONE process that drives every GPU itself -------------------------
     # (arborist(..., devices="all") -> arb_fit_trees_multi, the console script's default on a multi-GPU box).  Runs
@@ -564,12 +577,7 @@ def run_gpu_arm(args):
             "metric": METRIC, "value": value, "unit": "trees/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms / steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(cfg, n, m, nnz, K, per, T),
-                       "run": RUN, "parallelism": f"tree-sharded x{world}",
-                       "l2": "inputs larger than L2: per-step working set (panel partials + posteriors of "
-                             "all trees in flight) is tens of GB, far above the 126 MB L2; no flush needed",
-                       "timing": "CUDA events on the library's launching stream around each fit + torch "
-                                 "events around the ELBO gather; max over ranks"},
+            "config": bench_config(cfg, n, m, nnz, K, per, T, world),
             "tree_iters_per_s": tree_iters_all / (dev_ms * 1e-3),
             "mean_tree_iters_per_tree": tree_iters / steps / len(shard),
             "wall_ms_per_step": 1e3 * wall / steps,

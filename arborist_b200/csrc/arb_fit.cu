@@ -3,10 +3,10 @@
 // Replaces the reference's tree loop and everything under it
 // (/root/reference/src/arborist/arborist.py, "A.py"):
 //   A.py:491-520   enumerate_presence          -> k_masks_from_parents / k_masks_from_presence
-//   A.py:200-250   compute_q_z_sparse          -> k_sweep<KP,true>  + k_finish_z
-//   A.py:325-375   compute_q_y_sparse          -> k_sweep<KP,false> + k_finish_y
+//   A.py:200-250   compute_q_z_sparse          -> k_seed_s + k_sweep<16,WITH_G=true,..>  + k_finish<GL,IS_Z=true,..>
+//   A.py:325-375   compute_q_y_sparse          -> k_seed_r + k_sweep<16,WITH_G=false,..> + k_finish<GL,IS_Z=false,..>
 //   A.py:378-420   compute_likelihood_sparse   -> fused into the q(z) sweep (G accumulators)
-//   A.py:253-299   entropy / KL                -> fused into k_finish_z / k_finish_y
+//   A.py:253-299   entropy / KL                -> fused into k_finish (finish_row)
 //   A.py:679-816   run_variational_inference   -> k_control (per-tree state machine on device)
 //   A.py:1089-1126 the sequential tree loop    -> many trees in flight ("slots"), one round of
 //                                                 kernels advances every active tree by one iteration
@@ -20,10 +20,15 @@
 // The sums of logs are accumulated as running products with the exponent peeled off every
 // `renorm_every` factors; one log per (row, clone) is taken in the finishing kernel.
 //
-// Sweep kernel data flow: a CTA owns (tree slot, panel).  The panel of the gathered operand
-// (S or R rows, padded to KP doubles = 64/128/256 B) is brought into shared memory with bulk
-// async copies (TMA, cp.async.bulk + mbarrier); groups of KP/2 lanes then walk the panel's
-// slice of the sparse stream row by row, each lane reading two adjacent clones (LDS.128).
+// Sweep kernel data flow: the columns of the trees in flight are packed side by side, four at a time, into
+// "virtual slots" of ARB_VW = 16 columns (128-byte rows), so no lane works on a padding column.  A CTA owns
+// (virtual slot, panel[, share of a split tail item]).  The panel of the gathered operand (S or R rows) is brought
+// into shared memory with bulk async copies (cp.async.bulk + mbarrier, the TMA engine's 1-D path); each warp then
+// walks its run of tiles of the sparse stream.  Four lanes share a segment (one row of the output); each lane owns
+// four of the 16 columns and reads them with two LDS.128 per nonzero (sweep_step).  The per-row products
+// (q(z) sweep: product and likelihood sum interleaved) leave as full 128-byte lines of "partial rows", one per
+// (panel, row); k_finish adds the panels of a row, takes the one log per (row, clone), the softmax, the ELBO terms
+// and writes the next sweep's operand.  See the comment above split_plan / k_sweep for the details.
 #include "arb_common.cuh"
 
 #include <algorithm>
@@ -1648,6 +1653,11 @@ static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, 
         if (rc != ARB_OK || done) break;
         // ---- enqueue round enq --------------------------------------------------------------------
         cudaEvent_t *ev = ctx->rev[enq % ARB_RING];
+        cudaError_t rec_err = cudaSuccess;              // first failure of this round's event records
+        auto rec = [&](cudaEvent_t e) {
+            const cudaError_t r = cudaEventRecord(e, st);
+            if (r != cudaSuccess && rec_err == cudaSuccess) rec_err = r;
+        };
         const int ubt = std::max(1, ub);
         if ((more_inits || enq == 0) && general) {
             k_first_pass_general<<<dim3(ws.nbz, ubt), FIN_THREADS, 0, st>>>(
@@ -1664,27 +1674,28 @@ static int fit_core(arb_ctx *ctx, int n_trees, int K, int max_iter, double tol, 
         }
         if (enq > 0) {                                  // the first round has first passes only
             launch_seed_r<GL>(ctx, w, tg.masks, w.list_y, ubt, K, w.ctl);
-            cudaEventRecord(ev[0], st);
+            rec(ev[0]);
             launch_sweep_y(ctx, L, w, ubt, w.ctl);
-            cudaEventRecord(ev[1], st);
+            rec(ev[1]);
             launch_finish_y<GL>(ctx, L, w, ws, tg.masks, w.list_y, ubt, w.ctl);
-            cudaEventRecord(ev[2], st);
+            rec(ev[2]);
             stats.launches += 3;
         } else {
-            cudaEventRecord(ev[0], st);
-            cudaEventRecord(ev[1], st);
-            cudaEventRecord(ev[2], st);
+            rec(ev[0]);
+            rec(ev[1]);
+            rec(ev[2]);
         }
-        cudaEventRecord(ev[3], st);
+        rec(ev[3]);
         launch_sweep_z(ctx, L, w, ubt, w.ctl);
-        cudaEventRecord(ev[4], st);
+        rec(ev[4]);
         launch_finish_z<GL>(ctx, L, w, ws, tg.masks, w.list_z, ubt, 0, hard, w.ctl);
-        cudaEventRecord(ev[5], st);
+        rec(ev[5]);
         stats.launches += 2;
         {
             cudaError_t e = cudaGetLastError();
+            if (e == cudaSuccess) e = rec_err;
             if (e != cudaSuccess) {
-                arb_set_error("fit round %d: launch failed: %s", enq, cudaGetErrorString(e));
+                arb_set_error("fit round %d: launch or event record failed: %s", enq, cudaGetErrorString(e));
                 rc = ARB_ERR_CUDA;
                 break;
             }

@@ -47,6 +47,10 @@ NCU_DRAM_BYTES_PER_TREE_SWEEP = {
     "config3": {"z": 28.2e6, "y": 14.1e6, "capture": "profiles/r2_full_summary.md (r2b)"},
     "config5": {"z": 17.2e6, "y": 8.0e6, "capture": "profiles/r2_full_summary.md (r2k5)"},
     "config4": {"z": 913e6, "y": 471e6, "capture": "profiles/r2_full_summary.md (r2k4)"},
+    # 100 trees in flight, second round: 29.83 MB per q(z) sweep launch, 6.66 MB per q(y) sweep launch -- the matrix,
+    # the operands and the partial rows of all 100 trees stay in the 126 MB L2, DRAM sees little of the 2 MB a
+    # tree-sweep moves algorithmically
+    "config2": {"z": 0.298e6, "y": 0.0666e6, "capture": "profiles/r3d_config2_summary.md"},
 }
 
 

@@ -31,11 +31,17 @@ def golden_frames(g):
     return trees, rc, cl
 
 
+_LAST_SYNTH = {}
+
+
 def synth_frames(name, tree_subset=None):
     """Inputs regenerated from the seeded generator (fixtures too big to store verbatim)."""
     from arborist_b200 import synth
 
-    d = synth.generate(synth.CONFIGS[name])
+    if name not in _LAST_SYNTH:                 # one data set is kept: neighbouring tests at config 4 (a minute of host
+        _LAST_SYNTH.clear()                     # time and 3 GB to generate) share it, nothing else accumulates
+        _LAST_SYNTH[name] = synth.generate(synth.CONFIGS[name])
+    d = _LAST_SYNTH[name]
     trees = d.trees if tree_subset is None else [d.trees[i] for i in tree_subset]
     return trees, d.read_counts_frame(), d.clusters_frame()
 

@@ -265,7 +265,7 @@ def test_api_config4_head(eng_mod):
     capped at 2, as the unmodified reference fitted them in the build container (36 min of numba on 8 threads,
     oracle/gen_golden.py config4_head; SURVEY.md 8(d) names these 2 trees as the parity sample): ELBOs to 1e-9,
     ELBO traces, iteration counts, ranking, MAP of all 50,000 SNVs and of the 100,000 cells identical except for
-    exact ties (54 cells of tree 0 with q = 1/3, 1/3, 1/3 to 13 digits; counted, bounded at 0.1 %), 32 recorded rows
+    exact ties (54 cells of tree 0 with q = 1/3, 1/3, 1/3 to 13 digits; counted, bounded at 60), 32 recorded rows
     of every posterior.  Generating the workload takes about a minute of host time."""
     from arborist_b200.arborist import arborist as fn
     g = load_golden("config4_head")
@@ -273,8 +273,8 @@ def test_api_config4_head(eng_mod):
     trees, rc, cl = synth_frames("config4", tree_subset=sub)
     assert np.array_equal(np.array(trees), g["trees"]) and len(rc) > 9e7
     lik, best, fits = _run_api(g, trees, rc, cl, device=0)
-    # 54 of tree 0's 100,000 cells are three-way ties (q = 1/3 each to 1e-13) after 2 iterations: allowance 0.1 %
-    _check_api(g, lik, best, fits, full_q=False, max_tie_rows=100)
+    # 54 of tree 0's 100,000 cells are three-way ties (q = 1/3 each to 1e-13) after 2 iterations: allowance = seen + 10 %
+    _check_api(g, lik, best, fits, full_q=False, max_tie_rows=60)
     eng = fn.last_stats["engine"]()
     assert eng.dims() == (int(g["n_cells"]), int(g["n_snvs"]), int(g["nnz"]), eng.dims()[3])
     pf = eng.last_fit_profile()

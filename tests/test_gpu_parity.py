@@ -295,6 +295,33 @@ def test_api_config4_head(eng_mod):
     del eng
 
 
+def test_api_config4_converged(eng_mod):
+    """BASELINE config 4 at its REAL shape, fitted TO CONVERGENCE: the generating tree and tree 0 of the candidate
+    set (as many of the two as oracle/gen_oracle_golden.py had finished; the fixture says which).  This is the
+    late-iteration regime that config4_head (2 iterations of the numba reference) cannot reach at 28 / 56 panels:
+    peaked posteriors, snapshot on strict improvement, convergence against the best ELBO (A.py:767-814).  Fixture
+    generated by the C oracle with 8 threads -- the thread count at which it reproduces the reference's own ELBO_0
+    at this shape bit for bit (profiles/r2_config4_elbo0_threads.md).  ELBOs and every later iteration's ELBO to
+    1e-9 (ELBO_0 to 1e-8, see test_api_config4_head), iteration counts and ranking exact, MAP exact up to counted
+    exact ties, 32 recorded rows of every posterior."""
+    from arborist_b200.arborist import arborist as fn
+    g = load_golden("config4_conv")
+    assert str(g["source"]) == "oracle" and int(g["omp_threads"]) == 8
+    sub = [int(i) for i in g["tree_subset"]]
+    assert sub[0] == int(g["true_tree_index"])
+    trees, rc, cl = synth_frames("config4", tree_subset=sub)
+    assert np.array_equal(np.array(trees), g["trees"])
+    lik, best, fits = _run_api(g, trees, rc, cl, device=0)
+    _check_api(g, lik, best, fits, full_q=False, max_tie_rows=60)
+    eng = fn.last_stats["engine"]()
+    assert eng.dims()[:3] == (int(g["n_cells"]), int(g["n_snvs"]), int(g["nnz"]))
+    elbo, tr = _check_traces(g, trees, eng)
+    np.testing.assert_allclose(tr[:, 1:], g["traces"][:, 1:], rtol=ELBO_RTOL)
+    np.testing.assert_allclose(tr[:, 0], g["traces"][:, 0], rtol=1e-8)
+    assert np.array_equal(elbo, np.array([lik[t] for t in range(len(trees))]))
+    del eng
+
+
 @pytest.mark.parametrize("name", ["tiny", "deep30"])
 def test_elbo_trace_and_presence(eng_mod, name):
     """Driver level: every iteration's ELBO (A.py:801-803) and the device-built genotype matrix."""
